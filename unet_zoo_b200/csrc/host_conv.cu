@@ -1,0 +1,588 @@
+// Host side of the tcgen05 convolution entry points: argument checking, TMA tensor-map construction,
+// tap / phase tables per convolution flavour, grid sizing, launch.  C ABI declared in include/unet_zoo_b200.h.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/unet_zoo_b200.h"
+#include "host_util.h"
+#include "igemm.cuh"
+
+namespace uz {
+cudaError_t launch_igemm_fwd(const IgemmParams& p, int bn, int grid, cudaStream_t stream);
+cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream);
+cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
+                                long long s_row, long long s_col, long long s_tap, int accumulate,
+                                cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+int cuda_error(cudaError_t e, const char* what) {
+  return set_error(UZ_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+int sm_count() {
+  static int cached = 0;
+  if (cached > 0) return cached;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+  int major = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  if (major != 10) return -2;
+  cached = n;
+  return n;
+}
+
+// ------------------------------------------------------------------------------------------------ tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+struct Lattice {
+  int oy, ox, step;
+};
+
+// 4-D (C, W, H, N) bf16 view of an NHWC activation (pixel stride ld elements), restricted to the pixel lattice
+// (oy + step*i, ox + step*j); box = (64 channels, tw, th, tn), 128-byte swizzle, zero fill outside.
+static int make_act_map(CUtensorMap* m, const void* ptr, int C, int ld, int N, int H, int W, Lattice lat, int tw,
+                        int th, int tn) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const int Hl = (H - lat.oy + lat.step - 1) / lat.step;
+  const int Wl = (W - lat.ox + lat.step - 1) / lat.step;
+  if (Hl < 1 || Wl < 1) return set_error(UZ_ERR_INVALID, "empty activation lattice (H=%d W=%d)", H, W);
+  const char* base = static_cast<const char*>(ptr) + (static_cast<size_t>(lat.oy) * W + lat.ox) * ld * 2;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Wl, (cuuint64_t)Hl, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2 * lat.step, (cuuint64_t)W * ld * 2 * lat.step,
+                           (cuuint64_t)H * W * ld * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<char*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled(activation C=%d ld=%d N=%d H=%d W=%d) failed: %d", C, ld,
+                     N, H, W, (int)r);
+  return UZ_OK;
+}
+
+// 3-D (K, taps, rows) bf16 packed weights, box (64, 1, bn).
+static int make_weight_map(CUtensorMap* m, const void* ptr, int K, int taps, int rows, int bn) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)taps, (cuuint64_t)rows};
+  cuuint64_t strides[2] = {(cuuint64_t)K * 2, (cuuint64_t)K * 2 * taps};
+  cuuint32_t box[3] = {64, 1, (cuuint32_t)bn};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled(weights K=%d taps=%d rows=%d) failed: %d", K, taps, rows,
+                     (int)r);
+  return UZ_OK;
+}
+
+static int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+static int ilog2(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return l;
+}
+// pick (tw, th, tn) with tw*th*tn == pixels, preferring 16-wide, square-ish patches inside one image
+static void pick_tile(int pixels, int H, int W, int* tw, int* th, int* tn) {
+  int w = pow2_ceil(W);
+  if (w > 16) w = 16;
+  if (w > pixels) w = pixels;
+  int h = pow2_ceil(H);
+  if (h > pixels / w) h = pixels / w;
+  *tw = w;
+  *th = h;
+  *tn = pixels / (w * h);
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// row/column decomposition of the stride-2 3x3 conv: input row 2y + r - 1 lives on lattice parity `par`, index y + d
+static void s2_tap(int r, int* par, int* d) {
+  if (r == 0) {
+    *par = 1;
+    *d = -1;
+  } else if (r == 1) {
+    *par = 0;
+    *d = 0;
+  } else {
+    *par = 1;
+    *d = 0;
+  }
+}
+
+struct ModeInfo {
+  int Hm, Wm;        // M index space (per image)
+  int Ho, Wo;        // output spatial size
+  int oscale;
+  int num_lat;
+  Lattice lat[4];
+  int num_phases;
+  int ntaps[4];
+  int btaps;         // tap extent of the packed weight tensor
+};
+
+static int build_mode(int mode, int H, int W, int out_h, int out_w, IgemmParams* p, ModeInfo* mi) {
+  memset(mi, 0, sizeof(*mi));
+  mi->oscale = 1;
+  mi->num_lat = 1;
+  mi->lat[0] = {0, 0, 1};
+  mi->num_phases = 1;
+  mi->Hm = H;
+  mi->Wm = W;
+  mi->Ho = H;
+  mi->Wo = W;
+  for (int ph = 0; ph < kMaxPhases; ++ph) {
+    p->phase_oy[ph] = 0;
+    p->phase_ox[ph] = 0;
+  }
+  auto set_tap = [&](int ph, int i, int dy, int dx, int btap, int lat) {
+    p->taps[ph].dy[i] = (int8_t)dy;
+    p->taps[ph].dx[i] = (int8_t)dx;
+    p->taps[ph].btap[i] = (int8_t)btap;
+    p->taps[ph].lat[i] = (int8_t)lat;
+  };
+  switch (mode) {
+    case UZ_CONV3X3:
+    case UZ_CONV3X3_DGRAD: {
+      const int sgn = (mode == UZ_CONV3X3) ? 1 : -1;
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, sgn * (r - 1), sgn * (s - 1), r * 3 + s, 0);
+      mi->ntaps[0] = 9;
+      mi->btaps = 9;
+      break;
+    }
+    case UZ_CONV1X1:
+      set_tap(0, 0, 0, 0, 0, 0);
+      mi->ntaps[0] = 1;
+      mi->btaps = 1;
+      break;
+    case UZ_CONV3X3_S2: {
+      mi->Hm = mi->Ho = (H - 1) / 2 + 1;
+      mi->Wm = mi->Wo = (W - 1) / 2 + 1;
+      mi->num_lat = 4;
+      for (int l = 0; l < 4; ++l) mi->lat[l] = {l >> 1, l & 1, 2};
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) {
+          int pr, dr, pc, dc;
+          s2_tap(r, &pr, &dr);
+          s2_tap(s, &pc, &dc);
+          set_tap(0, r * 3 + s, dr, dc, r * 3 + s, pr * 2 + pc);
+        }
+      mi->ntaps[0] = 9;
+      mi->btaps = 9;
+      break;
+    }
+    case UZ_CONV3X3_S2_DGRAD: {
+      // input = dY (H x W, low res); output dX (out_h x out_w) with (out_h-1)/2+1 == H
+      if ((out_h - 1) / 2 + 1 != H || (out_w - 1) / 2 + 1 != W)
+        return set_error(UZ_ERR_INVALID, "stride-2 dgrad: output %dx%d inconsistent with dY %dx%d", out_h, out_w, H,
+                         W);
+      mi->Ho = out_h;
+      mi->Wo = out_w;
+      mi->oscale = 2;
+      mi->num_phases = 4;
+      mi->btaps = 9;
+      for (int ph = 0; ph < 4; ++ph) {
+        const int py = ph >> 1, px = ph & 1;
+        p->phase_oy[ph] = (int8_t)py;
+        p->phase_ox[ph] = (int8_t)px;
+        // rows: py==0 -> (r=1, dy=0); py==1 -> (r=0, dy=+1), (r=2, dy=0)
+        int rr[2], rd[2], nr, cc[2], cd[2], nc;
+        if (py == 0) { nr = 1; rr[0] = 1; rd[0] = 0; } else { nr = 2; rr[0] = 0; rd[0] = 1; rr[1] = 2; rd[1] = 0; }
+        if (px == 0) { nc = 1; cc[0] = 1; cd[0] = 0; } else { nc = 2; cc[0] = 0; cd[0] = 1; cc[1] = 2; cd[1] = 0; }
+        int i = 0;
+        for (int a = 0; a < nr; ++a)
+          for (int b = 0; b < nc; ++b) set_tap(ph, i++, rd[a], cd[b], rr[a] * 3 + cc[b], 0);
+        mi->ntaps[ph] = i;
+      }
+      break;
+    }
+    case UZ_CONV1X1_S2:
+      mi->Hm = mi->Ho = (H - 1) / 2 + 1;
+      mi->Wm = mi->Wo = (W - 1) / 2 + 1;
+      mi->lat[0] = {0, 0, 2};
+      set_tap(0, 0, 0, 0, 0, 0);
+      mi->ntaps[0] = 1;
+      mi->btaps = 1;
+      break;
+    case UZ_CONV1X1_S2_DGRAD:
+      // only even output pixels receive gradient; caller zero-fills / accumulates the rest
+      if ((out_h - 1) / 2 + 1 != H || (out_w - 1) / 2 + 1 != W)
+        return set_error(UZ_ERR_INVALID, "stride-2 1x1 dgrad: output %dx%d inconsistent with dY %dx%d", out_h, out_w,
+                         H, W);
+      mi->Ho = out_h;
+      mi->Wo = out_w;
+      mi->oscale = 2;
+      set_tap(0, 0, 0, 0, 0, 0);
+      mi->ntaps[0] = 1;
+      mi->btaps = 1;
+      break;
+    case UZ_CONVT2X2:
+      mi->Ho = 2 * H;
+      mi->Wo = 2 * W;
+      mi->oscale = 2;
+      mi->num_phases = 4;
+      mi->btaps = 4;
+      for (int ph = 0; ph < 4; ++ph) {
+        p->phase_oy[ph] = (int8_t)(ph >> 1);
+        p->phase_ox[ph] = (int8_t)(ph & 1);
+        set_tap(ph, 0, 0, 0, ph, 0);
+        mi->ntaps[ph] = 1;
+      }
+      break;
+    case UZ_CONVT2X2_DGRAD:
+      if ((H & 1) || (W & 1)) return set_error(UZ_ERR_INVALID, "convT dgrad needs even dY size, got %dx%d", H, W);
+      mi->Hm = mi->Ho = H / 2;
+      mi->Wm = mi->Wo = W / 2;
+      mi->num_lat = 4;
+      for (int l = 0; l < 4; ++l) {
+        mi->lat[l] = {l >> 1, l & 1, 2};
+        set_tap(0, l, 0, 0, l, l);
+      }
+      mi->ntaps[0] = 4;
+      mi->btaps = 4;
+      break;
+    case UZ_UP2X_CONV3X3:
+      mi->Ho = 2 * H;
+      mi->Wo = 2 * W;
+      mi->oscale = 2;
+      mi->num_phases = 4;
+      mi->btaps = 9;
+      for (int ph = 0; ph < 4; ++ph) {
+        const int py = ph >> 1, px = ph & 1;
+        p->phase_oy[ph] = (int8_t)py;
+        p->phase_ox[ph] = (int8_t)px;
+        for (int r = 0; r < 3; ++r)
+          for (int s = 0; s < 3; ++s) {
+            // source row of upsampled row (2y + py + r - 1) is floor((2y + py + r - 1) / 2) = y + floor((py+r-1)/2)
+            const int dy = (py + r - 1 + 2) / 2 - 1;
+            const int dx = (px + s - 1 + 2) / 2 - 1;
+            set_tap(ph, r * 3 + s, dy, dx, r * 3 + s, 0);
+          }
+        mi->ntaps[ph] = 9;
+      }
+      break;
+    default:
+      return set_error(UZ_ERR_INVALID, "unknown conv mode %d", mode);
+  }
+  if (out_h != mi->Ho || out_w != mi->Wo)
+    return set_error(UZ_ERR_INVALID, "mode %d: expected output %dx%d, got %dx%d", mode, mi->Ho, mi->Wo, out_h, out_w);
+  return UZ_OK;
+}
+
+}  // namespace uz
+
+using namespace uz;
+
+extern "C" const char* uz_last_error(void) { return g_err; }
+extern "C" int uz_version(void) { return 100; }
+extern "C" int uz_device_sm_count(void) {
+  int n = sm_count();
+  if (n == -2) return set_error(UZ_ERR_UNSUPPORTED, "current device is not compute capability 10.x (sm_100a required)");
+  if (n < 0) return set_error(UZ_ERR_CUDA, "no CUDA device");
+  return n;
+}
+extern "C" int uz_conv_stats_rows(void) { return uz_device_sm_count(); }
+
+extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void* const* seg_ptr, const int* seg_c,
+                             const int* seg_ld, const void* w_packed, int cout, const float* bias, void* out,
+                             int out_ld, int out_h, int out_w, float* stats, int flags, void* stream) {
+  const int sms = uz_device_sm_count();
+  if (sms < 0) return sms;
+  if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bad activation size N=%d H=%d W=%d", N, H, W);
+  if (nseg < 1 || nseg > kMaxSegs) return set_error(UZ_ERR_INVALID, "nseg=%d out of range [1,%d]", nseg, kMaxSegs);
+  if (cout < 8 || (cout & 7) || (out_ld & 7) || out_ld < cout)
+    return set_error(UZ_ERR_INVALID, "cout=%d / out_ld=%d must be multiples of 8 with out_ld >= cout", cout, out_ld);
+  if (!aligned16(out) || !aligned16(w_packed)) return set_error(UZ_ERR_INVALID, "out / weights must be 16-byte aligned");
+  if ((flags & UZ_FLAG_STATS) && stats == nullptr) return set_error(UZ_ERR_INVALID, "UZ_FLAG_STATS without stats buffer");
+
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  ModeInfo mi;
+  int rc = build_mode(mode, H, W, out_h, out_w, &p, &mi);
+  if (rc != UZ_OK) return rc;
+  if (mi.num_phases > 1) {
+    for (int ph = 1; ph < mi.num_phases; ++ph)
+      if (mi.ntaps[ph] != mi.ntaps[0] && mode != UZ_CONV3X3_S2_DGRAD)
+        return set_error(UZ_ERR_INVALID, "internal: ragged tap table");
+  }
+  if (nseg * mi.num_lat > kMaxAMaps)
+    return set_error(UZ_ERR_UNSUPPORTED, "%d segments x %d lattices exceeds %d tensor maps", nseg, mi.num_lat, kMaxAMaps);
+
+  int tw, th, tn;
+  pick_tile(128, mi.Hm, mi.Wm, &tw, &th, &tn);
+  int ctot = 0;
+  for (int s = 0; s < nseg; ++s) {
+    if (seg_c[s] < 8 || (seg_c[s] & 7) || (seg_ld[s] & 7) || seg_ld[s] < seg_c[s] || !aligned16(seg_ptr[s]))
+      return set_error(UZ_ERR_INVALID, "segment %d: channels=%d ld=%d must be multiples of 8, pointer 16-B aligned", s,
+                       seg_c[s], seg_ld[s]);
+    p.seg_cblocks[s] = (seg_c[s] + 63) / 64;
+    p.seg_k0[s] = ctot;
+    ctot += seg_c[s];
+    for (int l = 0; l < mi.num_lat; ++l) {
+      rc = make_act_map(&p.amap[s * mi.num_lat + l], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, mi.lat[l], tw, th, tn);
+      if (rc != UZ_OK) return rc;
+    }
+  }
+  const int bn = cout <= 32 ? 32 : cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
+  rc = make_weight_map(&p.bmap, w_packed, ctot, mi.btaps, cout, bn);
+  if (rc != UZ_OK) return rc;
+
+  p.num_segs = nseg;
+  p.num_lat = mi.num_lat;
+  p.num_phases = mi.num_phases;
+  p.N = N;
+  p.H = mi.Hm;
+  p.W = mi.Wm;
+  p.tw_log2 = ilog2(tw);
+  p.th_log2 = ilog2(th);
+  p.xb = (mi.Wm + tw - 1) / tw;
+  p.yb = (mi.Hm + th - 1) / th;
+  p.nb = (N + tn - 1) / tn;
+  p.num_n_tiles = (cout + bn - 1) / bn;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.Ho = mi.Ho;
+  p.Wo = mi.Wo;
+  p.out_ld = out_ld;
+  p.oscale = mi.oscale;
+  p.ncols = cout;
+  p.bias = bias;
+  p.stats = stats;
+  p.flags = flags;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  if (flags & UZ_FLAG_STATS) {
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
+    if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
+  }
+  if (mode == UZ_CONV3X3_S2_DGRAD) {
+    // ragged tap counts per phase: one launch per phase (each is a 1-phase problem with its own tap table)
+    if (flags & UZ_FLAG_STATS) return set_error(UZ_ERR_UNSUPPORTED, "stats not supported for stride-2 dgrad");
+    for (int ph = 0; ph < 4; ++ph) {
+      IgemmParams q = p;
+      q.num_phases = 1;
+      q.taps[0] = p.taps[ph];
+      q.phase_oy[0] = p.phase_oy[ph];
+      q.phase_ox[0] = p.phase_ox[ph];
+      q.num_taps = mi.ntaps[ph];
+      q.total_tiles = q.xb * q.yb * q.nb * q.num_n_tiles;
+      const int grid = q.total_tiles < sms ? q.total_tiles : sms;
+      cudaError_t e = launch_igemm_fwd(q, bn, grid, st);
+      if (e != cudaSuccess) return cuda_error(e, "igemm_fwd launch");
+    }
+    return UZ_OK;
+  }
+  p.num_taps = mi.ntaps[0];
+  p.total_tiles = p.xb * p.yb * p.nb * p.num_n_tiles * p.num_phases;
+  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  cudaError_t e = launch_igemm_fwd(p, bn, grid, st);
+  if (e != cudaSuccess) return cuda_error(e, "igemm_fwd launch");
+  return UZ_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ wgrad
+namespace uz {
+struct WgPlan {
+  int rc;
+  int cp, cq, taps, phases;
+  int Hr, Wr;  // reduction pixel space per image
+  int tw, th, tn, xb, yb, nb, chunks;
+  int m_tiles, q_cblocks, atoms, n_slabs, splits;
+  size_t ws_bytes;
+};
+static WgPlan plan_wgrad(int mode, int N, int H, int W, int cin, int cout) {
+  WgPlan pl;
+  memset(&pl, 0, sizeof(pl));
+  pl.rc = UZ_OK;
+  pl.phases = 1;
+  pl.Hr = H;
+  pl.Wr = W;
+  pl.cp = cout;
+  pl.cq = cin;
+  switch (mode) {
+    case UZ_CONV3X3: pl.taps = 9; break;
+    case UZ_CONV1X1: pl.taps = 1; break;
+    case UZ_CONV3X3_S2: pl.taps = 9; pl.Hr = (H - 1) / 2 + 1; pl.Wr = (W - 1) / 2 + 1; break;
+    case UZ_CONV1X1_S2: pl.taps = 1; pl.Hr = (H - 1) / 2 + 1; pl.Wr = (W - 1) / 2 + 1; break;
+    case UZ_UP2X_CONV3X3: pl.taps = 9; pl.phases = 4; break;
+    case UZ_CONVT2X2: pl.taps = 4; pl.cp = cin; pl.cq = cout; break;
+    default: pl.rc = set_error(UZ_ERR_INVALID, "wgrad: unsupported mode %d", mode); return pl;
+  }
+  pick_tile(64, pl.Hr, pl.Wr, &pl.tw, &pl.th, &pl.tn);
+  pl.xb = (pl.Wr + pl.tw - 1) / pl.tw;
+  pl.yb = (pl.Hr + pl.th - 1) / pl.th;
+  pl.nb = (N + pl.tn - 1) / pl.tn;
+  pl.chunks = pl.xb * pl.yb * pl.nb;
+  pl.m_tiles = (pl.cp + 127) / 128;
+  pl.q_cblocks = (pl.cq + 63) / 64;
+  pl.atoms = pl.taps * pl.q_cblocks;
+  pl.n_slabs = (pl.atoms + 3) / 4;
+  const int items0 = pl.m_tiles * pl.n_slabs;
+  const int total_chunks = pl.chunks * pl.phases;
+  int sms = sm_count();
+  if (sms < 1) sms = 148;
+  int splits = 1;
+  if (items0 < 2 * sms) splits = (2 * sms + items0 - 1) / items0;
+  int max_splits = total_chunks / 8;
+  if (max_splits < 1) max_splits = 1;
+  if (splits > max_splits) splits = max_splits;
+  pl.splits = splits;
+  pl.ws_bytes = sizeof(float) * (size_t)splits * pl.cp * pl.taps * pl.cq;
+  return pl;
+}
+}  // namespace uz
+
+extern "C" size_t uz_conv_wgrad_workspace_bytes(int mode, int N, int H, int W, int cin, int cout) {
+  WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
+  return pl.rc == UZ_OK ? pl.ws_bytes : 0;
+}
+
+extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int cin, int x_ld, const void* dy,
+                             int cout, int dy_ld, float* dw, int cin_total, int c_off, int accumulate,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+  const int sms = uz_device_sm_count();
+  if (sms < 0) return sms;
+  if ((cin & 7) || (cout & 7) || (x_ld & 7) || (dy_ld & 7) || cin < 8 || cout < 8)
+    return set_error(UZ_ERR_INVALID, "wgrad: channel counts / strides must be multiples of 8");
+  if (!aligned16(x) || !aligned16(dy) || !aligned16(workspace))
+    return set_error(UZ_ERR_INVALID, "wgrad: pointers must be 16-byte aligned");
+  WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
+  if (pl.rc != UZ_OK) return pl.rc;
+  if (workspace_bytes < pl.ws_bytes)
+    return set_error(UZ_ERR_WORKSPACE, "wgrad: workspace %zu < required %zu bytes", workspace_bytes, pl.ws_bytes);
+
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  auto set_tap = [&](int ph, int i, int dy_, int dx_, int lat) {
+    p.taps[ph].dy[i] = (int8_t)dy_;
+    p.taps[ph].dx[i] = (int8_t)dx_;
+    p.taps[ph].btap[i] = (int8_t)i;
+    p.taps[ph].lat[i] = (int8_t)lat;
+  };
+  int rc = UZ_OK;
+  const Lattice full = {0, 0, 1};
+  switch (mode) {
+    case UZ_CONV3X3:
+      rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      if (rc == UZ_OK) rc = make_act_map(&p.qmap[0], x, cin, x_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, r - 1, s - 1, 0);
+      break;
+    case UZ_CONV1X1:
+      rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      if (rc == UZ_OK) rc = make_act_map(&p.qmap[0], x, cin, x_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      set_tap(0, 0, 0, 0, 0);
+      break;
+    case UZ_CONV3X3_S2:
+      rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, pl.Hr, pl.Wr, full, pl.tw, pl.th, pl.tn);
+      for (int l = 0; l < 4 && rc == UZ_OK; ++l)
+        rc = make_act_map(&p.qmap[l], x, cin, x_ld, N, H, W, Lattice{l >> 1, l & 1, 2}, pl.tw, pl.th, pl.tn);
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) {
+          int pr, dr, pc, dc;
+          s2_tap(r, &pr, &dr);
+          s2_tap(s, &pc, &dc);
+          set_tap(0, r * 3 + s, dr, dc, pr * 2 + pc);
+        }
+      break;
+    case UZ_CONV1X1_S2:
+      rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, pl.Hr, pl.Wr, full, pl.tw, pl.th, pl.tn);
+      if (rc == UZ_OK) rc = make_act_map(&p.qmap[0], x, cin, x_ld, N, H, W, Lattice{0, 0, 2}, pl.tw, pl.th, pl.tn);
+      set_tap(0, 0, 0, 0, 0);
+      break;
+    case UZ_UP2X_CONV3X3:
+      // pixel space = low-res (N,H,W); phase (py,px) pairs dY[2y+py, 2x+px] with x_low[y+dy, x+dx]
+      rc = make_act_map(&p.qmap[0], x, cin, x_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      for (int ph = 0; ph < 4 && rc == UZ_OK; ++ph) {
+        const int py = ph >> 1, px = ph & 1;
+        rc = make_act_map(&p.pmap[ph], dy, cout, dy_ld, N, 2 * H, 2 * W, Lattice{py, px, 2}, pl.tw, pl.th, pl.tn);
+        for (int r = 0; r < 3; ++r)
+          for (int s = 0; s < 3; ++s)
+            set_tap(ph, r * 3 + s, (py + r - 1 + 2) / 2 - 1, (px + s - 1 + 2) / 2 - 1, 0);
+      }
+      break;
+    case UZ_CONVT2X2:
+      // rows = input channels (P = x, low res), cols = output channels (Q = dY lattices of the 2H x 2W gradient)
+      rc = make_act_map(&p.pmap[0], x, cin, x_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
+      for (int l = 0; l < 4 && rc == UZ_OK; ++l) {
+        rc = make_act_map(&p.qmap[l], dy, cout, dy_ld, N, 2 * H, 2 * W, Lattice{l >> 1, l & 1, 2}, pl.tw, pl.th, pl.tn);
+        set_tap(0, l, 0, 0, l);
+      }
+      break;
+    default:
+      return set_error(UZ_ERR_INVALID, "wgrad: unsupported mode %d", mode);
+  }
+  if (rc != UZ_OK) return rc;
+
+  p.num_phases = pl.phases;
+  p.num_taps = pl.taps;
+  p.N = N;
+  p.H = pl.Hr;
+  p.W = pl.Wr;
+  p.tw_log2 = ilog2(pl.tw);
+  p.th_log2 = ilog2(pl.th);
+  p.xb = pl.xb;
+  p.yb = pl.yb;
+  p.nb = pl.nb;
+  p.chunks_per_phase = pl.chunks;
+  p.cp = pl.cp;
+  p.cq = pl.cq;
+  p.m_tiles = pl.m_tiles;
+  p.q_cblocks = pl.q_cblocks;
+  p.num_atoms = pl.atoms;
+  p.n_slabs = pl.n_slabs;
+  p.splits = pl.splits;
+  p.total_items = pl.m_tiles * pl.n_slabs * pl.splits;
+  p.partial = static_cast<float*>(workspace);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = p.total_items < sms ? p.total_items : sms;
+  cudaError_t e = launch_igemm_wgrad(p, grid, st);
+  if (e != cudaSuccess) return cuda_error(e, "igemm_wgrad launch");
+
+  long long s_row, s_col, s_tap = 1;
+  float* dst = dw;
+  if (mode == UZ_CONVT2X2) {
+    s_row = (long long)cout * 4;
+    s_col = 4;
+  } else {
+    s_row = (long long)cin_total * pl.taps;
+    s_col = pl.taps;
+    dst = dw + (long long)c_off * pl.taps;
+  }
+  e = launch_wgrad_reduce(p.partial, dst, pl.splits, pl.cp, pl.taps, pl.cq, s_row, s_col, s_tap, accumulate, st);
+  if (e != cudaSuccess) return cuda_error(e, "wgrad_reduce launch");
+  return UZ_OK;
+}

@@ -1,0 +1,75 @@
+// Shared declarations for the two tcgen05 implicit-GEMM kernels (forward-type and weight-gradient-type).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace uz {
+
+constexpr int kMaxAMaps = 8;    // A-operand tensor maps: (segment, lattice) pairs
+constexpr int kMaxSegs = 6;     // channel segments of a virtual concat
+constexpr int kMaxTaps = 36;    // filter taps per phase (36 = 4 phases x 9 for the fused up2x dgrad)
+constexpr int kMaxPhases = 4;   // output sub-lattices (2x2 scatter for transposed conv / nearest-up2x conv)
+
+struct TapTable {
+  int8_t dy[kMaxTaps];    // A-tile row shift (in A-lattice pixels)
+  int8_t dx[kMaxTaps];    // A-tile column shift
+  int8_t btap[kMaxTaps];  // tap coordinate in the packed weight tensor
+  int8_t lat[kMaxTaps];   // which lattice map of the segment this tap reads
+};
+
+enum IgemmFlags : int {
+  kFlagRelu = 1,
+  kFlagAccumulate = 2,  // out += result (bf16 read-modify-write)
+  kFlagStats = 4,       // per-channel sum / sum-of-squares of the stored (bf16-rounded) values
+};
+
+// Forward-type implicit GEMM:  out[pixel, col] = sum_{seg,tap,c} A_seg[pixel + shift(tap), c] * Wp[col, tap, k0(seg)+c]
+struct alignas(64) IgemmParams {
+  CUtensorMap amap[kMaxAMaps];  // 4-D (C, W, H, N) bf16 views, box (64, tw, th, tn), SWIZZLE_128B
+  CUtensorMap bmap;             // 3-D (Ctot, taps, cols) bf16 packed weights, box (64, 1, BN)
+  TapTable taps[kMaxPhases];
+  int8_t phase_oy[kMaxPhases];
+  int8_t phase_ox[kMaxPhases];
+  int num_segs;
+  int seg_cblocks[kMaxSegs];  // ceil(C_seg / 64)
+  int seg_k0[kMaxSegs];       // first weight-channel index of the segment
+  int num_lat;
+  int num_taps;
+  int num_phases;
+  int N, H, W;                 // extent of the M index space (A-lattice pixels)
+  int tw_log2, th_log2;        // M tile = tn x th x tw pixels = 128
+  int xb, yb, nb;              // tile counts along x, y, n
+  int num_n_tiles;
+  int total_tiles;             // xb*yb*nb*num_n_tiles*num_phases
+  // output: pixel (n, y*oscale + phase_oy, x*oscale + phase_ox) in an (N, Ho, Wo, out_ld) bf16 tensor
+  __nv_bfloat16* out;
+  int Ho, Wo, out_ld, oscale;
+  int ncols;                   // valid output columns (Cout)
+  const float* bias;           // optional, per column
+  float* stats;                // optional [gridDim.x][2][ncols] partial sums (kFlagStats)
+  int flags;
+};
+
+// Weight-gradient-type GEMM:  D[t][i, j] = sum_{phase, pixel} P[phase][pixel, i] * Q[pixel + shift(phase, t), j]
+struct alignas(64) WgradParams {
+  CUtensorMap pmap[kMaxPhases];  // un-shifted operand, one lattice view per phase; box (64, tw, th, tn)
+  CUtensorMap qmap[kMaxPhases];  // shifted operand, one view per lattice
+  TapTable taps[kMaxPhases];
+  int num_phases, num_taps;
+  int N, H, W;                   // pixel index space of the reduction
+  int tw_log2, th_log2;          // K chunk = tn x th x tw pixels = 64
+  int xb, yb, nb;
+  int chunks_per_phase;          // xb*yb*nb
+  int cp, cq;                    // channels of P (rows) and Q (cols)
+  int m_tiles;                   // ceil(cp / 128)
+  int q_cblocks;                 // ceil(cq / 64)
+  int num_atoms;                 // num_taps * q_cblocks
+  int n_slabs;                   // ceil(num_atoms / 4)
+  int splits;                    // split-K factor
+  int total_items;               // m_tiles * n_slabs * splits
+  float* partial;                // [splits][cp][num_taps][cq] fp32
+};
+
+}  // namespace uz
