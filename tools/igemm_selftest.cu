@@ -345,7 +345,7 @@ int main(int argc, char** argv) {
       {"convT2x2 128->64 16x16 N2 bias (-> cat slice)", UZ_CONVT2X2, 2, 16, 16, 1, {128}, 64, 0, true, 64},
       {"convT2x2 dgrad 64->128 32x32 N2", UZ_CONVT2X2_DGRAD, 2, 32, 32, 1, {64}, 128, 0, false, 0},
       {"up2x+conv3x3 128->64 16x16 N2", UZ_UP2X_CONV3X3, 2, 16, 16, 1, {128}, 64, 0, false, 0},
-      {"conv3x3 256->256 64x64 N4 (multi-wave) stats", UZ_CONV3X3, 4, 64, 64, 1, {256}, 256, UZ_FLAG_STATS, false, 0},
+      {"conv3x3 64->64 64x64 N5 (multi-wave) stats", UZ_CONV3X3, 5, 64, 64, 1, {64}, 64, UZ_FLAG_STATS, false, 0},
   };
   const WgCase wg[] = {
       {"wgrad conv3x3 64->64 32x32 N2", UZ_CONV3X3, 2, 32, 32, 64, 64},

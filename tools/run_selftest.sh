@@ -9,7 +9,7 @@ nvidia-smi --query-gpu=name,driver_version --format=csv >> "$LOG" 2>&1
 n=$("$BIN" count)
 fails=0
 for ((i = 0; i < n; i++)); do
-  timeout 90 "$BIN" "$i" >> "$LOG" 2>&1
+  timeout 60 "$BIN" "$i" >> "$LOG" 2>&1
   rc=$?
   if [[ $rc -ne 0 ]]; then
     echo "case $i exit code $rc" >> "$LOG"
