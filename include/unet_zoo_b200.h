@@ -41,14 +41,67 @@ int uz_version(void);
 int uz_device_sm_count(void);
 
 /* ------------------------------------------------------------------------------------------------------------
- * Weight packing: fp32 parameter -> bf16 operand  dst[a][t][b] = src[a*sa + b*sb + t*st]   (a<A, t<T, b<B)
+ * Weight packing: fp32 parameter -> bf16 operand
+ *   dst[a*dst_pitch + t*B + b] = bf16(src[a*sa + b*sb + t*st] * (row_scale ? row_scale[a] : 1))   (a<A, t<T, b<B)
  *   Conv2d fwd  (OIHW [Co,Ci,kh,kw])      : A=Co T=kh*kw B=Ci  sa=Ci*T sb=T  st=1
  *   Conv2d dgrad                           : A=Ci T=kh*kw B=Co  sa=T    sb=Ci*T st=1
  *   ConvTranspose2d fwd (IOHW [Ci,Co,2,2]) : A=Co T=4     B=Ci  sa=4    sb=Co*4 st=1
  *   ConvTranspose2d dgrad                  : A=Ci T=4     B=Co  sa=Co*4 sb=4   st=1
+ *   stem (im2col'd 3x3, K = 9*Ci padded)   : A=Co T=9     B=Ci  sa=Ci*9 sb=9   st=1  dst_pitch=kp (pad zeroed by caller)
+ * dst_pitch >= T*B (elements).  row_scale folds an inference-mode BatchNorm scale into the output-channel rows.
  * Replaces: the implicit weight reads of nn.Conv2d / nn.ConvTranspose2d (common_layers.py:28,31,104). */
 int uz_pack_weight(const float* src, void* dst_bf16, int A, int T, int B, long long sa, long long sb, long long st,
-                   void* stream);
+                   long long dst_pitch, const float* row_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Input staging.  The reference feeds NCHW fp32 images (training_loop.py:109, unet.py:31).
+ *  uz_stem_im2col : out[n,y,x, t*cin+ci] = x[n,ci,y+r-1,x+s-1] (t=r*3+s, zero outside / for columns >= 9*cin), NHWC
+ *                   bf16 with kp in {16,32,64} channels; the low-channel stem conv then runs as a 1x1 GEMM over it
+ *                   (common_layers.py:28 with in_channels=3; resunet.py:26,32).
+ *  uz_nchw_to_nhwc: layout + dtype change with zero channel padding up to a multiple of 8 (in_channels >= 8). */
+int uz_stem_im2col(const float* x, int N, int cin, int H, int W, void* out, int kp, void* stream);
+int uz_nchw_to_nhwc(const float* x, int N, int C, int H, int W, void* out, int out_ld, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * BatchNorm2d, training mode (common_layers.py:29,32; attention_unet.py:13,20,27; nested_unet.py:8,10).
+ *  partial statistics: fp32 [rows][2][C] (sum, sum of squares) - produced by uz_conv_igemm(UZ_FLAG_STATS) with
+ *  rows = uz_conv_stats_rows(), or by uz_bn_stats for an arbitrary tensor with rows = uz_reduce_rows().
+ *  uz_bn_finalize: bn[4][C] = {mean, invstd, scale = gamma*invstd, shift = beta - mean*scale}; running_mean /
+ *    running_var updated exactly like nn.BatchNorm2d (EMA with `momentum`, unbiased variance), may be NULL.
+ *  uz_bn_apply   : y = act(z*scale + shift [+ residual]); `pooled` (optional) receives MaxPool2d(2,2)(y)
+ *    (common_layers.py:90,94); y may be NULL when only the pooled tensor is wanted; scale==shift==NULL -> identity. */
+int uz_reduce_rows(void);
+int uz_bn_stats(const void* x, int ld, long long npix, int C, float* partial, void* stream);
+int uz_bn_finalize(const float* partial, int rows, int C, long long count, const float* gamma, const float* beta,
+                   float eps, float momentum, float* running_mean, float* running_var, float* bn, void* stream);
+int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, const float* scale, const float* shift, int relu,
+                const void* residual, int res_ld, void* y, int y_ld, void* pooled, int pooled_ld, void* stream);
+
+/* Backward of y = [ReLU](BN(z)) fused with the MaxPool2d(2,2) gradient routing:
+ *   g  = (dy + route(dpool)) * [relu ? (y > 0) : 1]       route(): first maximum of each 2x2 window (row-major scan)
+ *   dz = gamma*invstd * (g - mean(g) - x^ * mean(g*x^)),  dgamma = sum g*x^,  dbeta = sum g,  dbias = sum dz
+ * dy and dpool are each optional (not both NULL).  dgamma/dbeta/dbias are fp32 [C] (NULL to skip); `accumulate`
+ * adds into them.  Replaces autograd through BatchNorm2d/ReLU/MaxPool2d for the call sites above. */
+size_t uz_bn_bwd_workspace_bytes(int C);
+int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, const void* dpool, int dpool_ld, int N, int H, int W,
+              int C, const float* bn, int relu, void* dz, int dz_ld, float* dgamma, float* dbeta, float* dbias,
+              int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+
+/* out[c] (+)= sum over pixels x[p, c]  (bias gradient of ConvTranspose2d / plain Conv2d). */
+size_t uz_colsum_workspace_bytes(int C);
+int uz_colsum(const void* x, int ld, long long npix, int C, float* out, int accumulate, void* workspace,
+              size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * 1x1 classifier head: logits[n,k,h,w] (fp32, NCHW) = b[k] + sum_c w[k,c] * y[n,h,w,c]   (no activation)
+ * Replaces OutConv (common_layers.py:125-128), attention_unet.py:70, nested_unet.py:61-69, resunet.py:49-52.
+ * Backward: dy[p,c] = sum_k dlogits[p,k] w[k,c] (bf16), dw[k,c] = sum_p dlogits[p,k] y[p,c], db[k] = sum_p dlogits. */
+int uz_head_fwd(const void* y, int ld, int N, int H, int W, int C, int K, const float* w, const float* b,
+                float* logits, void* stream);
+size_t uz_head_bwd_workspace_bytes(int C);
+int uz_head_bwd(const void* y, int ld, const float* dlogits, int N, int H, int W, int C, int K, const float* w,
+                void* dy, int dy_ld, float* dw, float* db, int accumulate, void* workspace, size_t workspace_bytes,
+                void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Implicit-GEMM convolutions on tcgen05 (forward-type).  `mode` selects the gather / scatter pattern. */

@@ -1,0 +1,761 @@
+// Bandwidth-bound kernels of the UNet hot path (sm_100a): weight packing, stem im2col, BatchNorm statistics /
+// finalize / apply (+ReLU, +2x2 max-pool, +residual), BatchNorm+ReLU(+max-pool) backward, per-channel sums.
+// All activations are NHWC bf16 addressed as (pointer, pixel stride `ld`), 8 channels (16 bytes) per access.
+// Every thread keeps one fixed group of 8 channels for its whole lifetime so the per-channel constants live in
+// registers; reductions are two-stage (per-block partials, then a deterministic finalize) - no float atomics.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/unet_zoo_b200.h"
+#include "host_util.h"
+
+namespace uz {
+
+// ---------------------------------------------------------------------------------------------- small device helpers
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = __uint_as_float(v.x << 16);
+  f[1] = __uint_as_float(v.x & 0xFFFF0000u);
+  f[2] = __uint_as_float(v.y << 16);
+  f[3] = __uint_as_float(v.y & 0xFFFF0000u);
+  f[4] = __uint_as_float(v.z << 16);
+  f[5] = __uint_as_float(v.z & 0xFFFF0000u);
+  f[6] = __uint_as_float(v.w << 16);
+  f[7] = __uint_as_float(v.w & 0xFFFF0000u);
+}
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
+}
+__device__ __forceinline__ float bf16_round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+  f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// launch geometry shared by the "fixed channel group per thread" kernels
+struct Geo {
+  int cv;      // channel groups (C / 8)
+  int block;   // threads per block, multiple of cv
+  int ppb;     // items (pixels or 2x2 quads) per block iteration
+  int grid;
+};
+static Geo make_geo(int C, long long items, int blocks_per_sm) {
+  Geo g;
+  g.cv = C / 8;
+  g.ppb = 256 / g.cv;
+  if (g.ppb < 1) g.ppb = 1;
+  g.block = g.ppb * g.cv;
+  int sms = sm_count();
+  if (sms < 1) sms = 148;
+  long long need = (items + g.ppb - 1) / g.ppb;
+  long long cap = static_cast<long long>(sms) * blocks_per_sm;
+  g.grid = static_cast<int>(need < cap ? need : cap);
+  if (g.grid < 1) g.grid = 1;
+  return g;
+}
+
+// ---------------------------------------------------------------------------------------------- weight packing
+// dst[a*dst_pitch + t*B + b] = bf16(src[a*sa + b*sb + t*st] * (row_scale ? row_scale[a] : 1))
+__global__ void pack_weight_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int A, int T, int B,
+                                   long long sa, long long sb, long long st, long long dst_pitch,
+                                   const float* __restrict__ row_scale) {
+  const long long total = static_cast<long long>(A) * B;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i % B);
+    const int a = static_cast<int>(i / B);
+    const float sc = row_scale ? __ldg(row_scale + a) : 1.f;
+    const float* s = src + a * sa + b * sb;
+    __nv_bfloat16* d = dst + a * dst_pitch + b;
+    for (int t = 0; t < T; ++t) d[static_cast<long long>(t) * B] = __float2bfloat16_rn(__ldg(s + t * st) * sc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- stem im2col
+// out[n, y, x, t*cin + ci] = x[n, ci, y + r - 1, x + s - 1] (t = r*3 + s), zero outside the image and for columns
+// >= 9*cin.  One thread per pixel; reads are coalesced along W and served mostly by L1 (each input is used 9 times).
+template <int KP>
+__global__ void stem_im2col_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int cin, int H,
+                                   int W) {
+  const long long npix = static_cast<long long>(N) * H * W;
+  const long long plane = static_cast<long long>(H) * W;
+  for (long long p = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; p < npix;
+       p += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int xw = static_cast<int>(p % W);
+    const long long r0 = p / W;
+    const int yh = static_cast<int>(r0 % H);
+    const int n = static_cast<int>(r0 / H);
+    const float* xb = x + static_cast<long long>(n) * cin * plane;
+    float v[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) v[k] = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int yy = yh + t / 3 - 1, xx = xw + t % 3 - 1;
+      const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      for (int ci = 0; ci < cin; ++ci) {
+        const int k = t * cin + ci;
+        if (k < KP) v[k] = ok ? __ldg(xb + ci * plane + static_cast<long long>(yy) * W + xx) : 0.f;
+      }
+    }
+    uint4* o = reinterpret_cast<uint4*>(out + p * KP);
+#pragma unroll
+    for (int g = 0; g < KP / 8; ++g) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = v[g * 8 + j];
+      o[g] = pack8(f);
+    }
+  }
+}
+
+// plain NCHW fp32 -> NHWC bf16 with channel padding (columns >= C are zero); one thread per (pixel, 8 channels)
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int C, int H,
+                                    int W, int out_ld, int cpad) {
+  const long long plane = static_cast<long long>(H) * W;
+  const int cv = cpad / 8;
+  const long long total = static_cast<long long>(N) * plane * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    // pixel is the fast index so that the fp32 reads of one channel plane coalesce
+    const long long pix = i % (static_cast<long long>(N) * plane);
+    const int g = static_cast<int>(i / (static_cast<long long>(N) * plane));
+    const int n = static_cast<int>(pix / plane);
+    const long long hw = pix % plane;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      f[j] = c < C ? __ldg(x + (static_cast<long long>(n) * C + c) * plane + hw) : 0.f;
+    }
+    *reinterpret_cast<uint4*>(out + pix * out_ld + g * 8) = pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- BatchNorm statistics
+// per-channel sum / sum of squares of an arbitrary NHWC bf16 tensor -> partial[block][2][C]
+__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int ld, long long npix, int C, int cv, int ppb,
+                                float* __restrict__ partial) {
+  extern __shared__ float red[];  // [ppb][cv][16]
+  const int g = threadIdx.x % cv;
+  const int pl = threadIdx.x / cv;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  for (long long p = static_cast<long long>(blockIdx.x) * ppb + pl; p < npix; p += static_cast<long long>(gridDim.x) * ppb) {
+    float f[8];
+    unpack8(ldg16(x + p * ld + g * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s[j] += f[j];
+      q[j] = fmaf(f[j], f[j], q[j]);
+    }
+  }
+  float* mine = red + static_cast<size_t>(threadIdx.x) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  if (pl == 0) {
+    for (int r = 1; r < ppb; ++r) {
+      const float* o = red + (static_cast<size_t>(r) * cv + g) * 16;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += o[j];
+        q[j] += o[8 + j];
+      }
+    }
+    float* dst = partial + static_cast<size_t>(blockIdx.x) * 2 * C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      dst[g * 8 + j] = s[j];
+      dst[C + g * 8 + j] = q[j];
+    }
+  }
+}
+
+// partial[rows][2][C] -> bn[4][C] = {mean, invstd, scale, shift}; running statistics updated like nn.BatchNorm2d
+// (momentum EMA, unbiased variance for running_var).  One thread per channel, fp64 accumulation.
+__global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                   float momentum, float* __restrict__ running_mean, float* __restrict__ running_var,
+                                   float* __restrict__ bn) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int r = 0; r < rows; ++r) {
+    s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
+    q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
+  }
+  const double mean = s / count;
+  double var = q / count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float invstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+  const float ga = gamma ? gamma[c] : 1.f;
+  const float be = beta ? beta[c] : 0.f;
+  const float scale = ga * invstd;
+  bn[c] = static_cast<float>(mean);
+  bn[C + c] = invstd;
+  bn[2 * C + c] = scale;
+  bn[3 * C + c] = be - static_cast<float>(mean) * scale;
+  if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(mean);
+  if (running_var) {
+    const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(unbiased);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- BatchNorm apply
+// y = act(z*scale + shift [+ residual]) ; POOL additionally writes the 2x2 max of y.  item = pixel or 2x2 quad.
+template <bool POOL>
+__global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, int N, int H, int W, int C, int cv,
+                                int ppb, const float* __restrict__ scale, const float* __restrict__ shift, int relu,
+                                const __nv_bfloat16* __restrict__ res, int res_ld, __nv_bfloat16* __restrict__ y,
+                                int y_ld, __nv_bfloat16* __restrict__ pooled, int pooled_ld) {
+  const int g = threadIdx.x % cv;
+  const int pl = threadIdx.x / cv;
+  float sc[8], sh[8];
+  if (scale) {
+    load8f(scale + g * 8, sc);
+    load8f(shift + g * 8, sh);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = 1.f;
+      sh[j] = 0.f;
+    }
+  }
+  const int Hq = POOL ? H / 2 : H, Wq = POOL ? W / 2 : W;
+  const long long items = static_cast<long long>(N) * Hq * Wq;
+  for (long long it = static_cast<long long>(blockIdx.x) * ppb + pl; it < items;
+       it += static_cast<long long>(gridDim.x) * ppb) {
+    if (!POOL) {
+      float f[8];
+      unpack8(ldg16(z + it * z_ld + g * 8), f);
+      if (res) {
+        float r[8];
+        unpack8(ldg16(res + it * res_ld + g * 8), r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]) + r[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+      }
+      if (relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      *reinterpret_cast<uint4*>(y + it * y_ld + g * 8) = pack8(f);
+    } else {
+      const int qx = static_cast<int>(it % Wq);
+      const long long r0 = it / Wq;
+      const int qy = static_cast<int>(r0 % Hq);
+      const int n = static_cast<int>(r0 / Hq);
+      const long long p00 = (static_cast<long long>(n) * H + 2 * qy) * W + 2 * qx;
+      const long long pix[4] = {p00, p00 + 1, p00 + W, p00 + W + 1};
+      uint4 raw[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) raw[i] = ldg16(z + pix[i] * z_ld + g * 8);
+      float m[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float f[8];
+        unpack8(raw[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          f[j] = fmaf(f[j], sc[j], sh[j]);
+          if (relu) f[j] = fmaxf(f[j], 0.f);
+        }
+        const uint4 o = pack8(f);
+        if (y) *reinterpret_cast<uint4*>(y + pix[i] * y_ld + g * 8) = o;
+        unpack8(o, f);  // pool the values as stored
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = i == 0 ? f[j] : fmaxf(m[j], f[j]);
+      }
+      *reinterpret_cast<uint4*>(pooled + it * pooled_ld + g * 8) = pack8(m);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- BatchNorm(+ReLU)(+pool) backward
+// g = (dy + routed(dpool)) * [relu ? (z*scale+shift > 0) : 1] ;  x^ = (z - mean) * invstd
+// reduce:  partial[block][2][C] = { sum g, sum g*x^ }
+// apply :  dz = scale*g + A + B*z   with A,B from bn_bwd_finalize   (== scale*(g - mean(g) - x^*mean(g*x^)))
+struct BwdArgs {
+  const __nv_bfloat16* z;
+  int z_ld;
+  const __nv_bfloat16* dy;     // may be null
+  int dy_ld;
+  const __nv_bfloat16* dpool;  // may be null (POOL only)
+  int dpool_ld;
+  int N, H, W, C, cv, ppb;
+  const float* bn;             // [4][C] mean, invstd, scale, shift
+  int relu;
+};
+
+template <bool POOL>
+__device__ __forceinline__ void bwd_item_grad(const BwdArgs& a, long long it, int g, const float (&sc)[8],
+                                              const float (&sh)[8], float (&zv)[POOL ? 4 : 1][8],
+                                              float (&gv)[POOL ? 4 : 1][8], long long (&pix)[POOL ? 4 : 1]) {
+  if (!POOL) {
+    pix[0] = it;
+    unpack8(ldg16(a.z + it * a.z_ld + g * 8), zv[0]);
+    if (a.dy) {
+      unpack8(ldg16(a.dy + it * a.dy_ld + g * 8), gv[0]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gv[0][j] = 0.f;
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (!(fmaf(zv[0][j], sc[j], sh[j]) > 0.f)) gv[0][j] = 0.f;
+    }
+  } else {
+    const int Hq = a.H / 2, Wq = a.W / 2;
+    const int qx = static_cast<int>(it % Wq);
+    const long long r0 = it / Wq;
+    const int qy = static_cast<int>(r0 % Hq);
+    const int n = static_cast<int>(r0 / Hq);
+    const long long p00 = (static_cast<long long>(n) * a.H + 2 * qy) * a.W + 2 * qx;
+    pix[0] = p00;
+    pix[1] = p00 + 1;
+    pix[2] = p00 + a.W;
+    pix[3] = p00 + a.W + 1;
+    uint4 zr[4], dr[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) zr[i] = ldg16(a.z + pix[i] * a.z_ld + g * 8);
+    if (a.dy) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dr[i] = ldg16(a.dy + pix[i] * a.dy_ld + g * 8);
+    }
+    float dp[8];
+    if (a.dpool) {
+      unpack8(ldg16(a.dpool + it * a.dpool_ld + g * 8), dp);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dp[j] = 0.f;
+    }
+    float yv[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      unpack8(zr[i], zv[i]);
+      if (a.dy) {
+        unpack8(dr[i], gv[i]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gv[i][j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float u = fmaf(zv[i][j], sc[j], sh[j]);
+        if (a.relu) u = fmaxf(u, 0.f);
+        yv[i][j] = bf16_round(u);  // the forward pooled the stored (bf16) activations
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // first maximum in row-major window order wins (nn.MaxPool2d index semantics)
+      int am = 0;
+      float mv = yv[0][j];
+#pragma unroll
+      for (int i = 1; i < 4; ++i)
+        if (yv[i][j] > mv) {
+          mv = yv[i][j];
+          am = i;
+        }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (i == am) gv[i][j] += dp[j];
+        if (a.relu && !(yv[i][j] > 0.f)) gv[i][j] = 0.f;
+      }
+    }
+  }
+}
+
+template <bool POOL>
+__global__ void bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partial) {
+  extern __shared__ float red[];
+  const int g = threadIdx.x % a.cv;
+  const int pl = threadIdx.x / a.cv;
+  float mean[8], invstd[8], sc[8], sh[8];
+  load8f(a.bn + g * 8, mean);
+  load8f(a.bn + a.C + g * 8, invstd);
+  load8f(a.bn + 2 * a.C + g * 8, sc);
+  load8f(a.bn + 3 * a.C + g * 8, sh);
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
+                               : static_cast<long long>(a.N) * a.H * a.W;
+  constexpr int NP = POOL ? 4 : 1;
+  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items;
+       it += static_cast<long long>(gridDim.x) * a.ppb) {
+    float zv[NP][8], gv[NP][8];
+    long long pix[NP];
+    bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
+#pragma unroll
+    for (int i = 0; i < NP; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += gv[i][j];
+        q[j] = fmaf(gv[i][j], (zv[i][j] - mean[j]) * invstd[j], q[j]);
+      }
+  }
+  float* mine = red + static_cast<size_t>(threadIdx.x) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  if (pl == 0) {
+    for (int r = 1; r < a.ppb; ++r) {
+      const float* o = red + (static_cast<size_t>(r) * a.cv + g) * 16;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += o[j];
+        q[j] += o[8 + j];
+      }
+    }
+    float* dst = partial + static_cast<size_t>(blockIdx.x) * 2 * a.C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      dst[g * 8 + j] = s[j];
+      dst[a.C + g * 8 + j] = q[j];
+    }
+  }
+}
+
+// partial[rows][2][C] -> dgamma, dbeta (+=) and coef[2][C] = {A, B}
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
+                                       const float* __restrict__ bn, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta, int accumulate, float* __restrict__ coef) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int r = 0; r < rows; ++r) {
+    s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
+    q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
+  }
+  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + static_cast<float>(q);
+  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + static_cast<float>(s);
+  const double mean = bn[c], invstd = bn[C + c], scale = bn[2 * C + c];
+  const double c1 = s / count, c2 = q / count;
+  coef[c] = static_cast<float>(-scale * c1 + scale * c2 * invstd * mean);
+  coef[C + c] = static_cast<float>(-scale * c2 * invstd);
+}
+
+template <bool POOL>
+__global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
+                                    int dz_ld, float* __restrict__ dbias_partial) {
+  extern __shared__ float red[];
+  const int g = threadIdx.x % a.cv;
+  const int pl = threadIdx.x / a.cv;
+  float sc[8], sh[8], ca[8], cb[8];
+  load8f(a.bn + 2 * a.C + g * 8, sc);
+  load8f(a.bn + 3 * a.C + g * 8, sh);
+  load8f(coef + g * 8, ca);
+  load8f(coef + a.C + g * 8, cb);
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
+                               : static_cast<long long>(a.N) * a.H * a.W;
+  constexpr int NP = POOL ? 4 : 1;
+  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items;
+       it += static_cast<long long>(gridDim.x) * a.ppb) {
+    float zv[NP][8], gv[NP][8];
+    long long pix[NP];
+    bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], gv[i][j], fmaf(cb[j], zv[i][j], ca[j]));
+      const uint4 w = pack8(o);
+      *reinterpret_cast<uint4*>(dz + pix[i] * dz_ld + g * 8) = w;
+      if (dbias_partial) {
+        unpack8(w, o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] += o[j];
+      }
+    }
+  }
+  if (dbias_partial) {
+    float* mine = red + static_cast<size_t>(threadIdx.x) * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mine[j] = s[j];
+    __syncthreads();
+    if (pl == 0) {
+      for (int r = 1; r < a.ppb; ++r) {
+        const float* o = red + (static_cast<size_t>(r) * a.cv + g) * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] += o[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dbias_partial[static_cast<size_t>(blockIdx.x) * a.C + g * 8 + j] = s[j];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- column sums
+// partial[block][C] = per-channel sum over this block's pixels
+__global__ void colsum_kernel(const __nv_bfloat16* __restrict__ x, int ld, long long npix, int C, int cv, int ppb,
+                              float* __restrict__ partial) {
+  extern __shared__ float red[];
+  const int g = threadIdx.x % cv;
+  const int pl = threadIdx.x / cv;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  for (long long p = static_cast<long long>(blockIdx.x) * ppb + pl; p < npix; p += static_cast<long long>(gridDim.x) * ppb) {
+    float f[8];
+    unpack8(ldg16(x + p * ld + g * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += f[j];
+  }
+  float* mine = red + static_cast<size_t>(threadIdx.x) * 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) mine[j] = s[j];
+  __syncthreads();
+  if (pl == 0) {
+    for (int r = 1; r < ppb; ++r) {
+      const float* o = red + (static_cast<size_t>(r) * cv + g) * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += o[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) partial[static_cast<size_t>(blockIdx.x) * C + g * 8 + j] = s[j];
+  }
+}
+
+// out[c] (+)= sum_r partial[r][c]
+__global__ void reduce_rows_kernel(const float* __restrict__ partial, int rows, int C, float* __restrict__ out,
+                                   int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0;
+  for (int r = 0; r < rows; ++r) s += static_cast<double>(partial[static_cast<size_t>(r) * C + c]);
+  out[c] = (accumulate ? out[c] : 0.f) + static_cast<float>(s);
+}
+
+}  // namespace uz
+
+using namespace uz;
+
+// ================================================================================================ C ABI
+static bool a16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+#define UZ_REQUIRE_DEVICE()                \
+  do {                                     \
+    const int sms_ = uz_device_sm_count(); \
+    if (sms_ < 0) return sms_;             \
+  } while (0)
+#define UZ_CHECK_LAUNCH(what)                                   \
+  do {                                                          \
+    cudaError_t e_ = cudaGetLastError();                        \
+    if (e_ != cudaSuccess) return cuda_error(e_, what);         \
+  } while (0)
+
+extern "C" int uz_pack_weight(const float* src, void* dst_bf16, int A, int T, int B, long long sa, long long sb,
+                              long long st, long long dst_pitch, const float* row_scale, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  if (A < 1 || T < 1 || B < 1 || dst_pitch < static_cast<long long>(T) * B)
+    return set_error(UZ_ERR_INVALID, "pack_weight: bad extents A=%d T=%d B=%d pitch=%lld", A, T, B, dst_pitch);
+  const long long total = static_cast<long long>(A) * B;
+  int blocks = static_cast<int>((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  pack_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst_bf16), A, T, B, sa, sb, st, dst_pitch, row_scale);
+  UZ_CHECK_LAUNCH("pack_weight launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_stem_im2col(const float* x, int N, int cin, int H, int W, void* out, int kp, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  if (cin < 1 || 9 * cin > kp || !a16(out))
+    return set_error(UZ_ERR_INVALID, "stem_im2col: 9*cin=%d must fit kp=%d, output 16-B aligned", 9 * cin, kp);
+  const long long npix = static_cast<long long>(N) * H * W;
+  int blocks = static_cast<int>((npix + 127) / 128);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  __nv_bfloat16* o = static_cast<__nv_bfloat16*>(out);
+  switch (kp) {
+    case 16: stem_im2col_kernel<16><<<blocks, 128, 0, st>>>(x, o, N, cin, H, W); break;
+    case 32: stem_im2col_kernel<32><<<blocks, 128, 0, st>>>(x, o, N, cin, H, W); break;
+    case 64: stem_im2col_kernel<64><<<blocks, 128, 0, st>>>(x, o, N, cin, H, W); break;
+    default: return set_error(UZ_ERR_UNSUPPORTED, "stem_im2col: kp must be 16, 32 or 64 (got %d)", kp);
+  }
+  UZ_CHECK_LAUNCH("stem_im2col launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_nchw_to_nhwc(const float* x, int N, int C, int H, int W, void* out, int out_ld, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  const int cpad = (C + 7) / 8 * 8;
+  if (out_ld < cpad || (out_ld & 7) || !a16(out))
+    return set_error(UZ_ERR_INVALID, "nchw_to_nhwc: out_ld=%d must be a multiple of 8 >= %d", out_ld, cpad);
+  const long long total = static_cast<long long>(N) * H * W * (cpad / 8);
+  int blocks = static_cast<int>((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  nchw_to_nhwc_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<__nv_bfloat16*>(out), N, C,
+                                                                            H, W, out_ld, cpad);
+  UZ_CHECK_LAUNCH("nchw_to_nhwc launch");
+  return UZ_OK;
+}
+
+static int check_act(const char* who, const void* p, int C, int ld) {
+  if (p == nullptr || !a16(p) || C < 8 || (C & 7) || (ld & 7) || ld < C || C > 2048)
+    return set_error(UZ_ERR_INVALID, "%s: activation needs 16-B aligned pointer, C (=%d) and ld (=%d) multiples of 8, 8 <= C <= 2048",
+                     who, C, ld);
+  return UZ_OK;
+}
+
+extern "C" int uz_reduce_rows() { return uz_device_sm_count() * 4; }
+
+extern "C" int uz_bn_stats(const void* x, int ld, long long npix, int C, float* partial, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("bn_stats", x, C, ld);
+  if (rc) return rc;
+  const Geo g = make_geo(C, npix, 4);
+  // always fill uz_reduce_rows() rows so the consumer can use a fixed row count
+  const int rows = uz_reduce_rows();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(partial, 0, sizeof(float) * 2 * C * rows, st);
+  if (e != cudaSuccess) return cuda_error(e, "bn_stats memset");
+  bn_stats_kernel<<<g.grid, g.block, g.block * 16 * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), ld, npix,
+                                                                         C, g.cv, g.ppb, partial);
+  UZ_CHECK_LAUNCH("bn_stats launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_bn_finalize(const float* partial, int rows, int C, long long count, const float* gamma,
+                              const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                              float* bn, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  if (rows < 1 || C < 1 || count < 1) return set_error(UZ_ERR_INVALID, "bn_finalize: bad extents");
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      partial, rows, C, static_cast<double>(count), gamma, beta, eps, momentum, running_mean, running_var, bn);
+  UZ_CHECK_LAUNCH("bn_finalize launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, const float* scale, const float* shift,
+                           int relu, const void* residual, int res_ld, void* y, int y_ld, void* pooled, int pooled_ld,
+                           void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("bn_apply(z)", z, C, z_ld);
+  if (rc) return rc;
+  if (y && (rc = check_act("bn_apply(y)", y, C, y_ld))) return rc;
+  if (residual && (rc = check_act("bn_apply(residual)", residual, C, res_ld))) return rc;
+  if ((scale == nullptr) != (shift == nullptr)) return set_error(UZ_ERR_INVALID, "bn_apply: scale/shift must both be given");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (pooled) {
+    if ((rc = check_act("bn_apply(pooled)", pooled, C, pooled_ld))) return rc;
+    if ((H & 1) || (W & 1)) return set_error(UZ_ERR_INVALID, "bn_apply: pooling needs even H, W (got %dx%d)", H, W);
+    if (residual) return set_error(UZ_ERR_UNSUPPORTED, "bn_apply: residual + pool not supported");
+    const Geo g = make_geo(C, static_cast<long long>(N) * (H / 2) * (W / 2), 8);
+    bn_apply_kernel<true><<<g.grid, g.block, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(z), z_ld, N, H, W, C, g.cv, g.ppb, scale, shift, relu, nullptr, 0,
+        static_cast<__nv_bfloat16*>(y), y_ld, static_cast<__nv_bfloat16*>(pooled), pooled_ld);
+  } else {
+    if (!y) return set_error(UZ_ERR_INVALID, "bn_apply: no output");
+    const Geo g = make_geo(C, static_cast<long long>(N) * H * W, 8);
+    bn_apply_kernel<false><<<g.grid, g.block, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(z), z_ld, N, H, W, C, g.cv, g.ppb, scale, shift, relu,
+        static_cast<const __nv_bfloat16*>(residual), res_ld, static_cast<__nv_bfloat16*>(y), y_ld, nullptr, 0);
+  }
+  UZ_CHECK_LAUNCH("bn_apply launch");
+  return UZ_OK;
+}
+
+extern "C" size_t uz_bn_bwd_workspace_bytes(int C) {
+  const int rows = uz_reduce_rows();
+  if (rows < 0) return 0;
+  return sizeof(float) * static_cast<size_t>(rows) * 3 * C + sizeof(float) * 2 * C;
+}
+
+extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, const void* dpool, int dpool_ld, int N,
+                         int H, int W, int C, const float* bn, int relu, void* dz, int dz_ld, float* dgamma,
+                         float* dbeta, float* dbias, int accumulate, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("bn_bwd(z)", z, C, z_ld);
+  if (rc) return rc;
+  if ((rc = check_act("bn_bwd(dz)", dz, C, dz_ld))) return rc;
+  if (dy && (rc = check_act("bn_bwd(dy)", dy, C, dy_ld))) return rc;
+  if (dpool && (rc = check_act("bn_bwd(dpool)", dpool, C, dpool_ld))) return rc;
+  if (!dy && !dpool) return set_error(UZ_ERR_INVALID, "bn_bwd: no incoming gradient");
+  if (dpool && ((H & 1) || (W & 1))) return set_error(UZ_ERR_INVALID, "bn_bwd: pooling needs even H, W");
+  if (workspace_bytes < uz_bn_bwd_workspace_bytes(C) || !a16(workspace))
+    return set_error(UZ_ERR_WORKSPACE, "bn_bwd: workspace too small (%zu < %zu)", workspace_bytes,
+                     uz_bn_bwd_workspace_bytes(C));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool pool = dpool != nullptr;
+  const long long items = pool ? static_cast<long long>(N) * (H / 2) * (W / 2) : static_cast<long long>(N) * H * W;
+  const Geo g = make_geo(C, items, 4);
+  const int rows = g.grid;
+  float* partial = static_cast<float*>(workspace);
+  float* dbias_partial = partial + static_cast<size_t>(uz_reduce_rows()) * 2 * C;
+  float* coef = dbias_partial + static_cast<size_t>(uz_reduce_rows()) * C;
+  BwdArgs a;
+  a.z = static_cast<const __nv_bfloat16*>(z);
+  a.z_ld = z_ld;
+  a.dy = static_cast<const __nv_bfloat16*>(dy);
+  a.dy_ld = dy_ld;
+  a.dpool = static_cast<const __nv_bfloat16*>(dpool);
+  a.dpool_ld = dpool_ld;
+  a.N = N; a.H = H; a.W = W; a.C = C; a.cv = g.cv; a.ppb = g.ppb;
+  a.bn = bn;
+  a.relu = relu;
+  const size_t smem = static_cast<size_t>(g.block) * 16 * sizeof(float);
+  if (pool)
+    bn_bwd_reduce_kernel<true><<<g.grid, g.block, smem, st>>>(a, partial);
+  else
+    bn_bwd_reduce_kernel<false><<<g.grid, g.block, smem, st>>>(a, partial);
+  UZ_CHECK_LAUNCH("bn_bwd_reduce launch");
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, C, static_cast<double>(N) * H * W, bn, dgamma,
+                                                         dbeta, accumulate, coef);
+  UZ_CHECK_LAUNCH("bn_bwd_finalize launch");
+  float* dbp = dbias ? dbias_partial : nullptr;
+  if (pool)
+    bn_bwd_apply_kernel<true><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp);
+  else
+    bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp);
+  UZ_CHECK_LAUNCH("bn_bwd_apply launch");
+  if (dbias) {
+    reduce_rows_kernel<<<(C + 127) / 128, 128, 0, st>>>(dbias_partial, rows, C, dbias, accumulate);
+    UZ_CHECK_LAUNCH("bn_bwd dbias launch");
+  }
+  return UZ_OK;
+}
+
+extern "C" size_t uz_colsum_workspace_bytes(int C) {
+  const int rows = uz_reduce_rows();
+  return rows < 0 ? 0 : sizeof(float) * static_cast<size_t>(rows) * C;
+}
+
+extern "C" int uz_colsum(const void* x, int ld, long long npix, int C, float* out, int accumulate, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("colsum", x, C, ld);
+  if (rc) return rc;
+  if (workspace_bytes < uz_colsum_workspace_bytes(C)) return set_error(UZ_ERR_WORKSPACE, "colsum: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const Geo g = make_geo(C, npix, 4);
+  colsum_kernel<<<g.grid, g.block, g.block * 8 * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), ld, npix, C,
+                                                                      g.cv, g.ppb, static_cast<float*>(workspace));
+  UZ_CHECK_LAUNCH("colsum launch");
+  reduce_rows_kernel<<<(C + 127) / 128, 128, 0, st>>>(static_cast<const float*>(workspace), g.grid, C, out, accumulate);
+  UZ_CHECK_LAUNCH("colsum reduce launch");
+  return UZ_OK;
+}

@@ -1,0 +1,440 @@
+"""Graph executor of the UNet hot path on the sm_100a kernel library.
+
+The reference runs every layer as a separate ``torch.nn`` module call on NCHW fp32 tensors
+(``unet_zoo/models/common_layers.py``).  Here a model's ``forward`` is described once as a sequence of fused
+operators over NHWC bf16 activation views (:class:`Act`); each operator launches kernels of the C-ABI library
+(``include/unet_zoo_b200.h``) and, in training mode, records a closure on a tape that computes its gradients.
+``torch.cat`` never runs: producers write straight into channel slices of a pre-allocated wide buffer.
+
+PyTorch is used for device memory (caching allocator), streams and the autograd boundary only.
+"""
+import ctypes
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib as L
+
+_c_void_p = ctypes.c_void_p
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+class Buf:
+    """One NHWC bf16 device buffer [N, H, W, ld] plus (lazily) its gradient buffer of the same shape."""
+
+    __slots__ = ("data", "grad", "written", "N", "H", "W", "ld")
+
+    def __init__(self, N, H, W, ld, device):
+        self.data = torch.empty((N, H, W, ld), dtype=torch.bfloat16, device=device)
+        self.grad = None
+        self.written: List[Tuple[int, int]] = []  # channel intervals of `grad` that already hold a gradient
+        self.N, self.H, self.W, self.ld = N, H, W, ld
+
+    def grad_buf(self):
+        if self.grad is None:
+            self.grad = torch.empty_like(self.data)
+        return self.grad
+
+
+class Act:
+    """Channel slice [c0, c0+C) of a :class:`Buf` - the unit every kernel call works on (pointer + pixel stride)."""
+
+    __slots__ = ("buf", "c0", "C")
+
+    def __init__(self, buf: Buf, c0: int = 0, C: Optional[int] = None):
+        self.buf, self.c0 = buf, c0
+        self.C = buf.ld - c0 if C is None else C
+        if self.c0 % 8 or self.C % 8:
+            raise RuntimeError(f"unet_zoo_b200: channel slices must be multiples of 8 (c0={c0}, C={self.C})")
+
+    N = property(lambda s: s.buf.N)
+    H = property(lambda s: s.buf.H)
+    W = property(lambda s: s.buf.W)
+    ld = property(lambda s: s.buf.ld)
+    ptr = property(lambda s: s.buf.data.data_ptr() + 2 * s.c0)
+    npix = property(lambda s: s.buf.N * s.buf.H * s.buf.W)
+
+    def slice(self, c0, C):
+        return Act(self.buf, self.c0 + c0, C)
+
+    def gptr(self):
+        return self.buf.grad_buf().data_ptr() + 2 * self.c0
+
+    def grad_writes(self) -> List[Tuple[int, int, bool]]:
+        """Split this slice into maximal runs (c_off_in_slice, C, accumulate) and mark them written."""
+        lo, hi = self.c0, self.c0 + self.C
+        cuts = {lo, hi}
+        for a, b in self.buf.written:
+            if lo < a < hi:
+                cuts.add(a)
+            if lo < b < hi:
+                cuts.add(b)
+        cuts = sorted(cuts)
+        runs = []
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            acc = any(wa <= a and b <= wb for wa, wb in self.buf.written)
+            if runs and runs[-1][2] == acc and runs[-1][0] + runs[-1][1] == a - lo:
+                runs[-1] = (runs[-1][0], runs[-1][1] + (b - a), acc)
+            else:
+                runs.append((a - lo, b - a, acc))
+        self.buf.written.append((lo, hi))
+        return runs
+
+    def has_grad(self):
+        lo, hi = self.c0, self.c0 + self.C
+        return any(a < hi and lo < b for a, b in self.buf.written)
+
+    def to_nchw(self) -> torch.Tensor:  # debugging / tests
+        return self.buf.data[..., self.c0:self.c0 + self.C].permute(0, 3, 1, 2).float()
+
+
+class ParamGrads:
+    """Destination of parameter gradients: one flat fp32 buffer, parameters in registration order."""
+
+    def __init__(self, params: Sequence[torch.nn.Parameter], device, on_ready: Optional[Callable] = None):
+        self.offsets: Dict[int, Tuple[int, torch.Size]] = {}
+        total = 0
+        for p in params:
+            self.offsets[id(p)] = (total, p.shape)
+            total += (p.numel() + 3) // 4 * 4  # keep every gradient 16-byte aligned
+        self.flat = torch.zeros(total, dtype=torch.float32, device=device)
+        self.done = set()
+        self.on_ready = on_ready
+
+    def view(self, p) -> torch.Tensor:
+        off, shape = self.offsets[id(p)]
+        return self.flat[off:off + p.numel()].view(shape)
+
+    def ready(self, p):
+        """Called by the tape when the gradient of `p` is complete on the compute stream."""
+        self.done.add(id(p))
+        if self.on_ready is not None:
+            self.on_ready(p)
+
+
+class Ctx:
+    """Per-forward execution context: stream, scratch memory, tape, parameter-gradient sink."""
+
+    def __init__(self, device, training: bool, record: bool):
+        self.lib = L.load()
+        self.device = device
+        self.training = training
+        self.record = record
+        self.tape: List[Callable[["Ctx"], None]] = []
+        self.stream = torch.cuda.current_stream(device).cuda_stream
+        self.sms = self.lib.uz_device_sm_count()
+        if self.sms < 0:
+            L.check(self.sms, "device query")
+        self.stats_rows = self.lib.uz_conv_stats_rows()
+        self.reduce_rows = self.lib.uz_reduce_rows()
+        self._ws = None
+        self.pgrads: Optional[ParamGrads] = None
+        self.launches = 0
+
+    # ------------------------------------------------------------------ memory
+    def new_buf(self, N, H, W, C) -> Buf:
+        return Buf(N, H, W, C, self.device)
+
+    def new_act(self, N, H, W, C) -> Act:
+        return Act(self.new_buf(N, H, W, C))
+
+    def workspace(self, nbytes: int) -> torch.Tensor:
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def f32(self, *shape) -> torch.Tensor:
+        return torch.empty(shape, dtype=torch.float32, device=self.device)
+
+    # ------------------------------------------------------------------ kernel wrappers
+    def pack(self, w: torch.Tensor, kind: str, row_scale: Optional[torch.Tensor] = None, kp: int = 0) -> torch.Tensor:
+        """fp32 parameter -> bf16 GEMM operand [A][T][B] (see uz_pack_weight)."""
+        w = w.detach()
+        if not w.is_contiguous():
+            w = w.contiguous()
+        d0, d1 = w.shape[0], w.shape[1]
+        T = w.shape[2] * w.shape[3]
+        if kind == "conv_fwd":      # OIHW -> [Co][T][Ci]
+            A, B, sa, sb = d0, d1, d1 * T, T
+        elif kind == "conv_dgrad":  # OIHW -> [Ci][T][Co]
+            A, B, sa, sb = d1, d0, T, d1 * T
+        elif kind == "convt_fwd":   # IOHW -> [Co][4][Ci]
+            A, B, sa, sb = d1, d0, T, d1 * T
+        elif kind == "convt_dgrad":  # IOHW -> [Ci][4][Co]
+            A, B, sa, sb = d0, d1, d1 * T, T
+        elif kind == "stem":        # OIHW -> [Co][kp] with k = t*Ci + ci
+            A, B, sa, sb = d0, d1, d1 * T, T
+        else:
+            raise ValueError(kind)
+        pitch = T * B
+        if kind == "stem":
+            pitch = kp
+            out = torch.zeros((A, kp), dtype=torch.bfloat16, device=w.device)
+        else:
+            out = torch.empty((A, T, B), dtype=torch.bfloat16, device=w.device)
+        rc = self.lib.uz_pack_weight(w.data_ptr(), out.data_ptr(), A, T, B, sa, sb, 1, pitch, _ptr(row_scale), self.stream)
+        L.check(rc, "uz_pack_weight")
+        self.launches += 1
+        return out
+
+    def conv(self, mode: int, segs: Sequence[Act], wp: torch.Tensor, cout: int, bias: Optional[torch.Tensor],
+             out_ptr: int, out_ld: int, out_h: int, out_w: int, stats: Optional[torch.Tensor] = None, flags: int = 0,
+             in_grad: bool = False):
+        """uz_conv_igemm over a virtual concat of `segs` (activations, or their gradients when in_grad)."""
+        n = len(segs)
+        ptrs = (_c_void_p * n)(*[(s.gptr() if in_grad else s.ptr) for s in segs])
+        cs = (ctypes.c_int * n)(*[s.C for s in segs])
+        lds = (ctypes.c_int * n)(*[s.ld for s in segs])
+        a = segs[0]
+        rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
+                                    out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
+        L.check(rc, "uz_conv_igemm")
+        self.launches += 1
+
+    def wgrad(self, mode: int, x_ptr: int, N, H, W, cin: int, x_ld: int, dy_ptr: int, cout: int, dy_ld: int,
+              dw: torch.Tensor, cin_total: int, c_off: int, accumulate: bool = False):
+        need = self.lib.uz_conv_wgrad_workspace_bytes(mode, N, H, W, cin, cout)
+        ws = self.workspace(need)
+        rc = self.lib.uz_conv_wgrad(mode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total, c_off,
+                                    int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
+        L.check(rc, "uz_conv_wgrad")
+        self.launches += 2
+
+    def bn_finalize(self, stats: torch.Tensor, rows: int, C: int, count: int, bn_mod, bnbuf: torch.Tensor):
+        track = bn_mod.track_running_stats and bn_mod.running_mean is not None
+        mom = bn_mod.momentum
+        if track:
+            bn_mod.num_batches_tracked += 1
+            if mom is None:  # cumulative moving average, as nn.BatchNorm2d does for momentum=None
+                mom = 1.0 / float(bn_mod.num_batches_tracked)
+        rc = self.lib.uz_bn_finalize(stats.data_ptr(), rows, C, count, _ptr(bn_mod.weight), _ptr(bn_mod.bias),
+                                     bn_mod.eps, mom if mom is not None else 0.0,
+                                     _ptr(bn_mod.running_mean) if track else None,
+                                     _ptr(bn_mod.running_var) if track else None, bnbuf.data_ptr(), self.stream)
+        L.check(rc, "uz_bn_finalize")
+        self.launches += 1
+
+    def bn_apply(self, z: Act, scale_ptr, shift_ptr, relu: bool, y: Optional[Act], pooled: Optional[Act] = None,
+                 residual: Optional[Act] = None):
+        rc = self.lib.uz_bn_apply(z.ptr, z.ld, z.N, z.H, z.W, z.C, scale_ptr, shift_ptr, int(relu),
+                                  residual.ptr if residual else None, residual.ld if residual else 0,
+                                  y.ptr if y else None, y.ld if y else 0,
+                                  pooled.ptr if pooled else None, pooled.ld if pooled else 0, self.stream)
+        L.check(rc, "uz_bn_apply")
+        self.launches += 1
+
+    def bn_bwd(self, z: Act, dy_ptr, dy_ld, dpool_ptr, dpool_ld, bnbuf: torch.Tensor, relu: bool, dz_ptr: int, dz_ld: int,
+               dgamma, dbeta, dbias):
+        need = self.lib.uz_bn_bwd_workspace_bytes(z.C)
+        ws = self.workspace(need)
+        rc = self.lib.uz_bn_bwd(z.ptr, z.ld, dy_ptr, dy_ld, dpool_ptr, dpool_ld, z.N, z.H, z.W, z.C, bnbuf.data_ptr(),
+                                int(relu), dz_ptr, dz_ld, _ptr(dgamma), _ptr(dbeta), _ptr(dbias), 0, ws.data_ptr(),
+                                ws.numel(), self.stream)
+        L.check(rc, "uz_bn_bwd")
+        self.launches += 4 if dbias is not None else 3
+
+    def colsum(self, ptr: int, ld: int, npix: int, C: int, out: torch.Tensor, accumulate=False):
+        need = self.lib.uz_colsum_workspace_bytes(C)
+        ws = self.workspace(need)
+        rc = self.lib.uz_colsum(ptr, ld, npix, C, out.data_ptr(), int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
+        L.check(rc, "uz_colsum")
+        self.launches += 2
+
+    # ------------------------------------------------------------------ parameter gradients
+    def pgrad(self, p: torch.nn.Parameter) -> Optional[torch.Tensor]:
+        if p is None or not p.requires_grad:
+            return None
+        return self.pgrads.view(p)
+
+    def pready(self, *ps):
+        for p in ps:
+            if p is not None and p.requires_grad:
+                self.pgrads.ready(p)
+
+
+# ====================================================================================================== operators
+def _fold_bn(conv_bias: Optional[torch.Tensor], bn) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Inference-mode BatchNorm folded into (row_scale, bias) of the preceding convolution."""
+    invstd = torch.rsqrt(bn.running_var + bn.eps)
+    g = bn.weight if bn.weight is not None else torch.ones_like(invstd)
+    b = bn.bias if bn.bias is not None else torch.zeros_like(invstd)
+    scale = (g * invstd).float().contiguous()
+    cb = conv_bias if conv_bias is not None else torch.zeros_like(invstd)
+    bias = ((cb - bn.running_mean) * scale + b).float().contiguous()
+    return scale, bias
+
+
+def stem_input(ctx: Ctx, x: torch.Tensor) -> Tuple[Act, str]:
+    """NCHW fp32 images -> the operand of the first convolution.
+
+    in_channels <= 7: 3x3 im2col into one 64-wide K block (the stem conv then runs as a 1x1 GEMM);
+    otherwise a plain NHWC bf16 copy with channels padded to a multiple of 8.
+    """
+    N, cin, H, W = x.shape
+    if 9 * cin <= 64:
+        kp = 16 if 9 * cin <= 16 else 32 if 9 * cin <= 32 else 64
+        a = ctx.new_act(N, H, W, kp)
+        L.check(ctx.lib.uz_stem_im2col(x.data_ptr(), N, cin, H, W, a.ptr, kp, ctx.stream), "uz_stem_im2col")
+        ctx.launches += 1
+        return a, "im2col"
+    cpad = (cin + 7) // 8 * 8
+    a = ctx.new_act(N, H, W, cpad)
+    L.check(ctx.lib.uz_nchw_to_nhwc(x.data_ptr(), N, cin, H, W, a.ptr, cpad, ctx.stream), "uz_nchw_to_nhwc")
+    ctx.launches += 1
+    return a, "nhwc"
+
+
+def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None, pooled: Optional[Act] = None,
+                relu: bool = True, mode: int = L.CONV3X3, stem: Optional[str] = None, need_dx: bool = True) -> Act:
+    """[ReLU](BatchNorm2d(Conv2d(cat(xs)))) with optional MaxPool2d(2,2) second output.
+
+    Reference: DoubleConv / ConvBlock / VGGBlock halves (common_layers.py:28-33,47-57; nested_unet.py:13-22),
+    UpConvBlock with mode=UP2X_CONV3X3 (common_layers.py:70-76), DownSample pooling (common_layers.py:92-95).
+    Training: conv epilogue emits raw bf16 z + per-channel sum/sum-sq partials -> finalize -> one apply pass.
+    Inference: BatchNorm folded into the packed weights and bias, ReLU in the conv epilogue.
+    """
+    a0 = xs[0]
+    N, H, W = a0.N, a0.H, a0.W
+    cout = conv.out_channels
+    oscale = 2 if mode == L.UP2X_CONV3X3 else 1
+    if mode in (L.CONV3X3_S2, L.CONV1X1_S2):
+        Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    else:
+        Ho, Wo = H * oscale, W * oscale
+    if out is None:
+        out = ctx.new_act(N, Ho, Wo, cout)
+    is_stem = stem == "im2col"
+    conv_mode = L.CONV1X1 if is_stem else mode
+    cin_total = sum(a.C for a in xs)
+
+    if not ctx.training:
+        scale, bias = _fold_bn(conv.bias, bn) if bn is not None else (None, conv.bias)
+        wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", row_scale=scale, kp=a0.C if is_stem else 0)
+        ctx.conv(conv_mode, xs, wp, cout, bias, out.ptr, out.ld, Ho, Wo, None, L.FLAG_RELU if relu else 0)
+        if pooled is not None:
+            ctx.bn_apply(out, None, None, False, None, pooled)
+        return out
+
+    wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", kp=a0.C if is_stem else 0)
+    z = ctx.new_act(N, Ho, Wo, cout)
+    stats = ctx.f32(ctx.stats_rows, 2, cout)
+    ctx.conv(conv_mode, xs, wp, cout, conv.bias, z.ptr, z.ld, Ho, Wo, stats, L.FLAG_STATS)
+    bnbuf = ctx.f32(4, cout)
+    ctx.bn_finalize(stats, ctx.stats_rows, cout, N * Ho * Wo, bn, bnbuf)
+    ctx.bn_apply(z, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out, pooled)
+
+    if ctx.record:
+        def backward(c: Ctx):
+            has_dy = out.has_grad()
+            has_dp = pooled is not None and pooled.has_grad()
+            if not (has_dy or has_dp):
+                raise RuntimeError("unet_zoo_b200: conv_bn_act output has no gradient (unused output?)")
+            dgamma, dbeta = c.pgrad(bn.weight), c.pgrad(bn.bias)
+            dbias = c.pgrad(conv.bias) if conv.bias is not None else None
+            # dz overwrites z in place (same thread reads z[p] then writes dz[p])
+            c.bn_bwd(z, out.gptr() if has_dy else None, out.ld, pooled.gptr() if has_dp else None,
+                     pooled.ld if has_dp else 0, bnbuf, relu, z.ptr, z.ld, dgamma, dbeta, dbias)
+            c.pready(bn.weight, bn.bias, conv.bias)
+            _conv_backward(c, xs, conv, z, mode, is_stem, cin_total, need_dx)
+        ctx.tape.append(backward)
+    return out
+
+
+def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem: bool, cin_total: int, need_dx: bool):
+    """Weight gradient (tcgen05 split-K) and data gradient (flipped-weight implicit GEMM) of one convolution;
+    `dz` holds the gradient w.r.t. the convolution output (NHWC bf16)."""
+    a0 = xs[0]
+    cout = conv.out_channels
+    dw = c.pgrad(conv.weight)
+    if dw is not None:
+        if is_stem:
+            kp = a0.C
+            cin = conv.in_channels
+            tmp = c.f32(cout, kp)
+            c.wgrad(L.CONV1X1, a0.ptr, a0.N, a0.H, a0.W, kp, a0.ld, dz.ptr, cout, dz.ld, tmp, kp, 0)
+            dw.copy_(tmp[:, :9 * cin].view(cout, 9, cin).permute(0, 2, 1).reshape(dw.shape))
+        else:
+            off = 0
+            for a in xs:
+                c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, dw, cin_total, off)
+                off += a.C
+        c.pready(conv.weight)
+    if not need_dx or is_stem:
+        return
+    dgrad_mode = {L.CONV3X3: L.CONV3X3_DGRAD, L.CONV1X1: L.CONV1X1, L.CONV3X3_S2: L.CONV3X3_S2_DGRAD,
+                  L.CONV1X1_S2: L.CONV1X1_S2_DGRAD}.get(mode)
+    if dgrad_mode is None:
+        raise NotImplementedError(f"data gradient for conv mode {mode}")
+    wpd = c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
+    T = wpd.shape[1]
+    off = 0
+    for a in xs:
+        for (r0, rc, acc) in a.grad_writes():
+            w_rows = wpd[off + r0: off + r0 + rc]
+            c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, None,
+                   L.FLAG_ACCUMULATE if acc else 0)
+        off += a.C
+
+
+def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
+    """ConvTranspose2d(k=2, s=2) written straight into a channel slice of the concat buffer.
+
+    Reference: UpSample_UNet.up (common_layers.py:104,108) / UpsampleResUnet (common_layers.py:201-207).
+    Four 1x1 GEMMs (one per output phase) with a pixel-shuffle scatter epilogue.
+    """
+    cout = up.out_channels
+    wp = ctx.pack(up.weight, "convt_fwd")
+    ctx.conv(L.CONVT2X2, [x], wp, cout, up.bias, out.ptr, out.ld, 2 * x.H, 2 * x.W)
+    if ctx.record:
+        def backward(c: Ctx):
+            dw = c.pgrad(up.weight)
+            if dw is not None:
+                c.wgrad(L.CONVT2X2, x.ptr, x.N, x.H, x.W, x.C, x.ld, out.gptr(), cout, out.ld, dw, x.C, 0)
+            if up.bias is not None and up.bias.requires_grad:
+                c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(up.bias))
+            c.pready(up.weight, up.bias)
+            wpd = c.pack(up.weight, "convt_dgrad")  # [Cin][4][Cout]
+            gout = Act.__new__(Act)
+            gout.buf, gout.c0, gout.C = out.buf, out.c0, out.C
+            for (r0, rc, acc) in x.grad_writes():
+                c.conv(L.CONVT2X2_DGRAD, [gout], wpd[r0:r0 + rc], rc, None, x.gptr() + 2 * r0, x.ld, x.H, x.W, None,
+                       L.FLAG_ACCUMULATE if acc else 0, in_grad=True)
+        ctx.tape.append(backward)
+    return out
+
+
+def head1x1(ctx: Ctx, y: Act, conv) -> torch.Tensor:
+    """1x1 classifier head -> fp32 NCHW logits (OutConv, common_layers.py:125-128)."""
+    K = conv.out_channels
+    logits = torch.empty((y.N, K, y.H, y.W), dtype=torch.float32, device=ctx.device)
+    w = conv.weight.detach().reshape(K, -1)
+    rc = ctx.lib.uz_head_fwd(y.ptr, y.ld, y.N, y.H, y.W, y.C, K, w.data_ptr(), _ptr(conv.bias), logits.data_ptr(),
+                             ctx.stream)
+    L.check(rc, "uz_head_fwd")
+    ctx.launches += (K + 3) // 4
+    return logits
+
+
+def head1x1_backward(c: Ctx, y: Act, conv, dlogits: torch.Tensor):
+    K = conv.out_channels
+    dl = dlogits.contiguous().float()
+    w = conv.weight.detach().reshape(K, -1)
+    dw = c.pgrad(conv.weight)
+    db = c.pgrad(conv.bias) if conv.bias is not None else None
+    if dw is None:
+        dw = c.f32(K, y.C)
+    if db is None:
+        db = c.f32(K)
+    need = c.lib.uz_head_bwd_workspace_bytes(y.C)
+    ws = c.workspace(need)
+    runs = y.grad_writes()
+    if any(acc for _, _, acc in runs):
+        raise NotImplementedError("classifier head input already has a gradient")
+    rc = c.lib.uz_head_bwd(y.ptr, y.ld, dl.data_ptr(), y.N, y.H, y.W, y.C, K, w.data_ptr(), y.gptr(), y.ld,
+                           dw.data_ptr(), db.data_ptr(), 0, ws.data_ptr(), ws.numel(), c.stream)
+    L.check(rc, "uz_head_bwd")
+    c.launches += 3 * ((K + 3) // 4)
+    c.pready(conv.weight, conv.bias)
