@@ -1,0 +1,280 @@
+"""Headline benchmark: images/sec of the `unet` 3->1, 512x512, bf16-compute training step, batch 32 per GPU.
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference's CPU path (oracle port of it) on the host cores
+
+A step is the reference's training-loop body (unet_zoo/utils/training_loop.py:109-121): zero_grad -> forward ->
+BCEWithLogitsLoss -> backward (+ gradient all-reduce when N > 1) -> clip_grad_norm_(1.0) -> AdamW(lr 1e-4, wd 1e-5).
+Prints ONE JSON line on rank 0.  `value` = device-resident inputs; `e2e` = same step through the public API with the
+batch copied from pinned host memory and the loss read back every step.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+UNET_FWD_BWD_GFLOP_PER_IMG_512 = 1155.11   # conv + transposed-conv FLOPs (2*MAC), SURVEY.md section 6 / 8(d)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=32, help="images per GPU")
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--model", default="unet")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"tflops": float(p["bf16_tflops_sustained"]), "hbm": float(p["hbm_gbs"]), "src": "measured"}
+    except Exception:
+        return {"tflops": 1400.0, "hbm": 6650.0, "src": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_train_step_rate(model_name, size, steps, warmup, threads=None):
+    """img/s of the oracle port of the reference's CPU training step (fp32, batch 1) on this host's cores."""
+    import copy
+
+    import torch
+
+    import unet_zoo_b200
+    from oracle import reference_port as O
+    if threads:
+        torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    sd = copy.deepcopy(unet_zoo_b200.create_model(model_name).state_dict())
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()
+              if v.dtype.is_floating_point and "running_" not in k}
+    work = dict(sd)
+    work.update(leaves)
+    params = list(leaves.values())
+    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5)
+    x, m = O.synthetic_batch(1, 3, size, size)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        loss = O.bce_with_logits(O.FORWARDS[model_name](work, x, True), m)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        opt.step()
+        float(loss)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    return 1.0 / (sum(times) / len(times)), torch.get_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rate, cores = cpu_train_step_rate(args.model, args.size, args.steps, max(1, min(args.warmup, 2)))
+    sample = f"batch 1 of the {args.size}x{args.size} fp32 training step per step (oracle port of the reference path, torch CPU)"
+    line = {
+        "impl": "reference", "metric": "images/sec UNet 512^2 train step", "value": rate, "unit": "images/sec",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / rate,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.model} in=3 classes=1 {args.size}x{args.size} fwd+bwd training step, CPU"},
+        "cpu_baseline": {"value": rate, "unit": "images/sec", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    import unet_zoo_b200
+    from unet_zoo_b200 import engine as E
+    from unet_zoo_b200 import parallel as P
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    torch.manual_seed(0)
+    model = unet_zoo_b200.create_model(args.model, in_channels=3, num_classes=1).to(dev).train()
+    if world > 1:
+        model = P.DataParallel(model)          # bucketed NCCL all-reduce overlapped with backward
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True)
+    crit = torch.nn.BCEWithLogitsLoss()
+
+    B, S = args.batch, args.size
+    gx = torch.Generator().manual_seed(1234 + rank)
+    gm = torch.Generator().manual_seed(4321 + rank)
+    x_h = torch.randn(B, 3, S, S, generator=gx).pin_memory()
+    m_h = (torch.rand(B, 1, S, S, generator=gm) > 0.5).float().pin_memory()
+    x_d, m_d = x_h.to(dev), m_h.to(dev)
+
+    def step(x, m):
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = crit(out, m)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        opt.step()
+        return loss
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        sync()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    for _ in range(max(args.warmup, 3)):
+        step(x_d, m_d)
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms = timed(lambda: step(x_d, m_d), args.steps)
+    base = model.module if hasattr(model, "module") else model
+    launches = (base._last_launches + base._last_launches_bwd) * args.steps
+
+    def e2e_step():
+        x = x_h.to(dev, non_blocking=True)
+        m = m_h.to(dev, non_blocking=True)
+        return float(step(x, m).item())
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop() if sampler else None
+
+    # roofline leg: per-launch CUDA-event timing of the tensor-core kernels during one more step
+    E.PROFILE = []
+    step(x_d, m_d)
+    torch.cuda.synchronize()
+    agg = {}
+    for kind, flops, a, b in E.PROFILE:
+        t, f, n = agg.get(kind, (0.0, 0.0, 0))
+        agg[kind] = (t + a.elapsed_time(b), f + flops, n + 1)
+    E.PROFILE = None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    imgs = B * world * args.steps
+    value = imgs / (ms / 1000.0)
+    top = max(agg, key=lambda k: agg[k][0]) if agg else None
+    roof = None
+    if top:
+        t, f, n = agg[top]
+        ach = f / (t / 1000.0) / 1e12
+        roof = {"kernel": top, "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
+                "frac": ach / pk["tflops"], "traffic": None, "peak_source": pk["src"] + " (sustained bf16)",
+                "launches": n, "avg_launch_ms": t / n,
+                "families": {k: {"ms": v[0], "tflops": v[1] / (v[0] / 1000.0) / 1e12, "launches": v[2]}
+                             for k, v in agg.items()},
+                "step_tflops": value / world * UNET_FWD_BWD_GFLOP_PER_IMG_512 * (S / 512.0) ** 2 / 1000.0}
+    line = {
+        "metric": "images/sec UNet 512^2 bf16 train step", "value": value, "unit": "images/sec", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"{args.model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step "
+                               "(BASELINE.json configs[1])", "global_batch": B * world,
+                   "parallelism": f"dp{world}", "l2": "inputs larger than L2 (multi-GB activations per step)"},
+        "e2e": {"value": imgs / (ms_e2e / 1000.0), "unit": "images/sec",
+                "h2d_bytes_per_step": x_h.numel() * 4 + m_h.numel() * 4, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches, "roofline": roof, "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        rate, cores = cpu_train_step_rate(args.model, S, 3, 1)
+        line["cpu_baseline"] = {"value": rate, "unit": "images/sec", "cores": cores, "kind": "port",
+                                "sample": f"3 timed fp32 training steps at batch 1, {S}x{S} (oracle port, torch CPU)"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

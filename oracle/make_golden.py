@@ -1,0 +1,102 @@
+"""ORACLE tooling - generates tests/golden/*.pt by running the UNMODIFIED reference modules on CPU.
+
+Runs only in the build container (needs /root/reference).  The reference package cannot be imported as a whole
+(its registry eagerly imports models that need `timm`, models/__init__.py:5-25), so the five files of the hot path
+are loaded by file path under a synthetic package (route B).  Nothing is copied.
+
+    python oracle/make_golden.py            # writes tests/golden/<model>.pt
+
+Each fixture holds: the seed recipe, a fingerprint of the default-initialised state_dict (so tests can check that
+`torch.manual_seed(0); create_model(name)` reproduces the same weights), the train-mode logits and BCE loss of one
+synthetic batch, per-parameter gradient norms (+ full gradients of the small tensors), BatchNorm running statistics
+after that step, and the eval-mode logits computed afterwards.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+import torch
+
+REF = "/root/reference/unet_zoo/models"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+sys.dont_write_bytecode = True
+
+
+def load_reference():
+    pkg = types.ModuleType("refmodels")
+    pkg.__path__ = [REF]
+    sys.modules["refmodels"] = pkg
+    mods = {}
+    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet"):
+        spec = importlib.util.spec_from_file_location(f"refmodels.{name}", os.path.join(REF, name + ".py"))
+        m = importlib.util.module_from_spec(spec)
+        sys.modules[f"refmodels.{name}"] = m
+        spec.loader.exec_module(m)
+        mods[name] = m
+    return mods
+
+
+def build(mods, name, **kw):
+    if name == "unet":
+        return mods["unet"].UNet(in_channels=3, num_classes=1)
+    if name == "attention_unet":
+        return mods["attention_unet"].AttentionUNet(in_channels=3, num_classes=1, depth=5)
+    if name == "nested_unet":
+        return mods["nested_unet"].NestedUNet(in_channels=3, num_classes=1, depth=5,
+                                              deep_supervision=kw.get("deep_supervision", False))
+    if name == "resunet":
+        return mods["resunet"].ResUnet(in_channels=3, num_classes=1, filters=[64, 128, 256, 512])
+    raise ValueError(name)
+
+
+def fingerprint(sd):
+    return {k: (float(v.double().sum()), float(v.double().abs().sum())) for k, v in sd.items()}
+
+
+def main():
+    from oracle.reference_port import synthetic_batch
+    torch.set_num_threads(8)
+    mods = load_reference()
+    os.makedirs(OUT, exist_ok=True)
+    cases = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
+             ("nested_unet_ds", {"deep_supervision": True})]
+    for tag, kw in cases:
+        name = tag.replace("_ds", "")
+        torch.manual_seed(0)
+        model = build(mods, name, **kw)
+        fp = fingerprint(model.state_dict())
+        x, mask = synthetic_batch(2, 3, 64, 64)
+        model.train()
+        out = model(x)
+        outs = out if isinstance(out, list) else [out]
+        crit = torch.nn.BCEWithLogitsLoss()
+        loss = sum(crit(o, mask) for o in outs)
+        loss.backward()
+        grads = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
+        gold = {
+            "recipe": {"seed": 0, "batch": [2, 3, 64, 64], "seed_x": 1234, "seed_m": 4321, "kwargs": kw,
+                       "torch": str(torch.__version__)},
+            "fingerprint": fp,
+            "logits_train": [o.detach().clone() for o in outs],
+            "loss": float(loss),
+            "grad_norm": {k: float(g.double().norm()) for k, g in grads.items()},
+            "grad_small": {k: g for k, g in grads.items() if g.numel() <= 2048},
+            "bn_after": {k: v.detach().clone() for k, v in model.state_dict().items()
+                         if "running_" in k or "num_batches" in k},
+        }
+        model.eval()
+        with torch.no_grad():
+            oe = model(x)
+        gold["logits_eval"] = [o.clone() for o in (oe if isinstance(oe, list) else [oe])]
+        # README example (README.md:74-90): eval forward on randn(1,3,256,256) -> shape only (fresh default weights)
+        if tag == "unet":
+            gold["readme_shape"] = list(model(torch.randn(1, 3, 256, 256)).shape)
+        path = os.path.join(OUT, tag + ".pt")
+        torch.save(gold, path)
+        print(tag, "loss", gold["loss"], "bytes", os.path.getsize(path))
+
+
+if __name__ == "__main__":
+    main()

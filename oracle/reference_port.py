@@ -1,0 +1,219 @@
+"""ORACLE - test infrastructure only, never imported by the product package.
+
+CPU (fp32) restatement of the reference's hot path: the forward graphs of `unet`, `attention_unet`, `nested_unet`
+and `resunet` written as plain functions over a ``state_dict`` with the reference's key names.  The arithmetic of the
+reference lives in a third-party dependency that is not vendored under /root/reference: **PyTorch** (pinned by the
+reference at torch==2.2.2+cu121, requirements.txt:178; setup.py:24 asks for torch>=1.8.0; this image has 2.11.0).
+Each function therefore restates the published semantics of the torch.nn layer the reference calls, through
+``torch.nn.functional`` on CPU, and cites the reference call site it follows.
+
+Pinning: the reference ships no tests or golden vectors, so the oracle is pinned against
+outputs of the reference modules themselves, executed in the build container by ``oracle/make_golden.py`` and
+committed under ``tests/golden/``; ``tests/test_oracle_golden.py`` checks this file against them.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline / ``--impl reference`` legs may import
+this module.
+"""
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn.functional as F
+
+SD = Dict[str, torch.Tensor]
+
+
+class Runner:
+    """Carries the parameters, the train/eval flag and (in train mode) updates BatchNorm running statistics in `sd`."""
+
+    def __init__(self, sd: SD, training: bool):
+        self.sd = sd
+        self.training = training
+
+    # nn.Conv2d defaults: stride 1, dilation 1, groups 1 (common_layers.py:28)
+    def conv(self, x, key, stride=1, padding=0):
+        return F.conv2d(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"), stride=stride, padding=padding)
+
+    # nn.BatchNorm2d defaults: eps 1e-5, momentum 0.1, affine, track_running_stats (common_layers.py:29).
+    # Training: biased batch variance normalises, running_var gets the unbiased one; eval: running statistics.
+    def bn(self, x, key):
+        rm, rv = self.sd[key + ".running_mean"], self.sd[key + ".running_var"]
+        if self.training:
+            self.sd[key + ".num_batches_tracked"] += 1
+        return F.batch_norm(x, rm, rv, self.sd[key + ".weight"], self.sd[key + ".bias"], training=self.training,
+                            momentum=0.1, eps=1e-5)
+
+    def cbr(self, x, conv_key, bn_key, stride=1):
+        return F.relu(self.bn(self.conv(x, conv_key, stride=stride, padding=1), bn_key))
+
+    # DoubleConv / ConvBlock: nn.Sequential(conv, bn, relu, conv, bn, relu)  (common_layers.py:27-34, 46-57)
+    def double_conv(self, x, prefix):
+        x = self.cbr(x, prefix + ".0", prefix + ".1")
+        return self.cbr(x, prefix + ".3", prefix + ".4")
+
+    # nn.ConvTranspose2d(k=2, s=2): weight [Cin, Cout, 2, 2]  (common_layers.py:104)
+    def conv_transpose(self, x, key):
+        return F.conv_transpose2d(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"), stride=2)
+
+
+def _pad_to(x1, x2):
+    """F.pad of the upsampled tensor to the skip's size (common_layers.py:110-113)."""
+    dy, dx = x2.size(2) - x1.size(2), x2.size(3) - x1.size(3)
+    return F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])
+
+
+def unet_forward(sd: SD, x: torch.Tensor, training: bool) -> torch.Tensor:
+    """UNet.forward (unet.py:29-44): DownSample x4 -> bottle_neck -> UpSample_UNet x4 -> OutConv."""
+    r = Runner(sd, training)
+    skips = []
+    for i in range(1, 5):
+        down = r.double_conv(x, f"down_convolution_{i}.conv.conv_op")   # common_layers.py:93
+        skips.append(down)
+        x = F.max_pool2d(down, kernel_size=2, stride=2)                    # common_layers.py:94
+    x = r.double_conv(x, "bottle_neck.conv_op")                           # unet.py:36
+    for i in range(1, 5):
+        skip = skips[4 - i]
+        up = _pad_to(r.conv_transpose(x, f"up_convolution_{i}.up"), skip)  # common_layers.py:108-113
+        x = torch.cat([up, skip], 1)                                        # common_layers.py:115 (upsampled FIRST)
+        x = r.double_conv(x, f"up_convolution_{i}.conv.conv_op")
+    return r.conv(x, "out.conv")                                          # common_layers.py:125-128, raw logits
+
+
+def _attention_gate(r: Runner, g, x, prefix):
+    """AttentionBlock.forward (attention_unet.py:34-40)."""
+    g1 = r.bn(r.conv(g, prefix + ".w_g.0"), prefix + ".w_g.1")
+    x1 = r.bn(r.conv(x, prefix + ".w_x.0"), prefix + ".w_x.1")
+    psi = F.relu(g1 + x1)
+    psi = torch.sigmoid(r.bn(r.conv(psi, prefix + ".psi.0"), prefix + ".psi.1"))
+    return psi * x
+
+
+def attention_unet_forward(sd: SD, x: torch.Tensor, training: bool) -> torch.Tensor:
+    """AttentionUNet.forward (attention_unet.py:73-110); `depth` is ignored by the reference class."""
+    r = Runner(sd, training)
+    feats = []
+    for i in range(1, 6):
+        if i > 1:
+            x = F.max_pool2d(x, kernel_size=2, stride=2)                   # attention_unet.py:46,77
+        x = r.double_conv(x, f"conv{i}.conv")
+        feats.append(x)
+    d = feats[4]
+    for lvl in (5, 4, 3, 2):
+        # UpConvBlock: nn.Upsample(scale_factor=2) (nearest) -> conv3x3 -> BN -> ReLU (common_layers.py:69-76)
+        d = F.interpolate(d, scale_factor=2, mode="nearest")
+        d = r.cbr(d, f"up{lvl}.up.1", f"up{lvl}.up.2")
+        skip = _attention_gate(r, d, feats[lvl - 2], f"att{lvl}")
+        d = torch.cat((skip, d), dim=1)                                    # attention_unet.py:90 (gated skip FIRST)
+        d = r.double_conv(d, f"upconv{lvl}.conv")
+    return r.conv(d, "conv_1x1")
+
+
+def _vgg(r: Runner, x, prefix):
+    """VGGBlock.forward (nested_unet.py:13-22)."""
+    x = F.relu(r.bn(r.conv(x, prefix + ".conv1", padding=1), prefix + ".bn1"))
+    return F.relu(r.bn(r.conv(x, prefix + ".conv2", padding=1), prefix + ".bn2"))
+
+
+def nested_unet_forward(sd: SD, x: torch.Tensor, training: bool, deep_supervision: bool = False):
+    """NestedUNet.forward (nested_unet.py:71-106)."""
+    r = Runner(sd, training)
+    pool = lambda t: F.max_pool2d(t, 2, 2)                                                    # nested_unet.py:32
+    up = lambda t: F.interpolate(t, scale_factor=2, mode="bilinear", align_corners=True)      # nested_unet.py:33
+    X: Dict[tuple, torch.Tensor] = {}
+    X[0, 0] = _vgg(r, x, "conv0_0")
+    for i in range(1, 5):
+        X[i, 0] = _vgg(r, pool(X[i - 1, 0]), f"conv{i}_0")
+    # the reference evaluates column by column (nested_unet.py:81-93); BatchNorm updates make the order observable
+    for j in range(1, 5):
+        for i in range(0, 5 - j):
+            parts = [X[i, k] for k in range(j)] + [up(X[i + 1, j - 1])]
+            X[i, j] = _vgg(r, torch.cat(parts, 1), f"conv{i}_{j}")
+    if deep_supervision:
+        return [r.conv(X[0, j], f"final{j}") for j in range(1, 5)]
+    return r.conv(X[0, 4], "final")
+
+
+def _residual_conv(r: Runner, x, prefix, stride):
+    """ResidualConv.forward (common_layers.py:182-199): pre-activation block + (conv1x1 -> BN) skip."""
+    h = F.relu(r.bn(x, prefix + ".conv_block.0"))
+    h = r.conv(h, prefix + ".conv_block.2", stride=stride, padding=1)
+    h = F.relu(r.bn(h, prefix + ".conv_block.3"))
+    h = r.conv(h, prefix + ".conv_block.5", padding=1)
+    s = r.bn(r.conv(x, prefix + ".conv_skip.0", stride=stride), prefix + ".conv_skip.1")
+    return h + s
+
+
+def resunet_forward(sd: SD, x: torch.Tensor, training: bool) -> torch.Tensor:
+    """ResUnet.forward (resunet.py:54-79)."""
+    r = Runner(sd, training)
+    h = F.relu(r.bn(r.conv(x, "input_layer.0", padding=1), "input_layer.1"))
+    x1 = r.conv(h, "input_layer.3", padding=1) + r.conv(x, "input_skip.0", padding=1)   # resunet.py:56
+    x2 = _residual_conv(r, x1, "residual_conv_1", 2)
+    x3 = _residual_conv(r, x2, "residual_conv_2", 2)
+    x4 = _residual_conv(r, x3, "bridge", 2)
+    x4 = r.conv_transpose(x4, "upsample_1.upsample")
+    x6 = _residual_conv(r, torch.cat([x4, x3], 1), "up_residual_conv1", 1)               # resunet.py:63 (up FIRST)
+    x6 = r.conv_transpose(x6, "upsample_2.upsample")
+    x8 = _residual_conv(r, torch.cat([x6, x2], 1), "up_residual_conv2", 1)
+    x8 = r.conv_transpose(x8, "upsample_3.upsample")
+    x10 = _residual_conv(r, torch.cat([x8, x1], 1), "up_residual_conv3", 1)
+    return r.conv(x10, "output_layer.0")
+
+
+FORWARDS = {"unet": unet_forward, "attention_unet": attention_unet_forward, "nested_unet": nested_unet_forward,
+            "resunet": resunet_forward}
+
+
+def bce_with_logits(logits, target):
+    """nn.BCEWithLogitsLoss(), mean reduction (scripts/train.py:135)."""
+    return F.binary_cross_entropy_with_logits(logits, target)
+
+
+def dice_coefficient(logits, target, epsilon=1e-07, threshold=0.5):
+    """metrics.py:7-24: sigmoid -> >threshold -> flatten -> (2I+eps)/(U+eps); 1.0 when both masks are empty."""
+    pred = (torch.sigmoid(logits) > threshold).float().view(-1)
+    tgt = target.float().view(-1)
+    inter = (pred * tgt).sum()
+    union = pred.sum() + tgt.sum()
+    if union.item() == 0:
+        return torch.tensor(1.0)
+    return (2.0 * inter + epsilon) / (union + epsilon)
+
+
+def threshold_mask(logits, threshold=0.5):
+    """The thresholded prediction mask used by the Dice metric (metrics.py:11-12)."""
+    return torch.sigmoid(logits) > threshold
+
+
+def projection_loss(logits, target):
+    """Well-conditioned test loss: mean of logits * (+-1 pattern).  Its gradient has no common mode, so bf16 rounding
+    noise is not amplified by BatchNorm's mean subtraction the way the near-constant BCE gradient at init is."""
+    return (logits * (2.0 * target - 1.0)).mean()
+
+
+def train_step(name: str, sd: SD, x, target, loss_fn=None, **kw):
+    """One forward + BCE + backward in train mode on CPU: returns (logits, loss, {param key: grad}); `sd`'s BatchNorm
+    buffers are updated in place like the reference's modules would (training_loop.py:113-119)."""
+    leaves = {}
+    work = {}
+    for k, v in sd.items():
+        if v.dtype.is_floating_point and not (k.endswith("running_mean") or k.endswith("running_var")):
+            leaves[k] = v.detach().clone().requires_grad_(True)
+            work[k] = leaves[k]
+        else:
+            work[k] = v
+    out = FORWARDS[name](work, x, True, **kw)
+    outs = out if isinstance(out, list) else [out]
+    loss_fn = loss_fn or bce_with_logits
+    loss = sum(loss_fn(o, target) for o in outs)
+    loss.backward()
+    grads = {k: (t.grad if t.grad is not None else torch.zeros_like(t)) for k, t in leaves.items()}
+    return out, loss.detach(), grads
+
+
+def synthetic_batch(n, cin, h, w, seed_x=1234, seed_m=4321):
+    """The synthetic inputs of SURVEY.md section 8(d): x ~ N(0,1), mask ~ Bernoulli(0.5)."""
+    gx = torch.Generator().manual_seed(seed_x)
+    gm = torch.Generator().manual_seed(seed_m)
+    x = torch.randn(n, cin, h, w, generator=gx)
+    m = (torch.rand(n, 1, h, w, generator=gm) > 0.5).float()
+    return x, m

@@ -1,0 +1,63 @@
+"""The oracle (CPU restatement, oracle/reference_port.py) against fixtures produced by the reference modules
+themselves (oracle/make_golden.py).  CPU only."""
+import copy
+
+import pytest
+import torch
+
+from conftest import load_golden, rel_err, seeded_model
+from oracle import reference_port as O
+
+CASES = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
+         ("nested_unet_ds", {"deep_supervision": True})]
+
+
+@pytest.mark.parametrize("tag,kw", CASES)
+def test_oracle_matches_reference_outputs(tag, kw):
+    torch.set_num_threads(8)
+    name = tag.replace("_ds", "")
+    gold = load_golden(tag)
+    sd = copy.deepcopy(seeded_model(name, **kw).state_dict())
+    n, c, h, w = gold["recipe"]["batch"]
+    x, mask = O.synthetic_batch(n, c, h, w, gold["recipe"]["seed_x"], gold["recipe"]["seed_m"])
+    out, loss, grads = O.train_step(name, sd, x, mask, **kw)
+    outs = out if isinstance(out, list) else [out]
+    assert len(outs) == len(gold["logits_train"])
+    for o, g in zip(outs, gold["logits_train"]):
+        assert o.shape == g.shape
+        assert rel_err(o.detach(), g) < 1e-5
+    assert abs(float(loss) - gold["loss"]) < 1e-5
+    for k, gn in gold["grad_norm"].items():
+        assert abs(float(grads[k].double().norm()) - gn) <= 2e-4 * gn + 1e-7, k
+    for k, g in gold["grad_small"].items():
+        assert float((grads[k] - g).abs().max()) <= 2e-4 * float(g.abs().max()) + 1e-6, k
+    for k, v in gold["bn_after"].items():
+        assert torch.allclose(sd[k].double(), v.double(), rtol=1e-5, atol=1e-6), k
+    with torch.no_grad():
+        oe = O.FORWARDS[name](sd, x, False, **kw)
+    oes = oe if isinstance(oe, list) else [oe]
+    for o, g in zip(oes, gold["logits_eval"]):
+        assert rel_err(o, g) < 1e-5
+
+
+def test_threshold_is_bit_exact_with_sign_test():
+    """sigmoid(z) > 0.5 (metrics.py:11-12) agrees with z > 0 away from the fp32 saturation point; the parity tests use
+    the reference formulation itself."""
+    z = torch.linspace(-8, 8, 100001)
+    assert torch.equal(O.threshold_mask(z), z > 0)
+
+
+def test_dice_edge_cases():
+    z = torch.full((1, 1, 4, 4), -5.0)
+    assert float(O.dice_coefficient(z, torch.zeros(1, 1, 4, 4))) == 1.0     # empty union -> 1.0 (metrics.py:18-19)
+    t = torch.ones(1, 1, 4, 4)
+    assert abs(float(O.dice_coefficient(-z, t)) - 1.0) < 1e-6
+    assert float(O.dice_coefficient(z, t)) < 1e-6
+
+
+def test_readme_example_shape():
+    """README.md:74-90: unet on randn(1,3,256,256) -> (1,1,256,256)."""
+    assert load_golden("unet")["readme_shape"] == [1, 1, 256, 256]
+    sd = seeded_model("unet").state_dict()
+    with torch.no_grad():
+        assert list(O.unet_forward(sd, torch.randn(1, 3, 64, 64), False).shape) == [1, 1, 64, 64]

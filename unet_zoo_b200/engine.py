@@ -17,6 +17,28 @@ from . import _lib as L
 
 _c_void_p = ctypes.c_void_p
 
+# Optional per-launch timing of the tensor-core kernels (bench.py's roofline leg): when set to a list, every
+# uz_conv_igemm / uz_conv_wgrad call is bracketed by CUDA events on the launch stream and appended as
+# (kind, algorithmic_flops, start_event, end_event).  None (default) adds no overhead.
+PROFILE: Optional[list] = None
+_TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 9}
+
+
+class _Timed:
+    def __init__(self, kind, flops):
+        self.kind, self.flops = kind, flops
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            self.e1.record()
+            PROFILE.append((self.kind, self.flops, self.e0, self.e1))
+
 
 def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
@@ -132,6 +154,8 @@ class Ctx:
         self.reduce_rows = self.lib.uz_reduce_rows()
         self._ws = None
         self.pgrads: Optional[ParamGrads] = None
+        self.outputs: List[torch.Tensor] = []     # logits tensors, in the order the model returns them
+        self.out_grads: List[Optional[torch.Tensor]] = []
         self.launches = 0
 
     # ------------------------------------------------------------------ memory
@@ -189,8 +213,13 @@ class Ctx:
         cs = (ctypes.c_int * n)(*[s.C for s in segs])
         lds = (ctypes.c_int * n)(*[s.ld for s in segs])
         a = segs[0]
-        rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
-                                    out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
+        # algorithmic FLOPs: 2 * output pixels * cout * cin * taps (per output pixel; convT has one tap per output)
+        opix = a.N * out_h * out_w
+        taps = {L.CONVT2X2: 1, L.CONV3X3_S2_DGRAD: 2.25}.get(mode, _TAPS[mode])
+        flops = 2.0 * opix * cout * sum(s.C for s in segs) * taps
+        with _Timed("igemm_fwd", flops):
+            rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
+                                        out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
         L.check(rc, "uz_conv_igemm")
         self.launches += 1
 
@@ -198,8 +227,17 @@ class Ctx:
               dw: torch.Tensor, cin_total: int, c_off: int, accumulate: bool = False):
         need = self.lib.uz_conv_wgrad_workspace_bytes(mode, N, H, W, cin, cout)
         ws = self.workspace(need)
-        rc = self.lib.uz_conv_wgrad(mode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total, c_off,
-                                    int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
+        if mode == L.CONVT2X2:
+            flops = 2.0 * N * H * W * cin * cout * 4
+        elif mode in (L.CONV3X3_S2, L.CONV1X1_S2):
+            flops = 2.0 * N * ((H - 1) // 2 + 1) * ((W - 1) // 2 + 1) * cin * cout * _TAPS[mode]
+        elif mode == L.UP2X_CONV3X3:
+            flops = 2.0 * N * 4 * H * W * cin * cout * 9
+        else:
+            flops = 2.0 * N * H * W * cin * cout * _TAPS[mode]
+        with _Timed("igemm_wgrad", flops):
+            rc = self.lib.uz_conv_wgrad(mode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total,
+                                        c_off, int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
         L.check(rc, "uz_conv_wgrad")
         self.launches += 2
 
@@ -397,10 +435,8 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
                 c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(up.bias))
             c.pready(up.weight, up.bias)
             wpd = c.pack(up.weight, "convt_dgrad")  # [Cin][4][Cout]
-            gout = Act.__new__(Act)
-            gout.buf, gout.c0, gout.C = out.buf, out.c0, out.C
             for (r0, rc, acc) in x.grad_writes():
-                c.conv(L.CONVT2X2_DGRAD, [gout], wpd[r0:r0 + rc], rc, None, x.gptr() + 2 * r0, x.ld, x.H, x.W, None,
+                c.conv(L.CONVT2X2_DGRAD, [out], wpd[r0:r0 + rc], rc, None, x.gptr() + 2 * r0, x.ld, x.H, x.W, None,
                        L.FLAG_ACCUMULATE if acc else 0, in_grad=True)
         ctx.tape.append(backward)
     return out
@@ -415,6 +451,14 @@ def head1x1(ctx: Ctx, y: Act, conv) -> torch.Tensor:
                              ctx.stream)
     L.check(rc, "uz_head_fwd")
     ctx.launches += (K + 3) // 4
+    idx = len(ctx.outputs)
+    ctx.outputs.append(logits)
+    if ctx.record:
+        def backward(c: Ctx):
+            g = c.out_grads[idx] if idx < len(c.out_grads) else None
+            if g is not None:
+                head1x1_backward(c, y, conv, g)
+        ctx.tape.append(backward)
     return logits
 
 

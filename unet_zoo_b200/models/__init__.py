@@ -1,0 +1,75 @@
+"""Model factory - the drop-in boundary of the hot path.
+
+Mirrors the reference factory's contract (unet_zoo/models/__init__.py:59-61,78-238) for the four encoder-decoder
+models that BASELINE.json names: same signature, case-insensitive name lookup, the same always-popped keyword
+arguments (``in_channels``, ``num_classes``, ``image_size``, ``depth``), the same per-model constructor arguments,
+``ValueError`` for an unknown name and a warning (only) for ``pretrained=True``.  The reference's other twenty
+registry entries (transformer / axial-attention variants) are outside the hot path and raise NotImplementedError.
+"""
+from typing import Any, Dict, List
+
+import torch.nn as nn
+
+from .unet import UNet
+
+_model_entries: Dict[str, Any] = {"unet": UNet}
+
+try:  # the other three hot-path models register themselves as they are implemented
+    from .attention_unet import AttentionUNet
+    _model_entries["attention_unet"] = AttentionUNet
+except ImportError:  # pragma: no cover
+    pass
+try:
+    from .nested_unet import NestedUNet
+    _model_entries["nested_unet"] = NestedUNet
+except ImportError:  # pragma: no cover
+    pass
+try:
+    from .resunet import ResUnet
+    _model_entries["resunet"] = ResUnet
+except ImportError:  # pragma: no cover
+    pass
+
+# registry names of the reference that are deliberately not part of this build
+_OUT_OF_SCOPE = ("transatt_unet", "raunet", "da_transformer", "unet_transformer", "uctransnet", "multiresunet",
+                 "missformer", "vnet", "u2net", "u2netp", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
+                 "mmunet", "axialunet", "gated", "medt", "logo")
+
+
+def list_models() -> List[str]:
+    """Names accepted by :func:`create_model` (sorted, like the reference's list_models)."""
+    return sorted(_model_entries)
+
+
+def get_model_config(model_name: str, **kwargs) -> Dict[str, Any]:
+    """The hot-path models have no default-config function in the reference (models/__init__.py:54-57,63-76)."""
+    return {}
+
+
+def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Module:
+    name = model_name.lower()
+    if name not in _model_entries:
+        if name in _OUT_OF_SCOPE:
+            raise NotImplementedError(
+                f"'{model_name}' is a reference model outside the B200 hot path; available: {list_models()}")
+        raise ValueError(f"Unknown model: '{model_name}'. Available models: {list_models()}")
+    cls = _model_entries[name]
+
+    in_channels = kwargs.pop("in_channels", 3)
+    num_classes = kwargs.pop("num_classes", 1)
+    kwargs.pop("image_size", None)   # accepted for every model, used by none of these four
+    depth = kwargs.pop("depth", 5)
+
+    if name == "unet":
+        args = dict(in_channels=in_channels, num_classes=num_classes)
+    elif name == "attention_unet":
+        args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
+    elif name == "nested_unet":
+        args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth, deep_supervision=False)
+    else:  # resunet
+        args = dict(in_channels=in_channels, num_classes=num_classes, filters=[64, 128, 256, 512])
+    args.update(kwargs)              # leftovers reach the constructor (TypeError if it does not know them)
+    model = cls(**args)
+    if pretrained:
+        print(f"Warning: Pretrained weights not implemented for {model_name}. Initializing with random weights.")
+    return model

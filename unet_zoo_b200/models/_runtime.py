@@ -1,0 +1,92 @@
+"""nn.Module <-> fused-executor boundary shared by the four hot-path models.
+
+``forward(x)`` keeps the reference contract (NCHW float input -> raw NCHW logits, unet.py:29-44) while the whole
+network runs as one ``torch.autograd.Function``: forward launches the fused kernels and records a tape, backward
+replays the tape and hands one fp32 gradient per ``nn.Parameter`` back to autograd, so ``loss.backward()``,
+``clip_grad_norm_`` and any ``torch.optim`` optimizer work unchanged (training_loop.py:112-121).
+"""
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from .. import engine as E
+
+
+class _HotPathFn(torch.autograd.Function):
+    @staticmethod
+    def forward(fctx, model, x, *params):
+        ctx = E.Ctx(x.device, training=True, record=True)
+        outs = model._graph(ctx, x)
+        fctx.ectx = ctx
+        fctx.model = model
+        fctx.params = params
+        model._last_launches = ctx.launches
+        return tuple(outs)
+
+    @staticmethod
+    def backward(fctx, *douts):
+        ctx: E.Ctx = fctx.ectx
+        if ctx is None:
+            raise RuntimeError("unet_zoo_b200: backward called twice on the same forward (retain_graph is not "
+                               "supported: gradients overwrite the saved activations in place)")
+        fctx.ectx = None
+        model = fctx.model
+        params = fctx.params
+        ctx.stream = torch.cuda.current_stream(ctx.device).cuda_stream
+        ctx.launches = 0
+        make = getattr(model, "_uz_make_param_grads", None)
+        ctx.pgrads = make(params, ctx.device) if make is not None else E.ParamGrads(params, ctx.device)
+        ctx.out_grads = list(douts)
+        for step in reversed(ctx.tape):
+            step(ctx)
+        ctx.tape.clear()
+        model._last_launches_bwd = ctx.launches
+        finish = getattr(ctx.pgrads, "finish", None)
+        if finish is not None:
+            finish()
+        grads = [ctx.pgrads.view(p) if p.requires_grad else None for p in params]
+        return (None, None) + tuple(grads)
+
+
+class HotPathModel(nn.Module):
+    """Base class: input checks, train/eval dispatch, autograd wiring.  Subclasses implement ``_graph(ctx, x)``."""
+
+    _spatial_multiple = 16
+
+    def _check_input(self, x: torch.Tensor) -> torch.Tensor:
+        if not isinstance(x, torch.Tensor) or x.dim() != 4:
+            raise RuntimeError(f"{type(self).__name__}: expected a 4-D NCHW tensor")
+        if not x.is_cuda:
+            raise RuntimeError(f"{type(self).__name__}: input must be a CUDA tensor - this is the sm_100a build and "
+                               "has no CPU path (move the model and the batch to the GPU)")
+        p = next(self.parameters())
+        if p.device != x.device:
+            raise RuntimeError(f"{type(self).__name__}: parameters are on {p.device}, input on {x.device}")
+        if p.dtype != torch.float32:
+            raise RuntimeError(f"{type(self).__name__}: parameters must stay fp32 master weights (got {p.dtype}); "
+                               "bf16 compute is internal")
+        if x.shape[1] != self._in_channels:
+            raise RuntimeError(f"{type(self).__name__}: expected {self._in_channels} input channels, got {x.shape[1]}")
+        m = self._spatial_multiple
+        if x.shape[2] % m or x.shape[3] % m or x.shape[2] < m or x.shape[3] < m:
+            raise RuntimeError(f"{type(self).__name__}: H and W must be multiples of {m} (got {tuple(x.shape[2:])}); "
+                               "the reference's centre-padding of odd skip sizes is not implemented")
+        if x.requires_grad:
+            raise RuntimeError(f"{type(self).__name__}: gradients w.r.t. the input image are not implemented")
+        return x.float().contiguous()
+
+    def forward(self, x):
+        x = self._check_input(x)
+        with torch.cuda.device(x.device):
+            if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+                outs = _HotPathFn.apply(self, x, *self.parameters())
+            else:
+                with torch.no_grad():
+                    ctx = E.Ctx(x.device, training=self.training, record=False)
+                    outs = self._graph(ctx, x)
+                    self._last_launches = ctx.launches
+        return self._pack_outputs(list(outs))
+
+    def _pack_outputs(self, outs: List[torch.Tensor]):
+        return outs[0]
