@@ -1,0 +1,54 @@
+"""Data-parallel gradient bucketing over gloo (world_size 2, CPU): the host logic of unet_zoo_b200.parallel."""
+import os
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+from unet_zoo_b200 import parallel as P
+
+
+def test_plan_buckets_reverse_order_and_sizes():
+    b = P.plan_buckets([10, 20, 30, 40], bucket_bytes=200)
+    assert b == [[3, 2], [1, 0]]
+    assert P.plan_buckets([5], 1 << 20) == [[0]]
+    assert sorted(i for g in P.plan_buckets([7] * 9, 60) for i in g) == list(range(9))
+
+
+def _worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(100 + rank)                       # different weights per rank before the wrap
+    net = nn.Sequential(nn.Linear(8, 16), nn.BatchNorm1d(16), nn.Linear(16, 4))
+    dp = P.DataParallel(net, bucket_mb=0.0002)          # ~200-byte buckets -> several buckets
+    ref = [torch.zeros_like(p) for p in net.parameters()]
+    for p, r in zip(net.parameters(), ref):
+        r.copy_(p.detach())
+    gathered = [torch.zeros_like(ref[0]) for _ in range(world)]
+    dist.all_gather(gathered, ref[0])
+    same_weights = all(torch.equal(g, gathered[0]) for g in gathered)          # rank 0's parameters everywhere
+    params = list(net.parameters())
+    pg = net._uz_make_param_grads(params, torch.device("cpu"))
+    nb = len(pg.buckets)
+    for i, p in enumerate(params):
+        pg.view(p).fill_(float(rank + 1) * (i + 1))      # rank-dependent "gradients"
+    for p in reversed(params):                           # backward completes parameters in reverse order
+        pg.ready(p)
+    pg.finish()
+    ok = all(torch.allclose(pg.view(p), torch.full_like(p, 1.5 * (i + 1))) for i, p in enumerate(params))
+    sd_keys = list(dp.state_dict())
+    out[rank] = (same_weights, ok, nb, all(pg.launched), sd_keys == list(net.state_dict()))
+    dist.destroy_process_group()
+
+
+def test_bucketed_allreduce_world2():
+    mgr = mp.Manager()
+    out = mgr.dict()
+    port = 29500 + os.getpid() % 2000
+    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    for r in range(2):
+        same_weights, averaged, nb, launched, keys = out[r]
+        assert same_weights and averaged and launched and keys
+        assert nb >= 2

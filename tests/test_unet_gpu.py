@@ -1,0 +1,132 @@
+"""Whole-model parity of `unet` on the GPU: CUDA path (through create_model / nn.Module) vs the CPU oracle and the
+golden fixtures generated from the reference.  Tolerances are BASELINE.json's: bf16 compute within 2e-2 relative on
+logits (max|a-b| / max|b|), thresholded-mask agreement, threshold indexing bit-exact on identical logits."""
+import copy
+
+import pytest
+import torch
+
+from conftest import load_golden, rel_err, seeded_model
+from oracle import reference_port as O
+
+pytestmark = pytest.mark.gpu
+LOGIT_TOL_BF16 = 2e-2
+
+
+def _cuda_train_step(model, x, mask, loss_fn=O.bce_with_logits):
+    model.cuda().train()
+    out = model(x.cuda())
+    loss = loss_fn(out, mask.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    return out.detach().cpu(), float(loss)
+
+
+def test_unet_train_step_against_golden_and_oracle():
+    gold = load_golden("unet")
+    model = seeded_model("unet")
+    sd = copy.deepcopy(model.state_dict())
+    x, mask = O.synthetic_batch(*gold["recipe"]["batch"])
+    out, loss = _cuda_train_step(model, x, mask)
+    assert out.shape == gold["logits_train"][0].shape and out.dtype == torch.float32
+    assert rel_err(out, gold["logits_train"][0]) < LOGIT_TOL_BF16            # vs the reference's own output
+    assert abs(loss - gold["loss"]) < 2e-3
+    ref_out, ref_loss, ref_grads = O.train_step("unet", sd, x, mask)
+    assert rel_err(out, ref_out.detach()) < LOGIT_TOL_BF16
+    # BatchNorm running statistics after the step (momentum 0.1, unbiased running_var)
+    got = model.state_dict()
+    for k, v in gold["bn_after"].items():
+        if "running_" in k:
+            assert rel_err(got[k].cpu(), v) < 2e-2, k
+        else:
+            assert int(got[k]) == int(v), k
+    # the well-conditioned gradients (head, last BatchNorm) match the fp32 reference tightly
+    for k in ("out.conv.weight", "out.conv.bias", "up_convolution_4.conv.conv_op.4.weight"):
+        g = dict(model.named_parameters())[k].grad.cpu()
+        assert float((g - gold["grad_small"][k]).norm() / gold["grad_small"][k].norm()) < 2e-2, k
+    # every parameter received a finite gradient of the right shape
+    for k, p in model.named_parameters():
+        assert p.grad is not None and p.grad.shape == p.shape and bool(torch.isfinite(p.grad).all()), k
+
+
+def test_unet_gradients_no_noisier_than_bf16_autocast_of_the_reference():
+    """At random init the BCE gradient is ill-conditioned: torch's own bf16 autocast of the reference math deviates from
+    fp32 by 5-45 % per tensor (rel. L2).  Our bf16 path must stay within 1.3x of that floor (+2 %) for every weight."""
+    model = seeded_model("unet")
+    sd = copy.deepcopy(model.state_dict())
+    x, mask = O.synthetic_batch(4, 3, 128, 128)
+    _cuda_train_step(model, x, mask)
+    _, _, g32 = O.train_step("unet", copy.deepcopy(sd), x, mask)
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        _, _, g16 = O.train_step("unet", copy.deepcopy(sd), x, mask)
+    named = dict(model.named_parameters())
+    for k, ref in g32.items():
+        if not k.endswith("weight"):
+            continue
+        floor = float((g16[k].double() - ref.double()).norm() / ref.double().norm())
+        ours = float((named[k].grad.cpu().double() - ref.double()).norm() / ref.double().norm())
+        assert ours <= 1.3 * floor + 0.02, (k, ours, floor)
+
+
+def test_unet_eval_forward_and_mask_agreement():
+    gold = load_golden("unet")
+    model = seeded_model("unet")
+    x, mask = O.synthetic_batch(*gold["recipe"]["batch"])
+    _cuda_train_step(model, x, mask)                    # one step of running-stat updates, like the fixture
+    sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    model.eval()
+    with torch.no_grad():
+        out = model(x.cuda()).cpu()
+        ref = O.unet_forward(sd, x, False)              # oracle on the SAME (CUDA-updated) statistics
+    assert rel_err(out, ref) < LOGIT_TOL_BF16
+    assert rel_err(out, gold["logits_eval"][0]) < 3e-2  # fixture used the reference's own fp32 statistics
+    agree = float((O.threshold_mask(out) == O.threshold_mask(ref)).float().mean())
+    assert agree >= 0.999, agree
+    # bit-exact indexing: identical logits -> identical mask through the device-side formulation
+    dev_mask = (torch.sigmoid(ref.cuda()) > 0.5).cpu()
+    assert torch.equal(dev_mask, O.threshold_mask(ref))
+
+
+def test_unet_mask_agreement_train_mode_larger_batch():
+    model = seeded_model("unet")
+    sd = copy.deepcopy(model.state_dict())
+    x, mask = O.synthetic_batch(4, 3, 128, 128)
+    out, _ = _cuda_train_step(model, x, mask)
+    with torch.no_grad():
+        ref = O.unet_forward(sd, x, True)
+    assert rel_err(out, ref) < LOGIT_TOL_BF16
+    agree = float((O.threshold_mask(out) == O.threshold_mask(ref)).float().mean())
+    # random-init logits sit near the threshold (|z| ~ 0.1): 2e-2 relative noise flips ~0.2 % of them.  The 99.9 % bar
+    # of BASELINE.json is asserted in eval mode above; here we pin what bf16 training-mode statistics give.
+    assert agree >= 0.995, agree
+
+
+def test_unet_module_contract():
+    model = seeded_model("unet").cuda()
+    assert type(model).__name__ == "UNet"
+    with pytest.raises(RuntimeError, match="multiples of 16"):
+        model(torch.randn(1, 3, 60, 64, device="cuda"))
+    with pytest.raises(RuntimeError, match="input channels"):
+        model(torch.randn(1, 1, 64, 64, device="cuda"))
+    model.eval()
+    with torch.no_grad():
+        y = model(torch.randn(1, 3, 256, 256, device="cuda"))      # README.md:74-90
+    assert tuple(y.shape) == (1, 1, 256, 256)
+    # optimizer / clipping work on the parameters exactly as in training_loop.py:119-121
+    model.train()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-5)
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    losses = []
+    for _ in range(3):
+        opt.zero_grad()
+        loss = O.bce_with_logits(model(x.cuda()), m.cuda())
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0]
+    with pytest.raises(RuntimeError, match="backward called twice|retain_graph"):
+        out = model(x.cuda())
+        l2 = out.sum()
+        l2.backward(retain_graph=True)
+        l2.backward()
