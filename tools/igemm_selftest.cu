@@ -356,6 +356,9 @@ int main(int argc, char** argv) {
       {"wgrad conv1x1 s2 64->128 32x32 N2", UZ_CONV1X1_S2, 2, 32, 32, 64, 128},
       {"wgrad convT2x2 128->64 16x16 N2", UZ_CONVT2X2, 2, 16, 16, 128, 64},
       {"wgrad up2x+conv3x3 128->64 16x16 N2", UZ_UP2X_CONV3X3, 2, 16, 16, 128, 64},
+      {"wgrad2 conv3x3 64->64 16x8 N1 (one chunk)", UZ_CONV3X3, 1, 16, 8, 64, 64},
+      {"wgrad2 conv3x3 192->96 24x40 N2 (ragged)", UZ_CONV3X3, 2, 24, 40, 192, 96},
+      {"wgrad2 conv3x3 64->128 64x64 N3 (many chunks)", UZ_CONV3X3, 3, 64, 64, 64, 128},
   };
   const int nf = sizeof(fwd) / sizeof(fwd[0]), nw = sizeof(wg) / sizeof(wg[0]);
   if (argc > 1 && strcmp(argv[1], "count") == 0) {

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/unet_zoo_b200.h"
@@ -13,6 +14,7 @@
 namespace uz {
 cudaError_t launch_igemm_fwd(const IgemmParams& p, int bn, int grid, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream);
+cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream);
 cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
                                 long long s_row, long long s_col, long long s_tap, int accumulate,
                                 cudaStream_t stream);
@@ -465,7 +467,39 @@ static WgPlan plan_wgrad(int mode, int N, int H, int W, int cin, int cout) {
 }
 }  // namespace uz
 
+namespace uz {
+// second-generation kernel: 3x3 stride-1 on images of at least one 8x16 chunk
+static bool use_wgrad2(int mode, int H, int W) {
+  static const bool disabled = getenv("UZ_DISABLE_WGRAD2") != nullptr;
+  return !disabled && mode == UZ_CONV3X3 && H >= 16 && W >= 8;
+}
+struct Wg2Plan {
+  int xb, yb, chunks, co_blocks, ci_blocks, splits;
+  size_t ws_bytes;
+};
+static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
+  Wg2Plan pl;
+  pl.xb = (W + 7) / 8;
+  pl.yb = (H + 15) / 16;
+  pl.chunks = N * pl.xb * pl.yb;
+  pl.co_blocks = (cout + 63) / 64;
+  pl.ci_blocks = (cin + 63) / 64;
+  const int units = pl.co_blocks * pl.ci_blocks;
+  int sms = sm_count();
+  if (sms < 1) sms = 148;
+  int splits = (2 * sms + units - 1) / units;
+  int max_splits = pl.chunks / 4;
+  if (max_splits < 1) max_splits = 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  pl.splits = splits;
+  pl.ws_bytes = sizeof(float) * (size_t)splits * cout * 9 * cin;
+  return pl;
+}
+}  // namespace uz
+
 extern "C" size_t uz_conv_wgrad_workspace_bytes(int mode, int N, int H, int W, int cin, int cout) {
+  if (use_wgrad2(mode, H, W)) return plan_wgrad2(N, H, W, cin, cout).ws_bytes;
   WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
   return pl.rc == UZ_OK ? pl.ws_bytes : 0;
 }
@@ -479,6 +513,35 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
     return set_error(UZ_ERR_INVALID, "wgrad: channel counts / strides must be multiples of 8");
   if (!aligned16(x) || !aligned16(dy) || !aligned16(workspace))
     return set_error(UZ_ERR_INVALID, "wgrad: pointers must be 16-byte aligned");
+  if (use_wgrad2(mode, H, W)) {
+    const Wg2Plan p2 = plan_wgrad2(N, H, W, cin, cout);
+    if (workspace_bytes < p2.ws_bytes)
+      return set_error(UZ_ERR_WORKSPACE, "wgrad: workspace %zu < required %zu bytes", workspace_bytes, p2.ws_bytes);
+    Wgrad2Params q;
+    memset(&q, 0, sizeof(q));
+    const Lattice full2 = {0, 0, 1};
+    int rc2 = make_act_map(&q.xmap, x, cin, x_ld, N, H, W, full2, 10, 18, 1);
+    if (rc2 == UZ_OK) rc2 = make_act_map(&q.dzmap, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1);
+    if (rc2 != UZ_OK) return rc2;
+    q.xb = p2.xb;
+    q.yb = p2.yb;
+    q.total_chunks = p2.chunks;
+    q.cp = cout;
+    q.cq = cin;
+    q.co_blocks = p2.co_blocks;
+    q.ci_blocks = p2.ci_blocks;
+    q.splits = p2.splits;
+    q.total_items = p2.co_blocks * p2.ci_blocks * p2.splits;
+    q.partial = static_cast<float*>(workspace);
+    cudaStream_t st2 = static_cast<cudaStream_t>(stream);
+    const int grid2 = q.total_items < sms ? q.total_items : sms;
+    cudaError_t e2 = launch_igemm_wgrad2(q, grid2, st2);
+    if (e2 != cudaSuccess) return cuda_error(e2, "igemm_wgrad2 launch");
+    e2 = launch_wgrad_reduce(q.partial, dw + (long long)c_off * 9, p2.splits, cout, 9, cin, (long long)cin_total * 9, 9, 1,
+                             accumulate, st2);
+    if (e2 != cudaSuccess) return cuda_error(e2, "wgrad_reduce launch");
+    return UZ_OK;
+  }
   WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
   if (pl.rc != UZ_OK) return pl.rc;
   if (workspace_bytes < pl.ws_bytes)

@@ -72,4 +72,17 @@ struct alignas(64) WgradParams {
   float* partial;                // [splits][cp][num_taps][cq] fp32
 };
 
+// Second-generation 3x3 weight gradient (igemm_wgrad2.cu): one X halo box per 8x16-pixel chunk feeds all nine taps.
+struct alignas(64) Wgrad2Params {
+  CUtensorMap xmap;    // X:  4-D (C, W, H, N), box (64, 10, 18, 1), SWIZZLE_128B, zero fill outside the image
+  CUtensorMap dzmap;   // dZ: 4-D (C, W, H, N), box (64, 8, 16, 1)
+  int xb, yb;          // chunks along x (W/8) and y (H/16), rounded up
+  int total_chunks;    // N * yb * xb
+  int cp, cq;          // output channels (dZ) and input channels (X)
+  int co_blocks, ci_blocks;  // ceil(cp/64), ceil(cq/64)
+  int splits;          // split-K factor over the chunk range
+  int total_items;     // co_blocks * ci_blocks * splits
+  float* partial;      // [splits][cp][9][cq] fp32
+};
+
 }  // namespace uz

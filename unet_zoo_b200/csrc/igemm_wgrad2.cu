@@ -1,0 +1,224 @@
+// Weight gradient of the 3x3 / pad-1 / stride-1 convolution, second generation (sm_100a only).
+//
+//   dW[co, tap, ci] = sum over pixels  dZ[p, co] * X[p + shift(tap), ci]
+//
+// The first-generation kernel (igemm_wgrad.cu) loads one shifted X tile per filter tap, i.e. moves the activation nine
+// times through L2 and is L2->SM bandwidth bound (ncu, profiles/r01_a_*).  Here ONE TMA halo box of X
+// (64 channels x 10 x 18 pixels, SWIZZLE_128B) feeds all nine taps: tcgen05 shared-memory descriptors may start at any
+// 128-byte row of the box and step between 8-row groups with SBO = 1280 B (10 pixels) - verified on hardware by
+// tools/halo_probe.cu.  A work unit is (64 output channels) x (64 input channels) x (9 taps) x (a range of 8x16-pixel
+// chunks); per chunk it pulls 16 KB of dZ + 22.5 KB of X through L2 for 40 MMAs.
+//
+// GEMM orientation: both operands are "MN-major" (pixels = K are the slow axis of NHWC).  A = X halo with M = 128 =
+// TWO taps x 64 input channels: the descriptor's leading-dimension byte offset (distance between the two 64-element MN
+// atoms) is simply the address shift between the two taps (128 B for dx+1, 1280 B for dy+1), so five MMAs cover the nine
+// taps (the tenth half is discarded).  B = dZ chunk, N = 64 output channels.  D blocks live in 5 x 64 TMEM columns.
+#include "igemm.cuh"
+#include "ptx.cuh"
+
+namespace uz {
+
+constexpr int kW2Threads = 192;
+constexpr int kW2HaloW = 10, kW2HaloH = 18;
+constexpr int kW2HaloBytes = kW2HaloW * kW2HaloH * 128;  // 23040
+constexpr int kW2HaloSlot = 23552;                       // rounded up to 1024
+constexpr int kW2DzBytes = 128 * 128;                    // 8x16 pixels x 64 channels bf16
+constexpr int kW2StageBytes = kW2HaloSlot + kW2DzBytes;  // 39936
+constexpr int kW2Stages = 5;
+constexpr int kW2TmemCols = 512;
+constexpr int kW2SmemBytes = kW2Stages * kW2StageBytes + 256 + 1024;
+
+struct W2Item {
+  int co_blk, ci_blk, split, chunk_begin, chunk_end;
+};
+
+__device__ __forceinline__ W2Item w2_decode(const Wgrad2Params& p, int item) {
+  W2Item w;
+  const int units = p.co_blocks * p.ci_blocks;
+  w.split = item / units;
+  const int u = item - w.split * units;
+  w.co_blk = u / p.ci_blocks;
+  w.ci_blk = u - w.co_blk * p.ci_blocks;
+  const int base = p.total_chunks / p.splits, rem = p.total_chunks % p.splits;
+  w.chunk_begin = w.split * base + min(w.split, rem);
+  w.chunk_end = w.chunk_begin + base + (w.split < rem ? 1 : 0);
+  return w;
+}
+
+__global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_addr);
+  const uint32_t bar_base = base + kW2Stages * kW2StageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kW2Stages + s); };
+  const uint32_t tfull_bar = bar_base + 8u * (2 * kW2Stages);
+  const uint32_t tempty_bar = bar_base + 8u * (2 * kW2Stages + 1);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kW2Stages + 2);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem + kW2Stages * kW2StageBytes + 8 * (2 * kW2Stages + 2));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kW2Stages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tfull_bar, 1);
+    mbar_init(tempty_bar, 4);
+    mbar_fence_init();
+    tma_prefetch_desc(&p.xmap);
+    tma_prefetch_desc(&p.dzmap);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kW2TmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        const W2Item w = w2_decode(p, item);
+        for (int chunk = w.chunk_begin; chunk < w.chunk_end; ++chunk) {
+          const int xb = chunk % p.xb;
+          int r = chunk / p.xb;
+          const int yb = r % p.yb;
+          const int n = r / p.yb;
+          const int x0 = xb * 8, y0 = yb * 16;
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t halo_dst = base + stage * kW2StageBytes;
+          const uint32_t dz_dst = halo_dst + kW2HaloSlot;
+          mbar_expect_tx(full_bar(stage), kW2HaloBytes + kW2DzBytes);
+          tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+          tma_load_4d(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * 64, x0, y0, n);
+          if (++stage == kW2Stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);  // both operands MN-major
+      // tap pairs stacked along M: {first tap row offset (in halo pixels), byte distance to the second tap}
+      //   taps are (dy, dx) in {-1,0,1}^2 with tap index (dy+1)*3 + (dx+1); halo row of tap = (dy+1)*10 + (dx+1)
+      constexpr int pair_row[5] = {0 * 10 + 0, 1 * 10 + 0, 2 * 10 + 0, 0 * 10 + 2, 2 * 10 + 2};
+      constexpr int pair_lbo[5] = {128, 128, 128, 1280, 128};
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t acc_phase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        const W2Item w = w2_decode(p, item);
+        if (w.chunk_end <= w.chunk_begin) continue;
+        mbar_wait(tempty_bar, acc_phase ^ 1u);
+        tc_fence_after();
+        bool first = true;
+        for (int chunk = w.chunk_begin; chunk < w.chunk_end; ++chunk) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t halo = base + stage * kW2StageBytes;
+          const uint32_t dz = halo + kW2HaloSlot;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {  // 16 pixels = image rows 2j, 2j+1 of the chunk
+            const uint64_t bdesc = umma_smem_desc(dz + j * 2048, 1024, 1024);
+#pragma unroll
+            for (int b = 0; b < 5; ++b) {
+              const uint64_t adesc =
+                  umma_smem_desc(halo + pair_row[b] * 128 + j * 2 * kW2HaloW * 128, pair_lbo[b], kW2HaloW * 128);
+              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (first && j == 0) ? 0u : 1u);
+            }
+          }
+          first = false;
+          umma_commit(empty_bar(stage));
+          if (++stage == kW2Stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit(tfull_bar);
+        acc_phase ^= 1u;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (2..5): TMEM -> fp32 partials
+    const int q = warp & 3;
+    const int row = q * 32 + lane;   // accumulator row: half (tap of the pair) and input channel
+    const int half = row >> 6;
+    const int ci_l = row & 63;
+    constexpr int pair_tap[5][2] = {{0, 1}, {3, 4}, {6, 7}, {2, 5}, {8, -1}};
+    uint32_t acc_phase = 0;
+    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+      const W2Item w = w2_decode(p, item);
+      const bool has_work = w.chunk_end > w.chunk_begin;
+      if (has_work) {
+        mbar_wait(tfull_bar, acc_phase);
+        tc_fence_after();
+      }
+      const int ci = w.ci_blk * 64 + ci_l;
+      const int co0 = w.co_blk * 64;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      float* pbase = p.partial + static_cast<size_t>(w.split) * p.cp * 9 * p.cq;
+#pragma unroll 1
+      for (int b = 0; b < 5; ++b) {
+        const int tap = pair_tap[b][half];
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          uint32_t v[32];
+          if (has_work) {
+            tmem_ld32(t_addr + b * 64 + h * 32, v);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0u;
+          }
+          if (tap >= 0 && ci < p.cq) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int co = co0 + h * 32 + j;
+              if (co < p.cp) pbase[(static_cast<size_t>(co) * 9 + tap) * p.cq + ci] = __uint_as_float(v[j]);
+            }
+          }
+        }
+      }
+      if (has_work) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar);
+        acc_phase ^= 1u;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kW2TmemCols);
+  }
+}
+
+cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e =
+        cudaFuncSetAttribute(igemm_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  igemm_wgrad2_kernel<<<grid, kW2Threads, kW2SmemBytes, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace uz
