@@ -346,6 +346,10 @@ int main(int argc, char** argv) {
       {"convT2x2 dgrad 64->128 32x32 N2", UZ_CONVT2X2_DGRAD, 2, 32, 32, 1, {64}, 128, 0, false, 0},
       {"up2x+conv3x3 128->64 16x16 N2", UZ_UP2X_CONV3X3, 2, 16, 16, 1, {128}, 64, 0, false, 0},
       {"conv3x3 64->64 64x64 N5 (multi-wave) stats", UZ_CONV3X3, 5, 64, 64, 1, {64}, 64, UZ_FLAG_STATS, false, 0},
+      {"fwd2 conv3x3 256->256 32x32 N2 ring stats bias", UZ_CONV3X3, 2, 32, 32, 1, {256}, 256, UZ_FLAG_STATS, true, 0},
+      {"fwd2 conv3x3 64->512 16x24 N3 (2 n-tiles) stats relu", UZ_CONV3X3, 3, 16, 24, 1, {64}, 512, UZ_FLAG_STATS | UZ_FLAG_RELU, false, 64},
+      {"fwd2 conv3x3 dgrad 256->128 24x40 N2 ragged", UZ_CONV3X3_DGRAD, 2, 24, 40, 1, {256}, 128, 0, false, 0},
+      {"fwd2 conv3x3 (128+128)->128 64x64 N4 ring", UZ_CONV3X3, 4, 64, 64, 2, {128, 128}, 128, UZ_FLAG_STATS, false, 0},
   };
   const WgCase wg[] = {
       {"wgrad conv3x3 64->64 32x32 N2", UZ_CONV3X3, 2, 32, 32, 64, 64},

@@ -146,10 +146,14 @@ __global__ void head_bwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, con
 
 __global__ void head_reduce_kernel(const float* __restrict__ partial, int rows, int cols, float* __restrict__ out,
                                    int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= cols) return;
   double s = 0.0;
-  for (int r = 0; r < rows; ++r) s += static_cast<double>(partial[static_cast<size_t>(r) * cols + c]);
+  for (int r = lane; r < rows; r += 32) s += static_cast<double>(partial[static_cast<size_t>(r) * cols + c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane != 0) return;
   out[c] = (accumulate ? out[c] : 0.f) + static_cast<float>(s);
 }
 
@@ -250,8 +254,8 @@ extern "C" int uz_head_bwd(const void* y, int ld, const float* dlogits, int N, i
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_error(e, "head_bwd launch");
-    head_reduce_kernel<<<(kn * C + 127) / 128, 128, 0, st>>>(partial, grid, kn * C, dw + static_cast<size_t>(k0) * C, accumulate);
-    head_reduce_kernel<<<1, 128, 0, st>>>(bpartial, grid, kn, db + k0, accumulate);
+    head_reduce_kernel<<<(kn * C + 3) / 4, 128, 0, st>>>(partial, grid, kn * C, dw + static_cast<size_t>(k0) * C, accumulate);
+    head_reduce_kernel<<<(kn + 3) / 4, 128, 0, st>>>(bpartial, grid, kn, db + k0, accumulate);
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_error(e, "head_bwd reduce launch");
   }

@@ -13,6 +13,7 @@
 
 namespace uz {
 cudaError_t launch_igemm_fwd(const IgemmParams& p, int bn, int grid, cudaStream_t stream);
+cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream);
 cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
@@ -317,7 +318,104 @@ extern "C" int uz_device_sm_count(void) {
   if (n < 0) return set_error(UZ_ERR_CUDA, "no CUDA device");
   return n;
 }
-extern "C" int uz_conv_stats_rows(void) { return uz_device_sm_count(); }
+// rows of the per-channel statistics partials: one per (CTA, epilogue warp) of the persistent conv kernels
+extern "C" int uz_conv_stats_rows(void) {
+  const int n = uz_device_sm_count();
+  return n < 0 ? n : 4 * n;
+}
+
+namespace uz {
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+// Second-generation path (igemm_fwd2.cu).  Returns 1 when it handled the call, 0 when the first-generation kernel
+// should run, negative on error.
+static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* seg_ptr, const int* seg_c,
+                    const int* seg_ld, const void* w_packed, int cout, const float* bias, void* out, int out_ld,
+                    float* stats, int flags, int sms, cudaStream_t st) {
+  static const int disabled = env_int("UZ_DISABLE_FWD2", 0);
+  if (disabled) return 0;
+  if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1)) return 0;
+  if (H < 16 || W < 8 || nseg > kMaxSegs) return 0;
+  Igemm2Params p;
+  memset(&p, 0, sizeof(p));
+  const int pad = mode == UZ_CONV1X1 ? 0 : 1;
+  p.pad = pad;
+  p.halo_w = 8 + 2 * pad;
+  p.halo_bytes = p.halo_w * (16 + 2 * pad) * 128;
+  p.num_taps = pad ? 9 : 1;
+  for (int t = 0; t < p.num_taps; ++t) {
+    const int r = t / 3, s = t % 3;
+    if (mode == UZ_CONV3X3) p.tap_row[t] = r * p.halo_w + s;
+    else if (mode == UZ_CONV3X3_DGRAD) p.tap_row[t] = (2 - r) * p.halo_w + (2 - s);
+    else p.tap_row[t] = 0;
+    p.tap_b[t] = t;
+  }
+  const int bn = cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
+  int ctot = 0, kblocks = 0;
+  const Lattice full = {0, 0, 1};
+  for (int s = 0; s < nseg; ++s) {
+    p.seg_cblocks[s] = (seg_c[s] + 63) / 64;
+    p.seg_k0[s] = ctot;
+    ctot += seg_c[s];
+    kblocks += p.seg_cblocks[s];
+    int rc = make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
+    if (rc != UZ_OK) return rc;
+  }
+  p.num_segs = nseg;
+  p.kblocks = kblocks;
+  p.N = N; p.H = H; p.W = W;
+  p.xb = (W + 7) / 8;
+  p.yb = (H + 15) / 16;
+  p.m_tiles_real = N * p.xb * p.yb;
+  p.num_n_tiles = (cout + bn - 1) / bn;
+  // shared-memory plan
+  const int kMaxSmem = 232448 - 1024;  // 227 KB minus the alignment slack
+  const int a_slot = (p.halo_bytes + 1023) & ~1023;
+  const int b_item = bn * 128;
+  const int fixed = 2 * 16384 + 512;   // staging + barriers
+  const long long b_all = (long long)kblocks * p.num_taps * b_item;
+  int cluster = 1;
+  if (p.num_n_tiles == 1 && b_all + 2LL * a_slot + fixed <= kMaxSmem && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
+    p.b_stages = 0;
+    int as = (int)((kMaxSmem - fixed - b_all) / a_slot);
+    p.a_stages = as > 6 ? 6 : as;
+  } else {
+    cluster = env_int("UZ_FWD2_CLUSTER", 1);
+    if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
+    if (bn / cluster < 16) cluster = 1;
+    p.a_stages = kblocks == 1 ? 2 : 3;
+    int bs = (kMaxSmem - fixed - p.a_stages * a_slot) / b_item;
+    p.b_stages = bs > 12 ? 12 : bs;
+    if (p.b_stages < 2) return 0;
+  }
+  p.cluster = cluster;
+  p.m_tiles = (p.m_tiles_real + cluster - 1) / cluster * cluster;
+  p.total_tiles = p.m_tiles * p.num_n_tiles;
+  p.a_off = 0;
+  p.b_off = p.a_stages * a_slot;
+  const long long b_bytes = p.b_stages ? (long long)p.b_stages * b_item : b_all;
+  p.stg_off = (int)(p.b_off + b_bytes);
+  p.bar_off = p.stg_off + 2 * 16384;
+  const int smem_bytes = p.bar_off + 512 + 1024;
+  int rc = make_weight_map(&p.bmap, w_packed, ctot, p.num_taps, cout, bn / cluster);
+  if (rc != UZ_OK) return rc;
+  rc = make_act_map(&p.omap, out, cout, out_ld, N, H, W, full, 8, 16, 1);
+  if (rc != UZ_OK) return rc;
+  p.ncols = cout;
+  p.bias = bias;
+  p.stats = stats;
+  p.flags = flags;
+  int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  grid = grid / cluster * cluster;
+  if (grid < cluster) return 0;
+  cudaError_t e = launch_igemm_fwd2(p, bn, grid, smem_bytes, st);
+  if (e != cudaSuccess) return cuda_error(e, "igemm_fwd2 launch");
+  return 1;
+}
+}  // namespace uz
 
 extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void* const* seg_ptr, const int* seg_c,
                              const int* seg_ld, const void* w_packed, int cout, const float* bias, void* out,
@@ -387,8 +485,12 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 
   if (flags & UZ_FLAG_STATS) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * 4 * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
+  }
+  if (mi.num_phases == 1 && mi.oscale == 1) {
+    rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
+    if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }
   if (mode == UZ_CONV3X3_S2_DGRAD) {
     // ragged tap counts per phase: one launch per phase (each is a 1-phase problem with its own tap table)

@@ -85,4 +85,37 @@ struct alignas(64) Wgrad2Params {
   float* partial;      // [splits][cp][9][cq] fp32
 };
 
+// Second-generation forward-type implicit GEMM (igemm_fwd2.cu): conv3x3 / its data gradient / conv1x1 on 8x16-pixel
+// tiles.  One TMA halo box per (segment, 64-channel block) feeds every filter tap; the weight operand is either kept
+// resident in shared memory for the whole launch (small layers) or streamed through a ring, optionally multicast
+// across a thread-block cluster; the epilogue goes TMEM -> registers -> swizzled smem -> TMA store.
+struct alignas(64) Igemm2Params {
+  CUtensorMap amap[kMaxSegs];  // 4-D (C, W, H, N) bf16, box (64, 8+2*pad, 16+2*pad, 1), SWIZZLE_128B
+  CUtensorMap bmap;            // 3-D (Ctot, taps, cols) packed weights, box (64, 1, BN / cluster)
+  CUtensorMap omap;            // 4-D (cout, W, H, N) output view, box (64, 8, 16, 1), SWIZZLE_128B (TMA store)
+  int num_segs;
+  int seg_cblocks[kMaxSegs];
+  int seg_k0[kMaxSegs];
+  int num_taps;
+  int tap_row[9];              // halo row (pixel index in the box) of each tap's first pixel
+  int tap_b[9];                // tap coordinate in the packed weights
+  int pad;                     // 1 for 3x3, 0 for 1x1
+  int halo_w;                  // 8 + 2*pad
+  int halo_bytes;              // halo_w * (16 + 2*pad) * 128
+  int N, H, W;
+  int xb, yb;                  // tiles along x, y
+  int m_tiles;                 // N*yb*xb rounded up to a multiple of the cluster size
+  int m_tiles_real;
+  int num_n_tiles;
+  int total_tiles;             // m_tiles * num_n_tiles (tile = n_tile * m_tiles + m)
+  int kblocks;                 // sum of seg_cblocks
+  int a_stages, b_stages;      // ring depths; b_stages == 0 -> weights stationary (all kblocks*taps items resident)
+  int a_off, b_off, stg_off, bar_off;  // byte offsets from the 1024-aligned smem base
+  int cluster;                 // thread-block cluster size (1, 2 or 4): weight tiles are multicast when > 1
+  int ncols;                   // valid output columns (Cout)
+  const float* bias;
+  float* stats;                // [4*gridDim.x][2][ncols] partial sums (kFlagStats), zeroed by the host
+  int flags;
+};
+
 }  // namespace uz

@@ -1,0 +1,393 @@
+// Forward-type implicit-GEMM convolution, second generation (sm_100a only): conv3x3 (stride 1, pad 1), its data
+// gradient and conv1x1 on 8x16-pixel output tiles.
+//
+// Why: ncu showed the first-generation kernel (igemm_fwd.cu) bound by L2->SM bandwidth - every filter tap re-loads
+// its shifted A tile, the weight tile is re-loaded per output tile, and the epilogue scatters 16-byte stores.  Here
+//   * ONE TMA halo box (64 ch x 10 x 18 px, SWIZZLE_128B) per 64-channel block feeds all nine taps: the tcgen05
+//     descriptor of tap (dy,dx) starts (dy+1)*10+(dx+1) rows into the box with SBO = 1280 B (tools/halo_probe.cu);
+//   * weights are either resident in shared memory for the whole launch (layers whose packed weights fit) or streamed
+//     through their own ring by a dedicated producer warp, multicast across a thread-block cluster when one is used;
+//   * the epilogue writes TMEM -> registers -> swizzled staging tile -> TMA store (or TMA reduce-add when the output
+//     accumulates), and takes the BatchNorm column sums from the staged bf16 tile (conflict-free column reads).
+//
+// Warp roles (224 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2..5 = epilogue, 6 = B producer.
+#include <string.h>
+
+#include "igemm.cuh"
+#include "ptx.cuh"
+
+namespace uz {
+
+constexpr int kF2Threads = 224;
+constexpr int kF2StgBytes = 128 * 128;  // one staged 128-pixel x 64-channel bf16 chunk
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+struct F2Tile {
+  int n_tile, n, x0, y0;
+  bool dummy;
+};
+__device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile) {
+  F2Tile t;
+  t.n_tile = tile / p.m_tiles;
+  const int m = tile - t.n_tile * p.m_tiles;
+  t.dummy = m >= p.m_tiles_real;
+  const int xb = m % p.xb;
+  const int r = m / p.xb;
+  const int yb = r % p.yb;
+  t.n = t.dummy ? p.N : r / p.yb;  // n == N is outside every tensor map: loads are zero-filled, stores clipped
+  t.x0 = xb * 8;
+  t.y0 = yb * 16;
+  return t;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_constant__ Igemm2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_addr);
+  const uint32_t a_base = base + p.a_off, b_base = base + p.b_off, stg_base = base + p.stg_off;
+  const uint32_t bars = base + p.bar_off;
+  auto afull = [&](int s) { return bars + 8u * s; };
+  auto aempty = [&](int s) { return bars + 64u + 8u * s; };
+  auto bfull = [&](int s) { return bars + 128u + 8u * s; };
+  auto bempty = [&](int s) { return bars + 256u + 8u * s; };
+  auto tfull = [&](int s) { return bars + 384u + 8u * s; };
+  auto tempty = [&](int s) { return bars + 400u + 8u * s; };
+  const uint32_t tmem_slot = bars + 416u;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + p.bar_off + 416);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int cs = p.cluster;
+  const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
+  const uint16_t mc_mask = static_cast<uint16_t>((1u << cs) - 1u);
+  const bool ring = p.b_stages > 0;
+  const uint32_t a_slot = static_cast<uint32_t>(p.halo_bytes + 1023) & ~1023u;
+  constexpr uint32_t kBItem = BN * 128;
+  constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < p.a_stages; ++s) {
+      mbar_init(afull(s), 1);
+      mbar_init(aempty(s), 1);
+    }
+    const int nb = ring ? p.b_stages : 1;
+    for (int s = 0; s < nb; ++s) {
+      mbar_init(bfull(s), 1);
+      mbar_init(bempty(s), cs);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull(s), 1);
+      mbar_init(tempty(s), 4);
+    }
+    mbar_fence_init();
+    for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
+    tma_prefetch_desc(&p.bmap);
+    tma_prefetch_desc(&p.omap);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (cs > 1) cluster_sync_all();  // every CTA's barriers exist before any multicast / remote commit can arrive
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int cidx = blockIdx.x / cs;
+  const int nclusters = gridDim.x / cs;
+  const int ngroups = p.total_tiles / cs;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ A producer: one halo box per (segment, cblock)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int g = cidx; g < ngroups; g += nclusters) {
+        const F2Tile t = f2_decode(p, g * cs + rank);
+        for (int seg = 0; seg < p.num_segs; ++seg) {
+          const int ncb = p.seg_cblocks[seg];
+          for (int cb = 0; cb < ncb; ++cb) {
+            mbar_wait(aempty(stage), phase ^ 1u);
+            mbar_expect_tx(afull(stage), p.halo_bytes);
+            tma_load_4d(a_base + stage * a_slot, &p.amap[seg], afull(stage), cb * 64, t.x0 - p.pad, t.y0 - p.pad, t.n);
+            if (++stage == p.a_stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 6) {
+    // ------------------------------------------------------------------ B producer: weight tiles
+    if (lane == 0) {
+      if (!ring) {
+        // stationary: every (cblock, tap) tile is loaded once and stays for the whole launch (num_n_tiles == 1)
+        mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.kblocks * p.num_taps) * kBItem);
+        int item = 0;
+        for (int seg = 0; seg < p.num_segs; ++seg)
+          for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb)
+            for (int tap = 0; tap < p.num_taps; ++tap, ++item)
+              tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap], 0);
+      } else {
+        int stage = 0;
+        uint32_t phase = 0;
+        const int rows = BN / cs;
+        for (int g = cidx; g < ngroups; g += nclusters) {
+          const int n_tile = (g * cs) / p.m_tiles;
+          for (int seg = 0; seg < p.num_segs; ++seg) {
+            const int ncb = p.seg_cblocks[seg];
+            for (int cb = 0; cb < ncb; ++cb) {
+              const int k = p.seg_k0[seg] + cb * 64;
+              for (int tap = 0; tap < p.num_taps; ++tap) {
+                mbar_wait(bempty(stage), phase ^ 1u);
+                mbar_expect_tx(bfull(stage), kBItem);
+                const uint32_t dst = b_base + stage * kBItem;
+                if (cs == 1)
+                  tma_load_3d(dst, &p.bmap, bfull(stage), k, p.tap_b[tap], n_tile * BN);
+                else
+                  tma_load_3d_mc(dst + rank * rows * 128, &p.bmap, bfull(stage), k, p.tap_b[tap],
+                                 n_tile * BN + rank * rows, mc_mask);
+                if (++stage == p.b_stages) {
+                  stage = 0;
+                  phase ^= 1u;
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      const uint32_t a_sbo = p.halo_w * 128;
+      int astage = 0, bstage = 0, acc = 0;
+      uint32_t aphase = 0, bphase = 0, acc_phase = 0;
+      if (!ring) {
+        mbar_wait(bfull(0), 0);
+        tc_fence_after();
+      }
+      for (int g = cidx; g < ngroups; g += nclusters) {
+        mbar_wait(tempty(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        uint32_t accumulate = 0;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(afull(astage), aphase);
+          tc_fence_after();
+          const uint32_t halo = a_base + astage * a_slot;
+          for (int tap = 0; tap < p.num_taps; ++tap) {
+            uint32_t bsm;
+            if (ring) {
+              mbar_wait(bfull(bstage), bphase);
+              tc_fence_after();
+              bsm = b_base + bstage * kBItem;
+            } else {
+              bsm = b_base + (kb * p.num_taps + tap) * kBItem;
+            }
+            const uint32_t a_tap = halo + p.tap_row[tap] * 128;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              umma_bf16(d_tmem, umma_smem_desc(a_tap + k * 32, 16, a_sbo), umma_smem_desc(bsm + k * 32, 16, 1024), idesc,
+                        accumulate);
+              accumulate = 1;
+            }
+            if (ring) {
+              if (cs == 1)
+                umma_commit(bempty(bstage));
+              else
+                umma_commit_mc(bempty(bstage), mc_mask);
+              if (++bstage == p.b_stages) {
+                bstage = 0;
+                bphase ^= 1u;
+              }
+            }
+          }
+          umma_commit(aempty(astage));
+          if (++astage == p.a_stages) {
+            astage = 0;
+            aphase ^= 1u;
+          }
+        }
+        umma_commit(tfull(acc));
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (2..5)
+    const int q = warp & 3;            // TMEM lane quarter of this warp
+    const int et = threadIdx.x - 64;   // 0..127
+    const int row = q * 32 + lane;     // accumulator row = pixel (y = row >> 3, x = row & 7) of the tile
+    const bool do_stats = (p.flags & kFlagStats) != 0;
+    const bool do_relu = (p.flags & kFlagRelu) != 0;
+    const bool do_acc = (p.flags & kFlagAccumulate) != 0;
+    constexpr int kChunks = BN / 64;
+    float run_s[kChunks][2], run_q[kChunks][2];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) run_s[c][0] = run_s[c][1] = run_q[c][0] = run_q[c][1] = 0.f;
+    int run_ntile = -1;
+    auto flush_stats = [&]() {
+      if (run_ntile < 0) return;
+      float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 4 + (warp - 2)) * 2 * p.ncols;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int col = run_ntile * BN + c * 64 + 2 * lane + h;
+          if (col < p.ncols) {
+            dst[col] += run_s[c][h];
+            dst[p.ncols + col] += run_q[c][h];
+          }
+          run_s[c][h] = run_q[c][h] = 0.f;
+        }
+      }
+    };
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t it = 0;  // staging buffer toggle
+    for (int g = cidx; g < ngroups; g += nclusters) {
+      const F2Tile t = f2_decode(p, g * cs + rank);
+      const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
+      if (do_stats && t.n_tile != run_ntile) {
+        flush_stats();
+        run_ntile = t.n_tile;
+      }
+      mbar_wait(tfull(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int ch = 0; ch < kChunks; ++ch) {
+        const int col0 = t.n_tile * BN + ch * 64;
+        if (col0 >= p.ncols) break;  // uniform over the CTA
+        const uint32_t sbuf = stg_base + (it & 1u) * kF2StgBytes;
+        ++it;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t v[32];
+          tmem_ld32(t_addr + ch * 64 + h * 32, v);
+          tmem_ld_wait();
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + h * 32 + j < p.ncols) f[j] += __ldg(p.bias + col0 + h * 32 + j);
+          }
+          if (do_relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          if (!valid) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = 0.f;  // keeps out-of-image rows out of the column sums
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int chunk16 = h * 4 + c;  // 16-byte chunk index inside the 128-byte row
+            st_shared_v4(sbuf + row * 128 + ((chunk16 ^ (row & 7)) << 4), pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]),
+                         pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]), pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]),
+                         pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]));
+          }
+        }
+        fence_proxy_async_smem();
+        if (et == 0) tma_store_wait_read0();  // the previous store has finished reading the other staging buffer
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          if (do_acc)
+            tma_reduce_add_4d(&p.omap, sbuf, col0, t.x0, t.y0, t.n);
+          else
+            tma_store_4d(&p.omap, sbuf, col0, t.x0, t.y0, t.n);
+          tma_store_commit();
+        }
+        if (do_stats) {
+          // lane owns columns 2*lane, 2*lane+1 of the chunk; this warp sums its own 32 rows (bank-conflict free)
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+          for (int rr = 0; rr < 32; ++rr) {
+            const int r = q * 32 + rr;
+            const uint32_t w = ld_shared_u32(sbuf + r * 128 + (((lane >> 2) ^ (r & 7)) << 4) + (lane & 3) * 4);
+            const float lo = bf16_lo(w), hi = bf16_hi(w);
+            s0 += lo;
+            s1 += hi;
+            q0 = fmaf(lo, lo, q0);
+            q1 = fmaf(hi, hi, q1);
+          }
+          run_s[ch][0] += s0;
+          run_s[ch][1] += s1;
+          run_q[ch][0] += q0;
+          run_q[ch][1] += q1;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty(acc));
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
+    }
+    if (do_stats) flush_stats();
+    if (et == 0) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (cs > 1) cluster_sync_all();  // nobody leaves while a peer may still multicast into / signal this CTA
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+template <int BN>
+static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
+  static int configured = 0;
+  if (configured < smem_bytes) {
+    cudaError_t e =
+        cudaFuncSetAttribute(igemm_fwd2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return e;
+    configured = smem_bytes;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kF2Threads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  int nattr = 0;
+  if (p.cluster > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    nattr = 1;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = nattr;
+  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN>, p);
+}
+
+cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream) {
+  switch (bn) {
+    case 64: return launch_fwd2_bn<64>(p, grid, smem_bytes, stream);
+    case 128: return launch_fwd2_bn<128>(p, grid, smem_bytes, stream);
+    case 256: return launch_fwd2_bn<256>(p, grid, smem_bytes, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace uz

@@ -189,13 +189,21 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, 
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                    float momentum, float* __restrict__ running_mean, float* __restrict__ running_var,
                                    float* __restrict__ bn) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per channel: lanes stride over the partial rows, fp64 shuffle reduction (deterministic)
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
-  for (int r = 0; r < rows; ++r) {
+  for (int r = lane; r < rows; r += 32) {
     s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
     q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane != 0) return;
   const double mean = s / count;
   double var = q / count - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -440,13 +448,20 @@ __global__ void bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partia
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
                                        const float* __restrict__ bn, float* __restrict__ dgamma,
                                        float* __restrict__ dbeta, int accumulate, float* __restrict__ coef) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
-  for (int r = 0; r < rows; ++r) {
+  for (int r = lane; r < rows; r += 32) {
     s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
     q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane != 0) return;
   if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + static_cast<float>(q);
   if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + static_cast<float>(s);
   const double mean = bn[c], invstd = bn[C + c], scale = bn[2 * C + c];
@@ -542,10 +557,14 @@ __global__ void colsum_kernel(const __nv_bfloat16* __restrict__ x, int ld, long 
 // out[c] (+)= sum_r partial[r][c]
 __global__ void reduce_rows_kernel(const float* __restrict__ partial, int rows, int C, float* __restrict__ out,
                                    int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0;
-  for (int r = 0; r < rows; ++r) s += static_cast<double>(partial[static_cast<size_t>(r) * C + c]);
+  for (int r = lane; r < rows; r += 32) s += static_cast<double>(partial[static_cast<size_t>(r) * C + c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane != 0) return;
   out[c] = (accumulate ? out[c] : 0.f) + static_cast<float>(s);
 }
 
@@ -643,7 +662,7 @@ extern "C" int uz_bn_finalize(const float* partial, int rows, int C, long long c
                               float* bn, void* stream) {
   UZ_REQUIRE_DEVICE();
   if (rows < 1 || C < 1 || count < 1) return set_error(UZ_ERR_INVALID, "bn_finalize: bad extents");
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  bn_finalize_kernel<<<(C + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       partial, rows, C, static_cast<double>(count), gamma, beta, eps, momentum, running_mean, running_var, bn);
   UZ_CHECK_LAUNCH("bn_finalize launch");
   return UZ_OK;
@@ -723,7 +742,7 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   else
     bn_bwd_reduce_kernel<false><<<g.grid, g.block, smem, st>>>(a, partial);
   UZ_CHECK_LAUNCH("bn_bwd_reduce launch");
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, C, static_cast<double>(N) * H * W, bn, dgamma,
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, static_cast<double>(N) * H * W, bn, dgamma,
                                                          dbeta, accumulate, coef);
   UZ_CHECK_LAUNCH("bn_bwd_finalize launch");
   float* dbp = dbias ? dbias_partial : nullptr;
@@ -733,7 +752,7 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
     bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp);
   UZ_CHECK_LAUNCH("bn_bwd_apply launch");
   if (dbias) {
-    reduce_rows_kernel<<<(C + 127) / 128, 128, 0, st>>>(dbias_partial, rows, C, dbias, accumulate);
+    reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(dbias_partial, rows, C, dbias, accumulate);
     UZ_CHECK_LAUNCH("bn_bwd dbias launch");
   }
   return UZ_OK;
@@ -755,7 +774,7 @@ extern "C" int uz_colsum(const void* x, int ld, long long npix, int C, float* ou
   colsum_kernel<<<g.grid, g.block, g.block * 8 * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), ld, npix, C,
                                                                       g.cv, g.ppb, static_cast<float*>(workspace));
   UZ_CHECK_LAUNCH("colsum launch");
-  reduce_rows_kernel<<<(C + 127) / 128, 128, 0, st>>>(static_cast<const float*>(workspace), g.grid, C, out, accumulate);
+  reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(static_cast<const float*>(workspace), g.grid, C, out, accumulate);
   UZ_CHECK_LAUNCH("colsum reduce launch");
   return UZ_OK;
 }
