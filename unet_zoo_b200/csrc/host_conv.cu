@@ -318,10 +318,10 @@ extern "C" int uz_device_sm_count(void) {
   if (n < 0) return set_error(UZ_ERR_CUDA, "no CUDA device");
   return n;
 }
-// rows of the per-channel statistics partials: one per (CTA, epilogue warp) of the persistent conv kernels
+// rows of the per-channel statistics partials: one per (CTA, epilogue warp) of the persistent conv kernels (8 warps)
 extern "C" int uz_conv_stats_rows(void) {
   const int n = uz_device_sm_count();
-  return n < 0 ? n : 4 * n;
+  return n < 0 ? n : 8 * n;
 }
 
 namespace uz {
@@ -371,23 +371,34 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.yb = (H + 15) / 16;
   p.m_tiles_real = N * p.xb * p.yb;
   p.num_n_tiles = (cout + bn - 1) / bn;
-  // shared-memory plan
+  // shared-memory plan: [A ring][B ring or resident weights][1-2 staging tiles][barriers + bias]
   const int kMaxSmem = 232448 - 1024;  // 227 KB minus the alignment slack
   const int a_slot = (p.halo_bytes + 1023) & ~1023;
   const int b_item = bn * 128;
-  const int fixed = 2 * 16384 + 512;   // staging + barriers
+  const int kTail = 1536;              // barriers (512) + bias vector (1024)
   const long long b_all = (long long)kblocks * p.num_taps * b_item;
   int cluster = 1;
-  if (p.num_n_tiles == 1 && b_all + 2LL * a_slot + fixed <= kMaxSmem && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
-    p.b_stages = 0;
-    int as = (int)((kMaxSmem - fixed - b_all) / a_slot);
-    p.a_stages = as > 6 ? 6 : as;
-  } else {
+  bool stationary = false;
+  if (p.num_n_tiles == 1 && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
+    // weights resident for the whole launch, provided at least four halo stages still fit (TMA latency cover)
+    for (int nbuf = 2; nbuf >= 1 && !stationary; --nbuf) {
+      const long long left = (long long)kMaxSmem - kTail - nbuf * 16384 - b_all;
+      if (left >= (long long)env_int("UZ_FWD2_MIN_A", 2) * a_slot) {
+        stationary = true;
+        p.stg_bufs = nbuf;
+        p.b_stages = 0;
+        const int as = (int)(left / a_slot);
+        p.a_stages = as > 6 ? 6 : as;
+      }
+    }
+  }
+  if (!stationary) {
     cluster = env_int("UZ_FWD2_CLUSTER", 1);
     if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
     if (bn / cluster < 16) cluster = 1;
-    p.a_stages = kblocks == 1 ? 2 : 3;
-    int bs = (kMaxSmem - fixed - p.a_stages * a_slot) / b_item;
+    p.stg_bufs = bn == 256 ? 1 : 2;
+    p.a_stages = bn == 256 ? 2 : bn == 128 ? 3 : 4;
+    int bs = (kMaxSmem - kTail - p.stg_bufs * 16384 - p.a_stages * a_slot) / b_item;
     p.b_stages = bs > 12 ? 12 : bs;
     if (p.b_stages < 2) return 0;
   }
@@ -398,8 +409,8 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.b_off = p.a_stages * a_slot;
   const long long b_bytes = p.b_stages ? (long long)p.b_stages * b_item : b_all;
   p.stg_off = (int)(p.b_off + b_bytes);
-  p.bar_off = p.stg_off + 2 * 16384;
-  const int smem_bytes = p.bar_off + 512 + 1024;
+  p.bar_off = p.stg_off + p.stg_bufs * 16384;
+  const int smem_bytes = p.bar_off + kTail + 1024;
   int rc = make_weight_map(&p.bmap, w_packed, ctot, p.num_taps, cout, bn / cluster);
   if (rc != UZ_OK) return rc;
   rc = make_act_map(&p.omap, out, cout, out_ld, N, H, W, full, 8, 16, 1);
@@ -485,7 +496,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 
   if (flags & UZ_FLAG_STATS) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * 4 * sms, st);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * 8 * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
   if (mi.num_phases == 1 && mi.oscale == 1) {

@@ -111,10 +111,11 @@ struct alignas(64) Igemm2Params {
   int kblocks;                 // sum of seg_cblocks
   int a_stages, b_stages;      // ring depths; b_stages == 0 -> weights stationary (all kblocks*taps items resident)
   int a_off, b_off, stg_off, bar_off;  // byte offsets from the 1024-aligned smem base
+  int stg_bufs;                // staging tiles for the TMA-store epilogue (1 or 2)
   int cluster;                 // thread-block cluster size (1, 2 or 4): weight tiles are multicast when > 1
   int ncols;                   // valid output columns (Cout)
   const float* bias;
-  float* stats;                // [4*gridDim.x][2][ncols] partial sums (kFlagStats), zeroed by the host
+  float* stats;                // [8*gridDim.x][2][ncols] partial sums (kFlagStats), zeroed by the host
   int flags;
 };
 

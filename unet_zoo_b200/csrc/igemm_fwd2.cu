@@ -10,7 +10,8 @@
 //   * the epilogue writes TMEM -> registers -> swizzled staging tile -> TMA store (or TMA reduce-add when the output
 //     accumulates), and takes the BatchNorm column sums from the staged bf16 tile (conflict-free column reads).
 //
-// Warp roles (224 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2..5 = epilogue, 6 = B producer.
+// Warp roles (384 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2 = B producer, 3 = idle,
+// 4..11 = epilogue (two warps per TMEM lane quarter, each owning 32 of the 64 columns of a chunk).
 #include <string.h>
 
 #include "igemm.cuh"
@@ -18,11 +19,20 @@
 
 namespace uz {
 
-constexpr int kF2Threads = 224;
+constexpr int kF2Threads = 384;
+constexpr int kF2EpiThreads = 256;
 constexpr int kF2StgBytes = 128 * 128;  // one staged 128-pixel x 64-channel bf16 chunk
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
@@ -87,7 +97,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull(s), 1);
-      mbar_init(tempty(s), 4);
+      mbar_init(tempty(s), 8);
     }
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
@@ -129,7 +139,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         }
       }
     }
-  } else if (warp == 6) {
+  } else if (warp == 2) {
     // ------------------------------------------------------------------ B producer: weight tiles
     if (lane == 0) {
       if (!ring) {
@@ -171,9 +181,16 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
+    // The issue loop must stay ahead of the tensor core (64 cycles per MMA at BN = 128): descriptors are kept as
+    // (lo, hi) words, hi is loop invariant, lo advances by plain 32-bit adds (tap row offset, K step of 32 bytes).
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
-      const uint32_t a_sbo = p.halo_w * 128;
+      const uint32_t a_hi = ((static_cast<uint32_t>(p.halo_w * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+      const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      uint32_t tap_lo[9];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) tap_lo[t] = static_cast<uint32_t>(p.tap_row[t]) * 8u;  // rows of 128 B, in 16-B units
+      const int ntaps = p.num_taps;
       int astage = 0, bstage = 0, acc = 0;
       uint32_t aphase = 0, bphase = 0, acc_phase = 0;
       if (!ring) {
@@ -185,34 +202,46 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         uint32_t accumulate = 0;
+        uint32_t b_item = (b_base >> 4) | (1u << 16);   // stationary weights: walks through the resident tiles
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait(afull(astage), aphase);
           tc_fence_after();
-          const uint32_t halo = a_base + astage * a_slot;
-          for (int tap = 0; tap < p.num_taps; ++tap) {
-            uint32_t bsm;
-            if (ring) {
-              mbar_wait(bfull(bstage), bphase);
-              tc_fence_after();
-              bsm = b_base + bstage * kBItem;
-            } else {
-              bsm = b_base + (kb * p.num_taps + tap) * kBItem;
-            }
-            const uint32_t a_tap = halo + p.tap_row[tap] * 128;
+          const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              umma_bf16(d_tmem, umma_smem_desc(a_tap + k * 32, 16, a_sbo), umma_smem_desc(bsm + k * 32, 16, 1024), idesc,
-                        accumulate);
-              accumulate = 1;
-            }
-            if (ring) {
-              if (cs == 1)
-                umma_commit(bempty(bstage));
-              else
-                umma_commit_mc(bempty(bstage), mc_mask);
-              if (++bstage == p.b_stages) {
-                bstage = 0;
-                bphase ^= 1u;
+          for (int tap = 0; tap < 9; ++tap) {
+            if (tap < ntaps) {
+              uint32_t b_lo;
+              if (ring) {
+                mbar_wait(bfull(bstage), bphase);
+                tc_fence_after();
+                b_lo = ((b_base + bstage * kBItem) >> 4) | (1u << 16);
+              } else {
+                b_lo = b_item;
+                b_item += kBItem >> 4;
+              }
+              const uint32_t a_tap = a_lo + tap_lo[tap];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+                    "mov.b64 da, {%1, %2};\n\t"
+                    "mov.b64 db, {%3, %4};\n\t"
+                    "setp.ne.b32 p, %6, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+                    ::"r"(d_tmem), "r"(a_tap + 2u * k), "r"(a_hi), "r"(b_lo + 2u * k), "r"(b_hi), "r"(idesc),
+                      "r"(accumulate)
+                    : "memory");
+                accumulate = 1;
+              }
+              if (ring) {
+                if (cs == 1)
+                  umma_commit(bempty(bstage));
+                else
+                  umma_commit_mc(bempty(bstage), mc_mask);
+                if (++bstage == p.b_stages) {
+                  bstage = 0;
+                  bphase ^= 1u;
+                }
               }
             }
           }
@@ -227,22 +256,30 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         if (acc == 0) acc_phase ^= 1u;
       }
     }
-  } else {
-    // ------------------------------------------------------------------ epilogue warps (2..5)
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue warps (4..11)
+    const int ew = warp - 4;           // 0..7
     const int q = warp & 3;            // TMEM lane quarter of this warp
-    const int et = threadIdx.x - 64;   // 0..127
+    const int hcol = ew >> 2;          // which 32-column half of a 64-column chunk this warp converts
+    const int et = threadIdx.x - 128;  // 0..255
     const int row = q * 32 + lane;     // accumulator row = pixel (y = row >> 3, x = row & 7) of the tile
     const bool do_stats = (p.flags & kFlagStats) != 0;
     const bool do_relu = (p.flags & kFlagRelu) != 0;
     const bool do_acc = (p.flags & kFlagAccumulate) != 0;
+    const int nbuf = p.stg_bufs;
+    const uint32_t bias_s = bars + 512u;  // BN floats (zero beyond ncols / without bias)
     constexpr int kChunks = BN / 64;
     float run_s[kChunks][2], run_q[kChunks][2];
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) run_s[c][0] = run_s[c][1] = run_q[c][0] = run_q[c][1] = 0.f;
     int run_ntile = -1;
+    // column-sum reads: this warp sums rows [ew*16, ew*16+16) of the staged chunk, lane owns columns 2*lane, 2*lane+1
+    uint32_t st_off[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) st_off[j] = ((((lane >> 2) ^ j) << 4) + (lane & 3) * 4) + (ew * 16 + j) * 128;
     auto flush_stats = [&]() {
       if (run_ntile < 0) return;
-      float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 4 + (warp - 2)) * 2 * p.ncols;
+      float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 8 + ew) * 2 * p.ncols;
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
 #pragma unroll
@@ -261,52 +298,61 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     uint32_t it = 0;  // staging buffer toggle
     for (int g = cidx; g < ngroups; g += nclusters) {
       const F2Tile t = f2_decode(p, g * cs + rank);
+      const bool tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
       const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
-      if (do_stats && t.n_tile != run_ntile) {
-        flush_stats();
+      if (t.n_tile != run_ntile) {
+        if (do_stats) flush_stats();
         run_ntile = t.n_tile;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (et < BN) {
+          const int col = t.n_tile * BN + et;
+          st_shared_f32(bias_s + et * 4, (p.bias != nullptr && col < p.ncols) ? __ldg(p.bias + col) : 0.f);
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
       mbar_wait(tfull(acc), acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + hcol * 32;
 #pragma unroll 1
       for (int ch = 0; ch < kChunks; ++ch) {
         const int col0 = t.n_tile * BN + ch * 64;
         if (col0 >= p.ncols) break;  // uniform over the CTA
-        const uint32_t sbuf = stg_base + (it & 1u) * kF2StgBytes;
+        const uint32_t sbuf = stg_base + (nbuf == 2 ? (it & 1u) * kF2StgBytes : 0u);
         ++it;
+        uint32_t v[32];
+        tmem_ld32(t_addr + ch * 64, v);
+        if (nbuf == 1) {
+          if (et == 0) tma_store_wait_read0();  // the single staging tile is free again
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
+        tmem_ld_wait();
+        float f[32];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t v[32];
-          tmem_ld32(t_addr + ch * 64 + h * 32, v);
-          tmem_ld_wait();
-          float f[32];
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b4 = ld_shared_f4(bias_s + (ch * 64 + hcol * 32 + j4 * 4) * 4);
+          f[j4 * 4 + 0] = __uint_as_float(v[j4 * 4 + 0]) + b4.x;
+          f[j4 * 4 + 1] = __uint_as_float(v[j4 * 4 + 1]) + b4.y;
+          f[j4 * 4 + 2] = __uint_as_float(v[j4 * 4 + 2]) + b4.z;
+          f[j4 * 4 + 3] = __uint_as_float(v[j4 * 4 + 3]) + b4.w;
+        }
+        if (do_relu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if (p.bias != nullptr) {
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (!tile_full && !valid) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + h * 32 + j < p.ncols) f[j] += __ldg(p.bias + col0 + h * 32 + j);
-          }
-          if (do_relu) {
+          for (int j = 0; j < 32; ++j) f[j] = 0.f;  // keeps out-of-image rows out of the column sums
+        }
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-          }
-          if (!valid) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = 0.f;  // keeps out-of-image rows out of the column sums
-          }
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const int chunk16 = h * 4 + c;  // 16-byte chunk index inside the 128-byte row
-            st_shared_v4(sbuf + row * 128 + ((chunk16 ^ (row & 7)) << 4), pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]),
-                         pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]), pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]),
-                         pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]));
-          }
+        for (int c = 0; c < 4; ++c) {
+          const int chunk16 = hcol * 4 + c;  // 16-byte chunk index inside the 128-byte row
+          st_shared_v4(sbuf + row * 128 + ((chunk16 ^ (row & 7)) << 4), pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]),
+                       pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]), pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]),
+                       pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]));
         }
         fence_proxy_async_smem();
-        if (et == 0) tma_store_wait_read0();  // the previous store has finished reading the other staging buffer
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (nbuf == 2 && et == 0) tma_store_wait_read0();  // the previous store has left the other buffer
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
           if (do_acc)
             tma_reduce_add_4d(&p.omap, sbuf, col0, t.x0, t.y0, t.n);
@@ -315,12 +361,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
           tma_store_commit();
         }
         if (do_stats) {
-          // lane owns columns 2*lane, 2*lane+1 of the chunk; this warp sums its own 32 rows (bank-conflict free)
           float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-#pragma unroll 8
-          for (int rr = 0; rr < 32; ++rr) {
-            const int r = q * 32 + rr;
-            const uint32_t w = ld_shared_u32(sbuf + r * 128 + (((lane >> 2) ^ (r & 7)) << 4) + (lane & 3) * 4);
+#pragma unroll
+          for (int rr = 0; rr < 16; ++rr) {
+            const uint32_t w = ld_shared_u32(sbuf + st_off[rr & 7] + (rr >> 3) * 1024);
             const float lo = bf16_lo(w), hi = bf16_hi(w);
             s0 += lo;
             s1 += hi;
