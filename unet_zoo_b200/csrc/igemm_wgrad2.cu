@@ -130,14 +130,18 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           tc_fence_after();
           const uint32_t halo = base + stage * kW2StageBytes;
           const uint32_t dz = halo + kW2HaloSlot;
+          const uint32_t halo_lo = umma_desc_lo(halo, 0);
+          const uint32_t dz_lo = umma_desc_lo(dz, 1024);
+          constexpr uint32_t a_hi = umma_desc_hi(kW2HaloW * 128);
+          constexpr uint32_t b_hi = umma_desc_hi(1024);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 16 pixels = image rows 2j, 2j+1 of the chunk
-            const uint64_t bdesc = umma_smem_desc(dz + j * 2048, 1024, 1024);
 #pragma unroll
             for (int b = 0; b < 5; ++b) {
-              const uint64_t adesc =
-                  umma_smem_desc(halo + pair_row[b] * 128 + j * 2 * kW2HaloW * 128, pair_lbo[b], kW2HaloW * 128);
-              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (first && j == 0) ? 0u : 1u);
+              // start row of the tap pair (+ two halo rows per K step), LBO = byte distance to the pair's second tap
+              const uint32_t a_lo = halo_lo + ((pair_row[b] * 128 + j * 2 * kW2HaloW * 128) >> 4) + ((pair_lbo[b] >> 4) << 16);
+              umma_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + ((j * 2048) >> 4), b_hi, idesc,
+                              (first && j == 0) ? 0u : 1u);
             }
           }
           first = false;
