@@ -81,7 +81,7 @@ int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, const float
  *   g  = (dy + route(dpool)) * [relu ? (y > 0) : 1]       route(): first maximum of each 2x2 window (row-major scan)
  *   dz = gamma*invstd * (g - mean(g) - x^ * mean(g*x^)),  dgamma = sum g*x^,  dbeta = sum g,  dbias = sum dz
  * dy and dpool are each optional (not both NULL).  dgamma/dbeta/dbias are fp32 [C] (NULL to skip); `accumulate`
- * adds into them.  Replaces autograd through BatchNorm2d/ReLU/MaxPool2d for the call sites above. */
+ * bit 0 adds into them, bit 1 makes dz accumulate (dz += ..., for tensors with several consumers; not with dbias).  Replaces autograd through BatchNorm2d/ReLU/MaxPool2d for the call sites above. */
 size_t uz_bn_bwd_workspace_bytes(int C);
 int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, const void* dpool, int dpool_ld, int N, int H, int W,
               int C, const float* bn, int relu, void* dz, int dz_ld, float* dgamma, float* dbeta, float* dbias,
@@ -104,6 +104,37 @@ int uz_head_bwd(const void* y, int ld, const float* dlogits, int N, int H, int W
                 void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Additive attention gate (AttentionBlock, attention_unet.py:6-40): the two 1x1 convolutions W_g, W_x run through
+ * uz_conv_igemm(UZ_CONV1X1, UZ_FLAG_STATS) -> zg, zx (bf16 [npix, F], F = f_int <= 256) and uz_bn_finalize -> bn_g,
+ * bn_x ([4][F] = mean, invstd, scale, shift).  Then
+ *  uz_gate_psi_fwd: psi_raw[p] = b_psi + sum_c w_psi[c] * ReLU(BN_g(zg)[p,c] + BN_x(zx)[p,c])   (fp32 [npix])
+ *                   partial[uz_reduce_rows()][2][1] = sum / sum of squares of psi_raw -> uz_bn_finalize(C = 1) -> psi_bn[4]
+ *  uz_gate_apply  : out[p, c] = x[p, c] * sigmoid(psi_raw[p] * psi_bn.scale + psi_bn.shift)       (attention_unet.py:38-40)
+ *  uz_gate_bwd    : from dout = dL/dout:  dx (+)= a * dout;  through sigmoid, BN_psi (dgamma_psi, dbeta_psi), w_psi
+ *                   (dw_psi [F], db_psi [1]) and the ReLU into dr (bf16 [npix, F]) - the common dL/d(g1) = dL/d(x1),
+ *                   to be fed to uz_bn_bwd(zg, dy = dr, relu = 0) and uz_bn_bwd(zx, dy = dr, relu = 0).
+ * Inference: pass running-statistics scale/shift in bn_g, bn_x, psi_bn. */
+int uz_gate_psi_fwd(const void* zg, int zg_ld, const void* zx, int zx_ld, long long npix, int F, const float* bn_g,
+                    const float* bn_x, const float* w_psi, const float* b_psi, float* psi_raw, float* partial,
+                    void* stream);
+int uz_gate_apply(const void* x, int x_ld, const float* psi_raw, const float* psi_bn, long long npix, int C, void* out,
+                  int out_ld, void* stream);
+size_t uz_gate_bwd_workspace_bytes(long long npix, int F);
+int uz_gate_bwd(const void* x, int x_ld, const void* dout, int dout_ld, const float* psi_raw, const float* psi_bn,
+                long long npix, int C, void* dx, int dx_ld, int accumulate_dx, const void* zg, int zg_ld,
+                const void* zx, int zx_ld, int F, const float* bn_g, const float* bn_x, const float* w_psi, void* dr,
+                int dr_ld, float* dw_psi, float* db_psi, float* dgamma_psi, float* dbeta_psi, void* workspace,
+                size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True) (nested_unet.py:33,81-93).
+ *  fwd: x [N,H,W,C] -> out [N,2H,2W,C] written at (out, out_ld) - typically a channel slice of a concat buffer.
+ *  bwd: dx [N,H,W,C] (+)= gather of dout [N,2H,2W,C]; H, W are the LOW-resolution sizes in both calls. */
+int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);
+int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, void* dx, int dx_ld, int accumulate,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Implicit-GEMM convolutions on tcgen05 (forward-type).  `mode` selects the gather / scatter pattern. */
 #define UZ_CONV3X3 0        /* Conv2d k3 s1 p1        common_layers.py:28,31,47,52 ; nested_unet.py:7,9          */
 #define UZ_CONV3X3_DGRAD 1  /* its data gradient (weights packed with the dgrad strides)                         */
@@ -115,6 +146,7 @@ int uz_head_bwd(const void* y, int ld, const float* dlogits, int N, int H, int W
 #define UZ_CONVT2X2 7       /* ConvTranspose2d k2 s2  common_layers.py:104,204                                    */
 #define UZ_CONVT2X2_DGRAD 8
 #define UZ_UP2X_CONV3X3 9   /* nn.Upsample(scale 2, nearest) + Conv2d k3 p1   common_layers.py:70-73              */
+#define UZ_UP2X_CONV3X3_DGRAD 10 /* its data gradient w.r.t. the LOW-res input (weights packed with the dgrad strides) */
 
 #define UZ_FLAG_RELU 1
 #define UZ_FLAG_ACCUMULATE 2 /* out += result (used when a tensor has several consumers in backward) */

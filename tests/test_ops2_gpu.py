@@ -1,0 +1,191 @@
+"""Operator-level parity (GPU) of the operators added for attention_unet / nested_unet / resunet: attention gate,
+bilinear x2 (align_corners), nearest-x2 + conv3x3 (forward and data gradient), pre-activation BatchNorm, residual
+blocks with stride 1 / 2.  References are plain PyTorch fp32 on the same bf16-rounded operands."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from gpu_util import bf16r, get_grad, make_act, new_ctx, relmax, rel_l2, run_tape, set_grad
+from unet_zoo_b200 import _lib as L
+from unet_zoo_b200 import engine as E
+from unet_zoo_b200.models import _graphs as G
+from unet_zoo_b200.models.blocks import AttentionBlock, ResidualConv
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(autouse=True)
+def _exact_fp32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+
+
+def _round_weights(mod):
+    with torch.no_grad():
+        for m in mod.modules():
+            if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+                m.weight.copy_(bf16r(m.weight))
+            if isinstance(m, nn.BatchNorm2d):
+                m.weight.uniform_(0.5, 1.5)
+                m.bias.uniform_(-0.3, 0.3)
+
+
+@pytest.mark.parametrize("N,H,W,C", [(2, 8, 8, 32), (1, 5, 12, 64), (3, 16, 16, 8)])
+def test_bilinear2x_fwd_bwd(N, H, W, C):
+    x = bf16r(torch.randn(N, C, H, W, device=DEV))
+    ctx = new_ctx()
+    xa = make_act(ctx, x, ld=C + 8)
+    cat = ctx.new_buf(N, 2 * H, 2 * W, C + 16)
+    cat.data.fill_(3.0)
+    out = E.Act(cat, 16, C)
+    E.bilinear_up2x(ctx, xa, out)
+    xr = x.clone().requires_grad_(True)
+    ref = F.interpolate(xr, scale_factor=2, mode="bilinear", align_corners=True)
+    torch.cuda.synchronize()
+    assert relmax(out.to_nchw(), ref.detach()) < 1e-2
+    assert bool((cat.data[..., :16] == 3.0).all())
+    dy = bf16r(torch.randn_like(ref))
+    (ref * dy).sum().backward()
+    set_grad(out, dy)
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), xr.grad) < 1e-2
+    # accumulate form: a second consumer's gradient is added on top
+    ctx2 = new_ctx()
+    xb = make_act(ctx2, x)
+    out2 = ctx2.new_act(N, 2 * H, 2 * W, C)
+    E.bilinear_up2x(ctx2, xb, out2)
+    prev = bf16r(torch.randn_like(x))
+    set_grad(xb, prev)
+    set_grad(out2, dy)
+    run_tape(ctx2)
+    assert rel_l2(get_grad(xb), xr.grad + prev) < 1e-2
+
+
+@pytest.mark.parametrize("N,H,W,cin,cout", [(2, 8, 8, 128, 64), (1, 16, 8, 64, 64)])
+def test_up2x_conv_bn_relu_fwd_bwd(N, H, W, cin, cout):
+    """UpConvBlock (common_layers.py:63-80): nearest x2 folded into the conv gather; dgrad w.r.t. the low-res input."""
+    conv = nn.Conv2d(cin, cout, 3, padding=1).to(DEV)
+    bn = nn.BatchNorm2d(cout).to(DEV)
+    _round_weights(nn.Sequential(conv, bn))
+    x = bf16r(torch.randn(N, cin, H, W, device=DEV))
+    ctx = new_ctx(params=[conv.weight, conv.bias, bn.weight, bn.bias])
+    xa = make_act(ctx, x)
+    out = E.conv_bn_act(ctx, [xa], conv, bn, mode=L.UP2X_CONV3X3)
+    xr = x.clone().requires_grad_(True)
+    w = conv.weight.detach().clone().requires_grad_(True)
+    z = F.conv2d(F.interpolate(xr, scale_factor=2, mode="nearest"), w, conv.bias, padding=1)
+    zq = z + (bf16r(z.detach()) - z.detach())
+    y = F.relu(F.batch_norm(zq, None, None, bn.weight, bn.bias, training=True, eps=1e-5))
+    torch.cuda.synchronize()
+    assert tuple(out.to_nchw().shape) == (N, cout, 2 * H, 2 * W)
+    assert relmax(out.to_nchw(), y.detach()) < 1e-2
+    dy = bf16r(torch.randn_like(y) * 0.1)
+    (y * dy).sum().backward()
+    set_grad(out, dy)
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), xr.grad) < 1.5e-2
+    assert rel_l2(ctx.pgrads.view(conv.weight), w.grad) < 1e-2
+
+
+@pytest.mark.parametrize("N,H,W,C", [(2, 16, 16, 64), (1, 8, 8, 512), (2, 8, 16, 128)])
+def test_attention_gate_fwd_bwd(N, H, W, C):
+    att = AttentionBlock(C, C, C // 2).to(DEV)
+    _round_weights(att)
+    ref_att = _RefGate(att)
+    g = bf16r(torch.randn(N, C, H, W, device=DEV))
+    x = bf16r(torch.randn(N, C, H, W, device=DEV))
+    params = list(att.parameters())
+    ctx = new_ctx(params=params)
+    ga, xa = make_act(ctx, g), make_act(ctx, x)
+    cat = ctx.new_buf(N, H, W, 2 * C)
+    out = E.Act(cat, 0, C)
+    E.attention_gate(ctx, ga, xa, att, out)
+    gr, xr = g.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ref = ref_att(gr, xr)
+    torch.cuda.synchronize()
+    assert relmax(out.to_nchw(), ref.detach()) < 1.5e-2
+    dy = bf16r(torch.randn_like(ref) * 0.1)
+    prev = bf16r(torch.randn_like(x) * 0.1)           # x already carries a gradient from its other consumer
+    (ref * dy).sum().backward()
+    set_grad(out, dy)
+    set_grad(xa, prev)
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), xr.grad + prev) < 2e-2
+    assert rel_l2(get_grad(ga), gr.grad) < 3e-2
+    for name, p in att.named_parameters():
+        ours, want = ctx.pgrads.view(p), p.grad
+        if name.endswith("0.bias"):                   # conv bias under train-mode BN: true gradient is zero
+            continue
+        assert rel_l2(ours, want) < 5e-2, name                # zg, zx, dr carry one bf16 rounding each
+
+
+class _RefGate(nn.Module):
+    """AttentionBlock.forward of the reference (attention_unet.py:34-40) over our parameter container."""
+
+    def __init__(self, att):
+        super().__init__()
+        self.att = att
+
+    def forward(self, g, x):
+        a = self.att
+        bn = lambda t, m: F.batch_norm(t, None, None, m.weight, m.bias, training=True, eps=m.eps)
+        g1 = bn(F.conv2d(g, a.w_g[0].weight, a.w_g[0].bias), a.w_g[1])
+        x1 = bn(F.conv2d(x, a.w_x[0].weight, a.w_x[0].bias), a.w_x[1])
+        psi = F.relu(g1 + x1)
+        psi = torch.sigmoid(bn(F.conv2d(psi, a.psi[0].weight, a.psi[0].bias), a.psi[1]))
+        return x * psi
+
+
+@pytest.mark.parametrize("N,H,W,cin,cout,stride", [(2, 16, 16, 64, 128, 2), (2, 16, 16, 128, 64, 1), (1, 32, 16, 64, 64, 2)])
+def test_residual_conv_fwd_bwd(N, H, W, cin, cout, stride):
+    blk = ResidualConv(cin, cout, stride, 1).to(DEV)
+    _round_weights(blk)
+    x = bf16r(torch.randn(N, cin, H, W, device=DEV))
+    ctx = new_ctx(params=list(blk.parameters()))
+    xa = make_act(ctx, x)
+    out = G._residual_conv(ctx, xa, blk)
+    xr = x.clone().requires_grad_(True)
+    bn = lambda t, m: F.batch_norm(t, None, None, m.weight, m.bias, training=True, eps=m.eps)
+    cb, cs = blk.conv_block, blk.conv_skip
+    rq = lambda t: t + (bf16r(t.detach()) - t.detach())      # straight-through bf16 rounding at our storage points:
+    h = rq(F.relu(bn(xr, cb[0])))                            # rounding z before BN+ReLU decides which units the ReLU
+    h = rq(F.conv2d(h, cb[2].weight, None, stride=stride, padding=1))   # mask keeps; without it 0.2 % of the mask flips
+    h = rq(F.relu(bn(h, cb[3])))                             # and the bias-like gradients move by ~5 %
+    h = F.conv2d(h, cb[5].weight, None, padding=1)
+    ref = h + bn(F.conv2d(xr, cs[0].weight, None, stride=stride), cs[1])
+    torch.cuda.synchronize()
+    assert tuple(out.to_nchw().shape) == tuple(ref.shape)
+    assert relmax(out.to_nchw(), ref.detach()) < 2e-2
+    dy = bf16r(torch.randn_like(ref) * 0.1)
+    (ref * dy).sum().backward()
+    set_grad(out, dy)
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), xr.grad) < 3e-2
+    for name, p in blk.named_parameters():
+        assert rel_l2(ctx.pgrads.view(p), p.grad) < 3e-2, name
+
+
+def test_conv_plain_accumulates_and_backpropagates():
+    conv_a = nn.Conv2d(64, 64, 3, padding=1).to(DEV)
+    conv_b = nn.Conv2d(64, 64, 3, padding=1).to(DEV)
+    _round_weights(nn.Sequential(conv_a, conv_b))
+    xa_t = bf16r(torch.randn(2, 64, 16, 16, device=DEV))
+    xb_t = bf16r(torch.randn(2, 64, 16, 16, device=DEV))
+    ctx = new_ctx(params=list(conv_a.parameters()) + list(conv_b.parameters()))
+    xa, xb = make_act(ctx, xa_t), make_act(ctx, xb_t)
+    out = E.conv_plain(ctx, [xa], conv_a)
+    E.conv_plain(ctx, [xb], conv_b, out=out, accumulate=True)
+    ar, br = xa_t.clone().requires_grad_(True), xb_t.clone().requires_grad_(True)
+    ref = conv_a(ar) + conv_b(br)
+    torch.cuda.synchronize()
+    assert relmax(out.to_nchw(), ref.detach()) < 1.5e-2
+    dy = bf16r(torch.randn_like(ref))
+    (ref * dy).sum().backward()
+    set_grad(out, dy)
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), ar.grad) < 1e-2 and rel_l2(get_grad(xb), br.grad) < 1e-2
+    for p in list(conv_a.parameters()) + list(conv_b.parameters()):
+        assert rel_l2(ctx.pgrads.view(p), p.grad) < 5e-3

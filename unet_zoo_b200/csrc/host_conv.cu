@@ -298,6 +298,29 @@ static int build_mode(int mode, int H, int W, int out_h, int out_w, IgemmParams*
         mi->ntaps[ph] = 9;
       }
       break;
+    case UZ_UP2X_CONV3X3_DGRAD: {
+      // input = dZ of the up2x conv (H x W, high res); output = gradient of the LOW-res tensor (H/2 x W/2).
+      // Forward tap (r,s) of output phase (py,px) reads low-res row y' + floor((py+r-1)/2) for output row 2y'+py, so
+      // low-res pixel y collects dZ lattice (py,px) at index y - floor((py+r-1)/2): 36 taps over 4 strided views.
+      if ((H & 1) || (W & 1)) return set_error(UZ_ERR_INVALID, "up2x dgrad needs even dZ size, got %dx%d", H, W);
+      mi->Hm = mi->Ho = H / 2;
+      mi->Wm = mi->Wo = W / 2;
+      mi->num_lat = 4;
+      int i = 0;
+      for (int l = 0; l < 4; ++l) {
+        const int py = l >> 1, px = l & 1;
+        mi->lat[l] = {py, px, 2};
+        for (int r = 0; r < 3; ++r)
+          for (int sx = 0; sx < 3; ++sx) {
+            const int dyr = (py + r - 1 + 2) / 2 - 1;
+            const int dxs = (px + sx - 1 + 2) / 2 - 1;
+            set_tap(0, i++, -dyr, -dxs, r * 3 + sx, l);
+          }
+      }
+      mi->ntaps[0] = 36;
+      mi->btaps = 9;
+      break;
+    }
     default:
       return set_error(UZ_ERR_INVALID, "unknown conv mode %d", mode);
   }

@@ -472,7 +472,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
 
 template <bool POOL>
 __global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
-                                    int dz_ld, float* __restrict__ dbias_partial) {
+                                    int dz_ld, float* __restrict__ dbias_partial, int dz_accumulate) {
   extern __shared__ float red[];
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
@@ -497,6 +497,12 @@ __global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ c
       float o[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], gv[i][j], fmaf(cb[j], zv[i][j], ca[j]));
+      if (dz_accumulate) {  // the destination already holds a gradient from another consumer of the tensor
+        float old[8];
+        unpack8(*reinterpret_cast<const uint4*>(dz + pix[i] * dz_ld + g * 8), old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += old[j];
+      }
       const uint4 w = pack8(o);
       *reinterpret_cast<uint4*>(dz + pix[i] * dz_ld + g * 8) = w;
       if (dbias_partial) {
@@ -566,6 +572,16 @@ __global__ void reduce_rows_kernel(const float* __restrict__ partial, int rows, 
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane != 0) return;
   out[c] = (accumulate ? out[c] : 0.f) + static_cast<float>(s);
+}
+
+cudaError_t launch_bn_bwd_finalize(const float* partial, int rows, int C, double count, const float* bn, float* dgamma,
+                                   float* dbeta, int accumulate, float* coef, cudaStream_t st) {
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, count, bn, dgamma, dbeta, accumulate, coef);
+  return cudaGetLastError();
+}
+cudaError_t launch_reduce_rows(const float* partial, int rows, int C, float* out, int accumulate, cudaStream_t st) {
+  reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, out, accumulate);
+  return cudaGetLastError();
 }
 
 }  // namespace uz
@@ -719,6 +735,9 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
     return set_error(UZ_ERR_WORKSPACE, "bn_bwd: workspace too small (%zu < %zu)", workspace_bytes,
                      uz_bn_bwd_workspace_bytes(C));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int dz_acc = (accumulate & 2) ? 1 : 0;
+  if (dz_acc && dbias) return set_error(UZ_ERR_UNSUPPORTED, "bn_bwd: dz accumulation together with dbias");
+  accumulate &= 1;
   const bool pool = dpool != nullptr;
   const long long items = pool ? static_cast<long long>(N) * (H / 2) * (W / 2) : static_cast<long long>(N) * H * W;
   const Geo g = make_geo(C, items, 4);
@@ -747,9 +766,11 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   UZ_CHECK_LAUNCH("bn_bwd_finalize launch");
   float* dbp = dbias ? dbias_partial : nullptr;
   if (pool)
-    bn_bwd_apply_kernel<true><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp);
+    bn_bwd_apply_kernel<true><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
+                                                             dz_acc);
   else
-    bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp);
+    bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
+                                                              dz_acc);
   UZ_CHECK_LAUNCH("bn_bwd_apply launch");
   if (dbias) {
     reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(dbias_partial, rows, C, dbias, accumulate);

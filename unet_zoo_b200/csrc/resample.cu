@@ -1,0 +1,157 @@
+// Bilinear x2 upsampling with align_corners=True (reference: nn.Upsample(scale_factor=2, mode='bilinear',
+// align_corners=True), nested_unet.py:33, used ten times per forward, nested_unet.py:81-93) - pure HBM bandwidth.
+//
+// Forward reads the low-resolution NHWC bf16 tensor and writes straight into a channel slice of the destination
+// level's concat buffer (pointer + pixel stride), so neither the upsampled tensor nor torch.cat exist as separate
+// passes.  Source index arithmetic follows ATen exactly: scale = (in-1)/(out-1), src = scale*dst (fp32),
+// i0 = (int)src, i1 = i0 + (i0 < in-1), l1 = src - i0, l0 = 1 - l1.
+// Backward is written in gather form (no atomics, deterministic): every low-resolution pixel sums the contributions
+// of the few high-resolution pixels whose (i0, i1) touch it, recomputing their weights with the forward formula.
+#include "pw.cuh"
+
+namespace uz {
+
+__device__ __forceinline__ void bl_src(int dst, float scale, int in, int* i0, int* i1, float* l0, float* l1) {
+  const float src = scale * static_cast<float>(dst);
+  const int a = static_cast<int>(src);
+  *i0 = a;
+  *i1 = a + (a < in - 1 ? 1 : 0);
+  *l1 = src - static_cast<float>(a);
+  *l0 = 1.f - *l1;
+}
+
+__global__ void bilinear2x_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int cv,
+                                      __nv_bfloat16* __restrict__ out, int out_ld, float sy, float sx) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const long long total = static_cast<long long>(N) * Ho * Wo * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long r = i / cv;
+    const int ox = static_cast<int>(r % Wo);
+    r /= Wo;
+    const int oy = static_cast<int>(r % Ho);
+    const int n = static_cast<int>(r / Ho);
+    int y0, y1, x0, x1;
+    float ly0, ly1, lx0, lx1;
+    bl_src(oy, sy, H, &y0, &y1, &ly0, &ly1);
+    bl_src(ox, sx, W, &x0, &x1, &lx0, &lx1);
+    const __nv_bfloat16* base = x + static_cast<long long>(n) * H * W * x_ld + g * 8;
+    float a[8], b[8], c[8], d[8], o[8];
+    pw_unpack8(pw_ldg16(base + (static_cast<long long>(y0) * W + x0) * x_ld), a);
+    pw_unpack8(pw_ldg16(base + (static_cast<long long>(y0) * W + x1) * x_ld), b);
+    pw_unpack8(pw_ldg16(base + (static_cast<long long>(y1) * W + x0) * x_ld), c);
+    pw_unpack8(pw_ldg16(base + (static_cast<long long>(y1) * W + x1) * x_ld), d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = ly0 * (lx0 * a[j] + lx1 * b[j]) + ly1 * (lx0 * c[j] + lx1 * d[j]);
+    *reinterpret_cast<uint4*>(out + ((static_cast<long long>(n) * Ho + oy) * Wo + ox) * out_ld + g * 8) = pw_pack8(o);
+  }
+}
+
+// weight with which high-res index `o` contributes to low-res index `i` along one axis (0 when it does not)
+__device__ __forceinline__ float bl_weight(int o, int i, float scale, int in) {
+  int i0, i1;
+  float l0, l1;
+  bl_src(o, scale, in, &i0, &i1, &l0, &l1);
+  float w = 0.f;
+  if (i0 == i) w += l0;
+  if (i1 == i) w += l1;
+  return w;
+}
+
+constexpr int kBlCand = 8;  // candidate high-res rows / columns per low-res index: [2i-3, 2i+4]
+
+__global__ void bilinear2x_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int cv,
+                                      __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate, float sy, float sx) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long r = i / cv;
+    const int xl = static_cast<int>(r % W);
+    r /= W;
+    const int yl = static_cast<int>(r % H);
+    const int n = static_cast<int>(r / H);
+    float wy[kBlCand], wx[kBlCand];
+#pragma unroll
+    for (int k = 0; k < kBlCand; ++k) {
+      const int oy = 2 * yl - 3 + k, ox = 2 * xl - 3 + k;
+      wy[k] = (oy >= 0 && oy < Ho) ? bl_weight(oy, yl, sy, H) : 0.f;
+      wx[k] = (ox >= 0 && ox < Wo) ? bl_weight(ox, xl, sx, W) : 0.f;
+    }
+    float acc[8];
+    __nv_bfloat16* dst = dx + ((static_cast<long long>(n) * H + yl) * W + xl) * dx_ld + g * 8;
+    if (accumulate) {
+      pw_unpack8(*reinterpret_cast<const uint4*>(dst), acc);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    }
+    const __nv_bfloat16* base = dout + static_cast<long long>(n) * Ho * Wo * dout_ld + g * 8;
+#pragma unroll
+    for (int ky = 0; ky < kBlCand; ++ky) {
+      if (wy[ky] == 0.f) continue;
+      const int oy = 2 * yl - 3 + ky;
+#pragma unroll
+      for (int kx = 0; kx < kBlCand; ++kx) {
+        if (wx[kx] == 0.f) continue;
+        const int ox = 2 * xl - 3 + kx;
+        float f[8];
+        pw_unpack8(pw_ldg16(base + (static_cast<long long>(oy) * Wo + ox) * dout_ld), f);
+        const float w = wy[ky] * wx[kx];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(w, f[j], acc[j]);
+      }
+    }
+    *reinterpret_cast<uint4*>(dst) = pw_pack8(acc);
+  }
+}
+
+static int rs_check(const char* who, const void* p, int C, int ld) {
+  if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) || C < 8 || (C & 7) || (ld & 7) || ld < C)
+    return set_error(UZ_ERR_INVALID, "%s: needs a 16-B aligned pointer, channels (=%d) and ld (=%d) multiples of 8", who, C, ld);
+  return UZ_OK;
+}
+static int rs_grid(long long total) {
+  const int sms = uz_device_sm_count();
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(sms) * 16;
+  if (blocks > cap) blocks = cap;
+  return static_cast<int>(blocks < 1 ? 1 : blocks);
+}
+static float rs_scale(int in) { return in > 0 ? static_cast<float>(in - 1) / static_cast<float>(2 * in - 1) : 0.f; }
+
+}  // namespace uz
+
+using namespace uz;
+
+extern "C" int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
+                                 void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = rs_check("bilinear2x_fwd(x)", x, C, x_ld);
+  if (rc) return rc;
+  if ((rc = rs_check("bilinear2x_fwd(out)", out, C, out_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bilinear2x_fwd: bad size N=%d H=%d W=%d", N, H, W);
+  const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
+  bilinear2x_fwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld, rs_scale(H),
+      rs_scale(W));
+  PW_CHECK_LAUNCH("bilinear2x_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, void* dx, int dx_ld,
+                                 int accumulate, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = rs_check("bilinear2x_bwd(dout)", dout, C, dout_ld);
+  if (rc) return rc;
+  if ((rc = rs_check("bilinear2x_bwd(dx)", dx, C, dx_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bilinear2x_bwd: bad size N=%d H=%d W=%d", N, H, W);
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  bilinear2x_bwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate,
+      rs_scale(H), rs_scale(W));
+  PW_CHECK_LAUNCH("bilinear2x_bwd launch");
+  return UZ_OK;
+}

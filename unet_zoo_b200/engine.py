@@ -21,7 +21,7 @@ _c_void_p = ctypes.c_void_p
 # uz_conv_igemm / uz_conv_wgrad call is bracketed by CUDA events on the launch stream and appended as
 # (kind, algorithmic_flops, start_event, end_event).  None (default) adds no overhead.
 PROFILE: Optional[list] = None
-_TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 9}
+_TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 36}
 
 
 class _Timed:
@@ -111,6 +111,17 @@ class Act:
 
     def to_nchw(self) -> torch.Tensor:  # debugging / tests
         return self.buf.data[..., self.c0:self.c0 + self.C].permute(0, 3, 1, 2).float()
+
+
+class GradAct(Act):
+    """The gradient buffer of an :class:`Act` seen as an activation operand (dL/dy of a convolution without BatchNorm)."""
+
+    __slots__ = ()
+
+    def __init__(self, a: Act):
+        super().__init__(a.buf, a.c0, a.C)
+
+    ptr = property(lambda s: s.buf.grad_buf().data_ptr() + 2 * s.c0)
 
 
 class ParamGrads:
@@ -265,12 +276,12 @@ class Ctx:
         self.launches += 1
 
     def bn_bwd(self, z: Act, dy_ptr, dy_ld, dpool_ptr, dpool_ld, bnbuf: torch.Tensor, relu: bool, dz_ptr: int, dz_ld: int,
-               dgamma, dbeta, dbias):
+               dgamma, dbeta, dbias, dz_accumulate: bool = False):
         need = self.lib.uz_bn_bwd_workspace_bytes(z.C)
         ws = self.workspace(need)
         rc = self.lib.uz_bn_bwd(z.ptr, z.ld, dy_ptr, dy_ld, dpool_ptr, dpool_ld, z.N, z.H, z.W, z.C, bnbuf.data_ptr(),
-                                int(relu), dz_ptr, dz_ld, _ptr(dgamma), _ptr(dbeta), _ptr(dbias), 0, ws.data_ptr(),
-                                ws.numel(), self.stream)
+                                int(relu), dz_ptr, dz_ld, _ptr(dgamma), _ptr(dbeta), _ptr(dbias),
+                                2 if dz_accumulate else 0, ws.data_ptr(), ws.numel(), self.stream)
         L.check(rc, "uz_bn_bwd")
         self.launches += 4 if dbias is not None else 3
 
@@ -403,14 +414,17 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
     if not need_dx or is_stem:
         return
     dgrad_mode = {L.CONV3X3: L.CONV3X3_DGRAD, L.CONV1X1: L.CONV1X1, L.CONV3X3_S2: L.CONV3X3_S2_DGRAD,
-                  L.CONV1X1_S2: L.CONV1X1_S2_DGRAD}.get(mode)
+                  L.CONV1X1_S2: L.CONV1X1_S2_DGRAD, L.UP2X_CONV3X3: L.UP2X_CONV3X3_DGRAD}.get(mode)
     if dgrad_mode is None:
         raise NotImplementedError(f"data gradient for conv mode {mode}")
     wpd = c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
-    T = wpd.shape[1]
     off = 0
     for a in xs:
         for (r0, rc, acc) in a.grad_writes():
+            if mode == L.CONV1X1_S2 and not acc:
+                # the stride-2 1x1 gradient only touches even pixels: clear the slice, then accumulate
+                a.buf.grad_buf()[..., a.c0 + r0:a.c0 + r0 + rc].zero_()
+                acc = True
             w_rows = wpd[off + r0: off + r0 + rc]
             c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, None,
                    L.FLAG_ACCUMULATE if acc else 0)
@@ -482,3 +496,175 @@ def head1x1_backward(c: Ctx, y: Act, conv, dlogits: torch.Tensor):
     L.check(rc, "uz_head_bwd")
     c.launches += 3 * ((K + 3) // 4)
     c.pready(conv.weight, conv.bias)
+
+
+def _running_affine(bn, device) -> torch.Tensor:
+    """[4][C] = {mean, invstd, scale, shift} of an inference-mode BatchNorm (running statistics)."""
+    invstd = torch.rsqrt(bn.running_var.float() + bn.eps)
+    g = bn.weight.float() if bn.weight is not None else torch.ones_like(invstd)
+    b = bn.bias.float() if bn.bias is not None else torch.zeros_like(invstd)
+    scale = g * invstd
+    return torch.stack([bn.running_mean.float(), invstd, scale, b - bn.running_mean.float() * scale]).contiguous()
+
+
+def conv_stats(ctx: Ctx, xs: Sequence[Act], conv, bn, mode: int = L.CONV3X3) -> Tuple[Act, torch.Tensor]:
+    """Training-mode Conv2d + BatchNorm statistics without the apply pass: returns (raw bf16 z, bn[4][C])."""
+    a0 = xs[0]
+    cout = conv.out_channels
+    z = ctx.new_act(a0.N, a0.H, a0.W, cout)
+    wp = ctx.pack(conv.weight, "conv_fwd")
+    stats = ctx.f32(ctx.stats_rows, 2, cout)
+    ctx.conv(mode, xs, wp, cout, conv.bias, z.ptr, z.ld, a0.H, a0.W, stats, L.FLAG_STATS)
+    bnbuf = ctx.f32(4, cout)
+    ctx.bn_finalize(stats, ctx.stats_rows, cout, a0.npix, bn, bnbuf)
+    return z, bnbuf
+
+
+def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True) -> Act:
+    """[ReLU](BatchNorm2d(x)) on an existing activation - the pre-activation half of ResidualConv
+    (common_layers.py:185-186,189-190).  Training: one statistics pass + one apply pass; inference: apply only."""
+    out = ctx.new_act(x.N, x.H, x.W, x.C)
+    if not ctx.training:
+        aff = _running_affine(bn, ctx.device)
+        ctx.bn_apply(x, aff[2].data_ptr(), aff[3].data_ptr(), relu, out)
+        return out
+    rows = ctx.reduce_rows
+    stats = ctx.f32(rows, 2, x.C)
+    L.check(ctx.lib.uz_bn_stats(x.ptr, x.ld, x.npix, x.C, stats.data_ptr(), ctx.stream), "uz_bn_stats")
+    ctx.launches += 1
+    bnbuf = ctx.f32(4, x.C)
+    ctx.bn_finalize(stats, rows, x.C, x.npix, bn, bnbuf)
+    ctx.bn_apply(x, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out)
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: bn_act output has no gradient")
+            for (r0, rc, acc) in x.grad_writes():
+                xs_ = x.slice(r0, rc)
+                sub = bnbuf if rc == x.C else torch.stack([bnbuf[k, r0:r0 + rc] for k in range(4)]).contiguous()
+                dg, db = c.pgrad(bn.weight), c.pgrad(bn.bias)
+                c.bn_bwd(xs_, out.gptr() + 2 * r0, out.ld, None, 0, sub, relu, xs_.gptr(), x.ld,
+                         dg[r0:r0 + rc] if dg is not None else None, db[r0:r0 + rc] if db is not None else None, None,
+                         dz_accumulate=acc)
+            c.pready(bn.weight, bn.bias)
+        ctx.tape.append(backward)
+    return out
+
+
+def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mode: int = L.CONV3X3,
+               accumulate: bool = False, stem: Optional[str] = None, need_dx: bool = True) -> Act:
+    """Conv2d without normalisation or activation, optionally accumulating into `out` (out += conv(x)): the last
+    convolution of ResidualConv.conv_block added onto the skip branch (common_layers.py:191,198) and the two stem
+    convolutions of ResUnet summed in place (resunet.py:29-33,56)."""
+    a0 = xs[0]
+    cout = conv.out_channels
+    if mode in (L.CONV3X3_S2, L.CONV1X1_S2):
+        Ho, Wo = (a0.H - 1) // 2 + 1, (a0.W - 1) // 2 + 1
+    else:
+        Ho, Wo = a0.H, a0.W
+    if out is None:
+        if accumulate:
+            raise ValueError("accumulate needs an existing output")
+        out = ctx.new_act(a0.N, Ho, Wo, cout)
+    is_stem = stem == "im2col"
+    wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", kp=a0.C if is_stem else 0)
+    ctx.conv(L.CONV1X1 if is_stem else mode, xs, wp, cout, conv.bias, out.ptr, out.ld, Ho, Wo, None,
+             L.FLAG_ACCUMULATE if accumulate else 0)
+    if ctx.record:
+        cin_total = sum(a.C for a in xs)
+
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: conv_plain output has no gradient")
+            if conv.bias is not None and conv.bias.requires_grad:
+                c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(conv.bias))
+                c.pready(conv.bias)
+            _conv_backward(c, xs, conv, GradAct(out), mode, is_stem, cin_total, need_dx)
+        ctx.tape.append(backward)
+    return out
+
+
+def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:
+    """nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True) written into a concat slice
+    (nested_unet.py:33,81-93)."""
+    L.check(ctx.lib.uz_bilinear2x_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, ctx.stream), "uz_bilinear2x_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: upsampled tensor has no gradient")
+            for (r0, rc, acc) in x.grad_writes():
+                L.check(c.lib.uz_bilinear2x_bwd(out.gptr() + 2 * r0, out.ld, x.N, x.H, x.W, rc, x.gptr() + 2 * r0, x.ld,
+                                                int(acc), c.stream), "uz_bilinear2x_bwd")
+                c.launches += 1
+        ctx.tape.append(backward)
+    return out
+
+
+def attention_gate(ctx: Ctx, g: Act, x: Act, att, out: Act) -> Act:
+    """AttentionBlock.forward (attention_unet.py:34-40): out = x * sigmoid(BN(w_psi . ReLU(BN(W_g g) + BN(W_x x)))),
+    written into a channel slice of the decoder's concat buffer.  The 1x1 convolutions are tcgen05 GEMMs with the
+    BatchNorm statistics in their epilogue; everything else is three bandwidth kernels (csrc/gate.cu)."""
+    conv_g, bn_g = att.w_g[0], att.w_g[1]
+    conv_x, bn_x = att.w_x[0], att.w_x[1]
+    conv_p, bn_p = att.psi[0], att.psi[1]
+    F = conv_g.out_channels
+    npix = x.npix
+    lib = ctx.lib
+    if ctx.training:
+        zg, bg = conv_stats(ctx, [g], conv_g, bn_g, L.CONV1X1)
+        zx, bx = conv_stats(ctx, [x], conv_x, bn_x, L.CONV1X1)
+    else:
+        zg, zx = ctx.new_act(g.N, g.H, g.W, F), ctx.new_act(x.N, x.H, x.W, F)
+        ctx.conv(L.CONV1X1, [g], ctx.pack(conv_g.weight, "conv_fwd"), F, conv_g.bias, zg.ptr, zg.ld, g.H, g.W)
+        ctx.conv(L.CONV1X1, [x], ctx.pack(conv_x.weight, "conv_fwd"), F, conv_x.bias, zx.ptr, zx.ld, x.H, x.W)
+        bg, bx = _running_affine(bn_g, ctx.device), _running_affine(bn_x, ctx.device)
+    w_psi = conv_p.weight.detach().reshape(-1).contiguous()
+    psi_raw = ctx.f32(npix)
+    partial = ctx.f32(ctx.reduce_rows, 2, 1)
+    L.check(lib.uz_gate_psi_fwd(zg.ptr, zg.ld, zx.ptr, zx.ld, npix, F, bg.data_ptr(), bx.data_ptr(), w_psi.data_ptr(),
+                                _ptr(conv_p.bias), psi_raw.data_ptr(), partial.data_ptr(), ctx.stream), "uz_gate_psi_fwd")
+    ctx.launches += 1
+    if ctx.training:
+        bp = ctx.f32(4, 1)
+        ctx.bn_finalize(partial, ctx.reduce_rows, 1, npix, bn_p, bp)
+    else:
+        bp = _running_affine(bn_p, ctx.device)
+    L.check(lib.uz_gate_apply(x.ptr, x.ld, psi_raw.data_ptr(), bp.data_ptr(), npix, x.C, out.ptr, out.ld, ctx.stream),
+            "uz_gate_apply")
+    ctx.launches += 1
+
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: attention gate output has no gradient")
+            runs = x.grad_writes()
+            if all(acc for _, _, acc in runs):
+                acc_dx = 1
+            elif not any(acc for _, _, acc in runs):
+                acc_dx = 0
+            else:  # partly written: clear the untouched channel runs, then accumulate everywhere
+                for (r0, rc, acc) in runs:
+                    if not acc:
+                        x.buf.grad_buf()[..., x.c0 + r0:x.c0 + r0 + rc].zero_()
+                acc_dx = 1
+            dr = c.new_act(x.N, x.H, x.W, F)
+            dw = c.pgrad(conv_p.weight)
+            dwv = dw.view(-1) if dw is not None else c.f32(F)
+            db = c.pgrad(conv_p.bias) if conv_p.bias is not None else None
+            need = c.lib.uz_gate_bwd_workspace_bytes(npix, F)
+            ws = c.workspace(need)
+            rc_ = c.lib.uz_gate_bwd(x.ptr, x.ld, out.gptr(), out.ld, psi_raw.data_ptr(), bp.data_ptr(), npix, x.C,
+                                    x.gptr(), x.ld, acc_dx, zg.ptr, zg.ld, zx.ptr, zx.ld, F, bg.data_ptr(), bx.data_ptr(),
+                                    w_psi.data_ptr(), dr.ptr, dr.ld, dwv.data_ptr(), _ptr(db), _ptr(c.pgrad(bn_p.weight)),
+                                    _ptr(c.pgrad(bn_p.bias)), ws.data_ptr(), ws.numel(), c.stream)
+            L.check(rc_, "uz_gate_bwd")
+            c.launches += 5
+            c.pready(conv_p.weight, conv_p.bias, bn_p.weight, bn_p.bias)
+            for (z, bnb, conv, bn, src) in ((zg, bg, conv_g, bn_g, g), (zx, bx, conv_x, bn_x, x)):
+                c.bn_bwd(z, dr.ptr, dr.ld, None, 0, bnb, False, z.ptr, z.ld, c.pgrad(bn.weight), c.pgrad(bn.bias),
+                         c.pgrad(conv.bias) if conv.bias is not None else None)
+                c.pready(bn.weight, bn.bias, conv.bias)
+                _conv_backward(c, [src], conv, z, L.CONV1X1, False, src.C, True)
+        ctx.tape.append(backward)
+    return out
