@@ -390,14 +390,32 @@ __device__ __forceinline__ void bwd_item_grad(const BwdArgs& a, long long it, in
   }
 }
 
+// loads of one pixel on the no-pool path (issued for two pixels before any arithmetic: memory-level parallelism)
+struct BwdLoad {
+  uint4 z, d;
+};
+__device__ __forceinline__ void bwd_load(const BwdArgs& a, long long p, int g, BwdLoad& l) {
+  l.z = ldg16(a.z + p * a.z_ld + g * 8);
+  l.d = a.dy ? ldg16(a.dy + p * a.dy_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+}
+__device__ __forceinline__ void bwd_grad(const BwdArgs& a, const BwdLoad& l, const float (&sc)[8], const float (&sh)[8],
+                                         float (&zv)[8], float (&gv)[8]) {
+  unpack8(l.z, zv);
+  unpack8(l.d, gv);
+  if (a.relu) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (!(fmaf(zv[j], sc[j], sh[j]) > 0.f)) gv[j] = 0.f;
+  }
+}
+
+// partial[block][2][C] = { sum g, sum g*z }  (x^ = (z - mean)*invstd is applied in the finalize kernel)
 template <bool POOL>
-__global__ void bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partial) {
+__global__ void __launch_bounds__(256, POOL ? 1 : 3) bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partial) {
   extern __shared__ float red[];
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
-  float mean[8], invstd[8], sc[8], sh[8];
-  load8f(a.bn + g * 8, mean);
-  load8f(a.bn + a.C + g * 8, invstd);
+  float sc[8], sh[8];
   load8f(a.bn + 2 * a.C + g * 8, sc);
   load8f(a.bn + 3 * a.C + g * 8, sh);
   float s[8], q[8];
@@ -405,19 +423,44 @@ __global__ void bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partia
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
                                : static_cast<long long>(a.N) * a.H * a.W;
-  constexpr int NP = POOL ? 4 : 1;
-  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items;
-       it += static_cast<long long>(gridDim.x) * a.ppb) {
-    float zv[NP][8], gv[NP][8];
-    long long pix[NP];
-    bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
+  const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
+  if (POOL) {
+    constexpr int NP = POOL ? 4 : 1;
+    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += stride) {
+      float zv[NP][8], gv[NP][8];
+      long long pix[NP];
+      bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
 #pragma unroll
-    for (int i = 0; i < NP; ++i)
+      for (int i = 0; i < NP; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          s[j] += gv[i][j];
+          q[j] = fmaf(gv[i][j], zv[i][j], q[j]);
+        }
+    }
+  } else {
+    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += 2 * stride) {
+      const long long it1 = it + stride;
+      const bool has1 = it1 < items;
+      BwdLoad l0, l1;
+      bwd_load(a, it, g, l0);
+      if (has1) bwd_load(a, it1, g, l1);
+      float zv[8], gv[8];
+      bwd_grad(a, l0, sc, sh, zv, gv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        s[j] += gv[i][j];
-        q[j] = fmaf(gv[i][j], (zv[i][j] - mean[j]) * invstd[j], q[j]);
+        s[j] += gv[j];
+        q[j] = fmaf(gv[j], zv[j], q[j]);
       }
+      if (has1) {
+        bwd_grad(a, l1, sc, sh, zv, gv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          s[j] += gv[j];
+          q[j] = fmaf(gv[j], zv[j], q[j]);
+        }
+      }
+    }
   }
   float* mine = red + static_cast<size_t>(threadIdx.x) * 16;
 #pragma unroll
@@ -445,9 +488,11 @@ __global__ void bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partia
 }
 
 // partial[rows][2][C] -> dgamma, dbeta (+=) and coef[2][C] = {A, B}
+// q_is_gz: the second partial is sum g*z (not sum g*x^): sum g*x^ = invstd * (sum g*z - mean * sum g), in fp64
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
                                        const float* __restrict__ bn, float* __restrict__ dgamma,
-                                       float* __restrict__ dbeta, int accumulate, float* __restrict__ coef) {
+                                       float* __restrict__ dbeta, int accumulate, float* __restrict__ coef, int q_is_gz,
+                                       float* __restrict__ dbias) {
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= C) return;
@@ -462,18 +507,22 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
     q += __shfl_xor_sync(0xffffffffu, q, o);
   }
   if (lane != 0) return;
+  const double mean = bn[c], invstd = bn[C + c], scale = bn[2 * C + c];
+  if (q_is_gz) q = invstd * (q - mean * s);
   if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + static_cast<float>(q);
   if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + static_cast<float>(s);
-  const double mean = bn[c], invstd = bn[C + c], scale = bn[2 * C + c];
   const double c1 = s / count, c2 = q / count;
-  coef[c] = static_cast<float>(-scale * c1 + scale * c2 * invstd * mean);
-  coef[C + c] = static_cast<float>(-scale * c2 * invstd);
+  const double ca = -scale * c1 + scale * c2 * invstd * mean, cb = -scale * c2 * invstd;
+  coef[c] = static_cast<float>(ca);
+  coef[C + c] = static_cast<float>(cb);
+  // gradient of a conv bias in front of a train-mode BatchNorm = sum dz = scale*sum g + n*A + B*sum z, which is
+  // identically zero (sum z = n*mean); evaluated here in fp64 instead of summing the bf16-rounded dz tensor
+  if (dbias) dbias[c] = (accumulate ? dbias[c] : 0.f) + static_cast<float>(scale * s + count * ca + cb * count * mean);
 }
 
 template <bool POOL>
-__global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
+__global__ void __launch_bounds__(256, POOL ? 1 : 3) bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
                                     int dz_ld, float* __restrict__ dbias_partial, int dz_accumulate) {
-  extern __shared__ float red[];
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
   float sc[8], sh[8], ca[8], cb[8];
@@ -481,19 +530,32 @@ __global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ c
   load8f(a.bn + 3 * a.C + g * 8, sh);
   load8f(coef + g * 8, ca);
   load8f(coef + a.C + g * 8, cb);
-  float s[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = 0.f;
   const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
                                : static_cast<long long>(a.N) * a.H * a.W;
-  constexpr int NP = POOL ? 4 : 1;
-  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items;
-       it += static_cast<long long>(gridDim.x) * a.ppb) {
+  constexpr int NP = POOL ? 4 : 2;
+  const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
+  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += (POOL ? 1 : 2) * stride) {
     float zv[NP][8], gv[NP][8];
     long long pix[NP];
-    bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
+    int np = NP;
+    if (POOL) {
+      float (&zp)[POOL ? 4 : 1][8] = reinterpret_cast<float (&)[POOL ? 4 : 1][8]>(zv);
+      float (&gp)[POOL ? 4 : 1][8] = reinterpret_cast<float (&)[POOL ? 4 : 1][8]>(gv);
+      long long (&pp)[POOL ? 4 : 1] = reinterpret_cast<long long (&)[POOL ? 4 : 1]>(pix);
+      bwd_item_grad<POOL>(a, it, g, sc, sh, zp, gp, pp);
+    } else {
+      pix[0] = it;
+      pix[1] = it + stride;
+      if (pix[1] >= items) np = 1;
+      BwdLoad l0, l1;
+      bwd_load(a, pix[0], g, l0);
+      if (np == 2) bwd_load(a, pix[1], g, l1);
+      bwd_grad(a, l0, sc, sh, zv[0], gv[0]);
+      if (np == 2) bwd_grad(a, l1, sc, sh, zv[1], gv[1]);
+    }
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
+      if (i >= np) break;
       float o[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], gv[i][j], fmaf(cb[j], zv[i][j], ca[j]));
@@ -505,26 +567,6 @@ __global__ void bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ c
       }
       const uint4 w = pack8(o);
       *reinterpret_cast<uint4*>(dz + pix[i] * dz_ld + g * 8) = w;
-      if (dbias_partial) {
-        unpack8(w, o);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] += o[j];
-      }
-    }
-  }
-  if (dbias_partial) {
-    float* mine = red + static_cast<size_t>(threadIdx.x) * 8;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) mine[j] = s[j];
-    __syncthreads();
-    if (pl == 0) {
-      for (int r = 1; r < a.ppb; ++r) {
-        const float* o = red + (static_cast<size_t>(r) * a.cv + g) * 8;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] += o[j];
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) dbias_partial[static_cast<size_t>(blockIdx.x) * a.C + g * 8 + j] = s[j];
     }
   }
 }
@@ -576,7 +618,7 @@ __global__ void reduce_rows_kernel(const float* __restrict__ partial, int rows, 
 
 cudaError_t launch_bn_bwd_finalize(const float* partial, int rows, int C, double count, const float* bn, float* dgamma,
                                    float* dbeta, int accumulate, float* coef, cudaStream_t st) {
-  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, count, bn, dgamma, dbeta, accumulate, coef);
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, count, bn, dgamma, dbeta, accumulate, coef, 0, nullptr);
   return cudaGetLastError();
 }
 cudaError_t launch_reduce_rows(const float* partial, int rows, int C, float* out, int accumulate, cudaStream_t st) {
@@ -736,7 +778,6 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
                      uz_bn_bwd_workspace_bytes(C));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int dz_acc = (accumulate & 2) ? 1 : 0;
-  if (dz_acc && dbias) return set_error(UZ_ERR_UNSUPPORTED, "bn_bwd: dz accumulation together with dbias");
   accumulate &= 1;
   const bool pool = dpool != nullptr;
   const long long items = pool ? static_cast<long long>(N) * (H / 2) * (W / 2) : static_cast<long long>(N) * H * W;
@@ -762,9 +803,9 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
     bn_bwd_reduce_kernel<false><<<g.grid, g.block, smem, st>>>(a, partial);
   UZ_CHECK_LAUNCH("bn_bwd_reduce launch");
   bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, static_cast<double>(N) * H * W, bn, dgamma,
-                                                         dbeta, accumulate, coef);
+                                                         dbeta, accumulate, coef, 1, dbias);
   UZ_CHECK_LAUNCH("bn_bwd_finalize launch");
-  float* dbp = dbias ? dbias_partial : nullptr;
+  float* dbp = nullptr;  // the bias gradient is produced analytically by the finalize kernel
   if (pool)
     bn_bwd_apply_kernel<true><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
                                                              dz_acc);
@@ -772,10 +813,7 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
     bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
                                                               dz_acc);
   UZ_CHECK_LAUNCH("bn_bwd_apply launch");
-  if (dbias) {
-    reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(dbias_partial, rows, C, dbias, accumulate);
-    UZ_CHECK_LAUNCH("bn_bwd dbias launch");
-  }
+  (void)dbias_partial;
   return UZ_OK;
 }
 
