@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
 
   if (warp == 0) {
     // ------------------------------------------------------------------ A producer: one halo box per (segment, cblock)
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int g = cidx; g < ngroups; g += nclusters) {
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     }
   } else if (warp == 2) {
     // ------------------------------------------------------------------ B producer: weight tiles
-    if (lane == 0) {
+    if (elect_one()) {
       if (!ring) {
         // stationary: every (cblock, tap) tile is loaded once and stays for the whole launch (num_n_tiles == 1)
         mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.kblocks * p.num_taps) * kBItem);
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     // ------------------------------------------------------------------ MMA issuer (one thread)
     // The issue loop must stay ahead of the tensor core (64 cycles per MMA at BN = 128): descriptors are kept as
     // (lo, hi) words, hi is loop invariant, lo advances by plain 32-bit adds (tap row offset, K step of 32 bytes).
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
       const uint32_t a_hi = ((static_cast<uint32_t>(p.halo_w * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
       const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);

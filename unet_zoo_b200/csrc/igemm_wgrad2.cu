@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);  // both operands MN-major
       // tap pairs stacked along M: {first tap row offset (in halo pixels), byte distance to the second tap}
       //   taps are (dy, dx) in {-1,0,1}^2 with tap index (dy+1)*3 + (dx+1); halo row of tap = (dy+1)*10 + (dx+1)
