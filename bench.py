@@ -204,9 +204,11 @@ def main():
         sync()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        t0 = time.perf_counter()
         for _ in range(k):
             fn()
         e1.record()
+        timed.host_ms = (time.perf_counter() - t0) * 1000.0 / k   # host time to ENQUEUE one step (launch-bound check)
         sync()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
         if world > 1:
@@ -219,6 +221,7 @@ def main():
     if sampler:
         sampler.start()
     ms = timed(lambda: step(x_d, m_d), args.steps)
+    host_ms = timed.host_ms
     base = model.module if hasattr(model, "module") else model
     launches = (base._last_launches + base._last_launches_bwd) * args.steps
 
@@ -267,7 +270,7 @@ def main():
                    "parallelism": f"dp{world}", "l2": "inputs larger than L2 (multi-GB activations per step)"},
         "e2e": {"value": imgs / (ms_e2e / 1000.0), "unit": "images/sec",
                 "h2d_bytes_per_step": x_h.numel() * 4 + m_h.numel() * 4, "d2h_bytes_per_step": 4},
-        "gpu_launches": launches, "roofline": roof, "clocks": clocks,
+        "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms, "roofline": roof, "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
         rate, cores = cpu_train_step_rate(args.model, S, 3, 1)

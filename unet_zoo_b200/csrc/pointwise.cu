@@ -411,7 +411,7 @@ __device__ __forceinline__ void bwd_grad(const BwdArgs& a, const BwdLoad& l, con
 
 // partial[block][2][C] = { sum g, sum g*z }  (x^ = (z - mean)*invstd is applied in the finalize kernel)
 template <bool POOL>
-__global__ void __launch_bounds__(256, POOL ? 1 : 3) bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partial) {
+__global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_reduce_kernel(const BwdArgs a, float* __restrict__ partial) {
   extern __shared__ float red[];
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
@@ -521,7 +521,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
 }
 
 template <bool POOL>
-__global__ void __launch_bounds__(256, POOL ? 1 : 3) bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
+__global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
                                     int dz_ld, float* __restrict__ dbias_partial, int dz_accumulate) {
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
@@ -755,6 +755,19 @@ extern "C" int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, 
   return UZ_OK;
 }
 
+// grid of a persistent grid-stride kernel: exactly the number of blocks that are resident at once (no partial second
+// wave at reduced occupancy), capped by the number of partial-sum rows the workspace holds
+template <typename K>
+static int resident_grid(K kernel, int block, size_t smem, long long need, int cap_per_sm) {
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (per_sm > cap_per_sm) per_sm = cap_per_sm;
+  int sms = sm_count();
+  if (sms < 1) sms = 148;
+  const long long cap = static_cast<long long>(sms) * per_sm;
+  return static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
+}
+
 extern "C" size_t uz_bn_bwd_workspace_bytes(int C) {
   const int rows = uz_reduce_rows();
   if (rows < 0) return 0;
@@ -781,8 +794,14 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   accumulate &= 1;
   const bool pool = dpool != nullptr;
   const long long items = pool ? static_cast<long long>(N) * (H / 2) * (W / 2) : static_cast<long long>(N) * H * W;
-  const Geo g = make_geo(C, items, 4);
-  const int rows = g.grid;
+  Geo g = make_geo(C, items, 4);
+  const size_t smem = static_cast<size_t>(g.block) * 16 * sizeof(float);
+  const long long need = (items + g.ppb - 1) / g.ppb;
+  const int grid_r = pool ? resident_grid(bn_bwd_reduce_kernel<true>, g.block, smem, need, 4)
+                          : resident_grid(bn_bwd_reduce_kernel<false>, g.block, smem, need, 4);
+  const int grid_a = pool ? resident_grid(bn_bwd_apply_kernel<true>, g.block, 0, need, 4)
+                          : resident_grid(bn_bwd_apply_kernel<false>, g.block, 0, need, 4);
+  const int rows = grid_r;
   float* partial = static_cast<float*>(workspace);
   float* dbias_partial = partial + static_cast<size_t>(uz_reduce_rows()) * 2 * C;
   float* coef = dbias_partial + static_cast<size_t>(uz_reduce_rows()) * C;
@@ -796,21 +815,20 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   a.N = N; a.H = H; a.W = W; a.C = C; a.cv = g.cv; a.ppb = g.ppb;
   a.bn = bn;
   a.relu = relu;
-  const size_t smem = static_cast<size_t>(g.block) * 16 * sizeof(float);
   if (pool)
-    bn_bwd_reduce_kernel<true><<<g.grid, g.block, smem, st>>>(a, partial);
+    bn_bwd_reduce_kernel<true><<<grid_r, g.block, smem, st>>>(a, partial);
   else
-    bn_bwd_reduce_kernel<false><<<g.grid, g.block, smem, st>>>(a, partial);
+    bn_bwd_reduce_kernel<false><<<grid_r, g.block, smem, st>>>(a, partial);
   UZ_CHECK_LAUNCH("bn_bwd_reduce launch");
   bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, static_cast<double>(N) * H * W, bn, dgamma,
                                                          dbeta, accumulate, coef, 1, dbias);
   UZ_CHECK_LAUNCH("bn_bwd_finalize launch");
   float* dbp = nullptr;  // the bias gradient is produced analytically by the finalize kernel
   if (pool)
-    bn_bwd_apply_kernel<true><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
+    bn_bwd_apply_kernel<true><<<grid_a, g.block, 0, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
                                                              dz_acc);
   else
-    bn_bwd_apply_kernel<false><<<g.grid, g.block, smem, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
+    bn_bwd_apply_kernel<false><<<grid_a, g.block, 0, st>>>(a, coef, static_cast<__nv_bfloat16*>(dz), dz_ld, dbp,
                                                               dz_acc);
   UZ_CHECK_LAUNCH("bn_bwd_apply launch");
   (void)dbias_partial;
