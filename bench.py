@@ -23,7 +23,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-UNET_FWD_BWD_GFLOP_PER_IMG_512 = 1155.11   # conv + transposed-conv FLOPs (2*MAC), SURVEY.md section 6 / 8(d)
+# conv + transposed-conv FLOPs (2*MAC) of one fwd+bwd per image at 512x512, SURVEY.md section 6 / 8(d)
+FWD_BWD_GFLOP_PER_IMG_512 = {"unet": 1155.11, "attention_unet": 1593.29, "nested_unet": 827.20, "resunet": 931.44}
+UNET_FWD_BWD_GFLOP_PER_IMG_512 = FWD_BWD_GFLOP_PER_IMG_512["unet"]
 
 
 def parse():
@@ -36,6 +38,7 @@ def parse():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--model", default="unet")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="issue the step eagerly instead of replaying one CUDA graph")
     return ap.parse_args()
 
 
@@ -176,7 +179,8 @@ def main():
     if world > 1:
         model = P.DataParallel(model)          # bucketed NCCL all-reduce overlapped with backward
     params = [p for p in model.parameters() if p.requires_grad]
-    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True)
+    use_graph = world == 1 and not args.no_graph
+    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True, capturable=use_graph)
     crit = torch.nn.BCEWithLogitsLoss()
 
     B, S = args.batch, args.size
@@ -186,7 +190,7 @@ def main():
     m_h = (torch.rand(B, 1, S, S, generator=gm) > 0.5).float().pin_memory()
     x_d, m_d = x_h.to(dev), m_h.to(dev)
 
-    def step(x, m):
+    def eager_step(x, m):
         opt.zero_grad(set_to_none=True)
         out = model(x)
         loss = crit(out, m)
@@ -215,6 +219,15 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
+    step, graph_note = eager_step, "eager"
+    if use_graph:
+        from unet_zoo_b200.train_step import GraphedTrainStep
+        try:
+            step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=1.0, params=params)
+            graph_note = "one CUDA graph per step (unet_zoo_b200.train_step.GraphedTrainStep)"
+        except Exception as e:   # report, never hide: the JSON line says which mode was measured
+            graph_note = f"eager (graph capture failed: {type(e).__name__}: {e})"[:300]
+            torch.cuda.synchronize()
     for _ in range(max(args.warmup, 3)):
         step(x_d, m_d)
     sampler = ClockSampler(local) if rank == 0 else None
@@ -252,7 +265,7 @@ def main():
 
     # roofline leg: per-launch CUDA-event timing of the tensor-core kernels during one more step
     E.PROFILE = []
-    step(x_d, m_d)
+    eager_step(x_d, m_d)
     torch.cuda.synchronize()
     agg = {}
     for kind, flops, a, b in E.PROFILE:
@@ -277,14 +290,14 @@ def main():
                 "launches": n, "avg_launch_ms": t / n,
                 "families": {k: {"ms": v[0], "tflops": v[1] / (v[0] / 1000.0) / 1e12, "launches": v[2]}
                              for k, v in agg.items()},
-                "step_tflops": value / world * UNET_FWD_BWD_GFLOP_PER_IMG_512 * (S / 512.0) ** 2 / 1000.0}
+                "step_tflops": value / world * FWD_BWD_GFLOP_PER_IMG_512[args.model] * (S / 512.0) ** 2 / 1000.0}
     line = {
-        "metric": "images/sec UNet 512^2 bf16 train step", "value": value, "unit": "images/sec", "n_gpus": world,
+        "metric": "images/sec UNet 512^2 bf16 train step" if args.model == "unet" else f"images/sec {args.model} bf16 train step", "value": value, "unit": "images/sec", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": f"{args.model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step "
                                "(BASELINE.json configs[1])", "global_batch": B * world,
-                   "parallelism": f"dp{world}", "l2": "inputs larger than L2 (multi-GB activations per step)"},
+                   "parallelism": f"dp{world}", "launch": graph_note, "l2": "inputs larger than L2 (multi-GB activations per step)"},
         "e2e": {"value": imgs / (ms_e2e / 1000.0), "unit": "images/sec",
                 "h2d_bytes_per_step": x_h.numel() * 4 + m_h.numel() * 4, "d2h_bytes_per_step": 4},
         "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms, "roofline": roof, "clocks": clocks,

@@ -130,3 +130,41 @@ def test_unet_module_contract():
         l2 = out.sum()
         l2.backward(retain_graph=True)
         l2.backward()
+
+
+def test_graphed_train_step_matches_eager_steps():
+    """GraphedTrainStep replays exactly the kernels of the eager step: same losses, same parameters after 3 steps."""
+    from unet_zoo_b200.train_step import GraphedTrainStep
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    x, m = x.cuda(), m.cuda()
+    crit = torch.nn.BCEWithLogitsLoss()
+    results = []
+    for graphed in (False, True):
+        model = seeded_model("unet").cuda().train()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=1e-5, fused=True, capturable=True)
+        losses = []
+        if graphed:
+            sd0 = copy.deepcopy(model.state_dict())
+            step = GraphedTrainStep(model, crit, opt, x, m, max_norm=1.0, warmup=1)
+            model.load_state_dict(sd0)                       # undo the warm-up / capture updates
+            opt.state.clear() if False else None
+            for st in opt.state.values():                    # reset AdamW moments and step counters in place
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+            for _ in range(3):
+                losses.append(float(step(x, m)))
+        else:
+            for _ in range(3):
+                opt.zero_grad(set_to_none=True)
+                loss = crit(model(x), m)
+                loss.backward()
+                torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+                opt.step()
+                losses.append(float(loss))
+        results.append((losses, {k: v.detach().clone() for k, v in model.state_dict().items()}))
+    (l0, s0), (l1, s1) = results
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
+    for k in s0:
+        if s0[k].dtype.is_floating_point:
+            assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k

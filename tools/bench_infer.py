@@ -1,0 +1,61 @@
+"""BASELINE config #5: `resunet` (or any hot-path model) inference sweep over batch x resolution on one GPU.
+
+    python tools/bench_infer.py [--model resunet] [--sizes 256,384,512,768,1024] [--batches 1,2,4,8,16,32,64]
+
+Eval-mode forward (BatchNorm folded / running statistics), inputs resident on the device, CUDA-event timing of `iters`
+forwards after 3 warm-ups.  Prints one JSON line per (batch, size): images/s, ms, achieved conv TFLOP/s (algorithmic
+forward FLOPs of SURVEY.md section 6, scaled by H*W/512^2) and its fraction of the measured sustained bf16 peak.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+FWD_GFLOP_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="resunet")
+    ap.add_argument("--sizes", default="256,384,512,768,1024")
+    ap.add_argument("--batches", default="1,2,4,8,16,32,64")
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--max-pixels", type=float, default=64 * 512 * 512, help="skip (batch, size) above this many pixels")
+    a = ap.parse_args()
+    import torch
+    import unet_zoo_b200
+    try:
+        peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
+    except Exception:
+        peak = 1400.0
+    torch.manual_seed(0)
+    model = unet_zoo_b200.create_model(a.model).cuda().eval()
+    for s in [int(v) for v in a.sizes.split(",")]:
+        for b in [int(v) for v in a.batches.split(",")]:
+            if b * s * s > a.max_pixels:
+                continue
+            x = torch.randn(b, 3, s, s, device="cuda")
+            with torch.no_grad():
+                for _ in range(3):
+                    model(x)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(a.iters):
+                    model(x)
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / a.iters
+            tf = b * FWD_GFLOP_512[a.model] * (s / 512.0) ** 2 / ms      # GFLOP / ms = TFLOP/s
+            print(json.dumps({"model": a.model, "mode": "inference", "batch": b, "size": s, "ms": round(ms, 3),
+                              "images_per_sec": round(b / ms * 1000.0, 1), "conv_tflops": round(tf, 1),
+                              "frac_of_sustained_bf16_peak": round(tf / peak, 3),
+                              "launches": model._last_launches}), flush=True)
+            del x
+            torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,62 @@
+"""The reference's training-step body captured into ONE CUDA graph.
+
+``training_loop.py:112-121`` of the reference runs, per batch: ``zero_grad -> forward -> criterion -> backward ->
+clip_grad_norm_(1.0) -> optimizer.step()`` as ~300 separate launches issued from Python.  On a B200 the whole step is
+~50 ms of GPU work, so launch latency and host jitter between the many small kernels (BatchNorm finalizes, weight
+packing, reductions) are visible.  :class:`GraphedTrainStep` records the step once (every kernel of the C-ABI library
+is stream-ordered and allocation-free, the executor's buffers come from the graph's private memory pool) and replays
+it with a single ``cudaGraphLaunch`` per batch: no tracing compiler, the same kernels in the same order.
+
+Constraints: fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
+capturable=True)``); the learning-rate schedule, if any, must live in a device tensor.
+"""
+from typing import Callable, Iterable, Optional
+
+import torch
+
+
+class GraphedTrainStep:
+    def __init__(self, model: torch.nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
+                 example_x: torch.Tensor, example_target: torch.Tensor, max_norm: Optional[float] = 1.0,
+                 params: Optional[Iterable[torch.nn.Parameter]] = None, warmup: int = 3):
+        if not example_x.is_cuda:
+            raise RuntimeError("GraphedTrainStep needs CUDA tensors (there is no CPU path)")
+        self.model, self.criterion, self.optimizer, self.max_norm = model, criterion, optimizer, max_norm
+        self.params = [p for p in (params if params is not None else model.parameters()) if p.requires_grad]
+        self.x = example_x.clone()
+        self.target = example_target.clone()
+        self.loss: Optional[torch.Tensor] = None
+        self.out = None
+        dev = example_x.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                      # warm-up off the capture: lazy initialisation, autotuning
+            for _ in range(max(1, warmup)):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+
+    def _body(self):
+        self.optimizer.zero_grad(set_to_none=True)
+        self.out = self.model(self.x)
+        outs = self.out if isinstance(self.out, (list, tuple)) else [self.out]
+        loss = self.criterion(outs[0], self.target)
+        for o in outs[1:]:                                 # deep supervision: the reference sums the per-head losses
+            loss = loss + self.criterion(o, self.target)
+        loss.backward()
+        if self.max_norm is not None:
+            torch.nn.utils.clip_grad_norm_(self.params, self.max_norm)
+        self.optimizer.step()
+        self.loss = loss.detach()
+
+    def __call__(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """Run one training step on (x, target); returns the (device) loss tensor of this step."""
+        if x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x, non_blocking=True)
+        if target.data_ptr() != self.target.data_ptr():
+            self.target.copy_(target, non_blocking=True)
+        self.graph.replay()
+        return self.loss
