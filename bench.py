@@ -282,11 +282,17 @@ def main():
     value = imgs / (ms / 1000.0)
     top = max(agg, key=lambda k: agg[k][0]) if agg else None
     roof = None
+    traffic = None
+    try:   # DRAM bytes per launch of the family, from the committed ncu capture (profiles/r01_traffic.json)
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            traffic = json.load(f)[top]["dram_bytes_per_launch"] if args.model == "unet" and B == 32 and S == 512 else None
+    except Exception:
+        traffic = None
     if top:
         t, f, n = agg[top]
         ach = f / (t / 1000.0) / 1e12
         roof = {"kernel": top, "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
-                "frac": ach / pk["tflops"], "traffic": None, "peak_source": pk["src"] + " (sustained bf16)",
+                "frac": ach / pk["tflops"], "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)",
                 "launches": n, "avg_launch_ms": t / n,
                 "families": {k: {"ms": v[0], "tflops": v[1] / (v[0] / 1000.0) / 1e12, "launches": v[2]}
                              for k, v in agg.items()},
