@@ -360,11 +360,22 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
                     float* stats, int flags, int sms, cudaStream_t st) {
   static const int disabled = env_int("UZ_DISABLE_FWD2", 0);
   if (disabled) return 0;
-  if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1)) return 0;
+  if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1 || mode == UZ_CONVT2X2 ||
+        mode == UZ_CONVT2X2_DGRAD))
+    return 0;
+  // ConvTranspose2d k2s2 forward = four 1x1 GEMMs (one per output phase) stored through strided output views;
+  // its data gradient = one 1x1 GEMM whose K runs over the four strided views of dY (K = 4*Cout).
+  const bool convt = mode == UZ_CONVT2X2, convt_d = mode == UZ_CONVT2X2_DGRAD;
+  if (convt_d) {
+    if ((H & 1) || (W & 1) || nseg != 1) return 0;
+    H /= 2;
+    W /= 2;  // tile space = the low-resolution gradient
+  }
   if (H < 16 || W < 8 || nseg > kMaxSegs) return 0;
+  if (convt && (cout % 64) != 0) return 0;
   Igemm2Params p;
   memset(&p, 0, sizeof(p));
-  const int pad = mode == UZ_CONV1X1 ? 0 : 1;
+  const int pad = (mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD) ? 0 + 1 : 0;
   p.pad = pad;
   p.halo_w = 8 + 2 * pad;
   p.halo_bytes = p.halo_w * (16 + 2 * pad) * 128;
@@ -379,13 +390,25 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const int bn = cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
   int ctot = 0, kblocks = 0;
   const Lattice full = {0, 0, 1};
-  for (int s = 0; s < nseg; ++s) {
-    p.seg_cblocks[s] = (seg_c[s] + 63) / 64;
-    p.seg_k0[s] = ctot;
-    ctot += seg_c[s];
-    kblocks += p.seg_cblocks[s];
-    int rc = make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
-    if (rc != UZ_OK) return rc;
+  if (convt_d) {
+    for (int l = 0; l < 4; ++l) {
+      p.seg_cblocks[l] = (seg_c[0] + 63) / 64;
+      p.seg_k0[l] = ctot;
+      ctot += seg_c[0];
+      kblocks += p.seg_cblocks[l];
+      int rc = make_act_map(&p.amap[l], seg_ptr[0], seg_c[0], seg_ld[0], N, 2 * H, 2 * W, Lattice{l >> 1, l & 1, 2}, 8, 16, 1);
+      if (rc != UZ_OK) return rc;
+    }
+    nseg = 4;
+  } else {
+    for (int s = 0; s < nseg; ++s) {
+      p.seg_cblocks[s] = (seg_c[s] + 63) / 64;
+      p.seg_k0[s] = ctot;
+      ctot += seg_c[s];
+      kblocks += p.seg_cblocks[s];
+      int rc = make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
+      if (rc != UZ_OK) return rc;
+    }
   }
   p.num_segs = nseg;
   p.kblocks = kblocks;
@@ -394,6 +417,10 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.yb = (H + 15) / 16;
   p.m_tiles_real = N * p.xb * p.yb;
   p.num_n_tiles = (cout + bn - 1) / bn;
+  if (convt) {
+    p.nt_per_phase = p.num_n_tiles;
+    p.num_n_tiles *= 4;
+  }
   // shared-memory plan: [A ring][B ring or resident weights][1-2 staging tiles][barriers + bias]
   const int kMaxSmem = 232448 - 1024;  // 227 KB minus the alignment slack
   const int a_slot = (p.halo_bytes + 1023) & ~1023;
@@ -434,9 +461,16 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.stg_off = (int)(p.b_off + b_bytes);
   p.bar_off = p.stg_off + p.stg_bufs * 16384;
   const int smem_bytes = p.bar_off + kTail + 1024;
-  int rc = make_weight_map(&p.bmap, w_packed, ctot, p.num_taps, cout, bn / cluster);
+  // packed weights: conv [Cout][taps][Ctot]; ConvT fwd [Cout][4 phases][Cin] (the phase is the "tap" coordinate);
+  // ConvT dgrad [Cin][4][Cout] read as rows of K = 4*Cout
+  int rc = make_weight_map(&p.bmap, w_packed, ctot, convt ? 4 : p.num_taps, cout, bn / cluster);
   if (rc != UZ_OK) return rc;
-  rc = make_act_map(&p.omap, out, cout, out_ld, N, H, W, full, 8, 16, 1);
+  if (convt) {
+    for (int l = 0; l < 4 && rc == UZ_OK; ++l)
+      rc = make_act_map(&p.omap[l], out, cout, out_ld, N, 2 * H, 2 * W, Lattice{l >> 1, l & 1, 2}, 8, 16, 1);
+  } else {
+    rc = make_act_map(&p.omap[0], out, cout, out_ld, N, H, W, full, 8, 16, 1);
+  }
   if (rc != UZ_OK) return rc;
   p.ncols = cout;
   p.bias = bias;
@@ -522,7 +556,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * 8 * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
-  if (mi.num_phases == 1 && mi.oscale == 1) {
+  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2) {
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }

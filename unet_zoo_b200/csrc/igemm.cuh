@@ -92,7 +92,8 @@ struct alignas(64) Wgrad2Params {
 struct alignas(64) Igemm2Params {
   CUtensorMap amap[kMaxSegs];  // 4-D (C, W, H, N) bf16, box (64, 8+2*pad, 16+2*pad, 1), SWIZZLE_128B
   CUtensorMap bmap;            // 3-D (Ctot, taps, cols) packed weights, box (64, 1, BN / cluster)
-  CUtensorMap omap;            // 4-D (cout, W, H, N) output view, box (64, 8, 16, 1), SWIZZLE_128B (TMA store)
+  CUtensorMap omap[4];         // 4-D (cout, W, H, N) output view(s), box (64, 8, 16, 1), SWIZZLE_128B (TMA store);
+                               // transposed conv: one strided view per output phase (dy, dx) of the 2x2 scatter
   int num_segs;
   int seg_cblocks[kMaxSegs];
   int seg_k0[kMaxSegs];
@@ -113,6 +114,8 @@ struct alignas(64) Igemm2Params {
   int a_off, b_off, stg_off, bar_off;  // byte offsets from the 1024-aligned smem base
   int stg_bufs;                // staging tiles for the TMA-store epilogue (1 or 2)
   int cluster;                 // thread-block cluster size (1, 2 or 4): weight tiles are multicast when > 1
+  int nt_per_phase;            // 0: N tiles walk the output columns.  > 0 (ConvTranspose2d k2s2 as four 1x1 GEMMs): N tile
+                               // = (phase, column tile); the phase selects the weight "tap" coordinate and the output view
   int ncols;                   // valid output columns (Cout)
   const float* bias;
   float* stats;                // [8*gridDim.x][2][ncols] partial sums (kFlagStats), zeroed by the host

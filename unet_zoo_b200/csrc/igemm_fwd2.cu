@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
     tma_prefetch_desc(&p.bmap);
-    tma_prefetch_desc(&p.omap);
+    for (int i = 0; i < (p.nt_per_phase ? 4 : 1); ++i) tma_prefetch_desc(&p.omap[i]);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, kTmemCols);
@@ -156,6 +156,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         const int rows = BN / cs;
         for (int g = cidx; g < ngroups; g += nclusters) {
           const int n_tile = (g * cs) / p.m_tiles;
+          const int b_phase = p.nt_per_phase ? n_tile / p.nt_per_phase : -1;
+          const int b_row0 = (p.nt_per_phase ? n_tile % p.nt_per_phase : n_tile) * BN;
           for (int seg = 0; seg < p.num_segs; ++seg) {
             const int ncb = p.seg_cblocks[seg];
             for (int cb = 0; cb < ncb; ++cb) {
@@ -164,11 +166,11 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 mbar_wait(bempty(stage), phase ^ 1u);
                 mbar_expect_tx(bfull(stage), kBItem);
                 const uint32_t dst = b_base + stage * kBItem;
+                const int btap = b_phase >= 0 ? b_phase : p.tap_b[tap];
                 if (cs == 1)
-                  tma_load_3d(dst, &p.bmap, bfull(stage), k, p.tap_b[tap], n_tile * BN);
+                  tma_load_3d(dst, &p.bmap, bfull(stage), k, btap, b_row0);
                 else
-                  tma_load_3d_mc(dst + rank * rows * 128, &p.bmap, bfull(stage), k, p.tap_b[tap],
-                                 n_tile * BN + rank * rows, mc_mask);
+                  tma_load_3d_mc(dst + rank * rows * 128, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows, mc_mask);
                 if (++stage == p.b_stages) {
                   stage = 0;
                   phase ^= 1u;
@@ -300,12 +302,14 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       const F2Tile t = f2_decode(p, g * cs + rank);
       const bool tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
       const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
+      const int o_phase = p.nt_per_phase ? t.n_tile / p.nt_per_phase : 0;
+      const int row0 = (p.nt_per_phase ? t.n_tile % p.nt_per_phase : t.n_tile) * BN;   // first output column of the tile
       if (t.n_tile != run_ntile) {
         if (do_stats) flush_stats();
         run_ntile = t.n_tile;
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et < BN) {
-          const int col = t.n_tile * BN + et;
+          const int col = row0 + et;
           st_shared_f32(bias_s + et * 4, (p.bias != nullptr && col < p.ncols) ? __ldg(p.bias + col) : 0.f);
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + hcol * 32;
 #pragma unroll 1
       for (int ch = 0; ch < kChunks; ++ch) {
-        const int col0 = t.n_tile * BN + ch * 64;
+        const int col0 = row0 + ch * 64;
         if (col0 >= p.ncols) break;  // uniform over the CTA
         const uint32_t sbuf = stg_base + (nbuf == 2 ? (it & 1u) * kF2StgBytes : 0u);
         ++it;
@@ -355,9 +359,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
           if (do_acc)
-            tma_reduce_add_4d(&p.omap, sbuf, col0, t.x0, t.y0, t.n);
+            tma_reduce_add_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
           else
-            tma_store_4d(&p.omap, sbuf, col0, t.x0, t.y0, t.n);
+            tma_store_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
           tma_store_commit();
         }
         if (do_stats) {
