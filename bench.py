@@ -280,7 +280,7 @@ def main():
     pk = peaks()
     imgs = B * world * args.steps
     value = imgs / (ms / 1000.0)
-    top = max(agg, key=lambda k: agg[k][0]) if agg else None
+    top = max((k for k in agg if k.startswith("igemm")), key=lambda k: agg[k][0]) if agg else None
     roof = None
     traffic = None
     try:   # DRAM bytes per launch of the family, from the committed ncu capture (profiles/r01_traffic.json)
@@ -294,7 +294,10 @@ def main():
         roof = {"kernel": top, "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
                 "frac": ach / pk["tflops"], "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)",
                 "launches": n, "avg_launch_ms": t / n,
-                "families": {k: {"ms": v[0], "tflops": v[1] / (v[0] / 1000.0) / 1e12, "launches": v[2]}
+                "families": {k: ({"ms": v[0], "tflops": v[1] / (v[0] / 1000.0) / 1e12, "launches": v[2]}
+                                 if k.startswith("igemm") else
+                                 {"ms": v[0], "gbs": v[1] / (v[0] / 1000.0) / 1e9, "frac_hbm": v[1] / (v[0] / 1000.0) / 1e9 / pk["hbm"],
+                                  "launches": v[2]})
                              for k, v in agg.items()},
                 "step_tflops": value / world * FWD_BWD_GFLOP_PER_IMG_512[args.model] * (S / 512.0) ** 2 / 1000.0}
     line = {

@@ -27,16 +27,16 @@ __device__ __forceinline__ uint32_t h_pack2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
-template <int CV>
+template <int CV, int KT>
 __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, long long npix, long long plane, int C,
                                 int K, int k0, int kn, const float* __restrict__ w, const float* __restrict__ b,
                                 float* __restrict__ logits) {
   const int g = threadIdx.x % CV;
   const int slot = threadIdx.x / CV;
   const int spb = blockDim.x / CV;
-  float wr[kHeadKT][8];
+  float wr[KT][8];
 #pragma unroll
-  for (int k = 0; k < kHeadKT; ++k)
+  for (int k = 0; k < KT; ++k)
 #pragma unroll
     for (int j = 0; j < 8; ++j) wr[k][j] = k < kn ? __ldg(w + static_cast<size_t>(k0 + k) * C + g * 8 + j) : 0.f;
   const long long iters = (npix + static_cast<long long>(gridDim.x) * spb - 1) / (static_cast<long long>(gridDim.x) * spb);
@@ -50,9 +50,9 @@ __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, lon
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = 0.f;
     }
-    float acc[kHeadKT];
+    float acc[KT];
 #pragma unroll
-    for (int k = 0; k < kHeadKT; ++k) {
+    for (int k = 0; k < KT; ++k) {
       float s = 0.f;
 #pragma unroll
       for (int j = 0; j < 8; ++j) s = fmaf(wr[k][j], f[j], s);
@@ -63,25 +63,25 @@ __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, lon
     if (ok && g == 0) {
       const long long n = p / plane, hw = p - n * plane;
 #pragma unroll
-      for (int k = 0; k < kHeadKT; ++k)
+      for (int k = 0; k < KT; ++k)
         if (k < kn) logits[(n * K + k0 + k) * plane + hw] = acc[k] + (b ? __ldg(b + k0 + k) : 0.f);
     }
   }
 }
 
 // dy[p, c] (+)= sum_k dl[p,k] w[k,c] ;  partial[block][kn][C] = sum_p dl[p,k] y[p,c] ; bpartial[block][kn] = sum_p dl[p,k]
-template <int CV>
-__global__ void head_bwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, const float* __restrict__ dlogits,
+template <int CV, int KT>
+__global__ void __launch_bounds__(256, KT == 1 ? 4 : 2) head_bwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, const float* __restrict__ dlogits,
                                 long long npix, long long plane, int C, int K, int k0, int kn,
                                 const float* __restrict__ w, __nv_bfloat16* __restrict__ dy, int dy_ld, int dy_accumulate,
                                 float* __restrict__ partial, float* __restrict__ bpartial) {
-  extern __shared__ float red[];  // [blockDim][kHeadKT*8 + kHeadKT]
+  extern __shared__ float red[];  // [blockDim][KT*8 + KT]
   const int g = threadIdx.x % CV;
   const int slot = threadIdx.x / CV;
   const int spb = blockDim.x / CV;
-  float wr[kHeadKT][8], aw[kHeadKT][8], ab[kHeadKT];
+  float wr[KT][8], aw[KT][8], ab[KT];
 #pragma unroll
-  for (int k = 0; k < kHeadKT; ++k) {
+  for (int k = 0; k < KT; ++k) {
     ab[k] = 0.f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -101,7 +101,7 @@ __global__ void head_bwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, con
       for (int j = 0; j < 8; ++j) d[j] = 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < kHeadKT; ++k) {
+    for (int k = 0; k < KT; ++k) {
       if (k < kn) {
         const float dl = __ldg(dlogits + (n * K + k0 + k) * plane + hw);
         ab[k] += dl;
@@ -115,27 +115,27 @@ __global__ void head_bwd_kernel(const __nv_bfloat16* __restrict__ y, int ld, con
     *reinterpret_cast<uint4*>(dy + p * dy_ld + g * 8) =
         make_uint4(h_pack2(d[0], d[1]), h_pack2(d[2], d[3]), h_pack2(d[4], d[5]), h_pack2(d[6], d[7]));
   }
-  constexpr int kPer = kHeadKT * 8 + kHeadKT;
+  constexpr int kPer = KT * 8 + KT;
   float* mine = red + static_cast<size_t>(threadIdx.x) * kPer;
 #pragma unroll
-  for (int k = 0; k < kHeadKT; ++k) {
+  for (int k = 0; k < KT; ++k) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) mine[k * 8 + j] = aw[k][j];
-    mine[kHeadKT * 8 + k] = ab[k];
+    mine[KT * 8 + k] = ab[k];
   }
   __syncthreads();
   if (slot == 0) {
     for (int r = 1; r < spb; ++r) {
       const float* o = red + (static_cast<size_t>(r) * CV + g) * kPer;
 #pragma unroll
-      for (int k = 0; k < kHeadKT; ++k) {
+      for (int k = 0; k < KT; ++k) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) aw[k][j] += o[k * 8 + j];
-        ab[k] += o[kHeadKT * 8 + k];
+        ab[k] += o[KT * 8 + k];
       }
     }
 #pragma unroll
-    for (int k = 0; k < kHeadKT; ++k)
+    for (int k = 0; k < KT; ++k)
       if (k < kn) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) partial[(static_cast<size_t>(blockIdx.x) * kn + k) * C + g * 8 + j] = aw[k][j];
@@ -160,15 +160,24 @@ __global__ void head_reduce_kernel(const float* __restrict__ partial, int rows, 
 template <int CV>
 static void launch_head_fwd(int grid, int block, cudaStream_t st, const __nv_bfloat16* y, int ld, long long npix,
                             long long plane, int C, int K, int k0, int kn, const float* w, const float* b, float* lg) {
-  head_fwd_kernel<CV><<<grid, block, 0, st>>>(y, ld, npix, plane, C, K, k0, kn, w, b, lg);
+  if (kn == 1)
+    head_fwd_kernel<CV, 1><<<grid, block, 0, st>>>(y, ld, npix, plane, C, K, k0, kn, w, b, lg);
+  else
+    head_fwd_kernel<CV, kHeadKT><<<grid, block, 0, st>>>(y, ld, npix, plane, C, K, k0, kn, w, b, lg);
 }
 template <int CV>
 static void launch_head_bwd(int grid, int block, cudaStream_t st, const __nv_bfloat16* y, int ld, const float* dl,
                             long long npix, long long plane, int C, int K, int k0, int kn, const float* w,
                             __nv_bfloat16* dy, int dy_ld, int acc, float* partial, float* bpartial) {
-  const size_t smem = static_cast<size_t>(block) * (kHeadKT * 8 + kHeadKT) * sizeof(float);
-  head_bwd_kernel<CV><<<grid, block, smem, st>>>(y, ld, dl, npix, plane, C, K, k0, kn, w, dy, dy_ld, acc, partial,
-                                                 bpartial);
+  if (kn == 1) {
+    const size_t smem = static_cast<size_t>(block) * 9 * sizeof(float);
+    head_bwd_kernel<CV, 1><<<grid, block, smem, st>>>(y, ld, dl, npix, plane, C, K, k0, kn, w, dy, dy_ld, acc, partial,
+                                                      bpartial);
+  } else {
+    const size_t smem = static_cast<size_t>(block) * (kHeadKT * 8 + kHeadKT) * sizeof(float);
+    head_bwd_kernel<CV, kHeadKT><<<grid, block, smem, st>>>(y, ld, dl, npix, plane, C, K, k0, kn, w, dy, dy_ld, acc,
+                                                            partial, bpartial);
+  }
 }
 
 }  // namespace uz

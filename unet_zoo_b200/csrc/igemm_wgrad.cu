@@ -231,29 +231,57 @@ cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stre
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dst, int splits, int rows,
                                     int taps, int cols, long long s_row, long long s_col, long long s_tap,
                                     int accumulate) {
+  // block = (one row, 32 columns); thread = (tap, column).  Partial reads coalesce over the 32 columns of each tap; the
+  // sums are transposed through shared memory so that the block writes ONE contiguous run of 32*taps floats of the
+  // OIHW / IOHW destination (s_col == taps, s_tap == 1) instead of one scattered sector per element.
+  __shared__ float stage[9 * 33];
+  const int cchunks = (cols + 31) / 32;
+  const int row = blockIdx.x / cchunks;
+  const int c0 = (blockIdx.x % cchunks) * 32;
+  const int tap = threadIdx.x / 32, cl = threadIdx.x % 32;
+  const int col = c0 + cl;
   const long long total = static_cast<long long>(rows) * taps * cols;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    float s = 0.f;
-    for (int k = 0; k < splits; ++k) s += partial[k * total + i];
-    const int col = static_cast<int>(i % cols);
-    const long long r = i / cols;
-    const int tap = static_cast<int>(r % taps);
-    const int row = static_cast<int>(r / taps);
-    const long long o = row * s_row + col * s_col + tap * s_tap;
-    dst[o] = accumulate ? dst[o] + s : s;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (col < cols) {
+    const float* q = partial + (static_cast<long long>(row) * taps + tap) * cols + col;
+    int k = 0;
+    for (; k + 4 <= splits; k += 4) {
+      s0 += __ldg(q + (k + 0) * total);
+      s1 += __ldg(q + (k + 1) * total);
+      s2 += __ldg(q + (k + 2) * total);
+      s3 += __ldg(q + (k + 3) * total);
+    }
+    for (; k < splits; ++k) s0 += __ldg(q + k * total);
+  }
+  const float s = (s0 + s1) + (s2 + s3);
+  const bool dense = s_tap == 1 && s_col == taps;
+  if (!dense) {
+    if (col < cols) {
+      float* o = dst + row * s_row + col * s_col + tap * s_tap;
+      *o = accumulate ? *o + s : s;
+    }
+    return;
+  }
+  stage[tap * 33 + cl] = s;
+  __syncthreads();
+  const int ncol = min(32, cols - c0);
+  const int i = threadIdx.x;                 // position in the contiguous run: i = column_local * taps + tap
+  if (i < ncol * taps) {
+    const int c = i / taps, t = i - c * taps;
+    float* o = dst + row * s_row + static_cast<long long>(c0) * taps + i;
+    const float v = stage[t * 33 + c];
+    *o = accumulate ? *o + v : v;
   }
 }
 
 cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
                                 long long s_row, long long s_col, long long s_tap, int accumulate,
                                 cudaStream_t stream) {
-  const long long total = static_cast<long long>(rows) * taps * cols;
-  int blocks = static_cast<int>((total + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  if (blocks < 1) blocks = 1;
-  wgrad_reduce_kernel<<<blocks, 256, 0, stream>>>(partial, dst, splits, rows, taps, cols, s_row, s_col, s_tap,
-                                                  accumulate);
+  if (taps < 1 || taps > 9) return cudaErrorInvalidValue;
+  const long long blocks = static_cast<long long>(rows) * ((cols + 31) / 32);
+  if (blocks < 1 || blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
+  wgrad_reduce_kernel<<<static_cast<int>(blocks), taps * 32, 0, stream>>>(partial, dst, splits, rows, taps, cols, s_row,
+                                                                          s_col, s_tap, accumulate);
   return cudaGetLastError();
 }
 

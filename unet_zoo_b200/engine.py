@@ -18,8 +18,9 @@ from . import _lib as L
 _c_void_p = ctypes.c_void_p
 
 # Optional per-launch timing of the tensor-core kernels (bench.py's roofline leg): when set to a list, every
-# uz_conv_igemm / uz_conv_wgrad call is bracketed by CUDA events on the launch stream and appended as
-# (kind, algorithmic_flops, start_event, end_event).  None (default) adds no overhead.
+# uz_conv_igemm / uz_conv_wgrad / uz_bn_apply / uz_bn_bwd call is bracketed by CUDA events on the launch stream and
+# appended as (kind, algorithmic FLOPs (GEMM kinds) or bytes (bn_* kinds), start_event, end_event).  None (default)
+# adds no overhead.
 PROFILE: Optional[list] = None
 _TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 36}
 
@@ -268,10 +269,12 @@ class Ctx:
 
     def bn_apply(self, z: Act, scale_ptr, shift_ptr, relu: bool, y: Optional[Act], pooled: Optional[Act] = None,
                  residual: Optional[Act] = None):
-        rc = self.lib.uz_bn_apply(z.ptr, z.ld, z.N, z.H, z.W, z.C, scale_ptr, shift_ptr, int(relu),
-                                  residual.ptr if residual else None, residual.ld if residual else 0,
-                                  y.ptr if y else None, y.ld if y else 0,
-                                  pooled.ptr if pooled else None, pooled.ld if pooled else 0, self.stream)
+        nbytes = 2.0 * z.npix * z.C * (1 + (1 if y else 0) + (0.25 if pooled else 0) + (1 if residual else 0))
+        with _Timed("bn_apply", nbytes):
+            rc = self.lib.uz_bn_apply(z.ptr, z.ld, z.N, z.H, z.W, z.C, scale_ptr, shift_ptr, int(relu),
+                                      residual.ptr if residual else None, residual.ld if residual else 0,
+                                      y.ptr if y else None, y.ld if y else 0,
+                                      pooled.ptr if pooled else None, pooled.ld if pooled else 0, self.stream)
         L.check(rc, "uz_bn_apply")
         self.launches += 1
 
@@ -279,9 +282,13 @@ class Ctx:
                dgamma, dbeta, dbias, dz_accumulate: bool = False):
         need = self.lib.uz_bn_bwd_workspace_bytes(z.C)
         ws = self.workspace(need)
-        rc = self.lib.uz_bn_bwd(z.ptr, z.ld, dy_ptr, dy_ld, dpool_ptr, dpool_ld, z.N, z.H, z.W, z.C, bnbuf.data_ptr(),
-                                int(relu), dz_ptr, dz_ld, _ptr(dgamma), _ptr(dbeta), _ptr(dbias),
-                                2 if dz_accumulate else 0, ws.data_ptr(), ws.numel(), self.stream)
+        # algorithmic bytes: reduce pass reads dy, z (+ dpool/4); apply pass reads them again and writes dz
+        per = (1 if dy_ptr else 0) + 1 + (0.25 if dpool_ptr else 0)
+        nbytes = 2.0 * z.npix * z.C * (2 * per + 1 + (1 if dz_accumulate else 0))
+        with _Timed("bn_bwd", nbytes):
+            rc = self.lib.uz_bn_bwd(z.ptr, z.ld, dy_ptr, dy_ld, dpool_ptr, dpool_ld, z.N, z.H, z.W, z.C, bnbuf.data_ptr(),
+                                    int(relu), dz_ptr, dz_ld, _ptr(dgamma), _ptr(dbeta), _ptr(dbias),
+                                    2 if dz_accumulate else 0, ws.data_ptr(), ws.numel(), self.stream)
         L.check(rc, "uz_bn_bwd")
         self.launches += 4 if dbias is not None else 3
 

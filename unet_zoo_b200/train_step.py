@@ -28,6 +28,10 @@ class GraphedTrainStep:
         self.loss: Optional[torch.Tensor] = None
         self.out = None
         dev = example_x.device
+        # the warm-up runs on a side stream by design (torch's capture recipe); autograd's note about it is noise here
+        warn_off = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+        if warn_off is not None:
+            warn_off(False)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):                      # warm-up off the capture: lazy initialisation, autotuning
