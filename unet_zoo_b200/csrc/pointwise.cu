@@ -61,6 +61,19 @@ static Geo make_geo(int C, long long items, int blocks_per_sm) {
   return g;
 }
 
+// grid of a persistent grid-stride kernel: exactly the number of blocks that are resident at once (no partial second
+// wave at reduced occupancy), capped by the number of partial-sum rows the workspace holds
+template <typename K>
+static int resident_grid(K kernel, int block, size_t smem, long long need, int cap_per_sm) {
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (per_sm > cap_per_sm) per_sm = cap_per_sm;
+  int sms = sm_count();
+  if (sms < 1) sms = 148;
+  const long long cap = static_cast<long long>(sms) * per_sm;
+  return static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
+}
+
 // ---------------------------------------------------------------------------------------------- weight packing
 // dst[a*dst_pitch + t*B + b] = bf16(src[a*sa + b*sb + t*st] * (row_scale ? row_scale[a] : 1))
 __global__ void pack_weight_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int A, int T, int B,
@@ -224,6 +237,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, 
 
 // ---------------------------------------------------------------------------------------------- BatchNorm apply
 // y = act(z*scale + shift [+ residual]) ; POOL additionally writes the 2x2 max of y.  item = pixel or 2x2 quad.
+constexpr int kApplyUnroll = 4;
 template <bool POOL>
 __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, int N, int H, int W, int C, int cv,
                                 int ppb, const float* __restrict__ scale, const float* __restrict__ shift, int relu,
@@ -245,24 +259,41 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, i
   const int Hq = POOL ? H / 2 : H, Wq = POOL ? W / 2 : W;
   const long long items = static_cast<long long>(N) * Hq * Wq;
   for (long long it = static_cast<long long>(blockIdx.x) * ppb + pl; it < items;
-       it += static_cast<long long>(gridDim.x) * ppb) {
+       it += static_cast<long long>(gridDim.x) * ppb * (POOL ? 1 : kApplyUnroll)) {
     if (!POOL) {
-      float f[8];
-      unpack8(ldg16(z + it * z_ld + g * 8), f);
-      if (res) {
-        float r[8];
-        unpack8(ldg16(res + it * res_ld + g * 8), r);
+      // kApplyUnroll pixels per thread iteration: all loads are issued before the arithmetic (bytes in flight)
+      const long long stride = static_cast<long long>(gridDim.x) * ppb;
+      uint4 zr[kApplyUnroll], rr[kApplyUnroll];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]) + r[j];
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+      for (int u = 0; u < kApplyUnroll; ++u) {
+        const long long p = it + u * stride;
+        if (p < items) {
+          zr[u] = ldg16(z + p * z_ld + g * 8);
+          if (res) rr[u] = ldg16(res + p * res_ld + g * 8);
+        }
       }
-      if (relu) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      for (int u = 0; u < kApplyUnroll; ++u) {
+        const long long p = it + u * stride;
+        if (p < items) {
+          float f[8];
+          unpack8(zr[u], f);
+          if (res) {
+            float r[8];
+            unpack8(rr[u], r);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]) + r[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+          }
+          if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          *reinterpret_cast<uint4*>(y + p * y_ld + g * 8) = pack8(f);
+        }
       }
-      *reinterpret_cast<uint4*>(y + it * y_ld + g * 8) = pack8(f);
     } else {
       const int qx = static_cast<int>(it % Wq);
       const long long r0 = it / Wq;
@@ -390,6 +421,8 @@ __device__ __forceinline__ void bwd_item_grad(const BwdArgs& a, long long it, in
   }
 }
 
+constexpr int kBwdUnrollReduce = 4;
+constexpr int kBwdUnrollApply = 4;
 // loads of one pixel on the no-pool path (issued for two pixels before any arithmetic: memory-level parallelism)
 struct BwdLoad {
   uint4 z, d;
@@ -439,25 +472,22 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_reduce_kernel(const 
         }
     }
   } else {
-    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += 2 * stride) {
-      const long long it1 = it + stride;
-      const bool has1 = it1 < items;
-      BwdLoad l0, l1;
-      bwd_load(a, it, g, l0);
-      if (has1) bwd_load(a, it1, g, l1);
-      float zv[8], gv[8];
-      bwd_grad(a, l0, sc, sh, zv, gv);
+    constexpr int U = kBwdUnrollReduce;   // pixels in flight per thread: 2*U 16-byte loads issued before any arithmetic
+    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += U * stride) {
+      BwdLoad l[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        s[j] += gv[j];
-        q[j] = fmaf(gv[j], zv[j], q[j]);
-      }
-      if (has1) {
-        bwd_grad(a, l1, sc, sh, zv, gv);
+      for (int u = 0; u < U; ++u)
+        if (it + u * stride < items) bwd_load(a, it + u * stride, g, l[u]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          s[j] += gv[j];
-          q[j] = fmaf(gv[j], zv[j], q[j]);
+      for (int u = 0; u < U; ++u) {
+        if (it + u * stride < items) {
+          float zv[8], gv[8];
+          bwd_grad(a, l[u], sc, sh, zv, gv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s[j] += gv[j];
+            q[j] = fmaf(gv[j], zv[j], q[j]);
+          }
         }
       }
     }
@@ -521,7 +551,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
 }
 
 template <bool POOL>
-__global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
+__global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BwdArgs a, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dz,
                                     int dz_ld, float* __restrict__ dbias_partial, int dz_accumulate) {
   const int g = threadIdx.x % a.cv;
   const int pl = threadIdx.x / a.cv;
@@ -532,43 +562,47 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_apply_kernel(const B
   load8f(coef + a.C + g * 8, cb);
   const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
                                : static_cast<long long>(a.N) * a.H * a.W;
-  constexpr int NP = POOL ? 4 : 2;
   const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
-  for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += (POOL ? 1 : 2) * stride) {
-    float zv[NP][8], gv[NP][8];
-    long long pix[NP];
-    int np = NP;
-    if (POOL) {
-      float (&zp)[POOL ? 4 : 1][8] = reinterpret_cast<float (&)[POOL ? 4 : 1][8]>(zv);
-      float (&gp)[POOL ? 4 : 1][8] = reinterpret_cast<float (&)[POOL ? 4 : 1][8]>(gv);
-      long long (&pp)[POOL ? 4 : 1] = reinterpret_cast<long long (&)[POOL ? 4 : 1]>(pix);
-      bwd_item_grad<POOL>(a, it, g, sc, sh, zp, gp, pp);
-    } else {
-      pix[0] = it;
-      pix[1] = it + stride;
-      if (pix[1] >= items) np = 1;
-      BwdLoad l0, l1;
-      bwd_load(a, pix[0], g, l0);
-      if (np == 2) bwd_load(a, pix[1], g, l1);
-      bwd_grad(a, l0, sc, sh, zv[0], gv[0]);
-      if (np == 2) bwd_grad(a, l1, sc, sh, zv[1], gv[1]);
+  auto emit = [&](long long p, const float (&zv)[8], const float (&gv)[8]) {
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], gv[j], fmaf(cb[j], zv[j], ca[j]));
+    __nv_bfloat16* dst = dz + p * dz_ld + g * 8;
+    if (dz_accumulate) {  // the destination already holds a gradient from another consumer of the tensor
+      float old[8];
+      unpack8(*reinterpret_cast<const uint4*>(dst), old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += old[j];
     }
+    *reinterpret_cast<uint4*>(dst) = pack8(o);
+  };
+  if (POOL) {
+    constexpr int NP = POOL ? 4 : 1;
+    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += stride) {
+      float zv[NP][8], gv[NP][8];
+      long long pix[NP];
+      bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
 #pragma unroll
-    for (int i = 0; i < NP; ++i) {
-      if (i >= np) break;
-      float o[8];
+      for (int i = 0; i < NP; ++i) emit(pix[i], zv[i], gv[i]);
+    }
+  } else {
+    constexpr int U = kBwdUnrollApply;   // 2*U 16-byte loads in flight per thread; only the raw words stay live
+    for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += U * stride) {
+      BwdLoad l[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], gv[i][j], fmaf(cb[j], zv[i][j], ca[j]));
-      if (dz_accumulate) {  // the destination already holds a gradient from another consumer of the tensor
-        float old[8];
-        unpack8(*reinterpret_cast<const uint4*>(dz + pix[i] * dz_ld + g * 8), old);
+      for (int u = 0; u < U; ++u)
+        if (it + u * stride < items) bwd_load(a, it + u * stride, g, l[u]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += old[j];
+      for (int u = 0; u < U; ++u) {
+        if (it + u * stride < items) {
+          float zv[8], gv[8];
+          bwd_grad(a, l[u], sc, sh, zv, gv);
+          emit(it + u * stride, zv, gv);
+        }
       }
-      const uint4 w = pack8(o);
-      *reinterpret_cast<uint4*>(dz + pix[i] * dz_ld + g * 8) = w;
     }
   }
+  (void)dbias_partial;
 }
 
 // ---------------------------------------------------------------------------------------------- column sums
@@ -747,25 +781,14 @@ extern "C" int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, 
   } else {
     if (!y) return set_error(UZ_ERR_INVALID, "bn_apply: no output");
     const Geo g = make_geo(C, static_cast<long long>(N) * H * W, 8);
-    bn_apply_kernel<false><<<g.grid, g.block, 0, st>>>(
+    const long long items = static_cast<long long>(N) * H * W;
+    const int grid = resident_grid(bn_apply_kernel<false>, g.block, 0, (items + g.ppb - 1) / g.ppb, 8);
+    bn_apply_kernel<false><<<grid, g.block, 0, st>>>(
         static_cast<const __nv_bfloat16*>(z), z_ld, N, H, W, C, g.cv, g.ppb, scale, shift, relu,
         static_cast<const __nv_bfloat16*>(residual), res_ld, static_cast<__nv_bfloat16*>(y), y_ld, nullptr, 0);
   }
   UZ_CHECK_LAUNCH("bn_apply launch");
   return UZ_OK;
-}
-
-// grid of a persistent grid-stride kernel: exactly the number of blocks that are resident at once (no partial second
-// wave at reduced occupancy), capped by the number of partial-sum rows the workspace holds
-template <typename K>
-static int resident_grid(K kernel, int block, size_t smem, long long need, int cap_per_sm) {
-  int per_sm = 1;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
-  if (per_sm > cap_per_sm) per_sm = cap_per_sm;
-  int sms = sm_count();
-  if (sms < 1) sms = 148;
-  const long long cap = static_cast<long long>(sms) * per_sm;
-  return static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
 }
 
 extern "C" size_t uz_bn_bwd_workspace_bytes(int C) {
