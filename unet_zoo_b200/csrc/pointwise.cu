@@ -421,6 +421,69 @@ __device__ __forceinline__ void bwd_item_grad(const BwdArgs& a, long long it, in
   }
 }
 
+// Pooled path, register-lean form: the nine 16-byte words of one 2x2 quad (4 z, 4 dy, 1 dpool) stay raw; the gradient
+// is rebuilt two channels at a time and handed to `sink(word, pixel, z_lo, z_hi, g_lo, g_hi)`.
+struct QuadRaw {
+  uint32_t z[4][4], d[4][4], dp[4];
+  long long pix[4];
+};
+__device__ __forceinline__ void quad_load(const BwdArgs& a, long long it, int g, QuadRaw& r) {
+  const int Hq = a.H / 2, Wq = a.W / 2;
+  const int qx = static_cast<int>(it % Wq);
+  const long long r0 = it / Wq;
+  const int qy = static_cast<int>(r0 % Hq);
+  const int n = static_cast<int>(r0 / Hq);
+  const long long p00 = (static_cast<long long>(n) * a.H + 2 * qy) * a.W + 2 * qx;
+  r.pix[0] = p00;
+  r.pix[1] = p00 + 1;
+  r.pix[2] = p00 + a.W;
+  r.pix[3] = p00 + a.W + 1;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint4 v = ldg16(a.z + r.pix[i] * a.z_ld + g * 8);
+    r.z[i][0] = v.x; r.z[i][1] = v.y; r.z[i][2] = v.z; r.z[i][3] = v.w;
+    const uint4 d = a.dy ? ldg16(a.dy + r.pix[i] * a.dy_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+    r.d[i][0] = d.x; r.d[i][1] = d.y; r.d[i][2] = d.z; r.d[i][3] = d.w;
+  }
+  const uint4 p = a.dpool ? ldg16(a.dpool + it * a.dpool_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+  r.dp[0] = p.x; r.dp[1] = p.y; r.dp[2] = p.z; r.dp[3] = p.w;
+}
+template <typename Sink>
+__device__ __forceinline__ void quad_grad(const BwdArgs& a, const QuadRaw& r, const float (&sc)[8], const float (&sh)[8],
+                                          Sink&& sink) {
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int j = 2 * w + h;
+      float zv[4], yv[4], gv[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        zv[i] = h ? __uint_as_float(r.z[i][w] & 0xFFFF0000u) : __uint_as_float(r.z[i][w] << 16);
+        gv[i] = h ? __uint_as_float(r.d[i][w] & 0xFFFF0000u) : __uint_as_float(r.d[i][w] << 16);
+        float u = fmaf(zv[i], sc[j], sh[j]);
+        if (a.relu) u = fmaxf(u, 0.f);
+        yv[i] = bf16_round(u);  // the forward pooled the stored (bf16) activations
+      }
+      const float dp = h ? __uint_as_float(r.dp[w] & 0xFFFF0000u) : __uint_as_float(r.dp[w] << 16);
+      int am = 0;               // first maximum in row-major window order wins (nn.MaxPool2d index semantics)
+      float mv = yv[0];
+#pragma unroll
+      for (int i = 1; i < 4; ++i)
+        if (yv[i] > mv) {
+          mv = yv[i];
+          am = i;
+        }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (i == am) gv[i] += dp;
+        if (a.relu && !(yv[i] > 0.f)) gv[i] = 0.f;
+        sink(w, h, i, zv[i], gv[i]);
+      }
+    }
+  }
+}
+
 constexpr int kBwdUnrollReduce = 4;
 constexpr int kBwdUnrollApply = 4;
 // loads of one pixel on the no-pool path (issued for two pixels before any arithmetic: memory-level parallelism)
@@ -458,18 +521,13 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_reduce_kernel(const 
                                : static_cast<long long>(a.N) * a.H * a.W;
   const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
   if (POOL) {
-    constexpr int NP = POOL ? 4 : 1;
     for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += stride) {
-      float zv[NP][8], gv[NP][8];
-      long long pix[NP];
-      bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
-#pragma unroll
-      for (int i = 0; i < NP; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          s[j] += gv[i][j];
-          q[j] = fmaf(gv[i][j], zv[i][j], q[j]);
-        }
+      QuadRaw r;
+      quad_load(a, it, g, r);
+      quad_grad(a, r, sc, sh, [&](int w, int h, int, float zv, float gv) {
+        s[2 * w + h] += gv;
+        q[2 * w + h] = fmaf(gv, zv, q[2 * w + h]);
+      });
     }
   } else {
     constexpr int U = kBwdUnrollReduce;   // pixels in flight per thread: 2*U 16-byte loads issued before any arithmetic
@@ -577,13 +635,31 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BwdArgs a, c
     *reinterpret_cast<uint4*>(dst) = pack8(o);
   };
   if (POOL) {
-    constexpr int NP = POOL ? 4 : 1;
     for (long long it = static_cast<long long>(blockIdx.x) * a.ppb + pl; it < items; it += stride) {
-      float zv[NP][8], gv[NP][8];
-      long long pix[NP];
-      bwd_item_grad<POOL>(a, it, g, sc, sh, zv, gv, pix);
+      QuadRaw r;
+      quad_load(a, it, g, r);
+      float lo[4];               // low half of the output word being assembled, per pixel
+      uint32_t out[4][4];
+      quad_grad(a, r, sc, sh, [&](int w, int h, int i, float zv, float gv) {
+        const int j = 2 * w + h;
+        const float o = fmaf(sc[j], gv, fmaf(cb[j], zv, ca[j]));
+        if (h == 0) lo[i] = o;
+        else out[i][w] = pack2(lo[i], o);
+      });
 #pragma unroll
-      for (int i = 0; i < NP; ++i) emit(pix[i], zv[i], gv[i]);
+      for (int i = 0; i < 4; ++i) {
+        __nv_bfloat16* dst = dz + r.pix[i] * dz_ld + g * 8;
+        uint4 v = make_uint4(out[i][0], out[i][1], out[i][2], out[i][3]);
+        if (dz_accumulate) {
+          float old[8], cur[8];
+          unpack8(*reinterpret_cast<const uint4*>(dst), old);
+          unpack8(v, cur);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cur[j] += old[j];
+          v = pack8(cur);
+        }
+        *reinterpret_cast<uint4*>(dst) = v;
+      }
     }
   } else {
     constexpr int U = kBwdUnrollApply;   // 2*U 16-byte loads in flight per thread; only the raw words stay live
