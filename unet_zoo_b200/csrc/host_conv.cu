@@ -447,7 +447,8 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
     if (bn / cluster < 16) cluster = 1;
     p.stg_bufs = bn == 256 ? 1 : 2;
-    p.a_stages = bn == 256 ? 2 : bn == 128 ? 3 : 4;
+    p.a_stages = env_int("UZ_FWD2_A_STAGES", bn == 256 ? 2 : bn == 128 ? 3 : 4);
+    if (p.a_stages < 1 || p.a_stages > 6) p.a_stages = 2;
     int bs = (kMaxSmem - kTail - p.stg_bufs * 16384 - p.a_stages * a_slot) / b_item;
     p.b_stages = bs > 12 ? 12 : bs;
     if (p.b_stages < 2) return 0;
