@@ -104,6 +104,24 @@ int uz_head_bwd(const void* y, int ld, const float* dlogits, int N, int H, int W
                 void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Last DoubleConv half fused with the classifier head (training): the full-resolution activation y = ReLU(BN(z))
+ * between DoubleConv (common_layers.py:28-33) and OutConv (common_layers.py:125-128; attention_unet.py:70,
+ * nested_unet.py:69) is never written to memory.
+ *  uz_bn_head_fwd: logits[n,k,h,w] = b[k] + sum_c w[k,c] * act(scale[c]*z[n,h,w,c] + shift[c])   (fp32 NCHW)
+ *  uz_bn_head_bwd: given dlogits (fp32 NCHW) rebuilds y and dy[p,c] = sum_k dlogits[p,k] w[k,c] on the fly and runs the
+ *                  BatchNorm backward of uz_bn_bwd on it: dz (bf16, may alias z), dgamma, dbeta, dbias (conv bias in
+ *                  front of the BN), and the head's dw[k,c] = sum_p dlogits[p,k] y[p,c], db[k] = sum_p dlogits[p,k].
+ *                  bn = [4][C] {mean, invstd, scale, shift} of uz_bn_finalize; accumulate bit0: += into the parameter
+ *                  gradients.  C a power of two in [8, 256], K in [1, 4]. */
+size_t uz_bn_head_workspace_bytes(int C, int K);
+int uz_bn_head_fwd(const void* z, int z_ld, int N, int H, int W, int C, const float* scale, const float* shift,
+                   int relu, int K, const float* w, const float* b, float* logits, void* stream);
+int uz_bn_head_bwd(const void* z, int z_ld, int N, int H, int W, int C, const float* bn, int relu, int K,
+                   const float* w, const float* dlogits, void* dz, int dz_ld, float* dgamma, float* dbeta,
+                   float* dbias, float* dw, float* db, int accumulate, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Additive attention gate (AttentionBlock, attention_unet.py:6-40): the two 1x1 convolutions W_g, W_x run through
  * uz_conv_igemm(UZ_CONV1X1, UZ_FLAG_STATS) -> zg, zx (bf16 [npix, F], F = f_int <= 256) and uz_bn_finalize -> bn_g,
  * bn_x ([4][F] = mean, invstd, scale, shift).  Then

@@ -189,3 +189,36 @@ def test_conv_plain_accumulates_and_backpropagates():
     assert rel_l2(get_grad(xa), ar.grad) < 1e-2 and rel_l2(get_grad(xb), br.grad) < 1e-2
     for p in list(conv_a.parameters()) + list(conv_b.parameters()):
         assert rel_l2(ctx.pgrads.view(p), p.grad) < 5e-3
+
+
+@pytest.mark.parametrize("N,H,W,cin,cout,K", [(2, 24, 40, 64, 64, 1), (1, 16, 16, 64, 32, 2), (2, 9, 13, 128, 64, 3),
+                                              (1, 16, 24, 64, 64, 6)])
+def test_conv_bn_relu_head_fused_fwd_bwd(N, H, W, cin, cout, K):
+    """Last DoubleConv half + OutConv with the activation kept in registers (uz_bn_head_fwd / uz_bn_head_bwd);
+    K = 6 exercises the unfused fallback of the same operator."""
+    conv = nn.Conv2d(cin, cout, 3, padding=1).to(DEV)
+    bn = nn.BatchNorm2d(cout).to(DEV)
+    head = nn.Conv2d(cout, K, 1).to(DEV)
+    _round_weights(nn.Sequential(conv, bn))
+    x = bf16r(torch.randn(N, cin, H, W, device=DEV))
+    params = list(conv.parameters()) + list(bn.parameters()) + list(head.parameters())
+    ctx = new_ctx(params=params)
+    xa = make_act(ctx, x)
+    logits = E.conv_bn_act_head(ctx, [xa], conv, bn, head)
+    xr = x.clone().requires_grad_(True)
+    z = F.conv2d(xr, conv.weight, conv.bias, padding=1)
+    zq = z + (bf16r(z.detach()) - z.detach())
+    y = F.relu(F.batch_norm(zq, None, None, bn.weight, bn.bias, training=True, eps=1e-5))
+    ref = F.conv2d(y, head.weight, head.bias)
+    torch.cuda.synchronize()
+    assert logits.shape == ref.shape and logits.dtype == torch.float32
+    assert relmax(logits, ref.detach()) < (1e-2 if K > 4 else 2e-3)   # fused: y stays fp32; fallback rounds y to bf16
+    dl = torch.randn_like(ref) * 0.1
+    (ref * dl).sum().backward()
+    ctx.out_grads = [dl]
+    run_tape(ctx)
+    assert rel_l2(get_grad(xa), xr.grad) < 1.5e-2
+    for name, p in (("conv.w", conv.weight), ("bn.w", bn.weight), ("bn.b", bn.bias), ("head.w", head.weight),
+                    ("head.b", head.bias)):
+        assert rel_l2(ctx.pgrads.view(p), p.grad) < 1e-2, name
+    assert float(ctx.pgrads.view(conv.bias).abs().max()) < 1e-3      # bias in front of a train-mode BN: zero gradient

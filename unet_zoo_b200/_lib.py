@@ -50,6 +50,10 @@ _PROTOS = {
     "uz_head_bwd_workspace_bytes": (c_size_t, [c_int]),
     "uz_head_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, _P, _P, c_int, _P, c_size_t,
                             _P]),
+    "uz_bn_head_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "uz_bn_head_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, c_int, _P, _P, _P, _P]),
+    "uz_bn_head_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, _P, _P,
+                               _P, _P, c_int, _P, c_size_t, _P]),
 }
 
 _lib = None

@@ -387,7 +387,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     else p.tap_row[t] = 0;
     p.tap_b[t] = t;
   }
-  const int bn = cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
+  int bn = cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
   int ctot = 0, kblocks = 0;
   const Lattice full = {0, 0, 1};
   if (convt_d) {
@@ -423,8 +423,8 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   }
   // shared-memory plan: [A ring][B ring or resident weights][1-2 staging tiles][barriers + bias]
   const int kMaxSmem = 232448 - 1024;  // 227 KB minus the alignment slack
-  const int a_slot = (p.halo_bytes + 1023) & ~1023;
-  const int b_item = bn * 128;
+  int a_slot = (p.halo_bytes + 1023) & ~1023;
+  int b_item = bn * 128;
   const int kTail = 1536;              // barriers (512) + bias vector (1024)
   const long long b_all = (long long)kblocks * p.num_taps * b_item;
   int cluster = 1;
@@ -442,19 +442,34 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
       }
     }
   }
+  p.mp = 1;
+  if (!stationary && bn == 128 && env_int("UZ_FWD2_MP", 2) == 2) {
+    // streamed weights, 65..128 output channels: one 128-wide weight tile against TWO pixel tiles (4 x 128 TMEM columns
+    // with double buffering).  Measured: 128->128 @256^2 0.496 -> 0.455 ms, 256->128 0.921 -> 0.854 ms.  Wider layers
+    // stay on BN = 256 (one A read per 256 columns is cheaper in shared-memory bandwidth than two tiles x 128)
+    p.mp = 2;
+    bn = 128;
+    b_item = bn * 128;
+    a_slot *= 2;
+    p.num_n_tiles = (cout + bn - 1) / bn;
+    if (convt) {
+      p.nt_per_phase = p.num_n_tiles;
+      p.num_n_tiles *= 4;
+    }
+  }
   if (!stationary) {
     cluster = env_int("UZ_FWD2_CLUSTER", 1);
     if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
     if (bn / cluster < 16) cluster = 1;
     p.stg_bufs = bn == 256 ? 1 : 2;
-    p.a_stages = env_int("UZ_FWD2_A_STAGES", bn == 256 ? 2 : bn == 128 ? 3 : 4);
+    p.a_stages = env_int("UZ_FWD2_A_STAGES", p.mp == 2 ? (a_slot > 40000 ? 2 : 3) : bn == 256 ? 2 : bn == 128 ? 3 : 4);
     if (p.a_stages < 1 || p.a_stages > 6) p.a_stages = 2;
     int bs = (kMaxSmem - kTail - p.stg_bufs * 16384 - p.a_stages * a_slot) / b_item;
     p.b_stages = bs > 12 ? 12 : bs;
     if (p.b_stages < 2) return 0;
   }
   p.cluster = cluster;
-  p.m_tiles = (p.m_tiles_real + cluster - 1) / cluster * cluster;
+  p.m_tiles = ((p.m_tiles_real + p.mp - 1) / p.mp + cluster - 1) / cluster * cluster;
   p.total_tiles = p.m_tiles * p.num_n_tiles;
   p.a_off = 0;
   p.b_off = p.a_stages * a_slot;

@@ -105,7 +105,7 @@ struct alignas(64) Igemm2Params {
   int halo_bytes;              // halo_w * (16 + 2*pad) * 128
   int N, H, W;
   int xb, yb;                  // tiles along x, y
-  int m_tiles;                 // N*yb*xb rounded up to a multiple of the cluster size
+  int m_tiles;                 // work items along M: ceil(N*yb*xb / mp) rounded up to a multiple of the cluster size
   int m_tiles_real;
   int num_n_tiles;
   int total_tiles;             // m_tiles * num_n_tiles (tile = n_tile * m_tiles + m)
@@ -114,6 +114,9 @@ struct alignas(64) Igemm2Params {
   int a_off, b_off, stg_off, bar_off;  // byte offsets from the 1024-aligned smem base
   int stg_bufs;                // staging tiles for the TMA-store epilogue (1 or 2)
   int cluster;                 // thread-block cluster size (1, 2 or 4): weight tiles are multicast when > 1
+  int mp;                      // M tiles per work item (1 or 2).  2: every streamed weight tile feeds TWO pixel tiles (two
+                               // TMEM accumulators), halving the weight bytes an SM has to ingest per MMA cycle - the
+                               // streamed-weight layers were capped at ~72 % tensor-active by SM ingest (~50 B/clk)
   int nt_per_phase;            // 0: N tiles walk the output columns.  > 0 (ConvTranspose2d k2s2 as four 1x1 GEMMs): N tile
                                // = (phase, column tile); the phase selects the weight "tap" coordinate and the output view
   int ncols;                   // valid output columns (Cout)

@@ -44,10 +44,10 @@ struct F2Tile {
   int n_tile, n, x0, y0;
   bool dummy;
 };
-__device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile) {
+__device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile, int sub = 0) {
   F2Tile t;
   t.n_tile = tile / p.m_tiles;
-  const int m = tile - t.n_tile * p.m_tiles;
+  const int m = (tile - t.n_tile * p.m_tiles) * p.mp + sub;
   t.dummy = m >= p.m_tiles_real;
   const int xb = m % p.xb;
   const int r = m / p.xb;
@@ -58,7 +58,7 @@ __device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile) {
   return t;
 }
 
-template <int BN>
+template <int BN, int MP>
 __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_constant__ Igemm2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -81,9 +81,11 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
   const uint16_t mc_mask = static_cast<uint16_t>((1u << cs) - 1u);
   const bool ring = p.b_stages > 0;
-  const uint32_t a_slot = static_cast<uint32_t>(p.halo_bytes + 1023) & ~1023u;
+  const uint32_t a_half = static_cast<uint32_t>(p.halo_bytes + 1023) & ~1023u;  // one pixel tile's halo box
+  const uint32_t a_slot = a_half * MP;
   constexpr uint32_t kBItem = BN * 128;
-  constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  constexpr uint32_t kTmemCols = 2 * MP * BN < 32 ? 32 : 2 * MP * BN;
+  static_assert(kTmemCols <= 512, "accumulators exceed TMEM");
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < p.a_stages; ++s) {
@@ -124,13 +126,18 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       int stage = 0;
       uint32_t phase = 0;
       for (int g = cidx; g < ngroups; g += nclusters) {
-        const F2Tile t = f2_decode(p, g * cs + rank);
+        F2Tile t[MP];
+#pragma unroll
+        for (int sub = 0; sub < MP; ++sub) t[sub] = f2_decode(p, g * cs + rank, sub);
         for (int seg = 0; seg < p.num_segs; ++seg) {
           const int ncb = p.seg_cblocks[seg];
           for (int cb = 0; cb < ncb; ++cb) {
             mbar_wait(aempty(stage), phase ^ 1u);
-            mbar_expect_tx(afull(stage), p.halo_bytes);
-            tma_load_4d(a_base + stage * a_slot, &p.amap[seg], afull(stage), cb * 64, t.x0 - p.pad, t.y0 - p.pad, t.n);
+            mbar_expect_tx(afull(stage), p.halo_bytes * MP);
+#pragma unroll
+            for (int sub = 0; sub < MP; ++sub)
+              tma_load_4d(a_base + stage * a_slot + sub * a_half, &p.amap[seg], afull(stage), cb * 64, t[sub].x0 - p.pad,
+                          t[sub].y0 - p.pad, t[sub].n);
             if (++stage == p.a_stages) {
               stage = 0;
               phase ^= 1u;
@@ -202,8 +209,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       for (int g = cidx; g < ngroups; g += nclusters) {
         mbar_wait(tempty(acc), acc_phase ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
-        uint32_t accumulate = 0;
+        const uint32_t d_tmem = tmem_base + acc * (MP * BN);
         uint32_t b_item = (b_base >> 4) | (1u << 16);   // stationary weights: walks through the resident tiles
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait(afull(astage), aphase);
@@ -221,19 +227,22 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 b_lo = b_item;
                 b_item += kBItem >> 4;
               }
-              const uint32_t a_tap = a_lo + tap_lo[tap];
+              const uint32_t fresh = (kb == 0 && tap == 0) ? 0u : 1u;
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                asm volatile(
-                    "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-                    "mov.b64 da, {%1, %2};\n\t"
-                    "mov.b64 db, {%3, %4};\n\t"
-                    "setp.ne.b32 p, %6, 0;\n\t"
-                    "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
-                    ::"r"(d_tmem), "r"(a_tap + 2u * k), "r"(a_hi), "r"(b_lo + 2u * k), "r"(b_hi), "r"(idesc),
-                      "r"(accumulate)
-                    : "memory");
-                accumulate = 1;
+              for (int sub = 0; sub < MP; ++sub) {      // the same weight tile against each pixel tile of the item
+                const uint32_t a_tap = a_lo + sub * (a_half >> 4) + tap_lo[tap];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  asm volatile(
+                      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+                      "mov.b64 da, {%1, %2};\n\t"
+                      "mov.b64 db, {%3, %4};\n\t"
+                      "setp.ne.b32 p, %6, 0;\n\t"
+                      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+                      ::"r"(d_tmem + sub * BN), "r"(a_tap + 2u * k), "r"(a_hi), "r"(b_lo + 2u * k), "r"(b_hi), "r"(idesc),
+                        "r"(k == 0 ? fresh : 1u)
+                      : "memory");
+                }
               }
               if (ring) {
                 if (cs == 1)
@@ -299,14 +308,12 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     uint32_t acc_phase = 0;
     uint32_t it = 0;  // staging buffer toggle
     for (int g = cidx; g < ngroups; g += nclusters) {
-      const F2Tile t = f2_decode(p, g * cs + rank);
-      const bool tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
-      const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
-      const int o_phase = p.nt_per_phase ? t.n_tile / p.nt_per_phase : 0;
-      const int row0 = (p.nt_per_phase ? t.n_tile % p.nt_per_phase : t.n_tile) * BN;   // first output column of the tile
-      if (t.n_tile != run_ntile) {
+      const int item_ntile = (g * cs + rank) / p.m_tiles;
+      const int o_phase = p.nt_per_phase ? item_ntile / p.nt_per_phase : 0;
+      const int row0 = (p.nt_per_phase ? item_ntile % p.nt_per_phase : item_ntile) * BN;   // first output column of the tile
+      if (item_ntile != run_ntile) {
         if (do_stats) flush_stats();
-        run_ntile = t.n_tile;
+        run_ntile = item_ntile;
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et < BN) {
           const int col = row0 + et;
@@ -316,7 +323,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       }
       mbar_wait(tfull(acc), acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + hcol * 32;
+#pragma unroll 1
+      for (int sub = 0; sub < MP; ++sub) {
+      const F2Tile t = f2_decode(p, g * cs + rank, sub);
+      const bool tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
+      const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
+      const uint32_t t_addr =
+          tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (MP * BN) + sub * BN + hcol * 32;
 #pragma unroll 1
       for (int ch = 0; ch < kChunks; ++ch) {
         const int col0 = row0 + ch * 64;
@@ -381,6 +394,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
           run_q[ch][1] += q1;
         }
       }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty(acc));
@@ -400,12 +414,12 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   }
 }
 
-template <int BN>
+template <int BN, int MP>
 static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
   static int configured = 0;
   if (configured < smem_bytes) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_fwd2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
     configured = smem_bytes;
   }
@@ -426,14 +440,16 @@ static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_byte
   }
   cfg.attrs = attr;
   cfg.numAttrs = nattr;
-  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP>, p);
 }
 
 cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream) {
   switch (bn) {
-    case 64: return launch_fwd2_bn<64>(p, grid, smem_bytes, stream);
-    case 128: return launch_fwd2_bn<128>(p, grid, smem_bytes, stream);
-    case 256: return launch_fwd2_bn<256>(p, grid, smem_bytes, stream);
+    case 64: return launch_fwd2_bn<64, 1>(p, grid, smem_bytes, stream);
+    case 128:
+      return p.mp == 2 ? launch_fwd2_bn<128, 2>(p, grid, smem_bytes, stream)
+                       : launch_fwd2_bn<128, 1>(p, grid, smem_bytes, stream);
+    case 256: return launch_fwd2_bn<256, 1>(p, grid, smem_bytes, stream);
     default: return cudaErrorInvalidValue;
   }
 }

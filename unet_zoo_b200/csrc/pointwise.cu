@@ -727,8 +727,10 @@ __global__ void reduce_rows_kernel(const float* __restrict__ partial, int rows, 
 }
 
 cudaError_t launch_bn_bwd_finalize(const float* partial, int rows, int C, double count, const float* bn, float* dgamma,
-                                   float* dbeta, int accumulate, float* coef, cudaStream_t st) {
-  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, count, bn, dgamma, dbeta, accumulate, coef, 0, nullptr);
+                                   float* dbeta, int accumulate, float* coef, cudaStream_t st, int q_is_gz,
+                                   float* dbias) {
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, C, count, bn, dgamma, dbeta, accumulate, coef,
+                                                         q_is_gz, dbias);
   return cudaGetLastError();
 }
 cudaError_t launch_reduce_rows(const float* partial, int rows, int C, float* out, int accumulate, cudaStream_t st) {

@@ -43,7 +43,8 @@ __device__ __forceinline__ float pw_sigmoid(float v) { return 1.f / (1.f + __exp
 
 // launchers exported by pointwise.cu for reuse by the other translation units
 cudaError_t launch_bn_bwd_finalize(const float* partial, int rows, int C, double count, const float* bn, float* dgamma,
-                                   float* dbeta, int accumulate, float* coef, cudaStream_t st);
+                                   float* dbeta, int accumulate, float* coef, cudaStream_t st, int q_is_gz = 0,
+                                   float* dbias = nullptr);
 cudaError_t launch_reduce_rows(const float* partial, int rows, int C, float* out, int accumulate, cudaStream_t st);
 
 }  // namespace uz

@@ -505,6 +505,52 @@ def head1x1_backward(c: Ctx, y: Act, conv, dlogits: torch.Tensor):
     c.pready(conv.weight, conv.bias)
 
 
+def conv_bn_act_head(ctx: Ctx, xs: Sequence[Act], conv, bn, head, relu: bool = True) -> torch.Tensor:
+    """head(ReLU(BatchNorm2d(Conv2d(cat(xs))))) where the activation is consumed by the 1x1 head ONLY: the last
+    DoubleConv / VGGBlock half followed by OutConv (common_layers.py:28-33,125-128; attention_unet.py:70,108;
+    nested_unet.py:69,104).  Training: the full-resolution activation and its gradient are never stored
+    (uz_bn_head_fwd / uz_bn_head_bwd).  Inference, wide heads or odd widths fall back to conv_bn_act + head1x1."""
+    cout, K = conv.out_channels, head.out_channels
+    if not ctx.training or K > 4 or cout < 8 or cout > 256 or (cout & (cout - 1)):
+        return head1x1(ctx, conv_bn_act(ctx, xs, conv, bn, relu=relu), head)
+    a0 = xs[0]
+    N, H, W = a0.N, a0.H, a0.W
+    wp = ctx.pack(conv.weight, "conv_fwd")
+    z = ctx.new_act(N, H, W, cout)
+    stats = ctx.f32(ctx.stats_rows, 2, cout)
+    ctx.conv(L.CONV3X3, xs, wp, cout, conv.bias, z.ptr, z.ld, H, W, stats, L.FLAG_STATS)
+    bnbuf = ctx.f32(4, cout)
+    ctx.bn_finalize(stats, ctx.stats_rows, cout, N * H * W, bn, bnbuf)
+    logits = torch.empty((N, K, H, W), dtype=torch.float32, device=ctx.device)
+    hw_ = head.weight.detach().reshape(K, -1)
+    with _Timed("bn_apply", 2.0 * z.npix * cout):
+        rc = ctx.lib.uz_bn_head_fwd(z.ptr, z.ld, N, H, W, cout, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), int(relu), K,
+                                    hw_.data_ptr(), _ptr(head.bias), logits.data_ptr(), ctx.stream)
+    L.check(rc, "uz_bn_head_fwd")
+    ctx.launches += 1
+    idx = len(ctx.outputs)
+    ctx.outputs.append(logits)
+    if ctx.record:
+        def backward(c: Ctx):
+            g = c.out_grads[idx] if idx < len(c.out_grads) else None
+            if g is None:
+                raise RuntimeError("unet_zoo_b200: the classifier head received no gradient")
+            dl = g.contiguous().float()
+            dw, db = c.pgrad(head.weight), c.pgrad(head.bias) if head.bias is not None else None
+            ws = c.workspace(c.lib.uz_bn_head_workspace_bytes(cout, K))
+            with _Timed("bn_bwd", 6.0 * z.npix * cout):
+                rc = c.lib.uz_bn_head_bwd(z.ptr, z.ld, N, H, W, cout, bnbuf.data_ptr(), int(relu), K, hw_.data_ptr(),
+                                          dl.data_ptr(), z.ptr, z.ld, _ptr(c.pgrad(bn.weight)), _ptr(c.pgrad(bn.bias)),
+                                          _ptr(c.pgrad(conv.bias) if conv.bias is not None else None), _ptr(dw), _ptr(db),
+                                          0, ws.data_ptr(), ws.numel(), c.stream)
+            L.check(rc, "uz_bn_head_bwd")
+            c.launches += 5
+            c.pready(head.weight, head.bias, bn.weight, bn.bias, conv.bias)
+            _conv_backward(c, xs, conv, z, L.CONV3X3, False, sum(a.C for a in xs), True)
+        ctx.tape.append(backward)
+    return logits
+
+
 def _running_affine(bn, device) -> torch.Tensor:
     """[4][C] = {mean, invstd, scale, shift} of an inference-mode BatchNorm (running statistics)."""
     invstd = torch.rsqrt(bn.running_var.float() + bn.eps)

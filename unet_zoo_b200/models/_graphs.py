@@ -31,8 +31,10 @@ def attention_unet_graph(m, ctx: E.Ctx, x):
         g = E.conv_bn_act(ctx, [d], up[1], up[2], out=E.Act(cat, w, w), mode=L.UP2X_CONV3X3)
         E.attention_gate(ctx, g, skip, getattr(m, f"att{lvl}"), E.Act(cat, 0, w))
         (c1, b1), (c2, b2) = getattr(m, f"upconv{lvl}").units()
-        d = E.conv_bn_act(ctx, [E.conv_bn_act(ctx, [E.Act(cat)], c1, b1)], c2, b2)
-    E.head1x1(ctx, d, m.conv_1x1)
+        h = E.conv_bn_act(ctx, [E.Act(cat)], c1, b1)
+        if lvl > 2:
+            d = E.conv_bn_act(ctx, [h], c2, b2)
+    E.conv_bn_act_head(ctx, [h], c2, b2, m.conv_1x1)          # attention_unet.py:106-108, activation never stored
     return ctx.outputs
 
 
@@ -50,9 +52,11 @@ def nested_unet_graph(m, ctx: E.Ctx, x):
     def upslot(i, j):
         return E.Act(bufs[i], nb[i] * (5 - i) + nb[i + 1] * (j - 1), nb[i + 1])
 
-    def vgg(blk, xs, out, pooled=None, stem=None, need_dx=True):          # VGGBlock.forward, nested_unet.py:13-22
+    def vgg(blk, xs, out, pooled=None, stem=None, need_dx=True, head=None):   # VGGBlock.forward, nested_unet.py:13-22
         (c1, b1), (c2, b2) = blk.units()
         h = E.conv_bn_act(ctx, xs, c1, b1, stem=stem, need_dx=need_dx)
+        if head is not None:                                              # x0_4 feeds `final` only (nested_unet.py:104)
+            return E.conv_bn_act_head(ctx, [h], c2, b2, head)
         return E.conv_bn_act(ctx, [h], c2, b2, out=out, pooled=pooled)
 
     cur, stem = E.stem_input(ctx, x)
@@ -63,12 +67,11 @@ def nested_unet_graph(m, ctx: E.Ctx, x):
     for j in range(1, 5):                                                 # dense columns, nested_unet.py:81-93
         for i in range(0, 5 - j):
             up = E.bilinear_up2x(ctx, node(i + 1, j - 1), upslot(i, j))
-            vgg(getattr(m, f"conv{i}_{j}"), [E.Act(bufs[i], 0, nb[i] * j), up], node(i, j))
+            vgg(getattr(m, f"conv{i}_{j}"), [E.Act(bufs[i], 0, nb[i] * j), up], node(i, j),
+                head=m.final if (j == 4 and not m.deep_supervision) else None)
     if m.deep_supervision:                                                # nested_unet.py:95-102
         for k in range(1, 5):
             E.head1x1(ctx, node(0, k), getattr(m, f"final{k}"))
-    else:
-        E.head1x1(ctx, node(0, 4), m.final)
     return ctx.outputs
 
 

@@ -42,6 +42,8 @@ class UNet(HotPathModel):
             up = getattr(self, f"up_convolution_{j + 1}")
             E.conv_transpose2x2(ctx, cur, up.up, E.Act(cats[lvl], 0, widths[lvl]))
             (c1, b1), (c2, b2) = up.conv.units()
-            cur = E.conv_bn_act(ctx, [E.conv_bn_act(ctx, [E.Act(cats[lvl])], c1, b1)], c2, b2)
-        E.head1x1(ctx, cur, self.out.conv)
+            h = E.conv_bn_act(ctx, [E.Act(cats[lvl])], c1, b1)
+            if lvl > 0:
+                cur = E.conv_bn_act(ctx, [h], c2, b2)
+        E.conv_bn_act_head(ctx, [h], c2, b2, self.out.conv)     # last half + OutConv: the activation is never stored
         return ctx.outputs
