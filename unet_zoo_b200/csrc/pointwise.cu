@@ -196,6 +196,27 @@ __global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int ld, lon
   }
 }
 
+// lane-strided fp64 sums of one channel's {sum, sum-of-squares} partial rows; eight rows are loaded before any is added
+// (the kernel is a chain of dependent L2 round trips otherwise: ~15 us for 1184 rows)
+__device__ __forceinline__ void partial_column_sums(const float* __restrict__ partial, int rows, int C, int c, int lane,
+                                                    double& s, double& q) {
+  constexpr int U = 8;
+  for (int r0 = lane; r0 < rows; r0 += 32 * U) {
+    float a[U], b[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int r = r0 + 32 * u;
+      a[u] = r < rows ? __ldg(partial + static_cast<size_t>(r) * 2 * C + c) : 0.f;
+      b[u] = r < rows ? __ldg(partial + static_cast<size_t>(r) * 2 * C + C + c) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      s += static_cast<double>(a[u]);
+      q += static_cast<double>(b[u]);
+    }
+  }
+}
+
 // partial[rows][2][C] -> bn[4][C] = {mean, invstd, scale, shift}; running statistics updated like nn.BatchNorm2d
 // (momentum EMA, unbiased variance for running_var).  One thread per channel, fp64 accumulation.
 __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
@@ -207,10 +228,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, 
   const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
-  for (int r = lane; r < rows; r += 32) {
-    s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
-    q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
-  }
+  partial_column_sums(partial, rows, C, c, lane, s, q);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -585,10 +603,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
   const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
-  for (int r = lane; r < rows; r += 32) {
-    s += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + c]);
-    q += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + c]);
-  }
+  partial_column_sums(partial, rows, C, c, lane, s, q);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     s += __shfl_xor_sync(0xffffffffu, s, o);

@@ -48,13 +48,15 @@ def _ptr(t: Optional[torch.Tensor]):
 class Buf:
     """One NHWC bf16 device buffer [N, H, W, ld] plus (lazily) its gradient buffer of the same shape."""
 
-    __slots__ = ("data", "grad", "written", "N", "H", "W", "ld")
+    __slots__ = ("data", "grad", "written", "N", "H", "W", "ld", "want_gsum", "gsum")
 
     def __init__(self, N, H, W, ld, device):
         self.data = torch.empty((N, H, W, ld), dtype=torch.bfloat16, device=device)
         self.grad = None
         self.written: List[Tuple[int, int]] = []  # channel intervals of `grad` that already hold a gradient
         self.N, self.H, self.W, self.ld = N, H, W, ld
+        self.want_gsum = False   # a consumer of this buffer's gradient needs its per-channel sums (ConvT bias gradient)
+        self.gsum: List[Tuple[int, int, torch.Tensor]] = []   # (c_lo, c_hi, stats[rows][2][c_hi-c_lo]) from a dgrad epilogue
 
     def grad_buf(self):
         if self.grad is None:
@@ -104,6 +106,10 @@ class Act:
             else:
                 runs.append((a - lo, b - a, acc))
         self.buf.written.append((lo, hi))
+        for r0, rc, acc in runs:   # a second writer makes column sums taken by the first one stale
+            if acc and self.buf.gsum:
+                a, b = lo + r0, lo + r0 + rc
+                self.buf.gsum = [e for e in self.buf.gsum if e[1] <= a or b <= e[0]]
         return runs
 
     def has_grad(self):
@@ -433,8 +439,14 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
                 a.buf.grad_buf()[..., a.c0 + r0:a.c0 + r0 + rc].zero_()
                 acc = True
             w_rows = wpd[off + r0: off + r0 + rc]
-            c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, None,
-                   L.FLAG_ACCUMULATE if acc else 0)
+            stats = None
+            if a.buf.want_gsum and not acc and mode == L.CONV3X3:
+                # the epilogue's per-channel sums of this gradient ARE the bias gradient of the ConvTranspose2d that
+                # produced (part of) the buffer: saves a full read of the gradient (uz_colsum)
+                stats = c.f32(c.stats_rows, 2, rc)
+                a.buf.gsum.append((a.c0 + r0, a.c0 + r0 + rc, stats))
+            c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, stats,
+                   L.FLAG_STATS if stats is not None else (L.FLAG_ACCUMULATE if acc else 0))
         off += a.C
 
 
@@ -448,12 +460,20 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
     wp = ctx.pack(up.weight, "convt_fwd")
     ctx.conv(L.CONVT2X2, [x], wp, cout, up.bias, out.ptr, out.ld, 2 * x.H, 2 * x.W)
     if ctx.record:
+        want_db = up.bias is not None and up.bias.requires_grad
+        out.buf.want_gsum = out.buf.want_gsum or want_db
+
         def backward(c: Ctx):
             dw = c.pgrad(up.weight)
             if dw is not None:
                 c.wgrad(L.CONVT2X2, x.ptr, x.N, x.H, x.W, x.C, x.ld, out.gptr(), cout, out.ld, dw, x.C, 0)
-            if up.bias is not None and up.bias.requires_grad:
-                c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(up.bias))
+            if want_db:
+                lo, hi = out.c0, out.c0 + cout
+                hit = next((e for e in out.buf.gsum if e[0] <= lo and hi <= e[1]), None)
+                if hit is not None:
+                    torch.sum(hit[2][:, 0, lo - hit[0]:hi - hit[0]], dim=0, out=c.pgrad(up.bias))
+                else:
+                    c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(up.bias))
             c.pready(up.weight, up.bias)
             wpd = c.pack(up.weight, "convt_dgrad")  # [Cin][4][Cout]
             for (r0, rc, acc) in x.grad_writes():
