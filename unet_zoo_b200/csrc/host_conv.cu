@@ -424,10 +424,17 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   // shared-memory plan: [A ring][B ring or resident weights][1-2 staging tiles][barriers + bias]
   const int kMaxSmem = 232448 - 1024;  // 227 KB minus the alignment slack
   int a_slot = (p.halo_bytes + 1023) & ~1023;
-  int b_item = bn * 128;
+  // CTA pairs (cta_group::2): 1 = layers with <= 128 output channels (their N = 64 / 128 MMAs are bound by shared-memory
+  // read bandwidth: 192 / 128 B/clk against the 128 B/clk port; the pair halves the B bytes per CTA), 2 = all layers
+  const int pair_env = env_int("UZ_FWD2_PAIR", 1);
+  // measured per layer (tools/bench_conv.py): the pair wins when a tile carries >= 18 (cblock, tap) steps (+4..12 %, up
+  // to 1690 TFLOP/s); with fewer the tile is epilogue bound and pair mode adds ~1 us per tile pair
+  const bool pair_auto = kblocks * p.num_taps >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
+  p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 ? 1 : 0;
+  int b_item = bn * 128 / (p.pair ? 2 : 1);     // bytes of one weight tile per CTA
   const int kTail = 1536;              // barriers (512) + bias vector (1024)
   const long long b_all = (long long)kblocks * p.num_taps * b_item;
-  int cluster = 1;
+  int cluster = p.pair ? 2 : 1;
   bool stationary = false;
   if (p.num_n_tiles == 1 && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
     // weights resident for the whole launch, provided at least four halo stages still fit (TMA latency cover)
@@ -443,7 +450,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     }
   }
   p.mp = 1;
-  if (!stationary && bn == 128 && env_int("UZ_FWD2_MP", 2) == 2) {
+  if (!stationary && !p.pair && bn == 128 && env_int("UZ_FWD2_MP", 2) == 2) {
     // streamed weights, 65..128 output channels: one 128-wide weight tile against TWO pixel tiles (4 x 128 TMEM columns
     // with double buffering).  Measured: 128->128 @256^2 0.496 -> 0.455 ms, 256->128 0.921 -> 0.854 ms.  Wider layers
     // stay on BN = 256 (one A read per 256 columns is cheaper in shared-memory bandwidth than two tiles x 128)
@@ -458,9 +465,11 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     }
   }
   if (!stationary) {
-    cluster = env_int("UZ_FWD2_CLUSTER", 1);
-    if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
-    if (bn / cluster < 16) cluster = 1;
+    if (!p.pair) {
+      cluster = env_int("UZ_FWD2_CLUSTER", 1);
+      if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
+      if (bn / cluster < 16) cluster = 1;
+    }
     p.stg_bufs = bn == 256 ? 1 : 2;
     p.a_stages = env_int("UZ_FWD2_A_STAGES", p.mp == 2 ? (a_slot > 40000 ? 2 : 3) : bn == 256 ? 2 : bn == 128 ? 3 : 4);
     if (p.a_stages < 1 || p.a_stages > 6) p.a_stages = 2;

@@ -114,6 +114,9 @@ struct alignas(64) Igemm2Params {
   int a_off, b_off, stg_off, bar_off;  // byte offsets from the 1024-aligned smem base
   int stg_bufs;                // staging tiles for the TMA-store epilogue (1 or 2)
   int cluster;                 // thread-block cluster size (1, 2 or 4): weight tiles are multicast when > 1
+  int pair;                    // 1: the 2-cluster is a tcgen05 CTA pair (cta_group::2): ONE M = 256 MMA covers both CTAs'
+                               // pixel tiles, each CTA holds half of the weight rows (halves the B bytes read from shared
+                               // memory per MMA: N = 64 / 128 tiles are shared-memory-bandwidth bound otherwise)
   int mp;                      // M tiles per work item (1 or 2).  2: every streamed weight tile feeds TWO pixel tiles (two
                                // TMEM accumulators), halving the weight bytes an SM has to ingest per MMA cycle - the
                                // streamed-weight layers were capped at ~72 % tensor-active by SM ingest (~50 B/clk)

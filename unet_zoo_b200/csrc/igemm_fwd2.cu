@@ -58,7 +58,7 @@ __device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile, int
   return t;
 }
 
-template <int BN, int MP>
+template <int BN, int MP, int CG>
 __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_constant__ Igemm2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -71,9 +71,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   auto bfull = [&](int s) { return bars + 128u + 8u * s; };
   auto bempty = [&](int s) { return bars + 256u + 8u * s; };
   auto tfull = [&](int s) { return bars + 384u + 8u * s; };
-  auto tempty = [&](int s) { return bars + 400u + 8u * s; };
-  const uint32_t tmem_slot = bars + 416u;
-  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + p.bar_off + 416);
+  auto tempty = [&](int s) { return bars + 416u + 8u * s; };
+  const uint32_t tmem_slot = bars + 448u;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + p.bar_off + 448);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -83,8 +83,14 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   const bool ring = p.b_stages > 0;
   const uint32_t a_half = static_cast<uint32_t>(p.halo_bytes + 1023) & ~1023u;  // one pixel tile's halo box
   const uint32_t a_slot = a_half * MP;
-  constexpr uint32_t kBItem = BN * 128;
-  constexpr uint32_t kTmemCols = 2 * MP * BN < 32 ? 32 : 2 * MP * BN;
+  constexpr bool kPair = CG == 2;                // CTA pair: see Igemm2Params::pair
+  static_assert(!kPair || MP == 1, "pair mode has one pixel tile per CTA");
+  constexpr uint32_t kBItem = BN * 128 / CG;     // bytes of one (cblock, tap) weight tile held by THIS CTA
+  const bool leader = !kPair || rank == 0;
+  // accumulator stages: as many as TMEM holds, at most 4 (short-K layers are bound by the tfull -> epilogue -> tempty ->
+  // MMA round trip, which crosses SMs in pair mode)
+  constexpr int kAcc = 512 / (MP * BN) > 4 ? 4 : 512 / (MP * BN);
+  constexpr uint32_t kTmemCols = kAcc * MP * BN;
   static_assert(kTmemCols <= 512, "accumulators exceed TMEM");
 
   if (warp == 0 && lane == 0) {
@@ -95,11 +101,11 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     const int nb = ring ? p.b_stages : 1;
     for (int s = 0; s < nb; ++s) {
       mbar_init(bfull(s), 1);
-      mbar_init(bempty(s), cs);
+      mbar_init(bempty(s), kPair ? 1 : cs);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kAcc; ++s) {
       mbar_init(tfull(s), 1);
-      mbar_init(tempty(s), 8);
+      mbar_init(tempty(s), 8 * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
     }
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
@@ -107,8 +113,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     for (int i = 0; i < (p.nt_per_phase ? 4 : 1); ++i) tma_prefetch_desc(&p.omap[i]);
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, kTmemCols);
-    tmem_relinquish();
+    if (kPair) {
+      tmem_alloc2(tmem_slot, kTmemCols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(tmem_slot, kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -133,11 +144,17 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
           const int ncb = p.seg_cblocks[seg];
           for (int cb = 0; cb < ncb; ++cb) {
             mbar_wait(aempty(stage), phase ^ 1u);
-            mbar_expect_tx(afull(stage), p.halo_bytes * MP);
+            if (kPair) {   // both halos complete on the leader's barrier
+              if (leader) mbar_expect_tx(afull(stage), p.halo_bytes * 2);
+              tma_load_4d_pair(a_base + stage * a_slot, &p.amap[seg], afull(stage), cb * 64, t[0].x0 - p.pad,
+                               t[0].y0 - p.pad, t[0].n);
+            } else {
+              mbar_expect_tx(afull(stage), p.halo_bytes * MP);
 #pragma unroll
-            for (int sub = 0; sub < MP; ++sub)
-              tma_load_4d(a_base + stage * a_slot + sub * a_half, &p.amap[seg], afull(stage), cb * 64, t[sub].x0 - p.pad,
-                          t[sub].y0 - p.pad, t[sub].n);
+              for (int sub = 0; sub < MP; ++sub)
+                tma_load_4d(a_base + stage * a_slot + sub * a_half, &p.amap[seg], afull(stage), cb * 64,
+                            t[sub].x0 - p.pad, t[sub].y0 - p.pad, t[sub].n);
+            }
             if (++stage == p.a_stages) {
               stage = 0;
               phase ^= 1u;
@@ -151,12 +168,17 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     if (elect_one()) {
       if (!ring) {
         // stationary: every (cblock, tap) tile is loaded once and stays for the whole launch (num_n_tiles == 1)
-        mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.kblocks * p.num_taps) * kBItem);
+        if (leader) mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.kblocks * p.num_taps) * kBItem * CG);
         int item = 0;
         for (int seg = 0; seg < p.num_segs; ++seg)
           for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb)
-            for (int tap = 0; tap < p.num_taps; ++tap, ++item)
-              tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap], 0);
+            for (int tap = 0; tap < p.num_taps; ++tap, ++item) {
+              if (kPair)   // this CTA's half of the weight rows
+                tma_load_3d_pair(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap],
+                                 rank * (BN / 2));
+              else
+                tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap], 0);
+            }
       } else {
         int stage = 0;
         uint32_t phase = 0;
@@ -171,10 +193,12 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
               const int k = p.seg_k0[seg] + cb * 64;
               for (int tap = 0; tap < p.num_taps; ++tap) {
                 mbar_wait(bempty(stage), phase ^ 1u);
-                mbar_expect_tx(bfull(stage), kBItem);
+                if (leader) mbar_expect_tx(bfull(stage), kBItem * CG);
                 const uint32_t dst = b_base + stage * kBItem;
                 const int btap = b_phase >= 0 ? b_phase : p.tap_b[tap];
-                if (cs == 1)
+                if (kPair)
+                  tma_load_3d_pair(dst, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows);
+                else if (cs == 1)
                   tma_load_3d(dst, &p.bmap, bfull(stage), k, btap, b_row0);
                 else
                   tma_load_3d_mc(dst + rank * rows * 128, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows, mc_mask);
@@ -192,8 +216,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     // ------------------------------------------------------------------ MMA issuer (one thread)
     // The issue loop must stay ahead of the tensor core (64 cycles per MMA at BN = 128): descriptors are kept as
     // (lo, hi) words, hi is loop invariant, lo advances by plain 32-bit adds (tap row offset, K step of 32 bytes).
-    if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+    if (leader && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, BN, 0, 0);
       const uint32_t a_hi = ((static_cast<uint32_t>(p.halo_w * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
       const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
       uint32_t tap_lo[9];
@@ -233,19 +257,17 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 const uint32_t a_tap = a_lo + sub * (a_half >> 4) + tap_lo[tap];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  asm volatile(
-                      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-                      "mov.b64 da, {%1, %2};\n\t"
-                      "mov.b64 db, {%3, %4};\n\t"
-                      "setp.ne.b32 p, %6, 0;\n\t"
-                      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
-                      ::"r"(d_tmem + sub * BN), "r"(a_tap + 2u * k), "r"(a_hi), "r"(b_lo + 2u * k), "r"(b_hi), "r"(idesc),
-                        "r"(k == 0 ? fresh : 1u)
-                      : "memory");
+                  if (kPair)
+                    umma2_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_lo + 2u * k, b_hi, idesc, k == 0 ? fresh : 1u);
+                  else
+                    umma_bf16_words(d_tmem + sub * BN, a_tap + 2u * k, a_hi, b_lo + 2u * k, b_hi, idesc,
+                                    k == 0 ? fresh : 1u);
                 }
               }
               if (ring) {
-                if (cs == 1)
+                if (kPair)
+                  umma2_commit_mc(bempty(bstage));
+                else if (cs == 1)
                   umma_commit(bempty(bstage));
                 else
                   umma_commit_mc(bempty(bstage), mc_mask);
@@ -256,15 +278,23 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
               }
             }
           }
-          umma_commit(aempty(astage));
+          if (kPair)
+            umma2_commit_mc(aempty(astage));
+          else
+            umma_commit(aempty(astage));
           if (++astage == p.a_stages) {
             astage = 0;
             aphase ^= 1u;
           }
         }
-        umma_commit(tfull(acc));
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1u;
+        if (kPair)
+          umma2_commit_mc(tfull(acc));
+        else
+          umma_commit(tfull(acc));
+        if (++acc == kAcc) {
+          acc = 0;
+          acc_phase ^= 1u;
+        }
       }
     }
   } else if (warp >= 4) {
@@ -397,9 +427,16 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty(acc));
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1u;
+      if (lane == 0) {
+        if (kPair)
+          mbar_arrive_cluster(tempty(acc), 0);   // the accumulator pair is free when BOTH CTAs have drained theirs
+        else
+          mbar_arrive(tempty(acc));
+      }
+      if (++acc == kAcc) {
+        acc = 0;
+        acc_phase ^= 1u;
+      }
     }
     if (do_stats) flush_stats();
     if (et == 0) tma_store_wait_all();
@@ -410,16 +447,19 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   if (cs > 1) cluster_sync_all();  // nobody leaves while a peer may still multicast into / signal this CTA
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if (kPair)
+      tmem_dealloc2(tmem_base, kTmemCols);
+    else
+      tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
-template <int BN, int MP>
+template <int BN, int MP, int CG>
 static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
   static int configured = 0;
   if (configured < smem_bytes) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
     configured = smem_bytes;
   }
@@ -440,16 +480,21 @@ static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_byte
   }
   cfg.attrs = attr;
   cfg.numAttrs = nattr;
-  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP, CG>, p);
 }
 
 cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream) {
   switch (bn) {
-    case 64: return launch_fwd2_bn<64, 1>(p, grid, smem_bytes, stream);
+    case 64:
+      return p.pair ? launch_fwd2_bn<64, 1, 2>(p, grid, smem_bytes, stream)
+                    : launch_fwd2_bn<64, 1, 1>(p, grid, smem_bytes, stream);
     case 128:
-      return p.mp == 2 ? launch_fwd2_bn<128, 2>(p, grid, smem_bytes, stream)
-                       : launch_fwd2_bn<128, 1>(p, grid, smem_bytes, stream);
-    case 256: return launch_fwd2_bn<256, 1>(p, grid, smem_bytes, stream);
+      return p.pair      ? launch_fwd2_bn<128, 1, 2>(p, grid, smem_bytes, stream)
+             : p.mp == 2 ? launch_fwd2_bn<128, 2, 1>(p, grid, smem_bytes, stream)
+                         : launch_fwd2_bn<128, 1, 1>(p, grid, smem_bytes, stream);
+    case 256:
+      return p.pair ? launch_fwd2_bn<256, 1, 2>(p, grid, smem_bytes, stream)
+                    : launch_fwd2_bn<256, 1, 1>(p, grid, smem_bytes, stream);
     default: return cudaErrorInvalidValue;
   }
 }
