@@ -70,7 +70,7 @@ struct Lattice {
 // 4-D (C, W, H, N) bf16 view of an NHWC activation (pixel stride ld elements), restricted to the pixel lattice
 // (oy + step*i, ox + step*j); box = (64 channels, tw, th, tn), 128-byte swizzle, zero fill outside.
 static int make_act_map(CUtensorMap* m, const void* ptr, int C, int ld, int N, int H, int W, Lattice lat, int tw,
-                        int th, int tn) {
+                        int th, int tn, int box_c = 64) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const int Hl = (H - lat.oy + lat.step - 1) / lat.step;
@@ -80,11 +80,11 @@ static int make_act_map(CUtensorMap* m, const void* ptr, int C, int ld, int N, i
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Wl, (cuuint64_t)Hl, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)ld * 2 * lat.step, (cuuint64_t)W * ld * 2 * lat.step,
                            (cuuint64_t)H * W * ld * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
+  cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<char*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, box_c == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled(activation C=%d ld=%d N=%d H=%d W=%d) failed: %d", C, ld,
                      N, H, W, (int)r);
@@ -669,7 +669,7 @@ static bool use_wgrad2(int mode, int H, int W) {
   return !disabled && mode == UZ_CONV3X3 && H >= 16 && W >= 8;
 }
 struct Wg2Plan {
-  int xb, yb, chunks, co_blocks, ci_blocks, splits;
+  int xb, yb, chunks, co_blocks, ci_blocks, splits, pair, ci_units;
   size_t ws_bytes;
 };
 static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
@@ -679,9 +679,14 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   pl.chunks = N * pl.xb * pl.yb;
   pl.co_blocks = (cout + 63) / 64;
   pl.ci_blocks = (cin + 63) / 64;
-  const int units = pl.co_blocks * pl.ci_blocks;
   int sms = sm_count();
   if (sms < 1) sms = 148;
+  // CTA pairs (cta_group::2) over two adjacent input-channel blocks: the M = 128, N = 64 MMA of a single CTA reads
+  // 192 B/clk of shared memory (67 % ceiling, measured 59-64 % tensor-active); the pair halves the dZ bytes per CTA
+  pl.pair = (pl.ci_blocks >= 2 && sms >= 2 && env_int("UZ_WGRAD2_PAIR", 1)) ? 1 : 0;
+  pl.ci_units = pl.pair ? (pl.ci_blocks + 1) / 2 : pl.ci_blocks;
+  const int units = pl.co_blocks * pl.ci_units;
+  if (pl.pair) sms /= 2;   // work is scheduled over CTA pairs
   // split-K factor: minimise the makespan  waves(items) x (chunks per item + epilogue)  over the persistent grid -
   // an item count just above a multiple of the SM count would run a nearly empty extra wave (measured: 256->256 @128^2
   // took 1.43x its ideal time with 304 items on 148 SMs).  The epilogue (147 KB of fp32 partials, not overlapped with
@@ -730,7 +735,10 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
     const Lattice full2 = {0, 0, 1};
     int rc2 = make_act_map(&q.xmap, x, cin, x_ld, N, H, W, full2, 10, 18, 1);
     if (rc2 == UZ_OK) rc2 = make_act_map(&q.dzmap, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1);
+    if (rc2 == UZ_OK && p2.pair) rc2 = make_act_map(&q.dzmap_half, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1, 32);
     if (rc2 != UZ_OK) return rc2;
+    q.pair = p2.pair;
+    q.ci_units = p2.ci_units;
     q.xb = p2.xb;
     q.yb = p2.yb;
     q.total_chunks = p2.chunks;
@@ -739,10 +747,11 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
     q.co_blocks = p2.co_blocks;
     q.ci_blocks = p2.ci_blocks;
     q.splits = p2.splits;
-    q.total_items = p2.co_blocks * p2.ci_blocks * p2.splits;
+    q.total_items = p2.co_blocks * p2.ci_units * p2.splits;
     q.partial = static_cast<float*>(workspace);
     cudaStream_t st2 = static_cast<cudaStream_t>(stream);
-    const int grid2 = q.total_items < sms ? q.total_items : sms;
+    const int grid2 = p2.pair ? 2 * (q.total_items < sms / 2 ? q.total_items : sms / 2)
+                              : (q.total_items < sms ? q.total_items : sms);
     cudaError_t e2 = launch_igemm_wgrad2(q, grid2, st2);
     if (e2 != cudaSuccess) return cuda_error(e2, "igemm_wgrad2 launch");
     e2 = launch_wgrad_reduce(q.partial, dw + (long long)c_off * 9, p2.splits, cout, 9, cin, (long long)cin_total * 9, 9, 1,

@@ -83,6 +83,12 @@ struct alignas(64) Wgrad2Params {
   int splits;          // split-K factor over the chunk range
   int total_items;     // co_blocks * ci_blocks * splits
   float* partial;      // [splits][cp][9][cq] fp32
+  // CTA-pair mode (cta_group::2): the two CTAs of a cluster take two adjacent input-channel blocks of the same
+  // (output-channel block, chunk range); each loads its own X halo and HALF of the dZ chunk (32 channels), one
+  // M = 256, N = 64 MMA serves both.  Per CTA and MMA 5 KB instead of 6 KB leave shared memory (160 vs 192 B/clk).
+  CUtensorMap dzmap_half;  // dZ: box (32, 8, 16, 1), SWIZZLE_64B
+  int pair;                // 0 / 1
+  int ci_units;            // ci_blocks (single CTA) or ceil(ci_blocks / 2) (pair)
 };
 
 // Second-generation forward-type implicit GEMM (igemm_fwd2.cu): conv3x3 / its data gradient / conv1x1 on 8x16-pixel

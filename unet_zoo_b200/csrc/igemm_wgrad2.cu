@@ -13,6 +13,8 @@
 // TWO taps x 64 input channels: the descriptor's leading-dimension byte offset (distance between the two 64-element MN
 // atoms) is simply the address shift between the two taps (128 B for dx+1, 1280 B for dy+1), so five MMAs cover the nine
 // taps (the tenth half is discarded).  B = dZ chunk, N = 64 output channels.  D blocks live in 5 x 64 TMEM columns.
+#include <string.h>
+
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -32,20 +34,26 @@ struct W2Item {
   int co_blk, ci_blk, split, chunk_begin, chunk_end;
 };
 
-__device__ __forceinline__ W2Item w2_decode(const Wgrad2Params& p, int item) {
+// `rank` = CTA rank inside the pair (0 when single): the pair's CTAs take adjacent input-channel blocks
+__device__ __forceinline__ W2Item w2_decode(const Wgrad2Params& p, int item, int cg, int rank) {
   W2Item w;
-  const int units = p.co_blocks * p.ci_blocks;
+  const int units = p.co_blocks * p.ci_units;
   w.split = item / units;
   const int u = item - w.split * units;
-  w.co_blk = u / p.ci_blocks;
-  w.ci_blk = u - w.co_blk * p.ci_blocks;
+  w.co_blk = u / p.ci_units;
+  w.ci_blk = (u - w.co_blk * p.ci_units) * cg + rank;
   const int base = p.total_chunks / p.splits, rem = p.total_chunks % p.splits;
   w.chunk_begin = w.split * base + min(w.split, rem);
   w.chunk_end = w.chunk_begin + base + (w.split < rem ? 1 : 0);
   return w;
 }
 
+template <int CG>
 __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+  constexpr bool kPair = CG == 2;
+  const int rank = kPair ? static_cast<int>(cluster_ctarank()) : 0;
+  const bool leader = rank == 0;
+  const int first_item = blockIdx.x / CG, item_step = gridDim.x / CG;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
@@ -68,17 +76,23 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(tfull_bar, 1);
-    mbar_init(tempty_bar, 4);
+    mbar_init(tempty_bar, 4 * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&p.xmap);
-    tma_prefetch_desc(&p.dzmap);
+    tma_prefetch_desc(kPair ? &p.dzmap_half : &p.dzmap);
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, kW2TmemCols);
-    tmem_relinquish();
+    if (kPair) {
+      tmem_alloc2(tmem_slot, kW2TmemCols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(tmem_slot, kW2TmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (kPair) cluster_sync_all();   // the peer's barriers exist before a remote completion can reach them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -87,8 +101,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-        const W2Item w = w2_decode(p, item);
+      for (int item = first_item; item < p.total_items; item += item_step) {
+        const W2Item w = w2_decode(p, item, CG, rank);
         for (int chunk = w.chunk_begin; chunk < w.chunk_end; ++chunk) {
           const int xb = chunk % p.xb;
           int r = chunk / p.xb;
@@ -98,9 +112,15 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t halo_dst = base + stage * kW2StageBytes;
           const uint32_t dz_dst = halo_dst + kW2HaloSlot;
-          mbar_expect_tx(full_bar(stage), kW2HaloBytes + kW2DzBytes);
-          tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
-          tma_load_4d(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * 64, x0, y0, n);
+          if (kPair) {   // own halo + own half of the dZ chunk; everything completes on the leader's barrier
+            if (leader) mbar_expect_tx(full_bar(stage), 2 * kW2HaloBytes + kW2DzBytes);
+            tma_load_4d_pair(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+            tma_load_4d_pair(dz_dst, &p.dzmap_half, full_bar(stage), w.co_blk * 64 + rank * 32, x0, y0, n);
+          } else {
+            mbar_expect_tx(full_bar(stage), kW2HaloBytes + kW2DzBytes);
+            tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+            tma_load_4d(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * 64, x0, y0, n);
+          }
           if (++stage == kW2Stages) {
             stage = 0;
             phase ^= 1u;
@@ -110,8 +130,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
-    if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);  // both operands MN-major
+    if (leader && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 64, 1, 1);  // both operands MN-major
       // tap pairs stacked along M: {first tap row offset (in halo pixels), byte distance to the second tap}
       //   taps are (dy, dx) in {-1,0,1}^2 with tap index (dy+1)*3 + (dx+1); halo row of tap = (dy+1)*10 + (dx+1)
       constexpr int pair_row[5] = {0 * 10 + 0, 1 * 10 + 0, 2 * 10 + 0, 0 * 10 + 2, 2 * 10 + 2};
@@ -119,8 +139,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_phase = 0;
-      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-        const W2Item w = w2_decode(p, item);
+      for (int item = first_item; item < p.total_items; item += item_step) {
+        const W2Item w = w2_decode(p, item, CG, rank);
         if (w.chunk_end <= w.chunk_begin) continue;
         mbar_wait(tempty_bar, acc_phase ^ 1u);
         tc_fence_after();
@@ -133,25 +153,37 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           const uint32_t halo_lo = umma_desc_lo(halo, 0);
           const uint32_t dz_lo = umma_desc_lo(dz, 1024);
           constexpr uint32_t a_hi = umma_desc_hi(kW2HaloW * 128);
-          constexpr uint32_t b_hi = umma_desc_hi(1024);
+          // dZ: 128-byte pixel rows (SWIZZLE_128B), or the pair's 64-byte half rows (SWIZZLE_64B = layout code 4)
+          constexpr uint32_t b_hi = kPair ? (((512u >> 4) & 0x3FFFu) | (1u << 14) | (4u << 29)) : umma_desc_hi(1024);
+          constexpr uint32_t b_kstep = (kPair ? 1024u : 2048u) >> 4;   // 16 pixels further, in 16-byte units
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 16 pixels = image rows 2j, 2j+1 of the chunk
 #pragma unroll
             for (int b = 0; b < 5; ++b) {
               // start row of the tap pair (+ two halo rows per K step), LBO = byte distance to the pair's second tap
               const uint32_t a_lo = halo_lo + ((pair_row[b] * 128 + j * 2 * kW2HaloW * 128) >> 4) + ((pair_lbo[b] >> 4) << 16);
-              umma_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + ((j * 2048) >> 4), b_hi, idesc,
-                              (first && j == 0) ? 0u : 1u);
+              if (kPair)
+                umma2_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc,
+                                 (first && j == 0) ? 0u : 1u);
+              else
+                umma_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc,
+                                (first && j == 0) ? 0u : 1u);
             }
           }
           first = false;
-          umma_commit(empty_bar(stage));
+          if (kPair)
+            umma2_commit_mc(empty_bar(stage));
+          else
+            umma_commit(empty_bar(stage));
           if (++stage == kW2Stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(tfull_bar);
+        if (kPair)
+          umma2_commit_mc(tfull_bar);
+        else
+          umma_commit(tfull_bar);
         acc_phase ^= 1u;
       }
     }
@@ -163,8 +195,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     const int ci_l = row & 63;
     constexpr int pair_tap[5][2] = {{0, 1}, {3, 4}, {6, 7}, {2, 5}, {8, -1}};
     uint32_t acc_phase = 0;
-    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-      const W2Item w = w2_decode(p, item);
+    for (int item = first_item; item < p.total_items; item += item_step) {
+      const W2Item w = w2_decode(p, item, CG, rank);
       const bool has_work = w.chunk_end > w.chunk_begin;
       if (has_work) {
         mbar_wait(tfull_bar, acc_phase);
@@ -199,7 +231,12 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       if (has_work) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar);
+        if (lane == 0) {
+          if (kPair)
+            mbar_arrive_cluster(tempty_bar, 0);
+          else
+            mbar_arrive(tempty_bar);
+        }
         acc_phase ^= 1u;
       }
     }
@@ -207,22 +244,43 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
 
   tc_fence_before();
   __syncthreads();
+  if (kPair) cluster_sync_all();   // nobody leaves while the peer may still signal this CTA
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kW2TmemCols);
+    if (kPair)
+      tmem_dealloc2(tmem_base, kW2TmemCols);
+    else
+      tmem_dealloc(tmem_base, kW2TmemCols);
   }
 }
 
-cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream) {
+template <int CG>
+static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes);
+        cudaFuncSetAttribute(igemm_wgrad2_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes);
     if (e != cudaSuccess) return e;
     configured = true;
   }
-  igemm_wgrad2_kernel<<<grid, kW2Threads, kW2SmemBytes, stream>>>(p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kW2Threads);
+  cfg.dynamicSmemBytes = kW2SmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = CG > 1 ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, igemm_wgrad2_kernel<CG>, p);
+}
+
+cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream) {
+  return p.pair ? launch_wgrad2_cg<2>(p, grid, stream) : launch_wgrad2_cg<1>(p, grid, stream);
 }
 
 }  // namespace uz
