@@ -177,7 +177,7 @@ def main():
     torch.manual_seed(0)
     model = unet_zoo_b200.create_model(args.model, in_channels=3, num_classes=1).to(dev).train()
     if world > 1:
-        model = P.DataParallel(model)          # bucketed NCCL all-reduce overlapped with backward
+        model = P.DataParallel(model, bucket_mb=float(os.environ.get("UZ_BUCKET_MB", "25")))   # bucketed NCCL all-reduce overlapped with backward
     params = [p for p in model.parameters() if p.requires_grad]
     use_graph = world == 1 and not args.no_graph
     opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True, capturable=use_graph)
