@@ -8,7 +8,8 @@ import os
 from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libunet_zoo_b200.so")
+# UZ_LIB_PATH: load another build of the same library (A/B timing of two builds inside one GPU session)
+LIB_PATH = os.environ.get("UZ_LIB_PATH") or os.path.join(_HERE, "libunet_zoo_b200.so")
 
 # mode / flag constants (mirrors include/unet_zoo_b200.h)
 CONV3X3, CONV3X3_DGRAD, CONV1X1, CONV3X3_S2, CONV3X3_S2_DGRAD = 0, 1, 2, 3, 4

@@ -341,11 +341,8 @@ extern "C" int uz_device_sm_count(void) {
   if (n < 0) return set_error(UZ_ERR_CUDA, "no CUDA device");
   return n;
 }
-// rows of the per-channel statistics partials: one per (CTA, epilogue warp) of the persistent conv kernels (8 warps)
-extern "C" int uz_conv_stats_rows(void) {
-  const int n = uz_device_sm_count();
-  return n < 0 ? n : 8 * n;
-}
+// rows of the per-channel statistics partials: one per CTA of the persistent conv kernels
+extern "C" int uz_conv_stats_rows(void) { return uz_device_sm_count(); }
 
 namespace uz {
 static int env_int(const char* name, int dflt) {
@@ -578,7 +575,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 
   if (flags & UZ_FLAG_STATS) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * 8 * sms, st);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
   if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2) {

@@ -318,21 +318,35 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     uint32_t st_off[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) st_off[j] = ((((lane >> 2) ^ j) << 4) + (lane & 3) * 4) + (ew * 16 + j) * 128;
-    auto flush_stats = [&]() {
+    // One row of partials per CTA: the eight epilogue warps (16 tile rows each, all columns) are summed through the (idle)
+    // first staging tile before the flush - rare (n-tile change / end of kernel), deterministic order.
+    auto flush_stats = [&]() {   // called by all 256 epilogue threads
       if (run_ntile < 0) return;
-      float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 8 + ew) * 2 * p.ncols;
+      if (et == 0) tma_store_wait_read0();   // a TMA store may still be reading the staging tile
+      asm volatile("bar.sync 1, 256;" ::: "memory");
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int col = run_ntile * BN + c * 64 + 2 * lane + h;
-          if (col < p.ncols) {
-            dst[col] += run_s[c][h];
-            dst[p.ncols + col] += run_q[c][h];
-          }
+          const int col = c * 64 + 2 * lane + h;   // each warp holds all columns of its 16 tile rows
+          st_shared_f32(stg_base + ((ew * 2 + 0) * BN + col) * 4, run_s[c][h]);
+          st_shared_f32(stg_base + ((ew * 2 + 1) * BN + col) * 4, run_q[c][h]);
           run_s[c][h] = run_q[c][h] = 0.f;
         }
       }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      float* dst = p.stats + static_cast<size_t>(blockIdx.x) * 2 * p.ncols;
+      for (int i = et; i < 2 * BN; i += 256) {
+        const int which = i / BN, c = i - which * BN;
+        const int col = run_ntile * BN + c;
+        if (col < p.ncols) {
+          float v = 0.f;
+#pragma unroll
+          for (int w8 = 0; w8 < 8; ++w8) v += __uint_as_float(ld_shared_u32(stg_base + ((w8 * 2 + which) * BN + c) * 4));
+          dst[which * p.ncols + col] += v;
+        }
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // the staging tile is free for the next chunk
     };
     int acc = 0;
     uint32_t acc_phase = 0;
