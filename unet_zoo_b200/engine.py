@@ -349,6 +349,15 @@ def stem_input(ctx: Ctx, x: torch.Tensor) -> Tuple[Act, str]:
     return a, "nhwc"
 
 
+def _weight_for(conv, cin_total: int) -> torch.Tensor:
+    """The convolution weight as the GEMM sees it: input channels zero-padded up to the operand's channel count (only
+    the NHWC stem of models with in_channels > 7, whose image is padded to a multiple of 8 channels)."""
+    w = conv.weight.detach()
+    if cin_total == w.shape[1]:
+        return w
+    return torch.nn.functional.pad(w, (0, 0, 0, 0, 0, cin_total - w.shape[1]))
+
+
 def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None, pooled: Optional[Act] = None,
                 relu: bool = True, mode: int = L.CONV3X3, stem: Optional[str] = None, need_dx: bool = True) -> Act:
     """[ReLU](BatchNorm2d(Conv2d(cat(xs)))) with optional MaxPool2d(2,2) second output.
@@ -374,13 +383,15 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
 
     if not ctx.training:
         scale, bias = _fold_bn(conv.bias, bn) if bn is not None else (None, conv.bias)
-        wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", row_scale=scale, kp=a0.C if is_stem else 0)
+        wp = ctx.pack(conv.weight if is_stem else _weight_for(conv, cin_total), "stem" if is_stem else "conv_fwd",
+                      row_scale=scale, kp=a0.C if is_stem else 0)
         ctx.conv(conv_mode, xs, wp, cout, bias, out.ptr, out.ld, Ho, Wo, None, L.FLAG_RELU if relu else 0)
         if pooled is not None:
             ctx.bn_apply(out, None, None, False, None, pooled)
         return out
 
-    wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", kp=a0.C if is_stem else 0)
+    wp = ctx.pack(conv.weight if is_stem else _weight_for(conv, cin_total), "stem" if is_stem else "conv_fwd",
+                  kp=a0.C if is_stem else 0)
     z = ctx.new_act(N, Ho, Wo, cout)
     stats = ctx.f32(ctx.stats_rows, 2, cout)
     ctx.conv(conv_mode, xs, wp, cout, conv.bias, z.ptr, z.ld, Ho, Wo, stats, L.FLAG_STATS)
@@ -419,10 +430,14 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
             c.wgrad(L.CONV1X1, a0.ptr, a0.N, a0.H, a0.W, kp, a0.ld, dz.ptr, cout, dz.ld, tmp, kp, 0)
             dw.copy_(tmp[:, :9 * cin].view(cout, 9, cin).permute(0, 2, 1).reshape(dw.shape))
         else:
+            padded = cin_total != conv.in_channels      # NHWC stem with zero-padded input channels
+            tgt = c.f32(cout, cin_total, *conv.weight.shape[2:]) if padded else dw
             off = 0
             for a in xs:
-                c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, dw, cin_total, off)
+                c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, tgt, cin_total, off)
                 off += a.C
+            if padded:
+                dw.copy_(tgt[:, :conv.in_channels])
         c.pready(conv.weight)
     if not need_dx or is_stem:
         return
@@ -640,7 +655,8 @@ def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mod
             raise ValueError("accumulate needs an existing output")
         out = ctx.new_act(a0.N, Ho, Wo, cout)
     is_stem = stem == "im2col"
-    wp = ctx.pack(conv.weight, "stem" if is_stem else "conv_fwd", kp=a0.C if is_stem else 0)
+    wp = ctx.pack(conv.weight if is_stem else _weight_for(conv, sum(a.C for a in xs)), "stem" if is_stem else "conv_fwd",
+                  kp=a0.C if is_stem else 0)
     ctx.conv(L.CONV1X1 if is_stem else mode, xs, wp, cout, conv.bias, out.ptr, out.ld, Ho, Wo, None,
              L.FLAG_ACCUMULATE if accumulate else 0)
     if ctx.record:
