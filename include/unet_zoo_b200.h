@@ -149,6 +149,9 @@ int uz_gate_bwd(const void* x, int x_ld, const void* dout, int dout_ld, const fl
  *  fwd: x [N,H,W,C] -> out [N,2H,2W,C] written at (out, out_ld) - typically a channel slice of a concat buffer.
  *  bwd: dx [N,H,W,C] (+)= gather of dout [N,2H,2W,C]; H, W are the LOW-resolution sizes in both calls. */
 int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);
+/* nn.Upsample(scale_factor=2) (nearest, common_layers.py:70) materialised: out [N,2H,2W,C] = x[n, y>>1, x>>1, :].
+ * Used only for the weight gradient of UpConvBlock's convolution (3x3 wgrad kernel on the upsampled operand). */
+int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);
 int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, void* dx, int dx_ld, int accumulate,
                       void* stream);
 

@@ -126,6 +126,43 @@ static float rs_scale(int in) { return in > 0 ? static_cast<float>(in - 1) / sta
 
 using namespace uz;
 
+// nearest x2 (nn.Upsample(scale_factor=2), common_layers.py:70): out[n, oy, ox, :] = x[n, oy >> 1, ox >> 1, :]
+// Only the weight gradient of the up-conv needs the upsampled tensor (it runs the 3x3 halo-box wgrad kernel on it);
+// the forward and the data gradient fold the upsampling into the convolution's gather.
+namespace uz {
+__global__ void nearest2x_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int cv,
+                                     __nv_bfloat16* __restrict__ out, int out_ld) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const long long total = static_cast<long long>(N) * Ho * Wo * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long r = i / cv;
+    const int ox = static_cast<int>(r % Wo);
+    r /= Wo;
+    const int oy = static_cast<int>(r % Ho);
+    const int n = static_cast<int>(r / Ho);
+    const long long src = (static_cast<long long>(n) * H + (oy >> 1)) * W + (ox >> 1);
+    const long long dst = (static_cast<long long>(n) * Ho + oy) * Wo + ox;
+    *reinterpret_cast<uint4*>(out + dst * out_ld + g * 8) = pw_ldg16(x + src * x_ld + g * 8);
+  }
+}
+}  // namespace uz
+
+extern "C" int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
+                                void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = rs_check("nearest2x_fwd(x)", x, C, x_ld);
+  if (rc) return rc;
+  if ((rc = rs_check("nearest2x_fwd(out)", out, C, out_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "nearest2x_fwd: bad size N=%d H=%d W=%d", N, H, W);
+  const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
+  nearest2x_fwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld);
+  PW_CHECK_LAUNCH("nearest2x_fwd launch");
+  return UZ_OK;
+}
+
 extern "C" int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
                                  void* stream) {
   PW_REQUIRE_DEVICE();
