@@ -133,6 +133,15 @@ def cpu_train_step_rate(model_name, size, steps, warmup, threads=None):
     return 1.0 / (sum(times) / len(times)), torch.get_num_threads()
 
 
+def metric_name(model):
+    return "images/sec UNet 512^2 bf16 train step" if model == "unet" else f"images/sec {model} bf16 train step"
+
+
+def workload_name(model, B, S):
+    return (f"{model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step "
+            "(BASELINE.json configs[1])")
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -140,10 +149,11 @@ def run_reference(args):
     rate, cores = cpu_train_step_rate(args.model, args.size, args.steps, max(1, min(args.warmup, 2)))
     sample = f"batch 1 of the {args.size}x{args.size} fp32 training step per step (oracle port of the reference path, torch CPU)"
     line = {
-        "impl": "reference", "metric": "images/sec UNet 512^2 train step", "value": rate, "unit": "images/sec",
+        "impl": "reference", "metric": metric_name(args.model), "value": rate, "unit": "images/sec",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / rate,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.model} in=3 classes=1 {args.size}x{args.size} fwd+bwd training step, CPU"},
+        "config": {"workload": workload_name(args.model, args.batch, args.size),
+                   "sample": "each step = batch 1 of that workload on the host cores, fp32 (the reference has no bf16 path)"},
         "cpu_baseline": {"value": rate, "unit": "images/sec", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -301,11 +311,10 @@ def main():
                              for k, v in agg.items()},
                 "step_tflops": value / world * FWD_BWD_GFLOP_PER_IMG_512[args.model] * (S / 512.0) ** 2 / 1000.0}
     line = {
-        "metric": "images/sec UNet 512^2 bf16 train step" if args.model == "unet" else f"images/sec {args.model} bf16 train step", "value": value, "unit": "images/sec", "n_gpus": world,
+        "metric": metric_name(args.model), "value": value, "unit": "images/sec", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"{args.model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step "
-                               "(BASELINE.json configs[1])", "global_batch": B * world,
+        "config": {"workload": workload_name(args.model, B, S), "global_batch": B * world,
                    "parallelism": f"dp{world}", "launch": graph_note, "l2": "inputs larger than L2 (multi-GB activations per step)"},
         "e2e": {"value": imgs / (ms_e2e / 1000.0), "unit": "images/sec",
                 "h2d_bytes_per_step": x_h.numel() * 4 + m_h.numel() * 4, "d2h_bytes_per_step": 4},
