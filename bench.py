@@ -274,9 +274,16 @@ def main():
     clocks = sampler.stop() if sampler else None
 
     # roofline leg: per-launch CUDA-event timing of the tensor-core kernels during one more step
+    # (kernels timed one at a time: the side-stream overlap of the weight gradients is switched off for this step)
     E.PROFILE = []
+    overlap_env = os.environ.get("UZ_OVERLAP_WGRAD")
+    os.environ["UZ_OVERLAP_WGRAD"] = "0"
     eager_step(x_d, m_d)
     torch.cuda.synchronize()
+    if overlap_env is None:
+        del os.environ["UZ_OVERLAP_WGRAD"]
+    else:
+        os.environ["UZ_OVERLAP_WGRAD"] = overlap_env
     agg = {}
     for kind, flops, a, b in E.PROFILE:
         t, f, n = agg.get(kind, (0.0, 0.0, 0))

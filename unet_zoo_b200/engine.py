@@ -8,6 +8,7 @@ operators over NHWC bf16 activation views (:class:`Act`); each operator launches
 
 PyTorch is used for device memory (caching allocator), streams and the autograd boundary only.
 """
+import contextlib
 import ctypes
 import os
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
@@ -40,6 +41,19 @@ class _Timed:
         if PROFILE is not None:
             self.e1.record()
             PROFILE.append((self.kind, self.flops, self.e0, self.e1))
+
+
+_SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def side_stream(device) -> "torch.cuda.Stream":
+    """The per-device stream the weight-gradient GEMMs run on (see Ctx.on_side)."""
+    idx = torch.device(device).index
+    idx = torch.cuda.current_device() if idx is None else idx
+    st = _SIDE_STREAMS.get(idx)
+    if st is None:
+        st = _SIDE_STREAMS[idx] = torch.cuda.Stream(device=idx)
+    return st
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -172,6 +186,13 @@ class Ctx:
         self.stats_rows = self.lib.uz_conv_stats_rows()
         self.reduce_rows = self.lib.uz_reduce_rows()
         self._ws = None
+        # Weight gradients leave the critical path: they run on a side stream while the main stream continues with the
+        # data gradient's consumers.  The HBM-bound BatchNorm backward of layer L-1 then shares the SMs with the
+        # tensor-bound weight gradient of layer L (192-thread CTAs, 15 K registers: a BatchNorm block still fits).
+        self.overlap_wgrad = record and os.environ.get("UZ_OVERLAP_WGRAD", "1") != "0"
+        self._ws_main = None
+        self._ws_side = None
+        self._on_side = False
         self.pgrads: Optional[ParamGrads] = None
         self.outputs: List[torch.Tensor] = []     # logits tensors, in the order the model returns them
         self.out_grads: List[Optional[torch.Tensor]] = []
@@ -185,9 +206,35 @@ class Ctx:
         return Act(self.new_buf(N, H, W, C))
 
     def workspace(self, nbytes: int) -> torch.Tensor:
-        if self._ws is None or self._ws.numel() < nbytes:
+        if self._ws is None or self._ws.numel() < nbytes:   # one scratch buffer per stream (see on_side)
             self._ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
         return self._ws
+
+    @contextlib.contextmanager
+    def on_side(self):
+        """Enqueue the enclosed calls on the side stream, ordered after everything enqueued on the main stream so far.
+        Allocations made inside belong to the side stream; the caller joins the streams before the tensors shared with
+        the main stream can be released (`join_side`)."""
+        main = torch.cuda.current_stream(self.device)
+        side = side_stream(self.device)
+        side.wait_stream(main)
+        saved = (self.stream, self._ws)
+        self._ws_main = self._ws
+        self.stream, self._ws, self._on_side = side.cuda_stream, self._ws_side, True
+        try:
+            with torch.cuda.stream(side):
+                yield
+        finally:
+            self._ws_side = self._ws
+            self.stream, self._ws = saved
+            self._on_side = False
+            self.side_used = True
+
+    def join_side(self):
+        if getattr(self, "side_used", False):
+            torch.cuda.current_stream(self.device).wait_stream(side_stream(self.device))
+            self.side_used = False
+
 
     def f32(self, *shape) -> torch.Tensor:
         return torch.empty(shape, dtype=torch.float32, device=self.device)
@@ -423,7 +470,8 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
     a0 = xs[0]
     cout = conv.out_channels
     dw = c.pgrad(conv.weight)
-    if dw is not None:
+
+    def weight_gradient():
         if is_stem:
             kp = a0.C
             cin = conv.in_channels
@@ -449,30 +497,38 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
             if padded:
                 dw.copy_(tgt[:, :conv.in_channels])
         c.pready(conv.weight)
-    if not need_dx or is_stem:
-        return
-    dgrad_mode = {L.CONV3X3: L.CONV3X3_DGRAD, L.CONV1X1: L.CONV1X1, L.CONV3X3_S2: L.CONV3X3_S2_DGRAD,
-                  L.CONV1X1_S2: L.CONV1X1_S2_DGRAD, L.UP2X_CONV3X3: L.UP2X_CONV3X3_DGRAD}.get(mode)
-    if dgrad_mode is None:
-        raise NotImplementedError(f"data gradient for conv mode {mode}")
-    wpd = c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
-    off = 0
-    for a in xs:
-        for (r0, rc, acc) in a.grad_writes():
-            if mode == L.CONV1X1_S2 and not acc:
-                # the stride-2 1x1 gradient only touches even pixels: clear the slice, then accumulate
-                a.buf.grad_buf()[..., a.c0 + r0:a.c0 + r0 + rc].zero_()
-                acc = True
-            w_rows = wpd[off + r0: off + r0 + rc]
-            stats = None
-            if a.buf.want_gsum and not acc and mode == L.CONV3X3:
-                # the epilogue's per-channel sums of this gradient ARE the bias gradient of the ConvTranspose2d that
-                # produced (part of) the buffer: saves a full read of the gradient (uz_colsum)
-                stats = c.f32(c.stats_rows, 2, rc)
-                a.buf.gsum.append((a.c0 + r0, a.c0 + r0 + rc, stats))
-            c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, stats,
-                   L.FLAG_STATS if stats is not None else (L.FLAG_ACCUMULATE if acc else 0))
-        off += a.C
+
+    has_dgrad = need_dx and not is_stem
+    if dw is not None and not (has_dgrad and c.overlap_wgrad):
+        weight_gradient()
+    if has_dgrad:
+        dgrad_mode = {L.CONV3X3: L.CONV3X3_DGRAD, L.CONV1X1: L.CONV1X1, L.CONV3X3_S2: L.CONV3X3_S2_DGRAD,
+                      L.CONV1X1_S2: L.CONV1X1_S2_DGRAD, L.UP2X_CONV3X3: L.UP2X_CONV3X3_DGRAD}.get(mode)
+        if dgrad_mode is None:
+            raise NotImplementedError(f"data gradient for conv mode {mode}")
+        wpd = c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
+        off = 0
+        for a in xs:
+            for (r0, rc, acc) in a.grad_writes():
+                if mode == L.CONV1X1_S2 and not acc:
+                    # the stride-2 1x1 gradient only touches even pixels: clear the slice, then accumulate
+                    a.buf.grad_buf()[..., a.c0 + r0:a.c0 + r0 + rc].zero_()
+                    acc = True
+                w_rows = wpd[off + r0: off + r0 + rc]
+                stats = None
+                if a.buf.want_gsum and not acc and mode == L.CONV3X3:
+                    # the epilogue's per-channel sums of this gradient ARE the bias gradient of the ConvTranspose2d that
+                    # produced (part of) the buffer: saves a full read of the gradient (uz_colsum)
+                    stats = c.f32(c.stats_rows, 2, rc)
+                    a.buf.gsum.append((a.c0 + r0, a.c0 + r0 + rc, stats))
+                c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, stats,
+                       L.FLAG_STATS if stats is not None else (L.FLAG_ACCUMULATE if acc else 0))
+            off += a.C
+    if dw is not None and has_dgrad and c.overlap_wgrad:
+        # after the data gradient in stream order: the data gradient is on the critical path, the weight gradient only
+        # has to be finished by the end of backward (or by its gradient bucket's all-reduce)
+        with c.on_side():
+            weight_gradient()
 
 
 def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
@@ -490,8 +546,13 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
 
         def backward(c: Ctx):
             dw = c.pgrad(up.weight)
-            if dw is not None:
+
+            def weight_gradient():
                 c.wgrad(L.CONVT2X2, x.ptr, x.N, x.H, x.W, x.C, x.ld, out.gptr(), cout, out.ld, dw, x.C, 0)
+                c.pready(up.weight)
+
+            if dw is not None and not c.overlap_wgrad:
+                weight_gradient()
             if want_db:
                 lo, hi = out.c0, out.c0 + cout
                 hit = next((e for e in out.buf.gsum if e[0] <= lo and hi <= e[1]), None)
@@ -499,11 +560,14 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
                     torch.sum(hit[2][:, 0, lo - hit[0]:hi - hit[0]], dim=0, out=c.pgrad(up.bias))
                 else:
                     c.colsum(out.gptr(), out.ld, out.npix, cout, c.pgrad(up.bias))
-            c.pready(up.weight, up.bias)
+            c.pready(up.bias)
             wpd = c.pack(up.weight, "convt_dgrad")  # [Cin][4][Cout]
             for (r0, rc, acc) in x.grad_writes():
                 c.conv(L.CONVT2X2_DGRAD, [out], wpd[r0:r0 + rc], rc, None, x.gptr() + 2 * r0, x.ld, x.H, x.W, None,
                        L.FLAG_ACCUMULATE if acc else 0, in_grad=True)
+            if dw is not None and c.overlap_wgrad:
+                with c.on_side():
+                    weight_gradient()
         ctx.tape.append(backward)
     return out
 

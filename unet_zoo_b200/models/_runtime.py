@@ -40,6 +40,7 @@ class _HotPathFn(torch.autograd.Function):
         ctx.out_grads = list(douts)
         for step in reversed(ctx.tape):
             step(ctx)
+        ctx.join_side()                      # weight gradients ran on the side stream (engine.Ctx.on_side)
         ctx.tape.clear()
         model._last_launches_bwd = ctx.launches
         finish = getattr(ctx.pgrads, "finish", None)

@@ -14,7 +14,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from .engine import ParamGrads
+from .engine import ParamGrads, side_stream
 
 
 def plan_buckets(numels: Sequence[int], bucket_bytes: int) -> List[List[int]]:
@@ -74,6 +74,7 @@ class BucketedGrads(ParamGrads):
         chunk = self.flat[lo:hi]
         if self.comm_stream is not None:
             self.comm_stream.wait_stream(torch.cuda.current_stream(self.flat.device))
+            self.comm_stream.wait_stream(side_stream(self.flat.device))   # weight gradients are produced there
             with torch.cuda.stream(self.comm_stream):
                 dist.all_reduce(chunk, op=dist.ReduceOp.AVG, group=self.group)
         else:  # CPU / gloo (tests): no AVG reduction there
