@@ -168,3 +168,36 @@ def test_graphed_train_step_matches_eager_steps():
     for k in s0:
         if s0[k].dtype.is_floating_point:
             assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k
+
+
+def test_data_parallel_and_side_stream_gradients_match_the_plain_step(monkeypatch):
+    """Three ways to run the same step must give the same gradients bit for bit: everything on one stream, weight
+    gradients on the side stream (engine.Ctx.on_side), and the bucketed NCCL wrapper (world size 1: the all-reduce is
+    an identity, but buckets are launched on the communication stream while backward is still enqueueing)."""
+    import torch.distributed as dist
+    from unet_zoo_b200 import parallel as P
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    x, m = x.cuda(), m.cuda()
+    crit = torch.nn.BCEWithLogitsLoss()
+
+    def grads(wrap, overlap):
+        monkeypatch.setenv("UZ_OVERLAP_WGRAD", "1" if overlap else "0")
+        model = seeded_model("unet").cuda().train()
+        net = P.DataParallel(model, bucket_mb=4.0) if wrap else model
+        crit(net(x), m).backward()
+        torch.cuda.synchronize()
+        return {k: p.grad.clone() for k, p in model.named_parameters()}
+
+    plain = grads(False, False)
+    side = grads(False, True)
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1)
+    try:
+        wrapped = grads(True, True)
+    finally:
+        if created:
+            dist.destroy_process_group()
+    for k in plain:
+        assert torch.equal(plain[k], side[k]), k
+        assert torch.equal(plain[k], wrapped[k]), k
