@@ -285,7 +285,7 @@ def main():
     else:
         os.environ["UZ_OVERLAP_WGRAD"] = overlap_env
     agg = {}
-    for kind, flops, a, b in E.PROFILE:
+    for kind, flops, a, b, _tag in E.PROFILE:
         t, f, n = agg.get(kind, (0.0, 0.0, 0))
         agg[kind] = (t + a.elapsed_time(b), f + flops, n + 1)
     E.PROFILE = None

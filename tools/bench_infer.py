@@ -5,6 +5,8 @@
 Eval-mode forward (BatchNorm folded / running statistics), inputs resident on the device, CUDA-event timing of `iters`
 forwards after 3 warm-ups.  Prints one JSON line per (batch, size): images/s, ms, achieved conv TFLOP/s (algorithmic
 forward FLOPs of SURVEY.md section 6, scaled by H*W/512^2) and its fraction of the measured sustained bf16 peak.
+--graph replays the forward as one CUDA graph (unet_zoo_b200.train_step.GraphedInference) and reports both.
+--layers BATCH,SIZE prints the per-layer table of the convolution launches (CUDA events around every launch) as markdown.
 """
 import argparse
 import json
@@ -22,6 +24,8 @@ def main():
     ap.add_argument("--sizes", default="256,384,512,768,1024")
     ap.add_argument("--batches", default="1,2,4,8,16,32,64")
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--graph", action="store_true")
+    ap.add_argument("--layers", default="")
     ap.add_argument("--max-pixels", type=float, default=64 * 512 * 512, help="skip (batch, size) above this many pixels")
     a = ap.parse_args()
     import torch
@@ -32,6 +36,27 @@ def main():
         peak = 1400.0
     torch.manual_seed(0)
     model = unet_zoo_b200.create_model(a.model).cuda().eval()
+    if a.layers:
+        from unet_zoo_b200 import engine as E
+        b, sz = [int(v) for v in a.layers.split(",")]
+        x = torch.randn(b, 3, sz, sz, device="cuda")
+        with torch.no_grad():
+            for _ in range(3):
+                model(x)
+            E.PROFILE = []
+            model(x)
+            torch.cuda.synchronize()
+        rows = [(tag, flops, e0.elapsed_time(e1)) for kind, flops, e0, e1, tag in E.PROFILE if kind == "igemm_fwd"]
+        E.PROFILE = None
+        tot_ms = sum(r[2] for r in rows)
+        print(f"# {a.model} inference, batch {b}, {sz}x{sz}: convolution launches (eval mode, BatchNorm folded)\n")
+        print(f"sum of conv launches {tot_ms:.3f} ms, {sum(r[1] for r in rows) / tot_ms / 1e9:.0f} TFLOP/s; "
+              f"denominator: sustained bf16 peak {peak:.0f} TFLOP/s (MEASURED_PEAKS.json)\n")
+        print("| layer | GFLOP | ms | TFLOP/s | frac of tensor peak |\n|---|---|---|---|---|")
+        for tag, flops, ms in rows:
+            tf = flops / ms / 1e9
+            print(f"| {tag} | {flops / 1e9:.1f} | {ms:.3f} | {tf:.0f} | {tf / peak:.2f} |")
+        return
     for s in [int(v) for v in a.sizes.split(",")]:
         for b in [int(v) for v in a.batches.split(",")]:
             if b * s * s > a.max_pixels:
@@ -48,11 +73,28 @@ def main():
                 e1.record()
                 torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / a.iters
+            ms_graph = None
+            if a.graph:
+                from unet_zoo_b200.train_step import GraphedInference
+                g = GraphedInference(model, x)
+                for _ in range(3):
+                    g(x)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(a.iters):
+                    g(x)
+                e1.record()
+                torch.cuda.synchronize()
+                ms_graph = e0.elapsed_time(e1) / a.iters
+                del g
             tf = b * FWD_GFLOP_512[a.model] * (s / 512.0) ** 2 / ms      # GFLOP / ms = TFLOP/s
             print(json.dumps({"model": a.model, "mode": "inference", "batch": b, "size": s, "ms": round(ms, 3),
                               "images_per_sec": round(b / ms * 1000.0, 1), "conv_tflops": round(tf, 1),
                               "frac_of_sustained_bf16_peak": round(tf / peak, 3),
-                              "launches": model._last_launches}), flush=True)
+                              "launches": model._last_launches,
+                              **({"ms_graph": round(ms_graph, 3),
+                                  "images_per_sec_graph": round(b / ms_graph * 1000.0, 1)} if ms_graph else {})}),
+                  flush=True)
             del x
             torch.cuda.empty_cache()
 

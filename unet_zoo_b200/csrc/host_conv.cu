@@ -358,8 +358,15 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   static const int disabled = env_int("UZ_DISABLE_FWD2", 0);
   if (disabled) return 0;
   if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1 || mode == UZ_CONVT2X2 ||
-        mode == UZ_CONVT2X2_DGRAD))
+        mode == UZ_CONVT2X2_DGRAD || mode == UZ_CONV1X1_S2))
     return 0;
+  // 1x1 stride 2 (ResidualConv.conv_skip, common_layers.py:194) = a 1x1 GEMM over the even-pixel lattice of the input
+  const bool s2 = mode == UZ_CONV1X1_S2;
+  const int Hin = H, Win = W;
+  if (s2) {
+    H = (H - 1) / 2 + 1;
+    W = (W - 1) / 2 + 1;  // tile space = the output
+  }
   // ConvTranspose2d k2s2 forward = four 1x1 GEMMs (one per output phase) stored through strided output views;
   // its data gradient = one 1x1 GEMM whose K runs over the four strided views of dY (K = 4*Cout).
   const bool convt = mode == UZ_CONVT2X2, convt_d = mode == UZ_CONVT2X2_DGRAD;
@@ -403,7 +410,8 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
       p.seg_k0[s] = ctot;
       ctot += seg_c[s];
       kblocks += p.seg_cblocks[s];
-      int rc = make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
+      int rc = s2 ? make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, Hin, Win, Lattice{0, 0, 2}, 8, 16, 1)
+                  : make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
       if (rc != UZ_OK) return rc;
     }
   }
@@ -578,7 +586,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
-  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2) {
+  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2) {
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }

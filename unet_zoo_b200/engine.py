@@ -28,8 +28,8 @@ _TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 36}
 
 
 class _Timed:
-    def __init__(self, kind, flops):
-        self.kind, self.flops = kind, flops
+    def __init__(self, kind, flops, tag=""):
+        self.kind, self.flops, self.tag = kind, flops, tag
 
     def __enter__(self):
         if PROFILE is not None:
@@ -40,9 +40,12 @@ class _Timed:
     def __exit__(self, *a):
         if PROFILE is not None:
             self.e1.record()
-            PROFILE.append((self.kind, self.flops, self.e0, self.e1))
+            PROFILE.append((self.kind, self.flops, self.e0, self.e1, self.tag))
 
 
+_MODE_NAMES = {L.CONV3X3: "conv3x3", L.CONV1X1: "conv1x1", L.CONVT2X2: "convT2x2", L.CONV3X3_DGRAD: "conv3x3.dgrad",
+               L.CONVT2X2_DGRAD: "convT2x2.dgrad", L.CONV3X3_S2: "conv3x3s2", L.CONV1X1_S2: "conv1x1s2",
+               L.UP2X_CONV3X3: "up2x+conv3x3", L.UP2X_CONV3X3_DGRAD: "up2x+conv3x3.dgrad"}
 _SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
 
 
@@ -283,7 +286,8 @@ class Ctx:
         opix = a.N * out_h * out_w
         taps = {L.CONVT2X2: 1, L.CONV3X3_S2_DGRAD: 2.25}.get(mode, _TAPS[mode])
         flops = 2.0 * opix * cout * sum(s.C for s in segs) * taps
-        with _Timed("igemm_fwd", flops):
+        with _Timed("igemm_fwd", flops, f"{_MODE_NAMES.get(mode, mode)} {sum(s.C for s in segs)}->{cout} "
+                                         f"@{out_h}x{out_w} n{a.N}"):
             rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
                                         out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
         L.check(rc, "uz_conv_igemm")

@@ -64,3 +64,37 @@ class GraphedTrainStep:
             self.target.copy_(target, non_blocking=True)
         self.graph.replay()
         return self.loss
+
+
+class GraphedInference:
+    """Eval-mode forward of a hot-path model captured into one CUDA graph (fixed input shape): the ~56 launches of a
+    resunet forward cost ~1.6 ms of host time in eager mode, which dominates below ~4 images of 512x512
+    (evaluate.py / visualize.py style single-image calls, BASELINE config #5 small-batch corner)."""
+
+    def __init__(self, model: torch.nn.Module, example_x: torch.Tensor, warmup: int = 2):
+        if not example_x.is_cuda:
+            raise RuntimeError("GraphedInference needs CUDA tensors (there is no CPU path)")
+        if model.training:
+            raise RuntimeError("GraphedInference captures the eval-mode forward: call model.eval() first")
+        self.model = model
+        self.x = example_x.clone()
+        dev = example_x.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                model(self.x)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.out = model(self.x)
+
+    def __call__(self, x: torch.Tensor):
+        """Logits for x (same shape as the example); the returned tensor(s) are overwritten by the next call."""
+        if x.shape != self.x.shape:
+            raise RuntimeError(f"GraphedInference was captured for {tuple(self.x.shape)}, got {tuple(x.shape)}")
+        if x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.out
