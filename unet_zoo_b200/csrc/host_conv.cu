@@ -358,12 +358,16 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   static const int disabled = env_int("UZ_DISABLE_FWD2", 0);
   if (disabled) return 0;
   if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1 || mode == UZ_CONVT2X2 ||
-        mode == UZ_CONVT2X2_DGRAD || mode == UZ_CONV1X1_S2))
+        mode == UZ_CONVT2X2_DGRAD || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2))
     return 0;
   // 1x1 stride 2 (ResidualConv.conv_skip, common_layers.py:194) = a 1x1 GEMM over the even-pixel lattice of the input
-  const bool s2 = mode == UZ_CONV1X1_S2;
+  // 3x3 stride 2 (ResidualConv.conv_block, common_layers.py:188): the input splits into its four parity lattices; tap
+  // (r, s) reads lattice (r != 1, s != 1) shifted by (r == 0 ? -1 : 0, s == 0 ? -1 : 0) - four segments over the SAME
+  // channels, each with its own subset of the nine taps (1 + 2 + 2 + 4), one halo box per lattice and channel block
+  const bool s2 = mode == UZ_CONV1X1_S2, s2c = mode == UZ_CONV3X3_S2;
   const int Hin = H, Win = W;
-  if (s2) {
+  if (s2c && nseg != 1) return 0;
+  if (s2 || s2c) {
     H = (H - 1) / 2 + 1;
     W = (W - 1) / 2 + 1;  // tile space = the output
   }
@@ -379,7 +383,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   if (convt && (cout % 64) != 0) return 0;
   Igemm2Params p;
   memset(&p, 0, sizeof(p));
-  const int pad = (mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD) ? 0 + 1 : 0;
+  const int pad = (mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || s2c) ? 0 + 1 : 0;
   p.pad = pad;
   p.halo_w = 8 + 2 * pad;
   p.halo_bytes = p.halo_w * (16 + 2 * pad) * 128;
@@ -388,6 +392,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     const int r = t / 3, s = t % 3;
     if (mode == UZ_CONV3X3) p.tap_row[t] = r * p.halo_w + s;
     else if (mode == UZ_CONV3X3_DGRAD) p.tap_row[t] = (2 - r) * p.halo_w + (2 - s);
+    else if (s2c) p.tap_row[t] = (r == 0 ? 0 : 1) * p.halo_w + (s == 0 ? 0 : 1);
     else p.tap_row[t] = 0;
     p.tap_b[t] = t;
   }
@@ -404,6 +409,19 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
       if (rc != UZ_OK) return rc;
     }
     nseg = 4;
+  } else if (s2c) {
+    for (int l = 0; l < 4; ++l) {
+      p.seg_cblocks[l] = (seg_c[0] + 63) / 64;
+      p.seg_k0[l] = 0;
+      kblocks += p.seg_cblocks[l];
+      int rc = make_act_map(&p.amap[l], seg_ptr[0], seg_c[0], seg_ld[0], N, Hin, Win, Lattice{l >> 1, l & 1, 2}, p.halo_w,
+                            16 + 2 * pad, 1);
+      if (rc != UZ_OK) return rc;
+      for (int t = 0; t < 9; ++t)
+        if (((t / 3 != 1) ? 1 : 0) == (l >> 1) && ((t % 3 != 1) ? 1 : 0) == (l & 1)) p.seg_taps[l] |= 1 << t;
+    }
+    ctot = seg_c[0];
+    nseg = 4;
   } else {
     for (int s = 0; s < nseg; ++s) {
       p.seg_cblocks[s] = (seg_c[s] + 63) / 64;
@@ -417,6 +435,11 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   }
   p.num_segs = nseg;
   p.kblocks = kblocks;
+  p.b_items = 0;
+  for (int sg = 0; sg < nseg; ++sg) {
+    if (!s2c) p.seg_taps[sg] = (1 << p.num_taps) - 1;
+    p.b_items += p.seg_cblocks[sg] * __builtin_popcount(p.seg_taps[sg]);
+  }
   p.N = N; p.H = H; p.W = W;
   p.xb = (W + 7) / 8;
   p.yb = (H + 15) / 16;
@@ -434,11 +457,11 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const int pair_env = env_int("UZ_FWD2_PAIR", 1);
   // measured per layer (tools/bench_conv.py): the pair wins when a tile carries >= 18 (cblock, tap) steps (+4..12 %, up
   // to 1690 TFLOP/s); with fewer the tile is epilogue bound and pair mode adds ~1 us per tile pair
-  const bool pair_auto = kblocks * p.num_taps >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
+  const bool pair_auto = p.b_items >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
   p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 ? 1 : 0;
   int b_item = bn * 128 / (p.pair ? 2 : 1);     // bytes of one weight tile per CTA
   const int kTail = 1536;              // barriers (512) + bias vector (1024)
-  const long long b_all = (long long)kblocks * p.num_taps * b_item;
+  const long long b_all = (long long)p.b_items * b_item;
   int cluster = p.pair ? 2 : 1;
   bool stationary = false;
   if (p.num_n_tiles == 1 && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
@@ -586,7 +609,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
-  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2) {
+  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2) {
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }

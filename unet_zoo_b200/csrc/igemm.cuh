@@ -104,6 +104,9 @@ struct alignas(64) Igemm2Params {
   int seg_cblocks[kMaxSegs];
   int seg_k0[kMaxSegs];
   int num_taps;
+  int seg_taps[kMaxSegs];      // bit t set: segment uses tap t (all taps except for the stride-2 3x3 convolution, whose
+                               // four segments are the four parity lattices of ONE input, each with its own taps)
+  int b_items;                 // weight tiles per output tile = sum over segments of cblocks x taps used
   int tap_row[9];              // halo row (pixel index in the box) of each tap's first pixel
   int tap_b[9];                // tap coordinate in the packed weights
   int pad;                     // 1 for 3x3, 0 for 1x1

@@ -168,16 +168,18 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     if (elect_one()) {
       if (!ring) {
         // stationary: every (cblock, tap) tile is loaded once and stays for the whole launch (num_n_tiles == 1)
-        if (leader) mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.kblocks * p.num_taps) * kBItem * CG);
+        if (leader) mbar_expect_tx(bfull(0), static_cast<uint32_t>(p.b_items) * kBItem * CG);
         int item = 0;
         for (int seg = 0; seg < p.num_segs; ++seg)
           for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb)
-            for (int tap = 0; tap < p.num_taps; ++tap, ++item) {
+            for (int tap = 0; tap < p.num_taps; ++tap) {
+              if (!((p.seg_taps[seg] >> tap) & 1)) continue;
               if (kPair)   // this CTA's half of the weight rows
                 tma_load_3d_pair(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap],
                                  rank * (BN / 2));
               else
                 tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap], 0);
+              ++item;
             }
       } else {
         int stage = 0;
@@ -192,6 +194,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
             for (int cb = 0; cb < ncb; ++cb) {
               const int k = p.seg_k0[seg] + cb * 64;
               for (int tap = 0; tap < p.num_taps; ++tap) {
+                if (!((p.seg_taps[seg] >> tap) & 1)) continue;
                 mbar_wait(bempty(stage), phase ^ 1u);
                 if (leader) mbar_expect_tx(bfull(stage), kBItem * CG);
                 const uint32_t dst = b_base + stage * kBItem;
@@ -235,13 +238,16 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (MP * BN);
         uint32_t b_item = (b_base >> 4) | (1u << 16);   // stationary weights: walks through the resident tiles
-        for (int kb = 0; kb < p.kblocks; ++kb) {
+        uint32_t fresh = 0;   // 0 for the first MMA of the tile (overwrite the accumulator), 1 afterwards
+        for (int seg = 0; seg < p.num_segs; ++seg) {
+        const uint32_t seg_mask = static_cast<uint32_t>(p.seg_taps[seg]);
+        for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb) {
           mbar_wait(afull(astage), aphase);
           tc_fence_after();
           const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) {
-            if (tap < ntaps) {
+            if (tap < ntaps && ((seg_mask >> tap) & 1u)) {
               uint32_t b_lo;
               if (ring) {
                 mbar_wait(bfull(bstage), bphase);
@@ -251,7 +257,6 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 b_lo = b_item;
                 b_item += kBItem >> 4;
               }
-              const uint32_t fresh = (kb == 0 && tap == 0) ? 0u : 1u;
 #pragma unroll
               for (int sub = 0; sub < MP; ++sub) {      // the same weight tile against each pixel tile of the item
                 const uint32_t a_tap = a_lo + sub * (a_half >> 4) + tap_lo[tap];
@@ -264,6 +269,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                                     k == 0 ? fresh : 1u);
                 }
               }
+              fresh = 1u;
               if (ring) {
                 if (kPair)
                   umma2_commit_mc(bempty(bstage));
@@ -286,6 +292,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
             astage = 0;
             aphase ^= 1u;
           }
+        }
         }
         if (kPair)
           umma2_commit_mc(tfull(acc));
