@@ -192,6 +192,39 @@ int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int cin, int x_l
                   int dy_ld, float* dw, int cin_total, int c_off, int accumulate, void* workspace,
                   size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * fp32 parity mode (forward only).  BASELINE.json: "fp32 mode within 1e-4 relative on logits"; configs[0] = unet,
+ * batch 1, 256x256 fp32 forward (README.md:83-90).  Same operators and reference call sites as above, but on NHWC
+ * fp32 activations (`ld` in floats, any channel count) with CUDA-core FFMA arithmetic - the bf16 tensor-core
+ * kernels cannot meet 1e-4.  BatchNorm partial statistics have the uz_bn_stats row layout (rows = uz_reduce_rows(),
+ * fp64 accumulation inside) and go through uz_bn_finalize unchanged.
+ *  uz_f32_pack_weight: dst[t][ci][co] (fp32, [T][cin_total][coutp], zero padded) = src[co*s_co + ci*s_ci + t]
+ *                      * (row_scale ? row_scale[co] : 1).  Conv2d OIHW: s_co=Ci*T, s_ci=T; ConvTranspose2d IOHW
+ *                      [Ci,Co,2,2]: s_co=4, s_ci=Co*4 (T=4 output phases).  coutp = cout rounded up to 4.
+ *  uz_f32_conv       : modes UZ_CONV3X3, UZ_CONV1X1, UZ_CONV3X3_S2, UZ_CONV1X1_S2, UZ_UP2X_CONV3X3, UZ_CONVT2X2 over a
+ *                      virtual concat of up to UZ_F32_MAX_SEGS segments; flags UZ_FLAG_RELU / UZ_FLAG_ACCUMULATE;
+ *                      output size follows from `mode` (N,H,W describe the INPUT).
+ *  uz_f32_affine_act : y = act(z*scale + shift + residual) (+ MaxPool2d(2,2) second output; y may be NULL then);
+ *                      scale == shift == NULL -> identity.
+ *  uz_f32_bilinear2x : nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True) (nested_unet.py:33).
+ *  uz_f32_gate_apply : out = x * sigmoid(psi_raw*bn[2] + bn[3])   (attention_unet.py:38-40).
+ *  uz_f32_nchw_to_nhwc / uz_f32_nhwc_to_nchw: layout changes at the model boundary (input image, multi-class logits). */
+#define UZ_F32_MAX_SEGS 4
+int uz_f32_pack_weight(const float* src, float* dst, int T, int cin, int cin_total, int cout, int coutp,
+                       long long s_co, long long s_ci, const float* row_scale, void* stream);
+int uz_f32_conv(int mode, int N, int H, int W, int nseg, const void* const* seg_ptr, const int* seg_c,
+                const int* seg_ld, const float* w_packed, int cout, int coutp, const float* bias, float* out,
+                int out_ld, int flags, void* stream);
+int uz_f32_nchw_to_nhwc(const float* x, int N, int C, int H, int W, float* out, int out_ld, void* stream);
+int uz_f32_nhwc_to_nchw(const float* in, int in_ld, int N, int C, int H, int W, float* out, void* stream);
+int uz_f32_bn_stats(const float* x, int ld, long long npix, int C, float* partial, void* stream);
+int uz_f32_affine_act(const float* z, int z_ld, int N, int H, int W, int C, const float* scale, const float* shift,
+                      int relu, const float* residual, int res_ld, float* y, int y_ld, float* pooled, int pooled_ld,
+                      void* stream);
+int uz_f32_bilinear2x(const float* x, int x_ld, int N, int H, int W, int C, float* out, int out_ld, void* stream);
+int uz_f32_gate_apply(const float* x, int x_ld, const float* psi_raw, const float* bn_psi, long long npix, int C,
+                      float* out, int out_ld, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -56,6 +56,16 @@ _PROTOS = {
     "uz_bn_head_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, c_int, _P, _P, _P, _P]),
     "uz_bn_head_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, _P, _P,
                                _P, _P, c_int, _P, c_size_t, _P]),
+    # fp32 parity mode (forward only, csrc/f32.cu)
+    "uz_f32_pack_weight": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_longlong, c_longlong, _P, _P]),
+    "uz_f32_conv": (c_int, [c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, c_int, _P, _P, c_int, c_int, _P]),
+    "uz_f32_nchw_to_nhwc": (c_int, [_P, c_int, c_int, c_int, c_int, _P, c_int, _P]),
+    "uz_f32_nhwc_to_nchw": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P]),
+    "uz_f32_bn_stats": (c_int, [_P, c_int, c_longlong, c_int, _P, _P]),
+    "uz_f32_affine_act": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, _P, c_int, _P, c_int, _P, c_int,
+                                  _P]),
+    "uz_f32_bilinear2x": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P]),
+    "uz_f32_gate_apply": (c_int, [_P, c_int, _P, _P, c_longlong, c_int, _P, c_int, _P]),
 }
 
 _lib = None

@@ -64,12 +64,14 @@ def _ptr(t: Optional[torch.Tensor]):
 
 
 class Buf:
-    """One NHWC bf16 device buffer [N, H, W, ld] plus (lazily) its gradient buffer of the same shape."""
+    """One NHWC device buffer [N, H, W, ld] (bf16; fp32 in the forward-only parity mode) plus (lazily) its gradient
+    buffer of the same shape."""
 
-    __slots__ = ("data", "grad", "written", "N", "H", "W", "ld", "want_gsum", "gsum")
+    __slots__ = ("data", "grad", "written", "N", "H", "W", "ld", "want_gsum", "gsum", "esize")
 
-    def __init__(self, N, H, W, ld, device):
-        self.data = torch.empty((N, H, W, ld), dtype=torch.bfloat16, device=device)
+    def __init__(self, N, H, W, ld, device, dtype=torch.bfloat16):
+        self.data = torch.empty((N, H, W, ld), dtype=dtype, device=device)
+        self.esize = self.data.element_size()
         self.grad = None
         self.written: List[Tuple[int, int]] = []  # channel intervals of `grad` that already hold a gradient
         self.N, self.H, self.W, self.ld = N, H, W, ld
@@ -90,14 +92,14 @@ class Act:
     def __init__(self, buf: Buf, c0: int = 0, C: Optional[int] = None):
         self.buf, self.c0 = buf, c0
         self.C = buf.ld - c0 if C is None else C
-        if self.c0 % 8 or self.C % 8:
+        if buf.esize == 2 and (self.c0 % 8 or self.C % 8):
             raise RuntimeError(f"unet_zoo_b200: channel slices must be multiples of 8 (c0={c0}, C={self.C})")
 
     N = property(lambda s: s.buf.N)
     H = property(lambda s: s.buf.H)
     W = property(lambda s: s.buf.W)
     ld = property(lambda s: s.buf.ld)
-    ptr = property(lambda s: s.buf.data.data_ptr() + 2 * s.c0)
+    ptr = property(lambda s: s.buf.data.data_ptr() + s.buf.esize * s.c0)
     npix = property(lambda s: s.buf.N * s.buf.H * s.buf.W)
 
     def slice(self, c0, C):
@@ -176,11 +178,17 @@ class ParamGrads:
 class Ctx:
     """Per-forward execution context: stream, scratch memory, tape, parameter-gradient sink."""
 
-    def __init__(self, device, training: bool, record: bool):
+    def __init__(self, device, training: bool, record: bool, precision: str = "bf16"):
+        if precision not in ("bf16", "fp32"):
+            raise ValueError(f"unet_zoo_b200: precision must be 'bf16' or 'fp32' (got {precision!r})")
+        if precision == "fp32" and record:
+            raise RuntimeError("unet_zoo_b200: the fp32 parity mode is forward-only (no tape)")
         self.lib = L.load()
         self.device = device
         self.training = training
         self.record = record
+        self.fp32 = precision == "fp32"   # operators dispatch to engine_f32 (csrc/f32.cu)
+        self.act_dtype = torch.float32 if self.fp32 else torch.bfloat16
         self.tape: List[Callable[["Ctx"], None]] = []
         self.stream = torch.cuda.current_stream(device).cuda_stream
         self.sms = self.lib.uz_device_sm_count()
@@ -203,7 +211,7 @@ class Ctx:
 
     # ------------------------------------------------------------------ memory
     def new_buf(self, N, H, W, C) -> Buf:
-        return Buf(N, H, W, C, self.device)
+        return Buf(N, H, W, C, self.device, self.act_dtype)
 
     def new_act(self, N, H, W, C) -> Act:
         return Act(self.new_buf(N, H, W, C))
@@ -387,6 +395,8 @@ def stem_input(ctx: Ctx, x: torch.Tensor) -> Tuple[Act, str]:
     in_channels <= 7: 3x3 im2col into one 64-wide K block (the stem conv then runs as a 1x1 GEMM);
     otherwise a plain NHWC bf16 copy with channels padded to a multiple of 8.
     """
+    if ctx.fp32:
+        return _F32.stem_input(ctx, x)
     N, cin, H, W = x.shape
     if 9 * cin <= 64:
         kp = 16 if 9 * cin <= 16 else 32 if 9 * cin <= 32 else 64
@@ -419,6 +429,8 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
     Training: conv epilogue emits raw bf16 z + per-channel sum/sum-sq partials -> finalize -> one apply pass.
     Inference: BatchNorm folded into the packed weights and bias, ReLU in the conv epilogue.
     """
+    if ctx.fp32:
+        return _F32.conv_bn_act(ctx, xs, conv, bn, out=out, pooled=pooled, relu=relu, mode=mode, stem=stem, need_dx=need_dx)
     a0 = xs[0]
     N, H, W = a0.N, a0.H, a0.W
     cout = conv.out_channels
@@ -541,6 +553,8 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
     Reference: UpSample_UNet.up (common_layers.py:104,108) / UpsampleResUnet (common_layers.py:201-207).
     Four 1x1 GEMMs (one per output phase) with a pixel-shuffle scatter epilogue.
     """
+    if ctx.fp32:
+        return _F32.conv_transpose2x2(ctx, x, up, out)
     cout = up.out_channels
     wp = ctx.pack(up.weight, "convt_fwd")
     ctx.conv(L.CONVT2X2, [x], wp, cout, up.bias, out.ptr, out.ld, 2 * x.H, 2 * x.W)
@@ -578,6 +592,8 @@ def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
 
 def head1x1(ctx: Ctx, y: Act, conv) -> torch.Tensor:
     """1x1 classifier head -> fp32 NCHW logits (OutConv, common_layers.py:125-128)."""
+    if ctx.fp32:
+        return _F32.head1x1(ctx, y, conv)
     K = conv.out_channels
     logits = torch.empty((y.N, K, y.H, y.W), dtype=torch.float32, device=ctx.device)
     w = conv.weight.detach().reshape(K, -1)
@@ -623,6 +639,8 @@ def conv_bn_act_head(ctx: Ctx, xs: Sequence[Act], conv, bn, head, relu: bool = T
     DoubleConv / VGGBlock half followed by OutConv (common_layers.py:28-33,125-128; attention_unet.py:70,108;
     nested_unet.py:69,104).  Training: the full-resolution activation and its gradient are never stored
     (uz_bn_head_fwd / uz_bn_head_bwd).  Inference, wide heads or odd widths fall back to conv_bn_act + head1x1."""
+    if ctx.fp32:
+        return _F32.conv_bn_act_head(ctx, xs, conv, bn, head, relu=relu)
     cout, K = conv.out_channels, head.out_channels
     if not ctx.training or K > 4 or cout < 8 or cout > 256 or (cout & (cout - 1)):
         return head1x1(ctx, conv_bn_act(ctx, xs, conv, bn, relu=relu), head)
@@ -689,6 +707,8 @@ def conv_stats(ctx: Ctx, xs: Sequence[Act], conv, bn, mode: int = L.CONV3X3) -> 
 def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True) -> Act:
     """[ReLU](BatchNorm2d(x)) on an existing activation - the pre-activation half of ResidualConv
     (common_layers.py:185-186,189-190).  Training: one statistics pass + one apply pass; inference: apply only."""
+    if ctx.fp32:
+        return _F32.bn_act(ctx, x, bn, relu=relu)
     out = ctx.new_act(x.N, x.H, x.W, x.C)
     if not ctx.training:
         aff = _running_affine(bn, ctx.device)
@@ -722,6 +742,8 @@ def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mod
     """Conv2d without normalisation or activation, optionally accumulating into `out` (out += conv(x)): the last
     convolution of ResidualConv.conv_block added onto the skip branch (common_layers.py:191,198) and the two stem
     convolutions of ResUnet summed in place (resunet.py:29-33,56)."""
+    if ctx.fp32:
+        return _F32.conv_plain(ctx, xs, conv, out=out, mode=mode, accumulate=accumulate, stem=stem, need_dx=need_dx)
     a0 = xs[0]
     cout = conv.out_channels
     if mode in (L.CONV3X3_S2, L.CONV1X1_S2):
@@ -754,6 +776,8 @@ def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mod
 def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:
     """nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True) written into a concat slice
     (nested_unet.py:33,81-93)."""
+    if ctx.fp32:
+        return _F32.bilinear_up2x(ctx, x, out)
     L.check(ctx.lib.uz_bilinear2x_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, ctx.stream), "uz_bilinear2x_fwd")
     ctx.launches += 1
     if ctx.record:
@@ -772,6 +796,8 @@ def attention_gate(ctx: Ctx, g: Act, x: Act, att, out: Act) -> Act:
     """AttentionBlock.forward (attention_unet.py:34-40): out = x * sigmoid(BN(w_psi . ReLU(BN(W_g g) + BN(W_x x)))),
     written into a channel slice of the decoder's concat buffer.  The 1x1 convolutions are tcgen05 GEMMs with the
     BatchNorm statistics in their epilogue; everything else is three bandwidth kernels (csrc/gate.cu)."""
+    if ctx.fp32:
+        return _F32.attention_gate(ctx, g, x, att, out)
     conv_g, bn_g = att.w_g[0], att.w_g[1]
     conv_x, bn_x = att.w_x[0], att.w_x[1]
     conv_p, bn_p = att.psi[0], att.psi[1]
@@ -835,3 +861,6 @@ def attention_gate(ctx: Ctx, g: Act, x: Act, att, out: Act) -> Act:
                 _conv_backward(c, [src], conv, z, L.CONV1X1, False, src.C, True)
         ctx.tape.append(backward)
     return out
+
+
+from . import engine_f32 as _F32  # noqa: E402  (fp32 parity mode; imports this module back)

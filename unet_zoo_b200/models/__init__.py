@@ -59,6 +59,7 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
     num_classes = kwargs.pop("num_classes", 1)
     kwargs.pop("image_size", None)   # accepted for every model, used by none of these four
     depth = kwargs.pop("depth", 5)
+    precision = kwargs.pop("precision", "bf16")   # extension: "fp32" = forward-only parity mode (HotPathModel.set_precision)
 
     if name == "unet":
         args = dict(in_channels=in_channels, num_classes=num_classes)
@@ -70,6 +71,7 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
         args = dict(in_channels=in_channels, num_classes=num_classes, filters=[64, 128, 256, 512])
     args.update(kwargs)              # leftovers reach the constructor (TypeError if it does not know them)
     model = cls(**args)
+    model.set_precision(precision)
     if pretrained:
         print(f"Warning: Pretrained weights not implemented for {model_name}. Initializing with random weights.")
     return model

@@ -54,6 +54,16 @@ class HotPathModel(nn.Module):
     """Base class: input checks, train/eval dispatch, autograd wiring.  Subclasses implement ``_graph(ctx, x)``."""
 
     _spatial_multiple = 16
+    # "bf16": tensor-core kernels, forward + backward (default).  "fp32": forward-only parity mode on the FFMA kernels
+    # of csrc/f32.cu (BASELINE.json: fp32 logits within 1e-4 of the reference) - see set_precision().
+    precision = "bf16"
+
+    def set_precision(self, precision: str):
+        """Select the arithmetic of ``forward``: "bf16" (training and inference) or "fp32" (forward only)."""
+        if precision not in ("bf16", "fp32"):
+            raise ValueError(f"{type(self).__name__}: precision must be 'bf16' or 'fp32' (got {precision!r})")
+        self.precision = precision
+        return self
 
     def _check_input(self, x: torch.Tensor) -> torch.Tensor:
         if not isinstance(x, torch.Tensor) or x.dim() != 4:
@@ -80,7 +90,16 @@ class HotPathModel(nn.Module):
     def forward(self, x):
         x = self._check_input(x)
         with torch.cuda.device(x.device):
-            if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            if self.precision == "fp32":
+                if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+                    raise RuntimeError(f"{type(self).__name__}: the fp32 mode is a forward-only parity mode - call it "
+                                       "under torch.no_grad() (train-mode BatchNorm statistics are supported), or "
+                                       "set_precision('bf16') to train")
+                with torch.no_grad():
+                    ctx = E.Ctx(x.device, training=self.training, record=False, precision="fp32")
+                    outs = self._graph(ctx, x)
+                    self._last_launches = ctx.launches
+            elif self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
                 outs = _HotPathFn.apply(self, x, *self.parameters())
             else:
                 with torch.no_grad():
