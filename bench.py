@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--model", default="unet")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tail", default="fused", choices=["fused", "torch"],
+                    help="loss + clip + AdamW: the library's device-side tail (uz_bce_dice / uz_adamw_flat) or torch's")
     ap.add_argument("--no-graph", action="store_true", help="issue the step eagerly instead of replaying one CUDA graph")
     return ap.parse_args()
 
@@ -190,8 +192,18 @@ def main():
         model = P.DataParallel(model, bucket_mb=float(os.environ.get("UZ_BUCKET_MB", "25")))   # bucketed NCCL all-reduce overlapped with backward
     params = [p for p in model.parameters() if p.requires_grad]
     use_graph = world == 1 and not args.no_graph
-    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True, capturable=use_graph)
-    crit = torch.nn.BCEWithLogitsLoss()
+    if args.tail == "fused":
+        # BCE-with-logits + Dice + loss gradient in one pass, clip_grad_norm_(1.0) + AdamW as one flat update
+        # (training_loop.py:115-121 incl. the per-batch Dice of :81 that the torch tail below leaves out)
+        from unet_zoo_b200.loss import BCEDiceWithLogits
+        from unet_zoo_b200.optim import FlatAdamW
+        opt = FlatAdamW(params, lr=1e-4, weight_decay=1e-5, max_norm=1.0)
+        crit = BCEDiceWithLogits()
+        clip, tail_launches = None, 5
+    else:
+        opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-5, fused=True, capturable=use_graph)
+        crit = torch.nn.BCEWithLogitsLoss()
+        clip, tail_launches = 1.0, 0
 
     B, S = args.batch, args.size
     gx = torch.Generator().manual_seed(1234 + rank)
@@ -205,7 +217,8 @@ def main():
         out = model(x)
         loss = crit(out, m)
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        if clip is not None:
+            torch.nn.utils.clip_grad_norm_(params, clip)
         opt.step()
         return loss
 
@@ -233,7 +246,7 @@ def main():
     if use_graph:
         from unet_zoo_b200.train_step import GraphedTrainStep
         try:
-            step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=1.0, params=params)
+            step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=clip, params=params)
             graph_note = "one CUDA graph per step (unet_zoo_b200.train_step.GraphedTrainStep)"
         except Exception as e:   # report, never hide: the JSON line says which mode was measured
             graph_note = f"eager (graph capture failed: {type(e).__name__}: {e})"[:300]
@@ -246,7 +259,7 @@ def main():
     ms = timed(lambda: step(x_d, m_d), args.steps)
     host_ms = timed.host_ms
     base = model.module if hasattr(model, "module") else model
-    launches = (base._last_launches + base._last_launches_bwd) * args.steps
+    launches = (base._last_launches + base._last_launches_bwd + tail_launches) * args.steps
 
     # end to end: every step copies ITS batch from pinned host memory (on a copy stream, double-buffered so the copy of
     # batch i+1 overlaps the compute of batch i - what a prefetching input pipeline does) and reads the loss back
@@ -322,7 +335,9 @@ def main():
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(args.model, B, S), "global_batch": B * world,
-                   "parallelism": f"dp{world}", "launch": graph_note, "l2": "inputs larger than L2 (multi-GB activations per step)"},
+                   "parallelism": f"dp{world}", "launch": graph_note,
+                   "tail": ("uz_bce_dice + uz_adamw_flat (loss, Dice, clip, AdamW on the device)" if args.tail == "fused"
+                            else "torch BCEWithLogitsLoss + clip_grad_norm_ + fused AdamW"), "l2": "inputs larger than L2 (multi-GB activations per step)"},
         "e2e": {"value": imgs / (ms_e2e / 1000.0), "unit": "images/sec",
                 "h2d_bytes_per_step": x_h.numel() * 4 + m_h.numel() * 4, "d2h_bytes_per_step": 4},
         "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms, "roofline": roof, "clocks": clocks,

@@ -225,6 +225,26 @@ int uz_f32_bilinear2x(const float* x, int x_ld, int N, int H, int W, int C, floa
 int uz_f32_gate_apply(const float* x, int x_ld, const float* psi_raw, const float* bn_psi, long long npix, int C,
                       float* out, int out_ld, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Tail of the training step (training_loop.py:115-121): loss + metric + clip + optimizer as device-side passes with
+ * no host synchronisation.  Workspace for both calls: uz_tail_workspace_bytes().
+ *  uz_bce_dice  : result[0] = nn.BCEWithLogitsLoss()(logits, target) (mean; scripts/train.py:135),
+ *                 result[1] = dice_coefficient(logits, target) (metrics.py:7-24: sigmoid -> > 0.5 ->
+ *                 (2I + eps) / (U + eps), 1.0 when U == 0), result[2..4] = intersection, prediction sum, target sum;
+ *                 dlogits (optional) = (sigmoid(logits) - target) * grad_scale, i.e. the loss gradient for
+ *                 grad_scale = 1/n.  One pass over logits and target (fp32, n elements, 16-byte aligned).
+ *  uz_adamw_flat: torch.nn.utils.clip_grad_norm_(params, max_norm) + torch.optim.AdamW.step() over FLAT fp32 buffers
+ *                 (n elements each, 16-byte aligned; padding elements must be zero in params and grads).
+ *                 hyper[6] (device) = {lr, beta1, beta2, eps, weight_decay, max_norm (<= 0: no clipping)};
+ *                 state[5] (device) = {step, total_norm, clip_coef, bias_correction1, sqrt(bias_correction2)} -
+ *                 state[0] must persist between calls (zero before the first); grads are scaled by clip_coef in
+ *                 place like clip_grad_norm_ does. */
+size_t uz_tail_workspace_bytes(void);
+int uz_bce_dice(const float* logits, const float* target, long long n, float grad_scale, float dice_eps,
+                float* dlogits, float* result, void* workspace, size_t workspace_bytes, void* stream);
+int uz_adamw_flat(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, const float* hyper,
+                  float* state, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

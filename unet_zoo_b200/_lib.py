@@ -66,6 +66,10 @@ _PROTOS = {
                                   _P]),
     "uz_f32_bilinear2x": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P]),
     "uz_f32_gate_apply": (c_int, [_P, c_int, _P, _P, c_longlong, c_int, _P, c_int, _P]),
+    # training-step tail (csrc/tail.cu)
+    "uz_tail_workspace_bytes": (c_size_t, []),
+    "uz_bce_dice": (c_int, [_P, _P, c_longlong, c_float, c_float, _P, _P, _P, c_size_t, _P]),
+    "uz_adamw_flat": (c_int, [_P, _P, _P, _P, c_longlong, _P, _P, _P, c_size_t, _P]),
 }
 
 _lib = None
