@@ -110,8 +110,10 @@ def cpu_train_step_rate(model_name, size, steps, warmup, threads=None):
 
     import unet_zoo_b200
     from oracle import reference_port as O
-    if threads:
-        torch.set_num_threads(threads)
+    if not threads:
+        # all host cores: torchrun exports OMP_NUM_THREADS=1 to its workers, which would time a single thread
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(threads)
     torch.manual_seed(0)
     sd = copy.deepcopy(unet_zoo_b200.create_model(model_name).state_dict())
     leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()

@@ -7,6 +7,9 @@ forwards after 3 warm-ups.  Prints one JSON line per (batch, size): images/s, ms
 forward FLOPs of SURVEY.md section 6, scaled by H*W/512^2) and its fraction of the measured sustained bf16 peak.
 --graph replays the forward as one CUDA graph (unet_zoo_b200.train_step.GraphedInference) and reports both.
 --layers BATCH,SIZE prints the per-layer table of the convolution launches (CUDA events around every launch) as markdown.
+Under torchrun (N > 1) every rank runs the same sweep on its own GPU with `batch` images PER GPU (the batch is sharded,
+inference needs no communication - "replicas only"); times are the max over ranks and rank 0 prints whole-job img/s:
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 tools/bench_infer.py --graph
 """
 import argparse
 import json
@@ -30,6 +33,28 @@ def main():
     a = ap.parse_args()
     import torch
     import unet_zoo_b200
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+
+    def over_ranks(ms):
+        """Step time of the job = slowest replica (barrier before, max over ranks after)."""
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    def sync():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
     try:
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
     except Exception:
@@ -65,38 +90,42 @@ def main():
             with torch.no_grad():
                 for _ in range(3):
                     model(x)
-                torch.cuda.synchronize()
+                sync()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 for _ in range(a.iters):
                     model(x)
                 e1.record()
                 torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / a.iters
+            ms = over_ranks(e0.elapsed_time(e1) / a.iters)
             ms_graph = None
             if a.graph:
                 from unet_zoo_b200.train_step import GraphedInference
                 g = GraphedInference(model, x)
                 for _ in range(3):
                     g(x)
-                torch.cuda.synchronize()
+                sync()
                 e0.record()
                 for _ in range(a.iters):
                     g(x)
                 e1.record()
                 torch.cuda.synchronize()
-                ms_graph = e0.elapsed_time(e1) / a.iters
+                ms_graph = over_ranks(e0.elapsed_time(e1) / a.iters)
                 del g
             tf = b * FWD_GFLOP_512[a.model] * (s / 512.0) ** 2 / ms      # GFLOP / ms = TFLOP/s
-            print(json.dumps({"model": a.model, "mode": "inference", "batch": b, "size": s, "ms": round(ms, 3),
-                              "images_per_sec": round(b / ms * 1000.0, 1), "conv_tflops": round(tf, 1),
-                              "frac_of_sustained_bf16_peak": round(tf / peak, 3),
-                              "launches": model._last_launches,
-                              **({"ms_graph": round(ms_graph, 3),
-                                  "images_per_sec_graph": round(b / ms_graph * 1000.0, 1)} if ms_graph else {})}),
-                  flush=True)
+            if rank == 0:
+                line = {"model": a.model, "mode": "inference", "n_gpus": world, "batch_per_gpu": b, "size": s,
+                        "ms": round(ms, 3), "images_per_sec": round(world * b / ms * 1000.0, 1),
+                        "conv_tflops_per_gpu": round(tf, 1), "frac_of_sustained_bf16_peak": round(tf / peak, 3),
+                        "launches": model._last_launches}
+                if ms_graph:
+                    line.update(ms_graph=round(ms_graph, 3),
+                                images_per_sec_graph=round(world * b / ms_graph * 1000.0, 1))
+                print(json.dumps(line), flush=True)
             del x
             torch.cuda.empty_cache()
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
