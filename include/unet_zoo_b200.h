@@ -245,6 +245,17 @@ int uz_bce_dice(const float* logits, const float* target, long long n, float gra
 int uz_adamw_flat(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, const float* hyper,
                   float* state, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Input pipeline tail on the device (datasets.py:40-44,59; training_loop.py:109-110): the decoded bytes travel
+ * (3 + 1 bytes per pixel instead of 12 + 4) and the device normalises.
+ *  uz_stem_im2col_u8: img NHWC uint8 [N,H,W,cin] (as PIL decodes it) -> ToTensor (/255) -> Normalize((v-mean)/std)
+ *                     -> bf16 -> the 3x3 im2col operand that uz_stem_im2col writes for the normalised fp32 tensor.
+ *                     mean / std are HOST arrays of cin floats (cin <= 7).
+ *  uz_mask_u8_to_f32: out = (mask/255 > 0.5) ? 1 : 0  (fp32; the mask transform of datasets.py:46-49,59). */
+int uz_stem_im2col_u8(const uint8_t* img, int N, int cin, int H, int W, const float* mean_host, const float* std_host,
+                      void* out, int kp, void* stream);
+int uz_mask_u8_to_f32(const uint8_t* mask, long long n, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

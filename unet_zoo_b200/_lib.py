@@ -70,6 +70,9 @@ _PROTOS = {
     "uz_tail_workspace_bytes": (c_size_t, []),
     "uz_bce_dice": (c_int, [_P, _P, c_longlong, c_float, c_float, _P, _P, _P, c_size_t, _P]),
     "uz_adamw_flat": (c_int, [_P, _P, _P, _P, c_longlong, _P, _P, _P, c_size_t, _P]),
+    # input pipeline tail (csrc/input.cu)
+    "uz_stem_im2col_u8": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, _P, c_int, _P]),
+    "uz_mask_u8_to_f32": (c_int, [_P, c_longlong, _P, _P]),
 }
 
 _lib = None

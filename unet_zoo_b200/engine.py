@@ -205,6 +205,7 @@ class Ctx:
         self._ws_side = None
         self._on_side = False
         self.pgrads: Optional[ParamGrads] = None
+        self.input_norm = None                    # (mean, std) when the model is fed decoded uint8 images
         self.outputs: List[torch.Tensor] = []     # logits tensors, in the order the model returns them
         self.out_grads: List[Optional[torch.Tensor]] = []
         self.launches = 0
@@ -401,6 +402,14 @@ def stem_input(ctx: Ctx, x: torch.Tensor) -> Tuple[Act, str]:
     if 9 * cin <= 64:
         kp = 16 if 9 * cin <= 16 else 32 if 9 * cin <= 32 else 64
         a = ctx.new_act(N, H, W, kp)
+        if x.dtype == torch.uint8:
+            # decoded bytes (NHWC uint8 behind an NCHW-shaped view): ToTensor + Normalize fused into the im2col pass
+            mean, std = ctx.input_norm
+            fm, fs = (ctypes.c_float * cin)(*mean), (ctypes.c_float * cin)(*std)
+            L.check(ctx.lib.uz_stem_im2col_u8(x.data_ptr(), N, cin, H, W, fm, fs, a.ptr, kp, ctx.stream),
+                    "uz_stem_im2col_u8")
+            ctx.launches += 1
+            return a, "im2col"
         L.check(ctx.lib.uz_stem_im2col(x.data_ptr(), N, cin, H, W, a.ptr, kp, ctx.stream), "uz_stem_im2col")
         ctx.launches += 1
         return a, "im2col"

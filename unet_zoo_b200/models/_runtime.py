@@ -17,6 +17,7 @@ class _HotPathFn(torch.autograd.Function):
     @staticmethod
     def forward(fctx, model, x, *params):
         ctx = E.Ctx(x.device, training=True, record=True)
+        ctx.input_norm = model._input_norm
         outs = model._graph(ctx, x)
         fctx.ectx = ctx
         fctx.model = model
@@ -65,9 +66,34 @@ class HotPathModel(nn.Module):
         self.precision = precision
         return self
 
+    _input_norm = None
+
+    def set_input_normalization(self, mean, std):
+        """Let ``forward`` take the DECODED image bytes: a uint8 tensor [N, H, W, C] (as PIL / the dataset's Resize
+        leaves it).  ToTensor (/255) and Normalize(mean, std) of the reference's dataset (datasets.py:40-44) then run
+        inside the stem kernel (uz_stem_im2col_u8) and the host->device copy shrinks 4x.  None, None switches it off."""
+        if mean is None or std is None:
+            self._input_norm = None
+            return self
+        mean, std = [float(v) for v in mean], [float(v) for v in std]
+        if len(mean) != self._in_channels or len(std) != self._in_channels or min(std) <= 0:
+            raise ValueError(f"{type(self).__name__}: mean / std need {self._in_channels} entries, std > 0")
+        self._input_norm = (mean, std)
+        return self
+
     def _check_input(self, x: torch.Tensor) -> torch.Tensor:
         if not isinstance(x, torch.Tensor) or x.dim() != 4:
             raise RuntimeError(f"{type(self).__name__}: expected a 4-D NCHW tensor")
+        if x.dtype == torch.uint8:
+            if self._input_norm is None:
+                raise RuntimeError(f"{type(self).__name__}: uint8 input needs set_input_normalization(mean, std)")
+            if self.precision != "bf16" or 9 * self._in_channels > 64:
+                raise RuntimeError(f"{type(self).__name__}: uint8 input is served by the bf16 im2col stem "
+                                   "(in_channels <= 7) only")
+            if x.shape[3] != self._in_channels:
+                raise RuntimeError(f"{type(self).__name__}: uint8 input must be [N, H, W, {self._in_channels}] "
+                                   f"(got {tuple(x.shape)})")
+            x = x.contiguous().permute(0, 3, 1, 2)     # NCHW-shaped view of the NHWC bytes; checks below apply as is
         if not x.is_cuda:
             raise RuntimeError(f"{type(self).__name__}: input must be a CUDA tensor - this is the sm_100a build and "
                                "has no CPU path (move the model and the batch to the GPU)")
@@ -85,7 +111,7 @@ class HotPathModel(nn.Module):
                                "the reference's centre-padding of odd skip sizes is not implemented")
         if x.requires_grad:
             raise RuntimeError(f"{type(self).__name__}: gradients w.r.t. the input image are not implemented")
-        return x.float().contiguous()
+        return x if x.dtype == torch.uint8 else x.float().contiguous()
 
     def forward(self, x):
         x = self._check_input(x)
@@ -104,6 +130,7 @@ class HotPathModel(nn.Module):
             else:
                 with torch.no_grad():
                     ctx = E.Ctx(x.device, training=self.training, record=False)
+                    ctx.input_norm = self._input_norm
                     outs = self._graph(ctx, x)
                     self._last_launches = ctx.launches
         return self._pack_outputs(list(outs))

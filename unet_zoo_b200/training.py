@@ -34,6 +34,33 @@ def dice_coefficient(prediction: torch.Tensor, target: torch.Tensor, epsilon: fl
     return torch.where(union == 0, torch.ones_like(union), (2.0 * inter + epsilon) / (union + epsilon))
 
 
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)   # datasets.py:43
+
+
+def to_device_batch(img: torch.Tensor, mask: torch.Tensor, device) -> Tuple[torch.Tensor, torch.Tensor]:
+    """training_loop.py:109-110 (`img.float().to(device)`, `mask.float().to(device)`).  uint8 tensors - the decoded
+    bytes: image [N,H,W,C], mask any shape with values 0..255 - are copied as they are (4x fewer bytes); the image is
+    normalised inside the model's stem kernel (HotPathModel.set_input_normalization) and the mask becomes
+    `(m/255 > 0.5).float()` (datasets.py:59) in one device pass (uz_mask_u8_to_f32)."""
+    if img.dtype == torch.uint8:
+        img = img.to(device, non_blocking=True)
+    else:
+        img = img.float().to(device, non_blocking=True)
+    if mask.dtype == torch.uint8:
+        from . import _lib as L
+        m8 = mask.to(device, non_blocking=True).contiguous()
+        if not m8.is_cuda:
+            raise RuntimeError("unet_zoo_b200.training: uint8 masks are converted on the GPU (there is no CPU path)")
+        out = torch.empty(m8.shape, dtype=torch.float32, device=m8.device)
+        with torch.cuda.device(m8.device):
+            L.check(L.load().uz_mask_u8_to_f32(m8.data_ptr(), m8.numel(), out.data_ptr(),
+                                               torch.cuda.current_stream(m8.device).cuda_stream), "uz_mask_u8_to_f32")
+        mask = out
+    else:
+        mask = mask.float().to(device, non_blocking=True)
+    return img, mask
+
+
 def _unwrap(model: nn.Module) -> nn.Module:
     return model.module if hasattr(model, "module") and isinstance(model.module, nn.Module) else model
 
@@ -65,9 +92,7 @@ def train_one_epoch(model: nn.Module, dataloader, optimizer, criterion, device, 
     clips_itself = getattr(optimizer, "param_groups", [{}])[0].get("max_norm") is not None
     n = 0
     for idx, batch in enumerate(dataloader):
-        img, mask = batch[0], batch[1]
-        img = img.float().to(device, non_blocking=True)
-        mask = mask.float().to(device, non_blocking=True)
+        img, mask = to_device_batch(batch[0], batch[1], device)
         optimizer.zero_grad()
         outputs = model(img)
         loss, main_logits, dc = _loss_and_dice(outputs, mask, criterion)
@@ -101,8 +126,7 @@ def validate_one_epoch(model: nn.Module, dataloader, criterion, device, model_na
     n = 0
     with torch.no_grad():
         for batch in dataloader:
-            img = batch[0].float().to(device, non_blocking=True)
-            mask = batch[1].float().to(device, non_blocking=True)
+            img, mask = to_device_batch(batch[0], batch[1], device)
             loss, _, dc = _loss_and_dice(model(img), mask, criterion)
             run_loss += loss
             run_dc += dc
