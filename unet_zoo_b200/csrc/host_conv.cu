@@ -697,7 +697,7 @@ static bool use_wgrad2(int mode, int H, int W) {
   return !disabled && mode == UZ_CONV3X3 && H >= 16 && W >= 8;
 }
 struct Wg2Plan {
-  int xb, yb, chunks, co_blocks, ci_blocks, splits, pair, ci_units;
+  int xb, yb, chunks, co_blocks, ci_blocks, splits, pair, ci_units, wide;
   size_t ws_bytes;
 };
 static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
@@ -705,7 +705,10 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   pl.xb = (W + 7) / 8;
   pl.yb = (H + 15) / 16;
   pl.chunks = N * pl.xb * pl.yb;
-  pl.co_blocks = (cout + 63) / 64;
+  // WIDE: 128 output channels per work unit, N = 128 MMAs in two passes over the chunk range (see igemm_wgrad2.cu):
+  // the N = 64 tile is capped by the shared-memory port at 67 % (single CTA) / 80 % (pair) of the tensor rate
+  pl.wide = (cout >= 128 && env_int("UZ_WGRAD2_WIDE", 1)) ? 1 : 0;
+  pl.co_blocks = pl.wide ? (cout + 127) / 128 : (cout + 63) / 64;
   pl.ci_blocks = (cin + 63) / 64;
   int sms = sm_count();
   if (sms < 1) sms = 148;
@@ -727,6 +730,8 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   for (int sp = 1; sp <= max_splits; ++sp) {
     const long long items = (long long)units * sp;
     const long long waves = (items + sms - 1) / sms;
+    // WIDE: per chunk 3 + 2 MMA groups of 64 cycles against 5 of 32, two epilogues of 384 + 256 columns against one
+    // of 320 - same relative weight of main loop and epilogue, so the same formula ranks the split factors
     const long long cost = waves * ((pl.chunks + sp - 1) / sp + 4);
     if (best < 0 || cost < best) {
       best = cost;
@@ -766,6 +771,7 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
     if (rc2 == UZ_OK && p2.pair) rc2 = make_act_map(&q.dzmap_half, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1, 32);
     if (rc2 != UZ_OK) return rc2;
     q.pair = p2.pair;
+    q.wide = p2.wide;
     q.ci_units = p2.ci_units;
     q.xb = p2.xb;
     q.yb = p2.yb;

@@ -89,6 +89,9 @@ struct alignas(64) Wgrad2Params {
   CUtensorMap dzmap_half;  // dZ: box (32, 8, 16, 1), SWIZZLE_64B
   int pair;                // 0 / 1
   int ci_units;            // ci_blocks (single CTA) or ceil(ci_blocks / 2) (pair)
+  // WIDE mode: output-channel blocks of 128 (co_blocks = ceil(cp/128)), N = 128 MMAs, two passes over the chunk range
+  // (tap pairs 0..2, then 3..4) because five 128-column accumulators exceed the 512 TMEM columns.
+  int wide;                // 0 / 1
 };
 
 // Second-generation forward-type implicit GEMM (igemm_fwd2.cu): conv3x3 / its data gradient / conv1x1 on 8x16-pixel

@@ -13,6 +13,14 @@
 // TWO taps x 64 input channels: the descriptor's leading-dimension byte offset (distance between the two 64-element MN
 // atoms) is simply the address shift between the two taps (128 B for dx+1, 1280 B for dy+1), so five MMAs cover the nine
 // taps (the tenth half is discarded).  B = dZ chunk, N = 64 output channels.  D blocks live in 5 x 64 TMEM columns.
+//
+// WIDE mode (output-channel blocks of 128): the M = 128 (x2 in a pair), N = 64, K = 16 MMA above reads its 4 KB A operand
+// (two taps x 64 channels x 16 pixels) in 32 tensor cycles = 128 B/clk, i.e. the A side alone saturates the 128 B/clk
+// shared-memory port whatever happens to B (ncu: tensor-memory path 81-85 % busy, tensor pipe 68-72 %).  Only a wider N
+// buys cycles per A byte, but five accumulators of 128 columns do not fit the 512 TMEM columns - so a work unit makes
+// TWO passes over its chunk range: tap pairs {0,1} {3,4} {6,7} (3 x 128 columns), then {2,5} {8,-} (2 x 128).  The X halo
+// and dZ are loaded once per pass (L2 hits); per CTA and MMA 4 KB (A) + 4 KB (B; 2 KB in a pair) leave shared memory in
+// 64 cycles = 128 (96) B/clk.
 #include <string.h>
 
 #include "igemm.cuh"
@@ -25,10 +33,14 @@ constexpr int kW2HaloW = 10, kW2HaloH = 18;
 constexpr int kW2HaloBytes = kW2HaloW * kW2HaloH * 128;  // 23040
 constexpr int kW2HaloSlot = 23552;                       // rounded up to 1024
 constexpr int kW2DzBytes = 128 * 128;                    // 8x16 pixels x 64 channels bf16
-constexpr int kW2StageBytes = kW2HaloSlot + kW2DzBytes;  // 39936
-constexpr int kW2Stages = 5;
 constexpr int kW2TmemCols = 512;
-constexpr int kW2SmemBytes = kW2Stages * kW2StageBytes + 256 + 1024;
+// per (CG, WIDE): bytes of dZ one CTA keeps per stage, stage size, ring depth
+__host__ __device__ constexpr int w2_dz_slot(int cg, int wide) { return (wide && cg == 1) ? 2 * kW2DzBytes : kW2DzBytes; }
+__host__ __device__ constexpr int w2_stage_bytes(int cg, int wide) { return kW2HaloSlot + w2_dz_slot(cg, wide); }
+__host__ __device__ constexpr int w2_stages(int cg, int wide) { return (wide && cg == 1) ? 4 : 5; }
+__host__ __device__ constexpr int w2_smem_bytes(int cg, int wide) {
+  return w2_stages(cg, wide) * w2_stage_bytes(cg, wide) + 256 + 1024;
+}
 
 struct W2Item {
   int co_blk, ci_blk, split, chunk_begin, chunk_end;
@@ -48,9 +60,14 @@ __device__ __forceinline__ W2Item w2_decode(const Wgrad2Params& p, int item, int
   return w;
 }
 
-template <int CG>
+template <int CG, int WIDE>
 __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
   constexpr bool kPair = CG == 2;
+  constexpr int kW2StageBytes = w2_stage_bytes(CG, WIDE);
+  constexpr int kW2Stages = w2_stages(CG, WIDE);
+  constexpr int kBN = WIDE ? 128 : 64;        // output channels per work unit = accumulator columns per tap pair
+  constexpr int kPasses = WIDE ? 2 : 1;       // WIDE: tap pairs 0..2 in the first pass over the chunks, 3..4 in the second
+  constexpr int kCoBlk = kBN;
   const int rank = kPair ? static_cast<int>(cluster_ctarank()) : 0;
   const bool leader = rank == 0;
   const int first_item = blockIdx.x / CG, item_step = gridDim.x / CG;
@@ -79,7 +96,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     mbar_init(tempty_bar, 4 * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&p.xmap);
-    tma_prefetch_desc(kPair ? &p.dzmap_half : &p.dzmap);
+    tma_prefetch_desc((kPair && !WIDE) ? &p.dzmap_half : &p.dzmap);
   }
   if (warp == 1) {
     if (kPair) {
@@ -103,6 +120,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       uint32_t phase = 0;
       for (int item = first_item; item < p.total_items; item += item_step) {
         const W2Item w = w2_decode(p, item, CG, rank);
+        for (int pass = 0; pass < kPasses; ++pass)
         for (int chunk = w.chunk_begin; chunk < w.chunk_end; ++chunk) {
           const int xb = chunk % p.xb;
           int r = chunk / p.xb;
@@ -112,10 +130,19 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t halo_dst = base + stage * kW2StageBytes;
           const uint32_t dz_dst = halo_dst + kW2HaloSlot;
-          if (kPair) {   // own halo + own half of the dZ chunk; everything completes on the leader's barrier
+          if (kPair && WIDE) {   // own halo + own 64 of the 128 dZ channels; completes on the leader's barrier
+            if (leader) mbar_expect_tx(full_bar(stage), 2 * kW2HaloBytes + 2 * kW2DzBytes);
+            tma_load_4d_pair(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+            tma_load_4d_pair(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * kCoBlk + rank * 64, x0, y0, n);
+          } else if (kPair) {   // own halo + own half of the dZ chunk; everything completes on the leader's barrier
             if (leader) mbar_expect_tx(full_bar(stage), 2 * kW2HaloBytes + kW2DzBytes);
             tma_load_4d_pair(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
             tma_load_4d_pair(dz_dst, &p.dzmap_half, full_bar(stage), w.co_blk * 64 + rank * 32, x0, y0, n);
+          } else if (WIDE) {    // two 64-channel dZ boxes side by side (the B descriptor's LBO spans them)
+            mbar_expect_tx(full_bar(stage), kW2HaloBytes + 2 * kW2DzBytes);
+            tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+            tma_load_4d(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * kCoBlk, x0, y0, n);
+            tma_load_4d(dz_dst + kW2DzBytes, &p.dzmap, full_bar(stage), w.co_blk * kCoBlk + 64, x0, y0, n);
           } else {
             mbar_expect_tx(full_bar(stage), kW2HaloBytes + kW2DzBytes);
             tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
@@ -131,7 +158,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
     if (leader && elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 64, 1, 1);  // both operands MN-major
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, kBN, 1, 1);  // both operands MN-major
       // tap pairs stacked along M: {first tap row offset (in halo pixels), byte distance to the second tap}
       //   taps are (dy, dx) in {-1,0,1}^2 with tap index (dy+1)*3 + (dx+1); halo row of tap = (dy+1)*10 + (dx+1)
       constexpr int pair_row[5] = {0 * 10 + 0, 1 * 10 + 0, 2 * 10 + 0, 0 * 10 + 2, 2 * 10 + 2};
@@ -142,6 +169,9 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       for (int item = first_item; item < p.total_items; item += item_step) {
         const W2Item w = w2_decode(p, item, CG, rank);
         if (w.chunk_end <= w.chunk_begin) continue;
+        for (int pass = 0; pass < kPasses; ++pass) {
+        const int b_begin = WIDE ? (pass == 0 ? 0 : 3) : 0;
+        const int b_end = WIDE ? (pass == 0 ? 3 : 5) : 5;
         mbar_wait(tempty_bar, acc_phase ^ 1u);
         tc_fence_after();
         bool first = true;
@@ -151,23 +181,25 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           const uint32_t halo = base + stage * kW2StageBytes;
           const uint32_t dz = halo + kW2HaloSlot;
           const uint32_t halo_lo = umma_desc_lo(halo, 0);
-          const uint32_t dz_lo = umma_desc_lo(dz, 1024);
+          // WIDE single CTA: N = 128 = two 64-channel boxes, LBO = distance between them
+          const uint32_t dz_lo = umma_desc_lo(dz, (WIDE && !kPair) ? kW2DzBytes : 1024);
           constexpr uint32_t a_hi = umma_desc_hi(kW2HaloW * 128);
-          // dZ: 128-byte pixel rows (SWIZZLE_128B), or the pair's 64-byte half rows (SWIZZLE_64B = layout code 4)
-          constexpr uint32_t b_hi = kPair ? (((512u >> 4) & 0x3FFFu) | (1u << 14) | (4u << 29)) : umma_desc_hi(1024);
-          constexpr uint32_t b_kstep = (kPair ? 1024u : 2048u) >> 4;   // 16 pixels further, in 16-byte units
+          // dZ: 128-byte pixel rows (SWIZZLE_128B), or the narrow pair's 64-byte half rows (SWIZZLE_64B = layout code 4)
+          constexpr bool kHalfRows = kPair && !WIDE;
+          constexpr uint32_t b_hi = kHalfRows ? (((512u >> 4) & 0x3FFFu) | (1u << 14) | (4u << 29)) : umma_desc_hi(1024);
+          constexpr uint32_t b_kstep = (kHalfRows ? 1024u : 2048u) >> 4;   // 16 pixels further, in 16-byte units
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 16 pixels = image rows 2j, 2j+1 of the chunk
 #pragma unroll
             for (int b = 0; b < 5; ++b) {
+              if (b < b_begin || b >= b_end) continue;
               // start row of the tap pair (+ two halo rows per K step), LBO = byte distance to the pair's second tap
               const uint32_t a_lo = halo_lo + ((pair_row[b] * 128 + j * 2 * kW2HaloW * 128) >> 4) + ((pair_lbo[b] >> 4) << 16);
+              const uint32_t d_col = tmem_base + (b - b_begin) * kBN;
               if (kPair)
-                umma2_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc,
-                                 (first && j == 0) ? 0u : 1u);
+                umma2_bf16_words(d_col, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc, (first && j == 0) ? 0u : 1u);
               else
-                umma_bf16_words(tmem_base + b * 64, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc,
-                                (first && j == 0) ? 0u : 1u);
+                umma_bf16_words(d_col, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc, (first && j == 0) ? 0u : 1u);
             }
           }
           first = false;
@@ -185,6 +217,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
         else
           umma_commit(tfull_bar);
         acc_phase ^= 1u;
+        }  // pass
       }
     }
   } else {
@@ -198,22 +231,26 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     for (int item = first_item; item < p.total_items; item += item_step) {
       const W2Item w = w2_decode(p, item, CG, rank);
       const bool has_work = w.chunk_end > w.chunk_begin;
+      const int ci = w.ci_blk * 64 + ci_l;
+      const int co0 = w.co_blk * kCoBlk;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      float* pbase = p.partial + static_cast<size_t>(w.split) * p.cp * 9 * p.cq;
+#pragma unroll 1
+      for (int pass = 0; pass < kPasses; ++pass) {
+      const int b_begin = WIDE ? (pass == 0 ? 0 : 3) : 0;
+      const int b_end = WIDE ? (pass == 0 ? 3 : 5) : 5;
       if (has_work) {
         mbar_wait(tfull_bar, acc_phase);
         tc_fence_after();
       }
-      const int ci = w.ci_blk * 64 + ci_l;
-      const int co0 = w.co_blk * 64;
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-      float* pbase = p.partial + static_cast<size_t>(w.split) * p.cp * 9 * p.cq;
 #pragma unroll 1
-      for (int b = 0; b < 5; ++b) {
+      for (int b = b_begin; b < b_end; ++b) {
         const int tap = pair_tap[b][half];
 #pragma unroll 1
-        for (int h = 0; h < 2; ++h) {
+        for (int h = 0; h < kBN / 32; ++h) {
           uint32_t v[32];
           if (has_work) {
-            tmem_ld32(t_addr + b * 64 + h * 32, v);
+            tmem_ld32(t_addr + (b - b_begin) * kBN + h * 32, v);
             tmem_ld_wait();
           } else {
 #pragma unroll
@@ -239,6 +276,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
         }
         acc_phase ^= 1u;
       }
+      }  // pass
     }
   }
 
@@ -254,12 +292,13 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
   }
 }
 
-template <int CG>
+template <int CG, int WIDE>
 static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_t stream) {
+  constexpr int kW2SmemBytes = w2_smem_bytes(CG, WIDE);
   static bool configured = false;
   if (!configured) {
-    cudaError_t e =
-        cudaFuncSetAttribute(igemm_wgrad2_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(igemm_wgrad2_kernel<CG, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kW2SmemBytes);
     if (e != cudaSuccess) return e;
     configured = true;
   }
@@ -276,11 +315,12 @@ static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = CG > 1 ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, igemm_wgrad2_kernel<CG>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_wgrad2_kernel<CG, WIDE>, p);
 }
 
 cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream) {
-  return p.pair ? launch_wgrad2_cg<2>(p, grid, stream) : launch_wgrad2_cg<1>(p, grid, stream);
+  if (p.wide) return p.pair ? launch_wgrad2_cg<2, 1>(p, grid, stream) : launch_wgrad2_cg<1, 1>(p, grid, stream);
+  return p.pair ? launch_wgrad2_cg<2, 0>(p, grid, stream) : launch_wgrad2_cg<1, 0>(p, grid, stream);
 }
 
 }  // namespace uz
