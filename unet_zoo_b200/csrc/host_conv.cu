@@ -16,6 +16,7 @@ cudaError_t launch_igemm_fwd(const IgemmParams& p, int bn, int grid, cudaStream_
 cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream);
+cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_row, int accumulate, cudaStream_t stream);
 cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
                                 long long s_row, long long s_col, long long s_tap, int accumulate,
                                 cudaStream_t stream);
@@ -707,9 +708,11 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   pl.chunks = N * pl.xb * pl.yb;
   // WIDE: 128 output channels per work unit, N = 128 MMAs in two passes over the chunk range (see igemm_wgrad2.cu):
   // the N = 64 tile is capped by the shared-memory port at 67 % (single CTA) / 80 % (pair) of the tensor rate
-  pl.wide = (cout >= 128 && env_int("UZ_WGRAD2_WIDE", 1)) ? 1 : 0;
-  pl.co_blocks = pl.wide ? (cout + 127) / 128 : (cout + 63) / 64;
   pl.ci_blocks = (cin + 63) / 64;
+  // measured per layer (tools/bench_wgrad.py): WIDE wins 2-19 % wherever the CTA pair applies; a single WIDE CTA
+  // (64 input channels) is 4 % slower than the N = 64 tile (its 4-stage ring of 55 KB stages is shallower)
+  pl.wide = (cout >= 128 && pl.ci_blocks >= 2 && env_int("UZ_WGRAD2_WIDE", 1)) ? 1 : 0;
+  pl.co_blocks = pl.wide ? (cout + 127) / 128 : (cout + 63) / 64;
   int sms = sm_count();
   if (sms < 1) sms = 148;
   // CTA pairs (cta_group::2) over two adjacent input-channel blocks: the M = 128, N = 64 MMA of a single CTA reads
@@ -739,7 +742,8 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
     }
   }
   pl.splits = splits;
-  pl.ws_bytes = sizeof(float) * (size_t)splits * cout * 9 * cin;
+  // tile-major partials: one contiguous 9 x (64 | 128) x 64 fp32 region per (split, co block, ci block)
+  pl.ws_bytes = sizeof(float) * (size_t)splits * pl.co_blocks * pl.ci_blocks * 9 * (pl.wide ? 128 : 64) * 64;
   return pl;
 }
 }  // namespace uz
@@ -788,8 +792,7 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
                               : (q.total_items < sms ? q.total_items : sms);
     cudaError_t e2 = launch_igemm_wgrad2(q, grid2, st2);
     if (e2 != cudaSuccess) return cuda_error(e2, "igemm_wgrad2 launch");
-    e2 = launch_wgrad_reduce(q.partial, dw + (long long)c_off * 9, p2.splits, cout, 9, cin, (long long)cin_total * 9, 9, 1,
-                             accumulate, st2);
+    e2 = launch_wgrad2_reduce(q, dw + (long long)c_off * 9, (long long)cin_total * 9, accumulate, st2);
     if (e2 != cudaSuccess) return cuda_error(e2, "wgrad_reduce launch");
     return UZ_OK;
   }

@@ -82,7 +82,7 @@ struct alignas(64) Wgrad2Params {
   int co_blocks, ci_blocks;  // ceil(cp/64), ceil(cq/64)
   int splits;          // split-K factor over the chunk range
   int total_items;     // co_blocks * ci_blocks * splits
-  float* partial;      // [splits][cp][9][cq] fp32
+  float* partial;      // tile-major fp32: [splits][co_blocks][ci_blocks][9][64 or 128 (wide)][64]
   // CTA-pair mode (cta_group::2): the two CTAs of a cluster take two adjacent input-channel blocks of the same
   // (output-channel block, chunk range); each loads its own X halo and HALF of the dZ chunk (32 channels), one
   // M = 256, N = 64 MMA serves both.  Per CTA and MMA 5 KB instead of 6 KB leave shared memory (160 vs 192 B/clk).

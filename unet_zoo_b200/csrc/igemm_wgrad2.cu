@@ -232,9 +232,12 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       const W2Item w = w2_decode(p, item, CG, rank);
       const bool has_work = w.chunk_end > w.chunk_begin;
       const int ci = w.ci_blk * 64 + ci_l;
-      const int co0 = w.co_blk * kCoBlk;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-      float* pbase = p.partial + static_cast<size_t>(w.split) * p.cp * 9 * p.cq;
+      // partials are TILE-major: [split][co block][ci block][tap][co_l][ci_l] - one contiguous 9 x kBN x 64 fp32 region
+      // per work unit.  (With the parameter layout [co][tap][ci] a unit scattered 256-byte pieces over a 9*cq*4-byte
+      // pitch: the epilogue of the weight-heavy layers ran at < 1 TB/s, 23-28 us per unit.)
+      float* pbase = p.partial + ((static_cast<size_t>(w.split) * p.co_blocks + w.co_blk) * p.ci_blocks + w.ci_blk) *
+                                     (9 * kBN * 64) + ci_l;
 #pragma unroll 1
       for (int pass = 0; pass < kPasses; ++pass) {
       const int b_begin = WIDE ? (pass == 0 ? 0 : 3) : 0;
@@ -257,11 +260,9 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
             for (int j = 0; j < 32; ++j) v[j] = 0u;
           }
           if (tap >= 0 && ci < p.cq) {
+            float* o = pbase + (tap * kBN + h * 32) * 64;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int co = co0 + h * 32 + j;
-              if (co < p.cp) pbase[(static_cast<size_t>(co) * 9 + tap) * p.cq + ci] = __uint_as_float(v[j]);
-            }
+            for (int j = 0; j < 32; ++j) o[j * 64] = __uint_as_float(v[j]);
           }
         }
       }
@@ -290,6 +291,62 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     else
       tmem_dealloc(tmem_base, kW2TmemCols);
   }
+}
+
+// dst[co][c_off + ci][tap] (OIHW, row pitch s_row floats) (+)= sum over splits of the tile-major partials.
+// block = (output channel, input-channel block): thread = (tap, lane) sums two columns over the splits (256-byte
+// contiguous reads per tap), the sums are transposed through shared memory and leave as ONE contiguous run of
+// 64 * 9 floats.
+__global__ void __launch_bounds__(288) wgrad2_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dst,
+                                                            int splits, int cp, int cq, int co_blocks, int ci_blocks,
+                                                            int bn, long long s_row, int accumulate) {
+  __shared__ float stage[9 * 65];
+  const int co = blockIdx.x / ci_blocks, ci_blk = blockIdx.x % ci_blocks;
+  const int tap = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int co_blk = co / bn, co_l = co % bn;
+  const size_t tile = static_cast<size_t>(9) * bn * 64;
+  const size_t split_stride = static_cast<size_t>(co_blocks) * ci_blocks * tile;
+  const float* q = partial + (static_cast<size_t>(co_blk) * ci_blocks + ci_blk) * tile +
+                   (static_cast<size_t>(tap) * bn + co_l) * 64 + lane;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+  int k = 0;
+  for (; k + 4 <= splits; k += 4) {   // eight independent loads in flight per thread
+    a0 += __ldg(q + (k + 0) * split_stride);
+    b0 += __ldg(q + (k + 0) * split_stride + 32);
+    a1 += __ldg(q + (k + 1) * split_stride);
+    b1 += __ldg(q + (k + 1) * split_stride + 32);
+    a2 += __ldg(q + (k + 2) * split_stride);
+    b2 += __ldg(q + (k + 2) * split_stride + 32);
+    a3 += __ldg(q + (k + 3) * split_stride);
+    b3 += __ldg(q + (k + 3) * split_stride + 32);
+  }
+  for (; k < splits; ++k) {
+    a0 += __ldg(q + k * split_stride);
+    b0 += __ldg(q + k * split_stride + 32);
+  }
+  a0 = (a0 + a1) + (a2 + a3);
+  b0 = (b0 + b1) + (b2 + b3);
+  a1 = 0.f;
+  b1 = 0.f;
+  stage[tap * 65 + lane] = a0 + a1;
+  stage[tap * 65 + lane + 32] = b0 + b1;
+  __syncthreads();
+  const int ncol = min(64, cq - ci_blk * 64);
+  float* o = dst + co * s_row + static_cast<long long>(ci_blk) * 64 * 9;
+  for (int i = threadIdx.x; i < ncol * 9; i += 288) {
+    const int c = i / 9, t = i - c * 9;
+    const float v = stage[t * 65 + c];
+    o[i] = accumulate ? o[i] + v : v;
+  }
+}
+
+cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_row, int accumulate,
+                                 cudaStream_t stream) {
+  const long long blocks = static_cast<long long>(p.cp) * p.ci_blocks;
+  if (blocks < 1 || blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
+  wgrad2_reduce_kernel<<<static_cast<int>(blocks), 288, 0, stream>>>(p.partial, dst, p.splits, p.cp, p.cq, p.co_blocks,
+                                                                     p.ci_blocks, p.wide ? 128 : 64, s_row, accumulate);
+  return cudaGetLastError();
 }
 
 template <int CG, int WIDE>
