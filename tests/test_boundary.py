@@ -90,3 +90,20 @@ def test_library_exports_every_declared_symbol():
     if not torch.cuda.is_available():
         lib.uz_last_error.restype = ctypes.c_char_p
         assert lib.uz_device_sm_count() < 0 and lib.uz_last_error()
+
+
+def test_precision_and_input_normalization_knobs_are_validated_on_the_host():
+    """Extensions of the factory / module surface: `precision` ("bf16" default, "fp32" forward-only parity mode) and
+    `set_input_normalization` (decoded uint8 batches).  Bad values fail on the host, before any device work."""
+    m = unet_zoo_b200.create_model("unet", precision="fp32")
+    assert m.precision == "fp32" and unet_zoo_b200.create_model("unet").precision == "bf16"
+    with pytest.raises(ValueError):
+        unet_zoo_b200.create_model("unet", precision="fp16")
+    with pytest.raises(ValueError):
+        m.set_input_normalization((0.5,), (0.5,))               # needs one entry per input channel
+    with pytest.raises(ValueError):
+        m.set_input_normalization((0.5, 0.5, 0.5), (0.5, 0.0, 0.5))
+    assert m.set_input_normalization((0.5, 0.5, 0.5), (0.2, 0.2, 0.2)) is m
+    assert len(m.state_dict()) == 136                           # neither knob adds parameters or buffers
+    with pytest.raises(RuntimeError):                           # still no CPU path, in either precision
+        m(torch.zeros(1, 3, 32, 32))
