@@ -40,7 +40,11 @@ class GraphedTrainStep:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # with a process group up, NCCL's watchdog thread polls events while we capture: only calls of THIS thread (and
+        # the work it enqueues, incl. the bucketed all-reduces on the communication stream) belong to the capture
+        import torch.distributed as dist
+        mode = "thread_local" if (dist.is_available() and dist.is_initialized()) else "global"
+        with torch.cuda.graph(self.graph, capture_error_mode=mode):
             self._body()
 
     def _body(self):
