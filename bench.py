@@ -193,8 +193,9 @@ def main():
     if world > 1:
         model = P.DataParallel(model, bucket_mb=float(os.environ.get("UZ_BUCKET_MB", "25")))   # bucketed NCCL all-reduce overlapped with backward
     params = [p for p in model.parameters() if p.requires_grad]
-    # N > 1: the graph then also holds the bucketed NCCL all-reduces (UZ_GRAPH_DDP=0 issues the step eagerly)
-    use_graph = (world == 1 or os.environ.get("UZ_GRAPH_DDP", "0") == "1") and not args.no_graph
+    # N > 1 issues the step eagerly: capturing the bucketed NCCL all-reduces of the communication stream into the
+    # step graph was tried (capture_error_mode="thread_local") and hung at N = 2; host enqueue is 24-36 ms of a 43-47 ms step
+    use_graph = world == 1 and not args.no_graph
     if args.tail == "fused":
         # BCE-with-logits + Dice + loss gradient in one pass, clip_grad_norm_(1.0) + AdamW as one flat update
         # (training_loop.py:115-121 incl. the per-batch Dice of :81 that the torch tail below leaves out)

@@ -7,7 +7,8 @@ packing, reductions) are visible.  :class:`GraphedTrainStep` records the step on
 is stream-ordered and allocation-free, the executor's buffers come from the graph's private memory pool) and replays
 it with a single ``cudaGraphLaunch`` per batch: no tracing compiler, the same kernels in the same order.
 
-Constraints: fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
+Constraints: single GPU (with the data-parallel wrapper the step is issued eagerly: capturing its NCCL all-reduces
+was tried and hung); fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
 capturable=True)``); the learning-rate schedule, if any, must live in a device tensor.
 """
 from typing import Callable, Iterable, Optional
@@ -40,11 +41,7 @@ class GraphedTrainStep:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
-        # with a process group up, NCCL's watchdog thread polls events while we capture: only calls of THIS thread (and
-        # the work it enqueues, incl. the bucketed all-reduces on the communication stream) belong to the capture
-        import torch.distributed as dist
-        mode = "thread_local" if (dist.is_available() and dist.is_initialized()) else "global"
-        with torch.cuda.graph(self.graph, capture_error_mode=mode):
+        with torch.cuda.graph(self.graph):
             self._body()
 
     def _body(self):
