@@ -29,7 +29,7 @@ def load_reference():
     pkg.__path__ = [REF]
     sys.modules["refmodels"] = pkg
     mods = {}
-    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet"):
+    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet"):
         spec = importlib.util.spec_from_file_location(f"refmodels.{name}", os.path.join(REF, name + ".py"))
         m = importlib.util.module_from_spec(spec)
         sys.modules[f"refmodels.{name}"] = m
@@ -48,6 +48,13 @@ def build(mods, name, **kw):
                                               deep_supervision=kw.get("deep_supervision", False))
     if name == "resunet":
         return mods["resunet"].ResUnet(in_channels=3, num_classes=1, filters=[64, 128, 256, 512])
+    if name == "transatt_unet":
+        # ScaledDotProductAttention's nn.Dropout(0.1) draws from the global RNG in train mode; the main fixture is
+        # taken with the knob of that nn.Dropout INSTANCE set to kw["attn_dropout"] (0.0: comparable across RNG
+        # engines); the as-is (p = 0.1) train logits are stored next to it under a fixed seed
+        model = mods["transatt_unet"].TransAttUNet(in_channels=3, num_classes=1, depth=5)
+        model.sdpa.dropout.p = kw.get("attn_dropout", 0.1)
+        return model
     raise ValueError(name)
 
 
@@ -61,7 +68,10 @@ def main():
     mods = load_reference()
     os.makedirs(OUT, exist_ok=True)
     cases = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
-             ("nested_unet_ds", {"deep_supervision": True})]
+             ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0})]
+    only = sys.argv[1:]
+    if only:
+        cases = [c for c in cases if c[0] in only]
     for tag, kw in cases:
         name = tag.replace("_ds", "")
         torch.manual_seed(0)
@@ -69,6 +79,16 @@ def main():
         fp = fingerprint(model.state_dict())
         x, mask = synthetic_batch(2, 3, 64, 64)
         model.train()
+        extra = {}
+        if name == "transatt_unet":            # the reference as is: attention dropout p = 0.1 under a fixed seed
+            sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+            model.sdpa.dropout.p = 0.1
+            torch.manual_seed(77)
+            with torch.no_grad():
+                extra["logits_train_dropout"] = model(x).clone()
+            extra["dropout_seed"] = 77
+            model.sdpa.dropout.p = kw["attn_dropout"]
+            model.load_state_dict(sd0)         # undo that forward's running-statistics update
         out = model(x)
         outs = out if isinstance(out, list) else [out]
         crit = torch.nn.BCEWithLogitsLoss()
@@ -86,6 +106,7 @@ def main():
             "bn_after": {k: v.detach().clone() for k, v in model.state_dict().items()
                          if "running_" in k or "num_batches" in k},
         }
+        gold.update(extra)
         model.eval()
         with torch.no_grad():
             oe = model(x)

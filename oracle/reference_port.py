@@ -159,8 +159,63 @@ def resunet_forward(sd: SD, x: torch.Tensor, training: bool) -> torch.Tensor:
     return r.conv(x10, "output_layer.0")
 
 
+
+def _double_convo(r: Runner, x, prefix):
+    """DoubleConvo: nn.Sequential(conv3x3, bn, relu, conv3x3, bn, relu) (common_layers.py:136-143)."""
+    x = r.cbr(x, prefix + ".double_conv.0", prefix + ".double_conv.1")
+    return r.cbr(x, prefix + ".double_conv.3", prefix + ".double_conv.4")
+
+
+def _position_embedding(sd: SD, x):
+    """PositionEmbeddingLearned.forward (transatt_unet.py:69-82): [col_embed(x index) | row_embed(y index)] on the
+    channel axis, broadcast over the batch."""
+    h, w = x.shape[-2:]
+    x_emb = F.embedding(torch.arange(w), sd["pos.col_embed.weight"])          # [w, 256]
+    y_emb = F.embedding(torch.arange(h), sd["pos.row_embed.weight"])          # [h, 256]
+    pos = torch.cat([x_emb[None].repeat(h, 1, 1), y_emb[:, None].repeat(1, w, 1)], dim=-1)
+    return pos.permute(2, 0, 1)[None].repeat(x.shape[0], 1, 1, 1)
+
+
+def _pam(r: Runner, x):
+    """PAM_Module.forward (transatt_unet.py:40-55)."""
+    b, c, h, w = x.shape
+    q = r.conv(x, "pam.query_conv").view(b, -1, h * w).permute(0, 2, 1)
+    k = r.conv(x, "pam.key_conv").view(b, -1, h * w)
+    att = F.softmax(torch.bmm(q, k), dim=-1)
+    v = r.conv(x, "pam.value_conv").view(b, -1, h * w)
+    out = torch.bmm(v, att.permute(0, 2, 1)).view(b, c, h, w)
+    return r.sd["pam.gamma"] * out + x
+
+
+def _sdpa(x, temperature: float, dropout_p: float, training: bool):
+    """ScaledDotProductAttention.forward with q = k = v = x (transatt_unet.py:91-107); nn.Dropout(0.1) on the
+    attention matrix is active in train mode (global CPU RNG)."""
+    b, d, h, w = x.shape
+    q = x.view(b, d, -1)
+    att = torch.matmul(q / temperature ** 0.5, q.permute(0, 2, 1))
+    att = F.dropout(F.softmax(att, dim=-1), p=dropout_p, training=training)
+    return torch.matmul(att, q).view(b, d, h, w)
+
+
+def transatt_unet_forward(sd: SD, x: torch.Tensor, training: bool, attn_dropout: float = 0.1) -> torch.Tensor:
+    """TransAttUNet.forward (transatt_unet.py:137-164), bilinear=True: inc, Down x4 (MaxPool2d(2) -> DoubleConvo,
+    common_layers.py:153-156), position embedding + (channel self-attention + PAM) at the bottleneck, Up x4
+    (bilinear align_corners=True, centre pad, cat [skip, upsampled], DoubleConvo; common_layers.py:171-180), OutConv."""
+    r = Runner(sd, training)
+    feats = [_double_convo(r, x, "inc")]
+    for i in range(1, 5):
+        feats.append(_double_convo(r, F.max_pool2d(feats[-1], 2), f"down{i}.maxpool_conv.1"))
+    x5 = feats[4] + _position_embedding(sd, feats[4])
+    y = _sdpa(x5, 512.0, attn_dropout, training) + _pam(r, x5)                    # transatt_unet.py:148-154
+    for i in range(1, 5):
+        skip = feats[4 - i]
+        up = _pad_to(F.interpolate(y, scale_factor=2, mode="bilinear", align_corners=True), skip)
+        y = _double_convo(r, torch.cat([skip, up], dim=1), f"up{i}.conv")       # common_layers.py:179 (skip FIRST)
+    return r.conv(y, "outc.conv")
+
+
 FORWARDS = {"unet": unet_forward, "attention_unet": attention_unet_forward, "nested_unet": nested_unet_forward,
-            "resunet": resunet_forward}
+            "resunet": resunet_forward, "transatt_unet": transatt_unet_forward}
 
 
 def bce_with_logits(logits, target):

@@ -13,13 +13,15 @@ from unet_zoo_b200.models import blocks
 
 
 def test_list_models_and_names():
-    assert unet_zoo_b200.list_models() == ["attention_unet", "nested_unet", "resunet", "unet"]
-    names = {"unet": "UNet", "attention_unet": "AttentionUNet", "nested_unet": "NestedUNet", "resunet": "ResUnet"}
+    assert unet_zoo_b200.list_models() == ["attention_unet", "nested_unet", "resunet", "transatt_unet", "unet"]
+    names = {"unet": "UNet", "attention_unet": "AttentionUNet", "nested_unet": "NestedUNet", "resunet": "ResUnet",
+             "transatt_unet": "TransAttUNet"}
     for n, cls in names.items():
         assert type(unet_zoo_b200.create_model(n.upper())).__name__ == cls      # case-insensitive (__init__.py:82)
 
 
-@pytest.mark.parametrize("name,count", [("unet", 136), ("attention_unet", 240), ("nested_unet", 212), ("resunet", 127)])
+@pytest.mark.parametrize("name,count", [("unet", 136), ("attention_unet", 240), ("nested_unet", 212), ("resunet", 127),
+                                        ("transatt_unet", 137)])
 def test_default_init_matches_reference(name, count):
     """Same keys, shapes and - under the same seed - bit-identical default initialisation as the reference modules."""
     fp = load_golden(name)["fingerprint"]
@@ -42,6 +44,10 @@ def test_factory_kwargs_contract(capsys):
     assert "Pretrained weights not implemented" in capsys.readouterr().out
     ds = unet_zoo_b200.create_model("nested_unet", deep_supervision=True)
     assert hasattr(ds, "final4") and not hasattr(ds, "final")
+    t = unet_zoo_b200.create_model("transatt_unet", depth=5, image_size=512)       # both swallowed, as in the reference
+    assert t.sdpa.dropout.p == 0.1 and t.pos.row_embed.weight.shape == (32, 256)
+    with pytest.raises(NotImplementedError, match="bilinear"):
+        unet_zoo_b200.create_model("transatt_unet", bilinear=False)
     r = unet_zoo_b200.create_model("resunet", filters=[32, 64, 128, 256], num_classes=2)
     assert r.output_layer[0].out_channels == 2 and "Warning: ResUnet" in capsys.readouterr().out
 

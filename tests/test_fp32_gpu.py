@@ -14,7 +14,7 @@ from oracle import reference_port as O
 pytestmark = pytest.mark.gpu
 LOGIT_TOL_FP32 = 1e-4
 CASES = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("nested_unet_ds", {"deep_supervision": True}),
-         ("resunet", {})]
+         ("resunet", {}), ("transatt_unet", {"attn_dropout": 0.0})]
 
 
 def _as_list(o):

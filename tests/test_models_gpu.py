@@ -17,7 +17,8 @@ from oracle import reference_port as O
 
 pytestmark = pytest.mark.gpu
 LOGIT_TOL_BF16 = 2e-2
-CASES = [("attention_unet", {}), ("nested_unet", {}), ("nested_unet_ds", {"deep_supervision": True}), ("resunet", {})]
+CASES = [("attention_unet", {}), ("nested_unet", {}), ("nested_unet_ds", {"deep_supervision": True}), ("resunet", {}),
+         ("transatt_unet", {"attn_dropout": 0.0})]     # SURVEY 8(f) rank 4; attention dropout off: CPU / CUDA RNGs differ
 
 
 def _as_list(o):
@@ -68,7 +69,7 @@ def test_train_step_against_golden_and_oracle(tag, kw):
         assert p.grad is not None and p.grad.shape == p.shape and bool(torch.isfinite(p.grad).all()), k
     # small, well-conditioned gradients (classifier head) against the reference's fp32 values
     for k, g in gold["grad_small"].items():
-        if k.startswith(("final", "conv_1x1", "output_layer")):
+        if k.startswith(("final", "conv_1x1", "output_layer", "outc")):
             got_g = named[k].grad.cpu()
             assert float((got_g - g).norm() / g.norm().clamp_min(1e-20)) < max(3e-2, max(tols)), k
 

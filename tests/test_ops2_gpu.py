@@ -33,8 +33,11 @@ def _round_weights(mod):
                 m.bias.uniform_(-0.3, 0.3)
 
 
-@pytest.mark.parametrize("N,H,W,C", [(2, 8, 8, 32), (1, 5, 12, 64), (3, 16, 16, 8)])
+@pytest.mark.parametrize("N,H,W,C", [(2, 8, 8, 32), (1, 5, 12, 64), (3, 16, 16, 8), (2, 3, 3, 16), (1, 2, 7, 8),
+                                     (2, 33, 20, 72), (1, 64, 64, 128)])
 def test_bilinear2x_fwd_bwd(N, H, W, C):
+    """Row-per-block kernels (H, W >= 3) and the element-per-thread fallback (H = 2), ragged sizes, a channel count that
+    is not a power of two."""
     x = bf16r(torch.randn(N, C, H, W, device=DEV))
     ctx = new_ctx()
     xa = make_act(ctx, x, ld=C + 8)

@@ -9,7 +9,7 @@ from conftest import load_golden, rel_err, seeded_model
 from oracle import reference_port as O
 
 CASES = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
-         ("nested_unet_ds", {"deep_supervision": True})]
+         ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0})]
 
 
 @pytest.mark.parametrize("tag,kw", CASES)
@@ -38,6 +38,20 @@ def test_oracle_matches_reference_outputs(tag, kw):
     oes = oe if isinstance(oe, list) else [oe]
     for o, g in zip(oes, gold["logits_eval"]):
         assert rel_err(o, g) < 1e-5
+
+
+def test_transatt_unet_attention_dropout_path():
+    """The reference AS IS (nn.Dropout(0.1) on the channel-attention matrix, transatt_unet.py:88,103) under the fixture's
+    RNG seed: the oracle's dropout restatement draws the same mask on CPU."""
+    gold = load_golden("transatt_unet")
+    sd = copy.deepcopy(seeded_model("transatt_unet").state_dict())
+    n, c, h, w = gold["recipe"]["batch"]
+    x, _ = O.synthetic_batch(n, c, h, w, gold["recipe"]["seed_x"], gold["recipe"]["seed_m"])
+    torch.manual_seed(gold["dropout_seed"])
+    with torch.no_grad():
+        out = O.transatt_unet_forward(sd, x, True)               # default attn_dropout = 0.1
+    assert rel_err(out, gold["logits_train_dropout"]) < 1e-5
+    assert rel_err(gold["logits_train"][0], gold["logits_train_dropout"]) > 1e-4     # the mask does matter
 
 
 def test_threshold_is_bit_exact_with_sign_test():

@@ -7,6 +7,8 @@
 // i0 = (int)src, i1 = i0 + (i0 < in-1), l1 = src - i0, l0 = 1 - l1.
 // Backward is written in gather form (no atomics, deterministic): every low-resolution pixel sums the contributions
 // of the few high-resolution pixels whose (i0, i1) touch it, recomputing their weights with the forward formula.
+#include <cstdlib>
+
 #include "pw.cuh"
 
 namespace uz {
@@ -108,6 +110,132 @@ __global__ void bilinear2x_bwd_kernel(const __nv_bfloat16* __restrict__ dout, in
   }
 }
 
+// acc += w * f on two fp32 lanes with one sm_100 packed FMA (fma.rn.f32x2); used by the forward (measured 0.437 ->
+// 0.411 ms at 32 x 256^2 x 64 together with the four-product form), not by the backward (0.532 -> 0.658 ms there)
+__device__ __forceinline__ void bl_fma2(float& a0, float& a1, float f0, float f1, float w) {
+  asm("{\n\t.reg .b64 ra, rw, rc;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rw, {%4, %4};\n\tmov.b64 rc, {%0, %1};\n\t"
+      "fma.rn.f32x2 rc, ra, rw, rc;\n\tmov.b64 {%0, %1}, rc;\n\t}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(f0), "f"(f1), "f"(w));
+}
+
+// ---- row-per-block forms (the default): the element-per-thread kernels above spend ~3 64-bit divisions per 16 bytes
+// moved and run instruction-bound at ~2 TB/s (ncu / torch.profiler, transatt_unet batch 32: 1.2 ms forward, 2.35 ms
+// backward for 2.5 GB).  Here a block owns one output row: the row decomposition (n, y) and the vertical taps are
+// computed once per row, the sweep over (x, channel group) uses 32-bit arithmetic, and the backward visits the six
+// candidate high-resolution columns [2x-2, 2x+3] unconditionally (weights are zero where a candidate does not
+// contribute) while skipping non-contributing candidate rows, which is a block-uniform branch.
+__global__ void __launch_bounds__(256)
+bilinear2x_fwd_rows_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int cv,
+                           __nv_bfloat16* __restrict__ out, int out_ld, float sy, float sx) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const int rows = N * Ho;
+  const int per_row = Wo * cv;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / Ho, oy = row - n * Ho;
+    int y0, y1;
+    float ly0, ly1;
+    bl_src(oy, sy, H, &y0, &y1, &ly0, &ly1);
+    const __nv_bfloat16* r0 = x + (static_cast<size_t>(n) * H + y0) * W * x_ld;
+    const __nv_bfloat16* r1 = x + (static_cast<size_t>(n) * H + y1) * W * x_ld;
+    __nv_bfloat16* orow = out + static_cast<size_t>(row) * Wo * out_ld;
+#pragma unroll 2
+    for (int e = threadIdx.x; e < per_row; e += 256) {
+      const int ox = e / cv, g = e - ox * cv;
+      int x0, x1;
+      float lx0, lx1;
+      bl_src(ox, sx, W, &x0, &x1, &lx0, &lx1);
+      const int o0 = x0 * x_ld + g * 8, o1 = x1 * x_ld + g * 8;
+      float a[8], b[8], c[8], d[8], o[8];
+      pw_unpack8(pw_ldg16(r0 + o0), a);
+      pw_unpack8(pw_ldg16(r0 + o1), b);
+      pw_unpack8(pw_ldg16(r1 + o0), c);
+      pw_unpack8(pw_ldg16(r1 + o1), d);
+      const float w00 = ly0 * lx0, w01 = ly0 * lx1, w10 = ly1 * lx0, w11 = ly1 * lx1;
+#pragma unroll
+      for (int j = 0; j < 8; j += 2) {
+        o[j] = w00 * a[j];
+        o[j + 1] = w00 * a[j + 1];
+        bl_fma2(o[j], o[j + 1], b[j], b[j + 1], w01);
+        bl_fma2(o[j], o[j + 1], c[j], c[j + 1], w10);
+        bl_fma2(o[j], o[j + 1], d[j], d[j + 1], w11);
+      }
+      *reinterpret_cast<uint4*>(orow + static_cast<size_t>(ox) * out_ld + g * 8) = pw_pack8(o);
+    }
+  }
+}
+
+constexpr int kBlWin = 6;  // candidate high-res rows / columns of low-res index i when the axis has >= 3 samples:
+                           // floor(s*o) in {i-1, i} with s = (in-1)/(2in-1)  =>  o in [2i-2, 2i+3]
+
+__global__ void __launch_bounds__(256)
+bilinear2x_bwd_rows_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int cv,
+                           __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate, float sy, float sx) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const int rows = N * H;
+  const int per_row = W * cv;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / H, yl = row - n * H;
+    float wy[kBlWin];
+#pragma unroll
+    for (int k = 0; k < kBlWin; ++k) {
+      const int oy = 2 * yl - 2 + k;
+      wy[k] = (oy >= 0 && oy < Ho) ? bl_weight(oy, yl, sy, H) : 0.f;
+    }
+    const __nv_bfloat16* img = dout + static_cast<size_t>(n) * Ho * Wo * dout_ld;
+    __nv_bfloat16* drow = dx + static_cast<size_t>(row) * W * dx_ld;
+    for (int e = threadIdx.x; e < per_row; e += 256) {
+      const int xl = e / cv, g = e - xl * cv;
+      float wx[kBlWin];
+      int off[kBlWin];
+#pragma unroll
+      for (int k = 0; k < kBlWin; ++k) {
+        const int ox = 2 * xl - 2 + k;
+        const bool in = ox >= 0 && ox < Wo;
+        wx[k] = in ? bl_weight(ox, xl, sx, W) : 0.f;
+        off[k] = (in ? ox : 2 * xl) * dout_ld + g * 8;       // out-of-image candidates re-read a valid pixel (weight 0)
+      }
+      float acc[8];
+      __nv_bfloat16* dst = drow + static_cast<size_t>(xl) * dx_ld + g * 8;
+      if (accumulate) {
+        pw_unpack8(*reinterpret_cast<const uint4*>(dst), acc);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+      }
+#pragma unroll
+      for (int ky = 0; ky < kBlWin; ++ky) {
+        if (wy[ky] == 0.f) continue;                            // same for every thread of the block
+        const __nv_bfloat16* hrow = img + static_cast<size_t>(2 * yl - 2 + ky) * Wo * dout_ld;
+        uint4 v[kBlWin];
+#pragma unroll
+        for (int kx = 0; kx < kBlWin; ++kx) v[kx] = pw_ldg16(hrow + off[kx]);
+#pragma unroll
+        for (int kx = 0; kx < kBlWin; ++kx) {
+          float f[8];
+          pw_unpack8(v[kx], f);
+          const float w = wy[ky] * wx[kx];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(w, f[j], acc[j]);   // (fma.rn.f32x2 here measured 24 % SLOWER)
+        }
+      }
+      *reinterpret_cast<uint4*>(dst) = pw_pack8(acc);
+    }
+  }
+}
+
+static bool rs_rows_ok(int N, int H, int W, int C, int ld_lo, int ld_hi) {
+  // 32-bit in-row offsets and row counts; the six-candidate window needs at least three samples per axis
+  return H >= 3 && W >= 3 && static_cast<long long>(N) * 2 * H < (1ll << 30) &&
+         static_cast<long long>(2 * W) * (ld_hi > ld_lo ? ld_hi : ld_lo) < (1ll << 30) && C >= 8 &&
+         std::getenv("UZ_BILINEAR_GEN1") == nullptr;
+}
+static int rs_row_grid(long long rows) {
+  const long long cap = static_cast<long long>(uz_device_sm_count()) * 8;   // 8 x 256 threads = one SM's worth of warps
+  return static_cast<int>(rows < cap ? (rows < 1 ? 1 : rows) : cap);
+}
+
 static int rs_check(const char* who, const void* p, int C, int ld) {
   if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) || C < 8 || (C & 7) || (ld & 7) || ld < C)
     return set_error(UZ_ERR_INVALID, "%s: needs a 16-B aligned pointer, channels (=%d) and ld (=%d) multiples of 8", who, C, ld);
@@ -170,6 +298,14 @@ extern "C" int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, i
   if (rc) return rc;
   if ((rc = rs_check("bilinear2x_fwd(out)", out, C, out_ld))) return rc;
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bilinear2x_fwd: bad size N=%d H=%d W=%d", N, H, W);
+  if (rs_rows_ok(N, H, W, C, x_ld, out_ld)) {
+    bilinear2x_fwd_rows_kernel<<<rs_row_grid(static_cast<long long>(N) * 2 * H), 256, 0,
+                                 static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld,
+        rs_scale(H), rs_scale(W));
+    PW_CHECK_LAUNCH("bilinear2x_fwd launch");
+    return UZ_OK;
+  }
   const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
   bilinear2x_fwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld, rs_scale(H),
@@ -185,6 +321,14 @@ extern "C" int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, in
   if (rc) return rc;
   if ((rc = rs_check("bilinear2x_bwd(dx)", dx, C, dx_ld))) return rc;
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bilinear2x_bwd: bad size N=%d H=%d W=%d", N, H, W);
+  if (rs_rows_ok(N, H, W, C, dx_ld, dout_ld)) {
+    bilinear2x_bwd_rows_kernel<<<rs_row_grid(static_cast<long long>(N) * H), 256, 0,
+                                 static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(dx), dx_ld,
+        accumulate, rs_scale(H), rs_scale(W));
+    PW_CHECK_LAUNCH("bilinear2x_bwd launch");
+    return UZ_OK;
+  }
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
   bilinear2x_bwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate,

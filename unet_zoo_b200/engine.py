@@ -801,6 +801,67 @@ def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:
     return out
 
 
+@contextlib.contextmanager
+def _island_math(tf32: bool):
+    """Pin the fp32 matmul / convolution precision of torch's own kernels for the duration of an island."""
+    saved = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = tf32
+    torch.backends.cudnn.allow_tf32 = tf32
+    try:
+        yield
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = saved
+
+
+def torch_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],
+                 out: Optional[Act] = None) -> Act:
+    """A sub-graph of stock torch ops between two fused operators: ``fn`` maps the NCHW fp32 image of `x` to an NCHW
+    tensor of the same spatial size (the attention bottleneck of transatt_unet, transatt_unet.py:143-154 - small
+    batched matmuls / softmaxes at 1/16 resolution that are not on the path BASELINE.json names).  The island runs on
+    the executor's stream; in training its local autograd graph is kept and differentiated from the tape, the gradients
+    of `params` (the island's own nn.Parameters) land in the flat gradient buffer like every other parameter's."""
+    xin = x.buf.data[..., x.c0:x.c0 + x.C].permute(0, 3, 1, 2).float().contiguous()
+    # fp32 parity mode: strict fp32 (1e-4 bar).  bf16 mode: the island's operands are bf16-rounded activations anyway, so
+    # its matmuls / 1x1 convolutions may use the TF32 tensor-core path of cuBLAS / cuDNN (fp32 accumulate)
+    tf32 = (not ctx.fp32) and os.environ.get("UZ_ISLAND_TF32", "1") != "0"
+    with _island_math(tf32):
+        if ctx.record:
+            xin.requires_grad_(True)
+            with torch.enable_grad():
+                y = fn(xin)
+        else:
+            y = fn(xin)
+    if y.dim() != 4 or y.shape[0] != x.N or y.shape[2:] != (x.H, x.W):
+        raise RuntimeError(f"unet_zoo_b200: torch island returned {tuple(y.shape)} for an input of "
+                           f"{(x.N, x.C, x.H, x.W)}")
+    if out is None:
+        out = ctx.new_act(x.N, x.H, x.W, y.shape[1])
+    out.buf.data[..., out.c0:out.c0 + out.C].copy_(y.detach().permute(0, 2, 3, 1))
+    if ctx.record:
+        params = [p for p in params if p.requires_grad]
+
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: torch island output has no gradient")
+            dy = out.buf.grad_buf()[..., out.c0:out.c0 + out.C].permute(0, 3, 1, 2).to(y.dtype)
+            with _island_math(tf32):
+                grads = torch.autograd.grad([y], [xin] + params, [dy], allow_unused=True)
+            gx = x.buf.grad_buf()
+            dx = grads[0].permute(0, 2, 3, 1)
+            for (r0, rc, acc) in x.grad_writes():
+                dst = gx[..., x.c0 + r0:x.c0 + r0 + rc]
+                if acc:
+                    dst.add_(dx[..., r0:r0 + rc])
+                else:
+                    dst.copy_(dx[..., r0:r0 + rc])
+            for p, g in zip(params, grads[1:]):
+                if g is not None:
+                    c.pgrad(p).copy_(g)
+            c.pready(*params)
+        ctx.tape.append(backward)
+    return out
+
+
 def attention_gate(ctx: Ctx, g: Act, x: Act, att, out: Act) -> Act:
     """AttentionBlock.forward (attention_unet.py:34-40): out = x * sigmoid(BN(w_psi . ReLU(BN(W_g g) + BN(W_x x)))),
     written into a channel slice of the decoder's concat buffer.  The 1x1 convolutions are tcgen05 GEMMs with the

@@ -1,9 +1,9 @@
 """Model factory - the drop-in boundary of the hot path.
 
 Mirrors the reference factory's contract (unet_zoo/models/__init__.py:59-61,78-238) for the four encoder-decoder
-models that BASELINE.json names: same signature, case-insensitive name lookup, the same always-popped keyword
+models that BASELINE.json names (plus `transatt_unet`, the first "next" model of SURVEY.md 8f rank 4): same signature, case-insensitive name lookup, the same always-popped keyword
 arguments (``in_channels``, ``num_classes``, ``image_size``, ``depth``), the same per-model constructor arguments,
-``ValueError`` for an unknown name and a warning (only) for ``pretrained=True``.  The reference's other twenty
+``ValueError`` for an unknown name and a warning (only) for ``pretrained=True``.  The reference's other nineteen
 registry entries (transformer / axial-attention variants) are outside the hot path and raise NotImplementedError.
 """
 from typing import Any, Dict, List
@@ -30,8 +30,14 @@ try:
 except ImportError:  # pragma: no cover
     pass
 
+try:  # first neighbouring model on the same blocks
+    from .transatt_unet import TransAttUNet
+    _model_entries["transatt_unet"] = TransAttUNet
+except ImportError:  # pragma: no cover
+    pass
+
 # registry names of the reference that are deliberately not part of this build
-_OUT_OF_SCOPE = ("transatt_unet", "raunet", "da_transformer", "unet_transformer", "uctransnet", "multiresunet",
+_OUT_OF_SCOPE = ("raunet", "da_transformer", "unet_transformer", "uctransnet", "multiresunet",
                  "missformer", "vnet", "u2net", "u2netp", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
                  "mmunet", "axialunet", "gated", "medt", "logo")
 
@@ -67,6 +73,8 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
     elif name == "nested_unet":
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth, deep_supervision=False)
+    elif name == "transatt_unet":    # models/__init__.py:106-109: `depth` is passed on and swallowed by **kwargs
+        args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
     else:  # resunet
         args = dict(in_channels=in_channels, num_classes=num_classes, filters=[64, 128, 256, 512])
     args.update(kwargs)              # leftovers reach the constructor (TypeError if it does not know them)
