@@ -194,9 +194,13 @@ def main():
     if world > 1:
         model = P.DataParallel(model, bucket_mb=float(os.environ.get("UZ_BUCKET_MB", "25")))   # bucketed NCCL all-reduce overlapped with backward
     params = [p for p in model.parameters() if p.requires_grad]
-    # N > 1 issues the step eagerly: capturing the bucketed NCCL all-reduces of the communication stream into the
-    # step graph was tried (capture_error_mode="thread_local") and hung at N = 2; host enqueue is 24-36 ms of a 43-47 ms step
-    use_graph = world == 1 and not args.no_graph
+    # N > 1: capturing the bucketed NCCL all-reduces of the communication stream into the step graph was tried
+    # (capture_error_mode="thread_local") and hung at N = 2.  Default there: two graphs (fwd+bwd | clip+AdamW) around ONE
+    # eager all-reduce of the flat gradient buffer (DataParallel.defer_sync); UZ_DP_GRAPH=0 or --no-graph issue the step
+    # eagerly with the bucketed all-reduces overlapped with backward (host enqueue 24-36 ms of a 43-47 ms step)
+    use_graph = not args.no_graph and (world == 1 or os.environ.get("UZ_DP_GRAPH", "1") != "0")
+    if world > 1 and use_graph:
+        model.defer_sync = True
     if args.tail == "fused":
         # BCE-with-logits + Dice + loss gradient in one pass, clip_grad_norm_(1.0) + AdamW as one flat update
         # (training_loop.py:115-121 incl. the per-batch Dice of :81 that the torch tail below leaves out)
@@ -222,6 +226,8 @@ def main():
         out = model(x)
         loss = crit(out, m)
         loss.backward()
+        if getattr(model, "defer_sync", False):
+            model.sync_gradients()
         if clip is not None:
             torch.nn.utils.clip_grad_norm_(params, clip)
         opt.step()
@@ -251,10 +257,18 @@ def main():
     if use_graph:
         from unet_zoo_b200.train_step import GraphedTrainStep
         try:
-            step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=clip, params=params)
-            graph_note = "one CUDA graph per step (unet_zoo_b200.train_step.GraphedTrainStep)"
+            if world > 1:
+                step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=clip, params=params,
+                                        grad_sync=model.sync_gradients)
+                graph_note = ("two CUDA graphs per step (fwd+bwd | clip+AdamW) around one eager NCCL all-reduce of the "
+                              "flat gradient buffer (unet_zoo_b200.train_step.GraphedTrainStep, grad_sync)")
+            else:
+                step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=clip, params=params)
+                graph_note = "one CUDA graph per step (unet_zoo_b200.train_step.GraphedTrainStep)"
         except Exception as e:   # report, never hide: the JSON line says which mode was measured
             graph_note = f"eager (graph capture failed: {type(e).__name__}: {e})"[:300]
+            if world > 1:
+                model.defer_sync = False
             torch.cuda.synchronize()
     for _ in range(max(args.warmup, 3)):
         step(x_d, m_d)

@@ -39,7 +39,23 @@ def _worker(rank, world, port, out):
     pg.finish()
     ok = all(torch.allclose(pg.view(p), torch.full_like(p, 1.5 * (i + 1))) for i, p in enumerate(params))
     sd_keys = list(dp.state_dict())
-    out[rank] = (same_weights, ok, nb, all(pg.launched), sd_keys == list(net.state_dict()))
+    # defer_sync mode (CUDA-graph step at N > 1): backward fills a plain flat buffer, one all-reduce afterwards
+    refused = False
+    net._last_param_grads = pg
+    try:
+        dp.sync_gradients()                              # the bucketed backward above already averaged
+    except RuntimeError:
+        refused = True
+    dp.defer_sync = True
+    pg2 = net._uz_make_param_grads(params, torch.device("cpu"))
+    for i, p in enumerate(params):
+        pg2.view(p).fill_(float(rank + 1) * (i + 2))
+        pg2.ready(p)                                     # no hook: nothing is launched
+    net._last_param_grads = pg2                          # what _HotPathFn.backward records
+    dp.sync_gradients()
+    ok2 = (type(pg2) is P.ParamGrads and refused and
+           all(torch.allclose(pg2.view(p), torch.full_like(p, 1.5 * (i + 2))) for i, p in enumerate(params)))
+    out[rank] = (same_weights, ok and ok2, nb, all(pg.launched), sd_keys == list(net.state_dict()))
     dist.destroy_process_group()
 
 

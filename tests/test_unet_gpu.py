@@ -201,3 +201,59 @@ def test_data_parallel_and_side_stream_gradients_match_the_plain_step(monkeypatc
     for k in plain:
         assert torch.equal(plain[k], side[k]), k
         assert torch.equal(plain[k], wrapped[k]), k
+
+
+def test_split_graph_data_parallel_step_matches_eager_steps():
+    """N > 1 launch mode: graph A (forward + backward into the flat gradient buffer), ONE eager NCCL all-reduce of that
+    buffer (DataParallel.defer_sync / sync_gradients), graph B (clip + FlatAdamW).  With a world of one the all-reduce
+    is an identity, so three replayed steps must reproduce three eager steps of the un-wrapped model."""
+    import torch.distributed as dist
+    from unet_zoo_b200 import parallel as P
+    from unet_zoo_b200.loss import BCEDiceWithLogits
+    from unet_zoo_b200.optim import FlatAdamW
+    from unet_zoo_b200.train_step import GraphedTrainStep
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    x, m = x.cuda(), m.cuda()
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29534", rank=0, world_size=1)
+    try:
+        results = []
+        for graphed in (False, True):
+            model = seeded_model("unet").cuda().train()
+            net = model
+            if graphed:
+                net = P.DataParallel(model)
+                net.defer_sync = True
+            params = list(model.parameters())
+            opt = FlatAdamW(params, lr=1e-3, weight_decay=1e-5, max_norm=1.0)
+            crit = BCEDiceWithLogits()
+            losses = []
+            if graphed:
+                sd0 = copy.deepcopy(model.state_dict())
+                step = GraphedTrainStep(net, crit, opt, x, m, max_norm=None, params=params, warmup=1,
+                                        grad_sync=net.sync_gradients)
+                assert step.graph_tail is not None and type(model._last_param_grads) is P.ParamGrads
+                model.load_state_dict(sd0)                   # undo the warm-up updates (copies into the flat buffer)
+                opt.exp_avg.zero_()
+                opt.exp_avg_sq.zero_()
+                opt.state.zero_()
+                for _ in range(3):
+                    losses.append(float(step(x, m)))
+            else:
+                for _ in range(3):
+                    opt.zero_grad(set_to_none=True)
+                    loss = crit(net(x), m)
+                    loss.backward()
+                    opt.step()
+                    losses.append(float(loss))
+            torch.cuda.synchronize()
+            results.append((losses, {k: v.detach().clone() for k, v in model.state_dict().items()}))
+    finally:
+        if created:
+            dist.destroy_process_group()
+    (l0, s0), (l1, s1) = results
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
+    for k in s0:
+        if s0[k].dtype.is_floating_point:
+            assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k

@@ -38,6 +38,7 @@ class _HotPathFn(torch.autograd.Function):
         ctx.launches = 0
         make = getattr(model, "_uz_make_param_grads", None)
         ctx.pgrads = make(params, ctx.device) if make is not None else E.ParamGrads(params, ctx.device)
+        model._last_param_grads = ctx.pgrads     # the flat gradient buffer of this step (parallel.sync_gradients)
         ctx.out_grads = list(douts)
         for step in reversed(ctx.tape):
             step(ctx)

@@ -7,6 +7,12 @@ fp32 buffer; it is cut into ~25 MB buckets in reverse registration order (the or
 soon as the tape reports the last gradient of a bucket an all-reduce is launched on a side stream while the remaining
 backward kernels keep running.  ``clip_grad_norm_`` / the optimizer then see averaged gradients
 (training_loop.py:119-121 order).
+
+Second mode (``DataParallel.defer_sync = True``): backward only fills the flat buffer and the caller averages it
+afterwards with ONE all-reduce (``sync_gradients()``).  That is what lets the step run from CUDA graphs at N > 1
+(``train_step.GraphedTrainStep(..., grad_sync=dp.sync_gradients)``): forward + backward replay as one graph, the
+all-reduce is issued eagerly behind it, clip + AdamW replay as a second graph - no NCCL call is ever captured.  The
+all-reduce is no longer hidden (124 MB over NVSwitch for unet), but the ~300 eager launches per step are.
 """
 from typing import List, Optional, Sequence
 
@@ -103,13 +109,31 @@ class DataParallel(nn.Module):
         self.bucket_bytes = int(bucket_mb * (1 << 20))
         p0 = next(module.parameters())
         self.comm_stream = torch.cuda.Stream(device=p0.device) if p0.is_cuda else None
+        self.defer_sync = False      # True: no all-reduce during backward, the caller runs sync_gradients() after it
         with torch.no_grad():
             for t in list(module.parameters()) + list(module.buffers()):
                 dist.broadcast(t, src=0, group=self.group)
         module._uz_make_param_grads = self._make_param_grads
 
     def _make_param_grads(self, params, device):
+        if self.defer_sync:
+            return ParamGrads(params, device)
         return BucketedGrads(params, device, self.group, self.bucket_bytes, self.comm_stream)
+
+    def sync_gradients(self):
+        """Average the flat gradient buffer of the last backward across ranks with one all-reduce on the current
+        stream (``defer_sync`` mode).  The buffer is the one ``p.grad`` of every parameter is a slice of."""
+        pg = getattr(self.module, "_last_param_grads", None)
+        if pg is None:
+            raise RuntimeError("DataParallel.sync_gradients: no backward has run on the wrapped model yet")
+        if isinstance(pg, BucketedGrads):
+            raise RuntimeError("DataParallel.sync_gradients: the last backward already all-reduced its buckets "
+                               "(set defer_sync = True before the step)")
+        if pg.flat.is_cuda:
+            dist.all_reduce(pg.flat, op=dist.ReduceOp.AVG, group=self.group)
+        else:  # CPU / gloo (tests): no AVG reduction there
+            dist.all_reduce(pg.flat, op=dist.ReduceOp.SUM, group=self.group)
+            pg.flat.div_(dist.get_world_size(self.group))
 
     def forward(self, *args, **kwargs):
         return self.module(*args, **kwargs)

@@ -7,8 +7,12 @@ packing, reductions) are visible.  :class:`GraphedTrainStep` records the step on
 is stream-ordered and allocation-free, the executor's buffers come from the graph's private memory pool) and replays
 it with a single ``cudaGraphLaunch`` per batch: no tracing compiler, the same kernels in the same order.
 
-Constraints: single GPU (with the data-parallel wrapper the step is issued eagerly: capturing its NCCL all-reduces
-was tried and hung); fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
+Data-parallel (N > 1): capturing the bucketed NCCL all-reduces inside the step graph was tried and hung, so no NCCL
+call is captured.  With ``grad_sync=`` (``parallel.DataParallel.sync_gradients`` on a wrapper in ``defer_sync`` mode)
+the step becomes graph A (zero_grad -> forward -> criterion -> backward into the flat gradient buffer), one eager
+all-reduce of that buffer, graph B (clip + optimizer step): three host calls per step instead of ~300.
+
+Constraints: fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
 capturable=True)``); the learning-rate schedule, if any, must live in a device tensor.
 """
 from typing import Callable, Iterable, Optional
@@ -19,7 +23,8 @@ import torch
 class GraphedTrainStep:
     def __init__(self, model: torch.nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
                  example_x: torch.Tensor, example_target: torch.Tensor, max_norm: Optional[float] = 1.0,
-                 params: Optional[Iterable[torch.nn.Parameter]] = None, warmup: int = 3):
+                 params: Optional[Iterable[torch.nn.Parameter]] = None, warmup: int = 3,
+                 grad_sync: Optional[Callable[[], None]] = None):
         if not example_x.is_cuda:
             raise RuntimeError("GraphedTrainStep needs CUDA tensors (there is no CPU path)")
         self.model, self.criterion, self.optimizer, self.max_norm = model, criterion, optimizer, max_norm
@@ -28,6 +33,7 @@ class GraphedTrainStep:
         self.target = example_target.clone()
         self.loss: Optional[torch.Tensor] = None
         self.out = None
+        self.grad_sync = grad_sync
         dev = example_x.device
         # the warm-up runs on a side stream by design (torch's capture recipe); autograd's note about it is noise here
         warn_off = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
@@ -41,10 +47,25 @@ class GraphedTrainStep:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self._body()
+        self.graph_tail = None
+        if grad_sync is None:
+            with torch.cuda.graph(self.graph):
+                self._body()
+        else:
+            # a process group is alive: its watchdog thread may touch the CUDA API while this thread captures
+            with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+                self._fwd_bwd()
+            self.graph_tail = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_tail, pool=self.graph.pool(), capture_error_mode="thread_local"):
+                self._tail()
 
     def _body(self):
+        self._fwd_bwd()
+        if self.grad_sync is not None:
+            self.grad_sync()
+        self._tail()
+
+    def _fwd_bwd(self):
         self.optimizer.zero_grad(set_to_none=True)
         self.out = self.model(self.x)
         outs = self.out if isinstance(self.out, (list, tuple)) else [self.out]
@@ -52,10 +73,12 @@ class GraphedTrainStep:
         for o in outs[1:]:                                 # deep supervision: the reference sums the per-head losses
             loss = loss + self.criterion(o, self.target)
         loss.backward()
+        self.loss = loss.detach()
+
+    def _tail(self):
         if self.max_norm is not None:
             torch.nn.utils.clip_grad_norm_(self.params, self.max_norm)
         self.optimizer.step()
-        self.loss = loss.detach()
 
     def __call__(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """Run one training step on (x, target); returns the (device) loss tensor of this step."""
@@ -64,6 +87,9 @@ class GraphedTrainStep:
         if target.data_ptr() != self.target.data_ptr():
             self.target.copy_(target, non_blocking=True)
         self.graph.replay()
+        if self.graph_tail is not None:
+            self.grad_sync()               # eager: one all-reduce of the flat gradient buffer on the current stream
+            self.graph_tail.replay()
         return self.loss
 
 
