@@ -105,45 +105,84 @@ __global__ void gate_apply_kernel(const __nv_bfloat16* __restrict__ x, int x_ld,
 // ---------------------------------------------------------------------------------------------- backward stage 1
 // a = sigmoid(BN(psi_raw)); dx (+)= a * dout; dpsi = sum_c dout*x; dsb = dpsi * a * (1-a)  (gradient at the BN_psi output)
 // partial[block][2] = { sum dsb, sum dsb * xhat }   with xhat = (psi_raw - mean) * invstd
-__global__ void gate_bwd_psi_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, const __nv_bfloat16* __restrict__ dout,
-                                    int dout_ld, const float* __restrict__ psi_raw, const float* __restrict__ psi_bn,
-                                    long long npix, int cv, __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate,
-                                    float* __restrict__ dsb, float* __restrict__ partial) {
+// LPP lanes share a pixel (LPP = channel groups of 8 rounded up to a power of two, at most 32), so a warp works on
+// 32 / LPP pixels at once - with one warp per pixel (first version) only 8 of 32 lanes were busy at C = 64, the
+// largest gate of attention_unet (1.72 ms per step for four gates, ~3x the HBM time of their bytes).  Two pixels per
+// lane group are in flight.
+template <int LPP>
+__global__ void __launch_bounds__(kGateBlock)
+gate_bwd_psi_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, const __nv_bfloat16* __restrict__ dout,
+                    int dout_ld, const float* __restrict__ psi_raw, const float* __restrict__ psi_bn,
+                    long long npix, int cv, __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate,
+                    float* __restrict__ dsb, float* __restrict__ partial) {
   __shared__ float red[2][kGateBlock / 32];
+  constexpr int PPW = 32 / LPP;   // pixels per warp and step
+  constexpr int U = 2;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+  const int sub = lane / LPP, gl = lane % LPP;
   const float mean = __ldg(psi_bn), invstd = __ldg(psi_bn + 1), sc = __ldg(psi_bn + 2), sh = __ldg(psi_bn + 3);
   float s = 0.f, q = 0.f;
   constexpr int wpb = kGateBlock / 32;
-  for (long long p = static_cast<long long>(blockIdx.x) * wpb + warp; p < npix; p += static_cast<long long>(gridDim.x) * wpb) {
-    const float pr = __ldg(psi_raw + p);
-    const float a = pw_sigmoid(fmaf(pr, sc, sh));
-    float dot = 0.f;
-    for (int g = lane; g < cv; g += 32) {
-      float xv[8], dv[8], o[8];
-      pw_unpack8(pw_ldg16(x + p * x_ld + g * 8), xv);
-      pw_unpack8(pw_ldg16(dout + p * dout_ld + g * 8), dv);
-      if (accumulate) {
-        pw_unpack8(*reinterpret_cast<const uint4*>(dx + p * dx_ld + g * 8), o);
-      } else {
+  const long long stride = static_cast<long long>(gridDim.x) * wpb * PPW;
+  // the loop bound is warp-uniform: every lane takes part in the shuffles below
+  for (long long base = (static_cast<long long>(blockIdx.x) * wpb + warp) * PPW; base < npix; base += U * stride) {
+    float dot[U], a[U], pr[U];
+    bool valid[U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        dot = fmaf(dv[j], xv[j], dot);
-        o[j] = fmaf(a, dv[j], o[j]);
-      }
-      *reinterpret_cast<uint4*>(dx + p * dx_ld + g * 8) = pw_pack8(o);
+    for (int u = 0; u < U; ++u) {
+      const long long p = base + u * stride + sub;
+      valid[u] = p < npix;
+      dot[u] = 0.f;
+      pr[u] = valid[u] ? __ldg(psi_raw + p) : 0.f;
+      a[u] = pw_sigmoid(fmaf(pr[u], sc, sh));
     }
-    dot = pw_warp_sum(dot);
-    if (lane == 0) {
-      const float d = dot * a * (1.f - a);
-      dsb[p] = d;
-      s += d;
-      q = fmaf(d, (pr - mean) * invstd, q);
+    for (int g = gl; g < cv; g += LPP) {
+      uint4 xr[U], dr[U], orr[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!valid[u]) continue;
+        const long long p = base + u * stride + sub;
+        xr[u] = pw_ldg16(x + p * x_ld + g * 8);
+        dr[u] = pw_ldg16(dout + p * dout_ld + g * 8);
+        if (accumulate) orr[u] = *reinterpret_cast<const uint4*>(dx + p * dx_ld + g * 8);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!valid[u]) continue;
+        const long long p = base + u * stride + sub;
+        float xv[8], dv[8], o[8];
+        pw_unpack8(xr[u], xv);
+        pw_unpack8(dr[u], dv);
+        if (accumulate) {
+          pw_unpack8(orr[u], o);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dot[u] = fmaf(dv[j], xv[j], dot[u]);
+          o[j] = fmaf(a[u], dv[j], o[j]);
+        }
+        *reinterpret_cast<uint4*>(dx + p * dx_ld + g * 8) = pw_pack8(o);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float d = dot[u];
+#pragma unroll
+      for (int o = LPP / 2; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+      if (gl == 0 && valid[u]) {
+        d = d * a[u] * (1.f - a[u]);
+        dsb[base + u * stride + sub] = d;
+        s += d;
+        q = fmaf(d, (pr[u] - mean) * invstd, q);
+      }
     }
   }
+  s = pw_warp_sum(s);   // lanes with gl != 0 hold zeros
+  q = pw_warp_sum(q);
   if (lane == 0) {
     red[0][warp] = s;
     red[1][warp] = q;
@@ -332,12 +371,24 @@ extern "C" int uz_gate_bwd(const void* x, int x_ld, const void* dout, int dout_l
 
   // stage 1: gate product backward + BN_psi reduction
   {
-    constexpr int wpb = kGateBlock / 32;
-    const long long need = (npix + wpb - 1) / wpb;
+    const int lpp = gate_lpp(C) > 32 ? 32 : gate_lpp(C);
+    const long long ppb = static_cast<long long>(kGateBlock / 32) * (32 / lpp);   // pixels per block and step
+    const long long need = (npix + ppb - 1) / ppb;
     const int grid = static_cast<int>(need < rows ? need : rows);
-    gate_bwd_psi_kernel<<<grid, kGateBlock, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_ld,
-                                                     static_cast<const __nv_bfloat16*>(dout), dout_ld, psi_raw, psi_bn, npix,
-                                                     C / 8, static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate_dx, dsb, partial);
+#define UZ_GATE_PSI(L)                                                                                           \
+  gate_bwd_psi_kernel<L><<<grid, kGateBlock, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_ld,                \
+                                                      static_cast<const __nv_bfloat16*>(dout), dout_ld, psi_raw, \
+                                                      psi_bn, npix, C / 8, static_cast<__nv_bfloat16*>(dx), dx_ld, \
+                                                      accumulate_dx, dsb, partial)
+    switch (lpp) {
+      case 1: UZ_GATE_PSI(1); break;
+      case 2: UZ_GATE_PSI(2); break;
+      case 4: UZ_GATE_PSI(4); break;
+      case 8: UZ_GATE_PSI(8); break;
+      case 16: UZ_GATE_PSI(16); break;
+      default: UZ_GATE_PSI(32); break;
+    }
+#undef UZ_GATE_PSI
     PW_CHECK_LAUNCH("gate_bwd_psi launch");
     cudaError_t e = launch_bn_bwd_finalize(partial, grid, 1, static_cast<double>(npix), psi_bn, dgamma_psi, dbeta_psi, 0,
                                            coef, st);
