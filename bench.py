@@ -143,8 +143,9 @@ def metric_name(model):
 
 
 def workload_name(model, B, S):
-    return (f"{model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step "
-            "(BASELINE.json configs[1])")
+    cfg = {"unet": "BASELINE.json configs[1]", "attention_unet": "BASELINE.json configs[2]",
+           "nested_unet": "BASELINE.json configs[3]"}.get(model, "not a BASELINE.json config")
+    return f"{model} in=3 classes=1, batch {B}/GPU, {S}x{S}, fwd+bwd+clip+AdamW training step ({cfg})"
 
 
 def run_reference(args):

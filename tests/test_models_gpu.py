@@ -132,3 +132,49 @@ def test_resunet_inference_shapes_of_the_sweep():
         with torch.no_grad():
             y = model(torch.randn(n, 3, s, s, device="cuda"))
         assert tuple(y.shape) == (n, 1, s, s) and bool(torch.isfinite(y).all())
+
+
+def test_transatt_unet_graphed_step_with_fused_tail_matches_eager_steps():
+    """The stock-torch bottleneck island inside one CUDA graph: three replayed steps of transatt_unet (fused criterion,
+    FlatAdamW - the island's `pos.*` / `pam.*` gradients must be slices of the same flat buffer) reproduce three eager
+    steps.  Attention dropout off: its Philox offsets differ between capture and eager issue order."""
+    from unet_zoo_b200.loss import BCEDiceWithLogits
+    from unet_zoo_b200.optim import FlatAdamW
+    from unet_zoo_b200.train_step import GraphedTrainStep
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    x, m = x.cuda(), m.cuda()
+    results = []
+    for graphed in (False, True):
+        model = seeded_model("transatt_unet", attn_dropout=0.0).cuda().train()
+        with torch.no_grad():
+            model.pam.gamma.fill_(0.5)                       # zero at init: let the PAM branch carry gradient
+        params = list(model.parameters())
+        opt = FlatAdamW(params, lr=1e-3, weight_decay=1e-5, max_norm=1.0)
+        crit = BCEDiceWithLogits()
+        losses = []
+        if graphed:
+            sd0 = copy.deepcopy(model.state_dict())
+            step = GraphedTrainStep(model, crit, opt, x, m, max_norm=None, params=params, warmup=1)
+            model.load_state_dict(sd0)
+            opt.exp_avg.zero_()
+            opt.exp_avg_sq.zero_()
+            opt.state.zero_()
+            for _ in range(3):
+                losses.append(float(step(x, m)))
+        else:
+            for _ in range(3):
+                opt.zero_grad(set_to_none=True)
+                loss = crit(model(x), m)
+                loss.backward()
+                opt.step()
+                losses.append(float(loss))
+            assert float(model.pam.query_conv.weight.grad.abs().sum()) > 0      # the island's parameters do train
+            assert float(model.pos.row_embed.weight.grad[:4].abs().sum()) > 0
+            assert float(model.pos.row_embed.weight.grad[4:].abs().sum()) == 0   # rows beyond the 4x4 map: untouched
+        torch.cuda.synchronize()
+        results.append((losses, {k: v.detach().clone() for k, v in model.state_dict().items()}))
+    (l0, s0), (l1, s1) = results
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-5, (l0, l1)
+    for k in s0:
+        if s0[k].dtype.is_floating_point:
+            assert torch.allclose(s0[k], s1[k], rtol=0, atol=2e-5), k
