@@ -174,6 +174,28 @@ def test_stem_im2col_conv_matches_conv3x3():
     assert rel_l2(ctx.pgrads.view(conv.weight), w.grad) < 2e-2
 
 
+@pytest.mark.parametrize("N,cin,H,W", [(2, 3, 32, 48), (1, 1, 16, 16), (3, 7, 40, 72), (1, 3, 9, 130), (2, 5, 64, 64)])
+def test_stem_im2col_is_exact(N, cin, H, W, monkeypatch):
+    """uz_stem_im2col (tiled kernel and the first-generation one) against F.unfold: pure data movement + one bf16
+    rounding, so bit-exact; column k = tap * cin + ci, zero padding columns, ragged sizes (tile = 8 x 64 pixels)."""
+    dev = torch.device("cuda", 0)
+    x = torch.randn(N, cin, H, W, device=dev)
+    cols = F.unfold(x, 3, padding=1).view(N, cin, 9, H, W).permute(0, 3, 4, 2, 1).reshape(N, H, W, 9 * cin)
+    outs = []
+    for gen1 in (False, True):
+        if gen1:
+            monkeypatch.setenv("UZ_STEM_GEN1", "1")
+        ctx = new_ctx(training=False, record=False)
+        a, kind = E.stem_input(ctx, x)
+        torch.cuda.synchronize()
+        assert kind == "im2col" and a.C in (16, 32, 64) and a.C >= 9 * cin
+        got = a.buf.data.float()
+        assert torch.equal(got[..., :9 * cin], cols.to(torch.bfloat16).float())
+        assert bool((got[..., 9 * cin:] == 0).all())
+        outs.append(got)
+    assert torch.equal(outs[0], outs[1])
+
+
 def test_eval_mode_folds_batchnorm():
     dev = torch.device("cuda", 0)
     conv, bn = _conv_bn(64, 128, dev)
