@@ -110,3 +110,31 @@ def test_decoded_uint8_batches_match_the_reference_dataset_transform():
     assert outs[0][0] == outs[1][0] and torch.equal(outs[0][1], outs[1][1])
     with pytest.raises(RuntimeError):
         seeded_model("unet", precision="fp32").to(dev).set_input_normalization(T.IMAGENET_MEAN, T.IMAGENET_STD)(x)
+
+
+@pytest.mark.parametrize("N,cin,H,W", [(2, 3, 32, 48), (1, 1, 16, 16), (2, 7, 24, 72), (1, 3, 9, 130)])
+def test_uint8_stem_operand_is_bit_identical_to_the_normalised_fp32_operand(N, cin, H, W, monkeypatch):
+    """uz_stem_im2col_u8 (tiled kernel and the first-generation per-pixel one) produces exactly the im2col operand that
+    uz_stem_im2col builds from the tensor the reference's dataset transform would have produced on the CPU."""
+    from unet_zoo_b200 import engine as E
+    dev = torch.device("cuda", 0)
+    g = torch.Generator().manual_seed(13)
+    img8 = torch.randint(0, 256, (N, H, W, cin), generator=g, dtype=torch.uint8)
+    mean = [0.1 + 0.1 * c for c in range(cin)]
+    std = [0.2 + 0.05 * c for c in range(cin)]
+    ref = (img8.permute(0, 3, 1, 2).float().div(255) - torch.tensor(mean)[None, :, None, None]) \
+        / torch.tensor(std)[None, :, None, None]
+    ctx = E.Ctx(dev, training=False, record=False)
+    want, _ = E.stem_input(ctx, ref.to(dev).contiguous())
+    got = []
+    for gen1 in (False, True):
+        if gen1:
+            monkeypatch.setenv("UZ_STEM_GEN1", "1")
+        ctx = E.Ctx(dev, training=False, record=False)
+        ctx.input_norm = (mean, std)
+        a, kind = E.stem_input(ctx, img8.to(dev).contiguous().permute(0, 3, 1, 2))
+        torch.cuda.synchronize()
+        assert kind == "im2col" and a.C == want.C
+        got.append(a.buf.data.clone())
+    assert torch.equal(got[0], got[1])
+    assert torch.equal(got[0], want.buf.data)
