@@ -232,3 +232,22 @@ def test_conv_bn_relu_head_fused_fwd_bwd(N, H, W, cin, cout, K):
                     ("head.b", head.bias)):
         assert rel_l2(ctx.pgrads.view(p), p.grad) < 1e-2, name
     assert float(ctx.pgrads.view(conv.bias).abs().max()) < 1e-3      # bias in front of a train-mode BN: zero gradient
+
+
+@pytest.mark.parametrize("N,H,W,C", [(2, 8, 8, 64), (1, 5, 13, 24), (3, 1, 1, 8), (1, 32, 32, 256)])
+def test_nearest2x_copy_is_exact(N, H, W, C, monkeypatch):
+    """uz_nearest2x_fwd (operand of the up-conv weight gradient): a pure copy, row-per-block and first-generation forms."""
+    x = bf16r(torch.randn(N, C, H, W, device=DEV))
+    ref = F.interpolate(x, scale_factor=2, mode="nearest")
+    for gen1 in (False, True):
+        if gen1:
+            monkeypatch.setenv("UZ_BILINEAR_GEN1", "1")
+        ctx = new_ctx()
+        xa = make_act(ctx, x, ld=C + 8)
+        buf = ctx.new_buf(N, 2 * H, 2 * W, C + 16)
+        buf.data.fill_(3.0)
+        out = E.Act(buf, 8, C)
+        L.check(ctx.lib.uz_nearest2x_fwd(xa.ptr, xa.ld, N, H, W, C, out.ptr, out.ld, ctx.stream), "uz_nearest2x_fwd")
+        torch.cuda.synchronize()
+        assert torch.equal(out.to_nchw(), ref)
+        assert bool((buf.data[..., :8] == 3.0).all()) and bool((buf.data[..., 8 + C:] == 3.0).all())

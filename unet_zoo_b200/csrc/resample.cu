@@ -277,6 +277,28 @@ __global__ void nearest2x_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_
 }
 }  // namespace uz
 
+namespace uz {
+// row-per-block form of the copy above (same reasoning as bilinear2x_fwd_rows_kernel: no 64-bit division per 16 bytes)
+__global__ void __launch_bounds__(256)
+nearest2x_fwd_rows_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int cv,
+                          __nv_bfloat16* __restrict__ out, int out_ld) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const int rows = N * Ho;
+  const int per_row = Wo * cv;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / Ho, oy = row - n * Ho;
+    const __nv_bfloat16* src = x + (static_cast<size_t>(n) * H + (oy >> 1)) * W * x_ld;
+    __nv_bfloat16* orow = out + static_cast<size_t>(row) * Wo * out_ld;
+#pragma unroll 4
+    for (int e = threadIdx.x; e < per_row; e += 256) {
+      const int ox = e / cv, g = e - ox * cv;
+      *reinterpret_cast<uint4*>(orow + static_cast<size_t>(ox) * out_ld + g * 8) =
+          pw_ldg16(src + static_cast<size_t>(ox >> 1) * x_ld + g * 8);
+    }
+  }
+}
+}  // namespace uz
+
 extern "C" int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
                                 void* stream) {
   PW_REQUIRE_DEVICE();
@@ -284,6 +306,14 @@ extern "C" int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, in
   if (rc) return rc;
   if ((rc = rs_check("nearest2x_fwd(out)", out, C, out_ld))) return rc;
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "nearest2x_fwd: bad size N=%d H=%d W=%d", N, H, W);
+  if (static_cast<long long>(N) * 2 * H < (1ll << 30) && static_cast<long long>(2 * W) * (C / 8) < (1ll << 30) &&
+      std::getenv("UZ_BILINEAR_GEN1") == nullptr) {
+    nearest2x_fwd_rows_kernel<<<rs_row_grid(static_cast<long long>(N) * 2 * H), 256, 0,
+                                static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld);
+    PW_CHECK_LAUNCH("nearest2x_fwd launch");
+    return UZ_OK;
+  }
   const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
   nearest2x_fwd_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C / 8, static_cast<__nv_bfloat16*>(out), out_ld);
