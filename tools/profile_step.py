@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--rows", type=int, default=30)
+    ap.add_argument("--eval", action="store_true", help="profile the eval-mode forward instead of a training step")
     a = ap.parse_args()
     torch.manual_seed(0)
     model = unet_zoo_b200.create_model(a.model).cuda().train()
@@ -27,7 +28,14 @@ def main():
     m = (torch.rand(a.batch, 1, a.size, a.size, device="cuda") > 0.5).float()
     crit = torch.nn.BCEWithLogitsLoss()
 
+    if a.eval:
+        model.eval()
+
     def step():
+        if a.eval:
+            with torch.no_grad():
+                model(x)
+            return
         model.zero_grad(set_to_none=True)
         out = model(x)
         outs = out if isinstance(out, (list, tuple)) else [out]
@@ -41,7 +49,8 @@ def main():
         torch.cuda.synchronize()
     rows = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)
     total = sum(e.device_time_total for e in rows)
-    print(f"{a.model} batch {a.batch} {a.size}^2: {total / 1000.0:.2f} ms of kernel time in one step (serialised sum)")
+    print(f"{a.model} batch {a.batch} {a.size}^2: {total / 1000.0:.2f} ms of kernel time in one "
+          f"{'eval forward' if a.eval else 'training step'} (serialised sum)")
     for e in rows[:a.rows]:
         print(f"{e.device_time_total / 1000.0:9.3f} ms {100.0 * e.device_time_total / total:5.1f} %  x{e.count:<4d} {e.key[:110]}")
 
