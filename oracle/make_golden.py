@@ -29,7 +29,7 @@ def load_reference():
     pkg.__path__ = [REF]
     sys.modules["refmodels"] = pkg
     mods = {}
-    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet"):
+    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet", "unet_transformer"):
         spec = importlib.util.spec_from_file_location(f"refmodels.{name}", os.path.join(REF, name + ".py"))
         m = importlib.util.module_from_spec(spec)
         sys.modules[f"refmodels.{name}"] = m
@@ -55,6 +55,8 @@ def build(mods, name, **kw):
         model = mods["transatt_unet"].TransAttUNet(in_channels=3, num_classes=1, depth=5)
         model.sdpa.dropout.p = kw.get("attn_dropout", 0.1)
         return model
+    if name == "unet_transformer":   # oracle groundwork for the next model (no CUDA path yet)
+        return mods["unet_transformer"].U_Transformer(in_channels=3, num_classes=1)
     raise ValueError(name)
 
 
@@ -68,7 +70,7 @@ def main():
     mods = load_reference()
     os.makedirs(OUT, exist_ok=True)
     cases = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
-             ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0})]
+             ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}), ("unet_transformer", {})]
     only = sys.argv[1:]
     if only:
         cases = [c for c in cases if c[0] in only]

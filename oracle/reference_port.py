@@ -214,8 +214,148 @@ def transatt_unet_forward(sd: SD, x: torch.Tensor, training: bool, attn_dropout:
     return r.conv(y, "outc.conv")
 
 
+
+# ------------------------------------------------------------------------------------------------ unet_transformer
+# Groundwork for the next SURVEY 8(f) rank-4 model: oracle + fixture only, the CUDA path does not exist yet
+# (unet_zoo_b200.create_model("unet_transformer") raises NotImplementedError).
+
+def _pos_enc_2d(inv_freq: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """PositionalEncodingPermute2D.forward (unet_transformer.py:68-113) for an NCHW tensor: the first `channels`
+    features encode the row index (sin | cos halves), the next `channels` the column index; `channels` = ceil(C/2)."""
+    b, c, h, w = x.shape
+    ch = 2 * inv_freq.numel()                                    # unet_transformer.py:73-76
+    sin_h = torch.arange(h, dtype=inv_freq.dtype)[:, None] * inv_freq[None]      # "pos_x": the first spatial axis
+    sin_w = torch.arange(w, dtype=inv_freq.dtype)[:, None] * inv_freq[None]
+    emb_h = torch.cat([sin_h.sin(), sin_h.cos()], dim=-1)[:, None, :]             # [h, 1, ch]
+    emb_w = torch.cat([sin_w.sin(), sin_w.cos()], dim=-1)                         # [w, ch]
+    emb = torch.zeros(h, w, 2 * ch, dtype=x.dtype)
+    emb[:, :, :ch] = emb_h
+    emb[:, :, ch:2 * ch] = emb_w
+    return emb[None, :, :, :c].repeat(b, 1, 1, 1).permute(0, 3, 1, 2)
+
+
+def _mhsa(sd: SD, x, prefix="MHSA"):
+    """MultiHeadSelfAttention.forward (unet_transformer.py:124-136).  MultiHeadDense is x @ W without bias
+    (:29-33); the softmax runs over dim=1 of the [b, hw, hw] score matrix - the QUERY axis - as the reference has it."""
+    b, c, h, w = x.shape
+    x = x + _pos_enc_2d(sd[prefix + ".pe.penc.inv_freq"], x)
+    t = x.reshape(b, c, h * w).permute(0, 2, 1)
+    q, k, v = t @ sd[prefix + ".query.weight"], t @ sd[prefix + ".key.weight"], t @ sd[prefix + ".value.weight"]
+    a = F.softmax(torch.bmm(q, k.permute(0, 2, 1)) / c ** 0.5, dim=1)
+    return torch.bmm(a, v).permute(0, 2, 1).reshape(b, c, h, w)
+
+
+def _mhca(r: Runner, y, s, prefix, attn_res=(64, 64)):
+    """MultiHeadCrossAttention.forward (unet_transformer.py:186-229): Y = decoder path (low resolution, more
+    channels), S = skip.  Q and K come from Y, V from the max-pooled skip, all adaptively pooled to `attn_res`."""
+    sd = r.sd
+    cs = s.shape[1]
+    s_pe = s + _pos_enc_2d(sd[prefix + ".Spe.penc.inv_freq"], s)
+    s_p = F.relu(r.bn(r.conv(F.max_pool2d(s_pe, 2), prefix + ".Sconv_process.1"), prefix + ".Sconv_process.2"))
+    y_pe = y + _pos_enc_2d(sd[prefix + ".Ype.penc.inv_freq"], y)
+    y_p = F.relu(r.bn(r.conv(y_pe, prefix + ".Yconv_process.0"), prefix + ".Yconv_process.1"))
+    qk = F.adaptive_avg_pool2d(y_p, attn_res).flatten(2).permute(0, 2, 1)
+    vs = F.adaptive_avg_pool2d(s_p, attn_res).flatten(2).permute(0, 2, 1)
+    q, k, v = qk @ sd[prefix + ".query.weight"], qk @ sd[prefix + ".key.weight"], vs @ sd[prefix + ".value.weight"]
+    a = F.softmax(torch.bmm(q, k.permute(0, 2, 1)) / cs ** 0.5, dim=1)
+    z = torch.bmm(a, v).permute(0, 2, 1).reshape(y.shape[0], cs, attn_res[0], attn_res[1])
+    z = F.interpolate(z, size=(2 * y.shape[2], 2 * y.shape[3]), mode="bilinear", align_corners=True)
+    z = F.relu(r.bn(r.conv(z, prefix + ".conv_after_attention.0"), prefix + ".conv_after_attention.1"))
+    y2 = F.interpolate(y_pe, scale_factor=2, mode="bilinear", align_corners=True)       # Yconv2_process[0]
+    y2 = r.conv(r.conv(y2, prefix + ".Yconv2_process.1", padding=1), prefix + ".Yconv2_process.2")
+    y2 = F.relu(r.bn(y2, prefix + ".Yconv2_process.3"))
+    return torch.cat([z, y2], dim=1)                                                     # unet_transformer.py:228
+
+
+def unet_transformer_forward(sd: SD, x: torch.Tensor, training: bool, attn_res=(64, 64)) -> torch.Tensor:
+    """U_Transformer.forward (unet_transformer.py:271-281): DoubleConv, three Down blocks, self-attention on the
+    1/8-scale map, three TransformerUp blocks (cross-attention + double conv, :231-254), OutConv."""
+    r = Runner(sd, training)
+    x1 = r.double_conv(x, "inc.conv_op")
+    x2 = _double_convo(r, F.max_pool2d(x1, 2), "down1.maxpool_conv.1")
+    x3 = _double_convo(r, F.max_pool2d(x2, 2), "down2.maxpool_conv.1")
+    x4 = _double_convo(r, F.max_pool2d(x3, 2), "down3.maxpool_conv.1")
+    y = _mhsa(sd, x4)
+    for i, skip in ((1, x3), (2, x2), (3, x1)):
+        y = _mhca(r, y, skip, f"up{i}.MHCA", attn_res)
+        y = r.cbr(y, f"up{i}.conv.0", f"up{i}.conv.1")
+        y = r.cbr(y, f"up{i}.conv.3", f"up{i}.conv.4")
+    return r.conv(y, "outc.conv")
+
+
+def unet_transformer_state_dict(seed: int = 0) -> SD:
+    """Default-initialised parameters and buffers of U_Transformer(3, 1) under `torch.manual_seed(seed)`: plain
+    torch.nn containers created in the reference's registration order (unet_transformer.py:256-269, :115-122,
+    :138-184, :231-246), so the RNG stream is consumed exactly as the reference consumes it.  The fixture's
+    fingerprint pins this (tests/test_oracle_golden.py)."""
+    import math
+
+    import torch.nn as nn
+
+    def cbr2(cin, cout, mid=None):
+        mid = mid or cout
+        return nn.Sequential(nn.Conv2d(cin, mid, 3, padding=1), nn.BatchNorm2d(mid), nn.ReLU(inplace=True),
+                             nn.Conv2d(mid, cout, 3, padding=1), nn.BatchNorm2d(cout), nn.ReLU(inplace=True))
+
+    class Dense(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.weight = nn.Parameter(torch.empty(d, d))
+            nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+
+    class PosEnc(nn.Module):
+        def __init__(self, channels):
+            super().__init__()
+            self.penc = nn.Module()
+            ch = int(math.ceil(channels / 2))
+            self.penc.register_buffer("inv_freq", 1.0 / (10000 ** (torch.arange(0, ch, 2).float() / ch)))
+
+    class MHSA(nn.Module):
+        def __init__(self, c):
+            super().__init__()
+            self.query, self.key, self.value = Dense(c), Dense(c), Dense(c)
+            self.pe = PosEnc(c)
+
+    class MHCA(nn.Module):
+        def __init__(self, cy, cs):
+            super().__init__()
+            self.Sconv_process = nn.Sequential(nn.MaxPool2d(2), nn.Conv2d(cs, cs, 1), nn.BatchNorm2d(cs), nn.ReLU())
+            self.Yconv_process = nn.Sequential(nn.Conv2d(cy, cs, 1), nn.BatchNorm2d(cs), nn.ReLU())
+            self.query, self.key, self.value = Dense(cs), Dense(cs), Dense(cs)
+            self.conv_after_attention = nn.Sequential(nn.Conv2d(cs, cs, 1), nn.BatchNorm2d(cs), nn.ReLU())
+            self.Yconv2_process = nn.Sequential(nn.Upsample(scale_factor=2), nn.Conv2d(cy, cy, 3, padding=1),
+                                                nn.Conv2d(cy, cs, 1), nn.BatchNorm2d(cs), nn.ReLU())
+            self.Spe, self.Ype = PosEnc(cs), PosEnc(cy)
+
+    class Up(nn.Module):
+        def __init__(self, cy, cs):
+            super().__init__()
+            self.MHCA = MHCA(cy, cs)
+            self.conv = cbr2(2 * cs, cs)
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.inc = nn.Module()
+            self.inc.conv_op = cbr2(3, 64)
+            for i, (a, b) in enumerate(((64, 128), (128, 256), (256, 512)), start=1):
+                down = nn.Module()
+                inner = nn.Module()
+                inner.double_conv = cbr2(a, b)
+                down.maxpool_conv = nn.Sequential(nn.MaxPool2d(2), inner)
+                setattr(self, f"down{i}", down)
+            self.MHSA = MHSA(512)
+            self.up1, self.up2, self.up3 = Up(512, 256), Up(256, 128), Up(128, 64)
+            self.outc = nn.Module()
+            self.outc.conv = nn.Conv2d(64, 1, 1)
+
+    torch.manual_seed(seed)
+    return {k: v.detach().clone() for k, v in Net().state_dict().items()}
+
+
 FORWARDS = {"unet": unet_forward, "attention_unet": attention_unet_forward, "nested_unet": nested_unet_forward,
-            "resunet": resunet_forward, "transatt_unet": transatt_unet_forward}
+            "resunet": resunet_forward, "transatt_unet": transatt_unet_forward,
+            "unet_transformer": unet_transformer_forward}
 
 
 def bce_with_logits(logits, target):

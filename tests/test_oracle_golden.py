@@ -54,6 +54,37 @@ def test_transatt_unet_attention_dropout_path():
     assert rel_err(gold["logits_train"][0], gold["logits_train_dropout"]) > 1e-4     # the mask does matter
 
 
+def test_unet_transformer_oracle_groundwork():
+    """Next SURVEY 8(f) rank-4 model, oracle side only (no CUDA path yet): the oracle's own default-init recipe
+    reproduces the reference's weights (fingerprint of all 209 state_dict entries) and its restatement of
+    U_Transformer.forward (self-attention, three cross-attention decoders) reproduces the reference's train / eval
+    outputs, loss, gradients and running statistics."""
+    torch.set_num_threads(8)
+    gold = load_golden("unet_transformer")
+    sd = O.unet_transformer_state_dict(gold["recipe"]["seed"])
+    assert list(sd) == list(gold["fingerprint"]) and len(sd) == 209
+    for k, v in sd.items():
+        fp = gold["fingerprint"][k]
+        assert float(v.double().sum()) == fp[0] and float(v.double().abs().sum()) == fp[1], k
+    n, c, h, w = gold["recipe"]["batch"]
+    x, mask = O.synthetic_batch(n, c, h, w, gold["recipe"]["seed_x"], gold["recipe"]["seed_m"])
+    out, loss, grads = O.train_step("unet_transformer", sd, x, mask)
+    assert rel_err(out.detach(), gold["logits_train"][0]) < 1e-5
+    assert abs(float(loss) - gold["loss"]) < 1e-5
+    for k, gn in gold["grad_norm"].items():
+        assert abs(float(grads[k].double().norm()) - gn) <= 2e-4 * gn + 1e-7, k
+    for k, g in gold["grad_small"].items():
+        assert float((grads[k] - g).abs().max()) <= 2e-4 * float(g.abs().max()) + 1e-6, k
+    for k, v in gold["bn_after"].items():
+        assert torch.allclose(sd[k].double(), v.double(), rtol=1e-5, atol=1e-6), k
+    with torch.no_grad():
+        oe = O.unet_transformer_forward(sd, x, False)
+    assert rel_err(oe, gold["logits_eval"][0]) < 1e-5
+    import unet_zoo_b200
+    with pytest.raises(NotImplementedError):                 # the product does not pretend to serve it
+        unet_zoo_b200.create_model("unet_transformer")
+
+
 def test_threshold_is_bit_exact_with_sign_test():
     """sigmoid(z) > 0.5 (metrics.py:11-12) agrees with z > 0 away from the fp32 saturation point; the parity tests use
     the reference formulation itself."""
