@@ -109,3 +109,43 @@ def test_torch_island_inference_keeps_no_graph():
         assert "torch island returned" in str(e)
     else:
         raise AssertionError("a spatial-size change inside the island must be rejected")
+
+
+def test_island_math_follows_the_tf32_api_the_process_uses():
+    """torch >= 2.9 raises when `allow_tf32` is read after `fp32_precision` was written (and vice versa): the island's
+    precision guard must work, and restore the previous setting, on either front end.  Run in a subprocess: the
+    choice of front end is sticky for the whole process."""
+    import subprocess
+    import sys
+    code = r'''
+import torch
+from unet_zoo_b200 import engine as E
+mm, cd = torch.backends.cuda.matmul, torch.backends.cudnn
+mm.allow_tf32, cd.allow_tf32 = False, True                    # legacy front end
+with E._island_math(True):
+    assert mm.allow_tf32 and cd.allow_tf32
+assert (mm.allow_tf32, cd.allow_tf32) == (False, True)
+with E._island_math(False):
+    assert not mm.allow_tf32 and not cd.allow_tf32
+assert (mm.allow_tf32, cd.allow_tf32) == (False, True)
+if hasattr(mm, "fp32_precision"):
+    mm.fp32_precision = "tf32"                                 # the application switches to the new front end:
+    cd.conv.fp32_precision = "tf32"                            # reading mm.allow_tf32 now raises inside torch
+    try:
+        mm.allow_tf32
+        mixed = False
+    except RuntimeError:
+        mixed = True
+    with E._island_math(False):
+        assert mm.fp32_precision != "tf32" and cd.conv.fp32_precision != "tf32"
+    assert (mm.fp32_precision, cd.conv.fp32_precision) == ("tf32", "tf32")
+    with E._island_math(True):
+        assert mm.fp32_precision == "tf32" and cd.conv.fp32_precision == "tf32"
+    assert (mm.fp32_precision, cd.conv.fp32_precision) == ("tf32", "tf32")
+    print("mixed" if mixed else "consistent")
+print("ok")
+'''
+    import os
+    env = dict(os.environ, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]

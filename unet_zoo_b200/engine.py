@@ -803,14 +803,28 @@ def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:
 
 @contextlib.contextmanager
 def _island_math(tf32: bool):
-    """Pin the fp32 matmul / convolution precision of torch's own kernels for the duration of an island."""
-    saved = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
-    torch.backends.cuda.matmul.allow_tf32 = tf32
-    torch.backends.cudnn.allow_tf32 = tf32
+    """Pin the fp32 matmul / convolution precision of torch's own kernels for the duration of an island.
+
+    torch >= 2.9 has two front ends for the same switches (`allow_tf32` and `fp32_precision`) and refuses to READ one
+    after the other was written: use whichever the process is already on."""
+    mm, cd = torch.backends.cuda.matmul, torch.backends.cudnn
+    try:
+        saved = (mm.allow_tf32, cd.allow_tf32)
+        legacy = True
+    except RuntimeError:            # the application set torch.backends.*.fp32_precision
+        saved = (mm.fp32_precision, cd.conv.fp32_precision)
+        legacy = False
+    if legacy:
+        mm.allow_tf32 = cd.allow_tf32 = tf32
+    else:
+        mm.fp32_precision = cd.conv.fp32_precision = "tf32" if tf32 else "ieee"
     try:
         yield
     finally:
-        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = saved
+        if legacy:
+            mm.allow_tf32, cd.allow_tf32 = saved
+        else:
+            mm.fp32_precision, cd.conv.fp32_precision = saved
 
 
 def torch_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],
