@@ -43,6 +43,21 @@ def test_position_table_limit_is_reported():
         raise AssertionError("a 33-row bottleneck map must be rejected (32-entry embedding, transatt_unet.py:59)")
 
 
+def test_oversized_input_is_rejected_before_any_kernel_runs():
+    model = seeded_model("transatt_unet")
+    for bad in (torch.zeros(1, 3, 528, 64), torch.zeros(1, 64, 528, 3, dtype=torch.uint8)):
+        try:
+            model(bad)
+        except RuntimeError as e:
+            assert "up to 512x512" in str(e), str(e)
+        else:
+            raise AssertionError("a 528-pixel side must be rejected (33 > 32 position entries)")
+    try:
+        model(torch.zeros(1, 3, 512, 512))                     # size is fine: the next check is the device
+    except RuntimeError as e:
+        assert "no CPU path" in str(e)
+
+
 class _HostCtx:
     """The members of engine.Ctx that torch_island touches, on host memory."""
 

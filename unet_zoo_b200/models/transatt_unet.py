@@ -4,7 +4,7 @@ bottleneck carries two attention branches.
 Parameters and wiring follow the reference (unet_zoo/models/transatt_unet.py:109-164; blocks
 common_layers.py:130-180): ``inc`` + four ``Down`` (MaxPool2d -> DoubleConvo), four bilinear ``Up`` blocks whose
 concat order is **[skip, upsampled]** (common_layers.py:179) and whose DoubleConvo narrows through
-``in_channels // 2``, ``OutConv``.  All of that - 99.6 % of the FLOPs at 512^2 - runs on the fused sm_100a operators:
+``in_channels // 2``, ``OutConv``.  All of that - 99.3 % of the FLOPs at 512^2 - runs on the fused sm_100a operators:
 the skip half of each decoder buffer is written by the encoder's BatchNorm pass (together with the pooled tensor), the
 upsampled half by ``uz_bilinear2x_fwd``; no cat / pool / pad kernels run.
 
@@ -126,6 +126,17 @@ class TransAttUNet(HotPathModel):
         # the reference swallows **kwargs; `attn_dropout` is honoured here so that parity tests can switch the
         # (RNG-dependent) attention dropout off on both sides
         self.sdpa = ScaledDotProductAttention(512, attn_dropout=kwargs.get("attn_dropout", 0.1))
+
+    def _check_input(self, x):
+        # the learned position table has 32 rows / columns for the 1/16-scale map (transatt_unet.py:59,132): say so
+        # before any kernel runs instead of failing inside the bottleneck
+        if isinstance(x, torch.Tensor) and x.dim() == 4:
+            h, w = (x.shape[1], x.shape[2]) if x.dtype == torch.uint8 else (x.shape[2], x.shape[3])
+            lim = 16 * self.pos.row_embed.num_embeddings
+            if h > lim or w > lim:
+                raise RuntimeError(f"TransAttUNet: inputs up to {lim}x{lim} are supported (got {h}x{w}): the reference's "
+                                   f"learned position embedding has {self.pos.row_embed.num_embeddings} entries per axis")
+        return super()._check_input(x)
 
     def _bottleneck(self, x5):
         """transatt_unet.py:143-154 on an NCHW fp32 tensor (stock torch)."""
