@@ -64,6 +64,35 @@ def fingerprint(sd):
     return {k: (float(v.double().sum()), float(v.double().abs().sum())) for k, v in sd.items()}
 
 
+def conditioned_case(mods, name, kw, x, mask):
+    """Second fixture per model on a WELL-CONDITIONED state: default init + randomised BatchNorm affine parameters
+    (oracle.reference_port.randomize_bn_affine), one train step of the unmodified reference under the
+    Gaussian projection loss, then its eval-mode forward.  The bf16 GPU tests hold the CUDA path to the north_star's
+    plain bars against THESE outputs (train mode at gamma = 1 / beta = 0 amplifies rounding 1.2x per layer)."""
+    from oracle.reference_port import bce_with_logits, gaussian_projection_loss, randomize_bn_affine
+    torch.manual_seed(0)
+    model = build(mods, name, **kw)
+    model.load_state_dict(randomize_bn_affine({k: v.clone() for k, v in model.state_dict().items()}))
+    model.train()
+    out = model(x)
+    outs = out if isinstance(out, list) else [out]
+    sum(gaussian_projection_loss(o, mask) for o in outs).backward()
+    grads = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
+    cond = {
+        "logits_train": [o.detach().clone() for o in outs],
+        "bce": float(sum(bce_with_logits(o.detach(), mask) for o in outs)),
+        "grad_norm": {k: float(g.double().norm()) for k, g in grads.items()},
+        "grad_small": {k: g for k, g in grads.items() if g.numel() <= 2048},
+        "bn_after": {k: v.detach().clone() for k, v in model.state_dict().items()
+                     if "running_" in k or "num_batches" in k},
+    }
+    model.eval()
+    with torch.no_grad():
+        oe = model(x)
+    cond["logits_eval"] = [o.clone() for o in (oe if isinstance(oe, list) else [oe])]
+    return cond
+
+
 def main():
     from oracle.reference_port import synthetic_batch
     torch.set_num_threads(8)
@@ -113,6 +142,7 @@ def main():
         with torch.no_grad():
             oe = model(x)
         gold["logits_eval"] = [o.clone() for o in (oe if isinstance(oe, list) else [oe])]
+        gold["cond"] = conditioned_case(mods, name, kw, x, mask)
         # README example (README.md:74-90): eval forward on randn(1,3,256,256) -> shape only (fresh default weights)
         if tag == "unet":
             gold["readme_shape"] = list(model(torch.randn(1, 3, 256, 256)).shape)

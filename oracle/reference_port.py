@@ -385,6 +385,22 @@ def projection_loss(logits, target):
     return (logits * (2.0 * target - 1.0)).mean()
 
 
+_GAUSS_PATTERNS: Dict[tuple, torch.Tensor] = {}
+
+
+def gaussian_projection_loss(logits, target):
+    """Well-conditioned test loss for gradient parity: mean(logits * r) with a fixed pattern r ~ N(0, 1) (seeded CPU
+    generator, cached per shape).  Like `projection_loss` its gradient has no common mode; unlike the +-1 pattern it
+    does not make dL/dz of the last layer TWO-VALUED - two-valued gradients round to bf16 with a systematic (not a
+    random) error whose per-channel sum, multiplied by the large mean of the post-ReLU activations, swamps the weight
+    gradient of the last convolution (measured: 110 % error for ours AND for torch's bf16 autocast)."""
+    key = tuple(logits.shape)
+    r = _GAUSS_PATTERNS.get(key)
+    if r is None:
+        r = _GAUSS_PATTERNS[key] = torch.randn(key, generator=torch.Generator().manual_seed(99))
+    return (logits * r.to(logits.device)).mean()
+
+
 def train_step(name: str, sd: SD, x, target, loss_fn=None, **kw):
     """One forward + BCE + backward in train mode on CPU: returns (logits, loss, {param key: grad}); `sd`'s BatchNorm
     buffers are updated in place like the reference's modules would (training_loop.py:113-119)."""
@@ -403,6 +419,28 @@ def train_step(name: str, sd: SD, x, target, loss_fn=None, **kw):
     loss.backward()
     grads = {k: (t.grad if t.grad is not None else torch.zeros_like(t)) for k, t in leaves.items()}
     return out, loss.detach(), grads
+
+
+def randomize_bn_affine(sd: SD, gamma=(0.8, 1.2), beta=(1.0, 2.0), seed: int = 7) -> SD:
+    """SURVEY.md 8(c) protocol step "randomise gamma / beta": every BatchNorm weight ~ U(gamma), bias ~ U(beta), in
+    place, from a seeded CPU generator (keys visited in state_dict order).
+
+    Why the full-resolution parity tests use it: at DEFAULT init (gamma 1, beta 0) a train-mode conv-BN-ReLU stack
+    amplifies any perturbation by ~sqrt(pi / (pi - 1)) = 1.21 per layer (ReLU of a zero-mean pre-activation keeps
+    half of the perturbation energy but only (1/2 - 1/(2 pi)) of the signal variance, the rest being a per-channel
+    mean the next BatchNorm subtracts).  Over the 35 BatchNorm layers of attention_unet that turns the 2^-9 rounding
+    of bf16 operands into a 30 % deviation of the logits for torch's OWN bf16 autocast of the reference - a
+    property of the function at that point, not of an implementation.  With beta in [1, 2] most units are in the
+    linear regime, the factor drops to ~1.05 per layer and 2e-2 on the logits is a meaningful bar."""
+    g = torch.Generator().manual_seed(seed)
+    for k, v in sd.items():
+        if v.dim() != 1:
+            continue
+        if k.endswith(".weight") and (k[:-len("weight")] + "running_mean") in sd:
+            v.copy_(torch.rand(v.shape, generator=g) * (gamma[1] - gamma[0]) + gamma[0])
+        elif k.endswith(".bias") and (k[:-len("bias")] + "running_mean") in sd:
+            v.copy_(torch.rand(v.shape, generator=g) * (beta[1] - beta[0]) + beta[0])
+    return sd
 
 
 def synthetic_batch(n, cin, h, w, seed_x=1234, seed_m=4321):

@@ -40,6 +40,32 @@ def test_oracle_matches_reference_outputs(tag, kw):
         assert rel_err(o, g) < 1e-5
 
 
+@pytest.mark.parametrize("tag,kw", CASES)
+def test_oracle_matches_reference_on_conditioned_state(tag, kw):
+    """Same pin on the well-conditioned state the bf16 parity tests use (randomised BatchNorm affine parameters,
+    Gaussian projection loss): train logits, BCE, gradients, running statistics, eval logits of the unmodified reference."""
+    torch.set_num_threads(8)
+    name = tag.replace("_ds", "")
+    gold = load_golden(tag)
+    cond = gold["cond"]
+    sd = O.randomize_bn_affine(copy.deepcopy(seeded_model(name, **kw).state_dict()))
+    n, c, h, w = gold["recipe"]["batch"]
+    x, mask = O.synthetic_batch(n, c, h, w, gold["recipe"]["seed_x"], gold["recipe"]["seed_m"])
+    out, _, grads = O.train_step(name, sd, x, mask, loss_fn=O.gaussian_projection_loss, **kw)
+    outs = out if isinstance(out, list) else [out]
+    for o, g in zip(outs, cond["logits_train"]):
+        assert rel_err(o.detach(), g) < 1e-5
+    assert abs(float(sum(O.bce_with_logits(o.detach(), mask) for o in outs)) - cond["bce"]) < 1e-5
+    for k, gn in cond["grad_norm"].items():
+        assert abs(float(grads[k].double().norm()) - gn) <= 5e-4 * gn + 1e-9, k
+    for k, v in cond["bn_after"].items():
+        assert torch.allclose(sd[k].double(), v.double(), rtol=1e-5, atol=1e-6), k
+    with torch.no_grad():
+        oe = O.FORWARDS[name](sd, x, False, **kw)
+    for o, g in zip(oe if isinstance(oe, list) else [oe], cond["logits_eval"]):
+        assert rel_err(o, g) < 1e-5
+
+
 def test_transatt_unet_attention_dropout_path():
     """The reference AS IS (nn.Dropout(0.1) on the channel-attention matrix, transatt_unet.py:88,103) under the fixture's
     RNG seed: the oracle's dropout restatement draws the same mask on CPU."""

@@ -312,7 +312,8 @@ int bh_bwd(const BhArgs& a, const float* bn, const float* dlogits, __nv_bfloat16
   float* dbpart = hwpart + static_cast<size_t>(max_rows) * K * a.C;
   float* coef = dbpart + static_cast<size_t>(max_rows) * K;
   const size_t smem = sizeof(float) * kBhThreads * (16 + 8 * K + K);
-  static bool configured = false;
+  static bool configured_dev[kMaxDevices] = {false};   // the attribute is per device
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(bn_head_bwd_reduce_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));

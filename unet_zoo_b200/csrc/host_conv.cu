@@ -35,16 +35,17 @@ int cuda_error(cudaError_t e, const char* what) {
 }
 
 int sm_count() {
-  static int cached = 0;
-  if (cached > 0) return cached;
+  static int cached[kMaxDevices] = {0};   // per device: a process may drive several GPUs (cuda:0 then cuda:1)
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  const bool slot_ok = dev >= 0 && dev < kMaxDevices;
+  if (slot_ok && cached[dev] != 0) return cached[dev];
   int n = 0;
   if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
   int major = 0;
   cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
-  if (major != 10) return -2;
-  cached = n;
+  if (major != 10) n = -2;
+  if (slot_ok) cached[dev] = n;
   return n;
 }
 

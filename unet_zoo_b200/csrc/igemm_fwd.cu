@@ -10,6 +10,7 @@
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
 // warps 2..5 = epilogue (TMEM -> registers -> bias/ReLU/stats -> bf16 NHWC stores).  Accumulators are
 // double-buffered in TMEM so the epilogue of tile i overlaps the main loop of tile i+1.
+#include "host_util.h"
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -332,7 +333,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) igemm_fwd_kernel(const __grid_
 template <int BN>
 static cudaError_t launch_fwd_bn(const IgemmParams& p, int grid, cudaStream_t stream) {
   using Cfg = FwdCfg<BN>;
-  static bool configured = false;
+  static bool configured_dev[kMaxDevices] = {false};   // the attribute is per device
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(igemm_fwd_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);

@@ -14,6 +14,7 @@
 // 4..11 = epilogue (two warps per TMEM lane quarter, each owning 32 of the 64 columns of a chunk).
 #include <string.h>
 
+#include "host_util.h"
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -477,12 +478,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
 
 template <int BN, int MP, int CG>
 static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
-  static int configured = 0;
-  if (configured < smem_bytes) {
+  static int configured[kMaxDevices] = {0};   // the attribute is per device
+  int& conf = configured[device_slot()];
+  if (conf < smem_bytes) {
     cudaError_t e =
         cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
-    configured = smem_bytes;
+    conf = smem_bytes;
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

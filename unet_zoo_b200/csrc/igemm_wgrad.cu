@@ -8,6 +8,7 @@
 // descriptors describe that as an MN-major atom (LBO = next 64-channel atom, SBO = next 8-pixel group).
 // A work item is (128 rows of P-channels) x (slab of up to 4 (tap, 64-channel) atoms of Q) x (split-K slice);
 // fp32 partials go to a workspace and a small reduce kernel sums the splits into the parameter-gradient layout.
+#include "host_util.h"
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -215,7 +216,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
 }
 
 cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream) {
-  static bool configured = false;
+  static bool configured_dev[kMaxDevices] = {false};   // the attribute is per device
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     cudaError_t e =
         cudaFuncSetAttribute(igemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes);

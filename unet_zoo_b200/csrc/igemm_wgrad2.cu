@@ -23,6 +23,7 @@
 // 64 cycles = 128 (96) B/clk.
 #include <string.h>
 
+#include "host_util.h"
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -352,7 +353,8 @@ cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_
 template <int CG, int WIDE>
 static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_t stream) {
   constexpr int kW2SmemBytes = w2_smem_bytes(CG, WIDE);
-  static bool configured = false;
+  static bool configured_dev[kMaxDevices] = {false};   // the attribute is per device
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(igemm_wgrad2_kernel<CG, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kW2SmemBytes);
