@@ -71,7 +71,7 @@ def main():
             E.PROFILE = []
             model(x)
             torch.cuda.synchronize()
-        rows = [(tag, flops, e0.elapsed_time(e1)) for kind, flops, e0, e1, tag in E.PROFILE if kind == "igemm_fwd"]
+        rows = [(tag, flops, e0.elapsed_time(e1)) for kind, flops, e0, e1, tag, _nb in E.PROFILE if kind == "igemm_fwd"]
         E.PROFILE = None
         tot_ms = sum(r[2] for r in rows)
         print(f"# {a.model} inference, batch {b}, {sz}x{sz}: convolution launches (eval mode, BatchNorm folded)\n")

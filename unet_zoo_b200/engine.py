@@ -21,15 +21,16 @@ _c_void_p = ctypes.c_void_p
 
 # Optional per-launch timing of the tensor-core kernels (bench.py's roofline leg): when set to a list, every
 # uz_conv_igemm / uz_conv_wgrad / uz_bn_apply / uz_bn_bwd call is bracketed by CUDA events on the launch stream and
-# appended as (kind, algorithmic FLOPs (GEMM kinds) or bytes (bn_* kinds), start_event, end_event).  None (default)
-# adds no overhead.
+# appended as (kind, algorithmic FLOPs (GEMM kinds) or bytes (bn_* kinds), start_event, end_event, tag, algorithmic
+# HBM bytes).  None (default) adds no overhead.
 PROFILE: Optional[list] = None
 _TAPS = {0: 9, 1: 9, 2: 1, 3: 9, 4: 9, 5: 1, 6: 1, 7: 1, 8: 4, 9: 9, 10: 36}
 
 
 class _Timed:
-    def __init__(self, kind, flops, tag=""):
+    def __init__(self, kind, flops, tag="", nbytes=None):
         self.kind, self.flops, self.tag = kind, flops, tag
+        self.nbytes = flops if nbytes is None else nbytes     # bandwidth kinds pass their bytes as `flops`
 
     def __enter__(self):
         if PROFILE is not None:
@@ -40,7 +41,7 @@ class _Timed:
     def __exit__(self, *a):
         if PROFILE is not None:
             self.e1.record()
-            PROFILE.append((self.kind, self.flops, self.e0, self.e1, self.tag))
+            PROFILE.append((self.kind, self.flops, self.e0, self.e1, self.tag, self.nbytes))
 
 
 _MODE_NAMES = {L.CONV3X3: "conv3x3", L.CONV1X1: "conv1x1", L.CONVT2X2: "convT2x2", L.CONV3X3_DGRAD: "conv3x3.dgrad",
@@ -294,9 +295,11 @@ class Ctx:
         # algorithmic FLOPs: 2 * output pixels * cout * cin * taps (per output pixel; convT has one tap per output)
         opix = a.N * out_h * out_w
         taps = {L.CONVT2X2: 1, L.CONV3X3_S2_DGRAD: 2.25}.get(mode, _TAPS[mode])
-        flops = 2.0 * opix * cout * sum(s.C for s in segs) * taps
-        with _Timed("igemm_fwd", flops, f"{_MODE_NAMES.get(mode, mode)} {sum(s.C for s in segs)}->{cout} "
-                                         f"@{out_h}x{out_w} n{a.N}"):
+        cin = sum(s.C for s in segs)
+        flops = 2.0 * opix * cout * cin * taps
+        # algorithmic HBM bytes: every operand once (input pixels, packed weights, output (read too when accumulating))
+        nbytes = 2.0 * (a.npix * cin + opix * cout * (2 if flags & L.FLAG_ACCUMULATE else 1) + wp.numel())
+        with _Timed("igemm_fwd", flops, f"{_MODE_NAMES.get(mode, mode)} {cin}->{cout} @{out_h}x{out_w} n{a.N}", nbytes):
             rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
                                         out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
         L.check(rc, "uz_conv_igemm")
@@ -314,7 +317,15 @@ class Ctx:
             flops = 2.0 * N * 4 * H * W * cin * cout * 9
         else:
             flops = 2.0 * N * H * W * cin * cout * _TAPS[mode]
-        with _Timed("igemm_wgrad", flops):
+        if mode in (L.CONVT2X2, L.UP2X_CONV3X3):
+            dy_pix = 4 * N * H * W
+        elif mode in (L.CONV3X3_S2, L.CONV1X1_S2):
+            dy_pix = N * ((H - 1) // 2 + 1) * ((W - 1) // 2 + 1)
+        else:
+            dy_pix = N * H * W
+        # algorithmic HBM bytes: x and dy once, the fp32 gradient block once (read too when accumulating)
+        nbytes = 2.0 * (N * H * W * cin + dy_pix * cout) + 4.0 * cin * cout * (4 if mode == L.CONVT2X2 else _TAPS[mode]) * (2 if accumulate else 1)
+        with _Timed("igemm_wgrad", flops, f"{_MODE_NAMES.get(mode, mode)}.wgrad {cin}->{cout} @{H}x{W} n{N}", nbytes):
             rc = self.lib.uz_conv_wgrad(mode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total,
                                         c_off, int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
         L.check(rc, "uz_conv_wgrad")

@@ -79,8 +79,18 @@ class BucketedGrads(ParamGrads):
         lo, hi = self.ranges[b]
         chunk = self.flat[lo:hi]
         if self.comm_stream is not None:
-            self.comm_stream.wait_stream(torch.cuda.current_stream(self.flat.device))
-            self.comm_stream.wait_stream(side_stream(self.flat.device))   # weight gradients are produced there
+            dev = self.flat.device
+            cur = torch.cuda.current_stream(dev)
+            side = side_stream(dev)                       # weight gradients are produced there
+            self.comm_stream.wait_stream(cur)
+            if side != cur:
+                # under CUDA-graph capture the side stream is only part of the capture once a weight gradient was
+                # issued on it; an event recorded on a stream OUTSIDE the capture must not be waited for from inside
+                # (nothing of this step can be pending there in that case)
+                with torch.cuda.stream(side):
+                    side_in_capture = torch.cuda.is_current_stream_capturing()
+                if side_in_capture or not torch.cuda.is_current_stream_capturing():
+                    self.comm_stream.wait_stream(side)
             with torch.cuda.stream(self.comm_stream):
                 dist.all_reduce(chunk, op=dist.ReduceOp.AVG, group=self.group)
         else:  # CPU / gloo (tests): no AVG reduction there

@@ -7,10 +7,17 @@ packing, reductions) are visible.  :class:`GraphedTrainStep` records the step on
 is stream-ordered and allocation-free, the executor's buffers come from the graph's private memory pool) and replays
 it with a single ``cudaGraphLaunch`` per batch: no tracing compiler, the same kernels in the same order.
 
-Data-parallel (N > 1): capturing the bucketed NCCL all-reduces inside the step graph was tried and hung, so no NCCL
-call is captured.  With ``grad_sync=`` (``parallel.DataParallel.sync_gradients`` on a wrapper in ``defer_sync`` mode)
-the step becomes graph A (zero_grad -> forward -> criterion -> backward into the flat gradient buffer), one eager
-all-reduce of that buffer, graph B (clip + optimizer step): three host calls per step instead of ~300.
+Data-parallel (N > 1), two modes:
+
+* ``capture_nccl=True`` (bench.py's default): the whole step INCLUDING the bucketed NCCL all-reduces of
+  ``parallel.DataParallel`` is one graph.  The all-reduces are captured on the wrapper's communication stream (forked
+  from / joined to the capturing stream by events, like the weight-gradient side stream), so on replay they overlap the
+  remaining backward kernels exactly as in the eager bucketed mode, at one host call per step.  Needs the process
+  group's watchdog not to poll CUDA events while this thread captures: set ``TORCH_NCCL_ASYNC_ERROR_HANDLING=0`` before
+  ``init_process_group`` (PyTorch's own requirement for whole-network capture with NCCL) - bench.py does.
+* ``grad_sync=`` (``parallel.DataParallel.sync_gradients`` on a wrapper in ``defer_sync`` mode): no NCCL call is
+  captured; the step becomes graph A (zero_grad -> forward -> criterion -> backward into the flat gradient buffer), one
+  eager all-reduce of that buffer (exposed), graph B (clip + optimizer step): three host calls per step.
 
 Constraints: fixed batch shape; an optimizer that can be captured (``torch.optim.AdamW(..., fused=True,
 capturable=True)``); the learning-rate schedule, if any, must live in a device tensor.
@@ -24,7 +31,7 @@ class GraphedTrainStep:
     def __init__(self, model: torch.nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
                  example_x: torch.Tensor, example_target: torch.Tensor, max_norm: Optional[float] = 1.0,
                  params: Optional[Iterable[torch.nn.Parameter]] = None, warmup: int = 3,
-                 grad_sync: Optional[Callable[[], None]] = None):
+                 grad_sync: Optional[Callable[[], None]] = None, capture_nccl: bool = False):
         if not example_x.is_cuda:
             raise RuntimeError("GraphedTrainStep needs CUDA tensors (there is no CPU path)")
         self.model, self.criterion, self.optimizer, self.max_norm = model, criterion, optimizer, max_norm
@@ -48,7 +55,11 @@ class GraphedTrainStep:
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
         self.graph_tail = None
-        if grad_sync is None:
+        if grad_sync is None and capture_nccl:
+            # a process group is alive (its threads may touch the CUDA API meanwhile): thread-local capture mode
+            with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+                self._body()
+        elif grad_sync is None:
             with torch.cuda.graph(self.graph):
                 self._body()
         else:
