@@ -268,3 +268,58 @@ def test_split_graph_data_parallel_step_matches_eager_steps():
     for k in s0:
         if s0[k].dtype.is_floating_point:
             assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k
+
+
+def test_overlapped_graph_data_parallel_step_matches_eager_steps():
+    """bench.py's default N > 1 launch mode: ONE CUDA graph per step with the bucketed NCCL all-reduces captured on the
+    communication stream (GraphedTrainStep(capture_nccl=True)).  World of one (the all-reduce is an identity), small
+    buckets so that several are launched mid-backward: three replayed steps reproduce three eager steps of the
+    un-wrapped model; the warm-up's side effects are undone by the constructor (restore_after_warmup)."""
+    import os
+
+    import torch.distributed as dist
+    from unet_zoo_b200 import parallel as P
+    from unet_zoo_b200.loss import BCEDiceWithLogits
+    from unet_zoo_b200.optim import FlatAdamW
+    from unet_zoo_b200.train_step import GraphedTrainStep
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    x, m = x.cuda(), m.cuda()
+    os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29535", rank=0, world_size=1)
+    try:
+        results = []
+        for graphed in (False, True):
+            model = seeded_model("unet").cuda().train()
+            net = P.DataParallel(model, bucket_mb=8.0) if graphed else model
+            params = list(model.parameters())
+            opt = FlatAdamW(params, lr=1e-3, weight_decay=1e-5, max_norm=1.0)
+            crit = BCEDiceWithLogits()
+            losses = []
+            if graphed:
+                step = GraphedTrainStep(net, crit, opt, x, m, max_norm=None, params=params, warmup=2, capture_nccl=True)
+                assert step.graph_tail is None and type(model._last_param_grads) is P.BucketedGrads
+                assert len(model._last_param_grads.buckets) > 3
+                assert float(opt.step_count) == 0.0          # warm-up undone: the optimizer has not stepped yet
+                for _ in range(3):
+                    losses.append(float(step(x, m)))
+            else:
+                for _ in range(3):
+                    opt.zero_grad(set_to_none=True)
+                    loss = crit(net(x), m)
+                    loss.backward()
+                    opt.step()
+                    losses.append(float(loss))
+            torch.cuda.synchronize()
+            results.append((losses, {k: v.detach().clone() for k, v in model.state_dict().items()}))
+    finally:
+        if created:
+            dist.destroy_process_group()
+    (l0, s0), (l1, s1) = results
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
+    for k in s0:
+        if s0[k].dtype.is_floating_point:
+            assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k
+        else:
+            assert torch.equal(s0[k], s1[k]), k

@@ -31,7 +31,8 @@ class GraphedTrainStep:
     def __init__(self, model: torch.nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
                  example_x: torch.Tensor, example_target: torch.Tensor, max_norm: Optional[float] = 1.0,
                  params: Optional[Iterable[torch.nn.Parameter]] = None, warmup: int = 3,
-                 grad_sync: Optional[Callable[[], None]] = None, capture_nccl: bool = False):
+                 grad_sync: Optional[Callable[[], None]] = None, capture_nccl: bool = False,
+                 restore_after_warmup: bool = True):
         if not example_x.is_cuda:
             raise RuntimeError("GraphedTrainStep needs CUDA tensors (there is no CPU path)")
         self.model, self.criterion, self.optimizer, self.max_norm = model, criterion, optimizer, max_norm
@@ -46,6 +47,10 @@ class GraphedTrainStep:
         warn_off = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
         if warn_off is not None:
             warn_off(False)
+        # the warm-up steps and the capture itself are REAL training steps on the example batch: weights, optimizer
+        # moments / step counter and BatchNorm running statistics are put back afterwards (in place - the graph holds
+        # their addresses), so the caller's first step starts from the state it handed in
+        saved = self._snapshot() if restore_after_warmup else None
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):                      # warm-up off the capture: lazy initialisation, autotuning
@@ -69,6 +74,35 @@ class GraphedTrainStep:
             self.graph_tail = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph_tail, pool=self.graph.pool(), capture_error_mode="thread_local"):
                 self._tail()
+        if saved is not None:
+            self._restore(saved)
+
+    def _snapshot(self):
+        opt = self.optimizer
+        if hasattr(opt, "exp_avg_sq") and hasattr(opt, "flat"):        # unet_zoo_b200.optim.FlatAdamW
+            ostate = ("flat", opt.exp_avg.clone(), opt.exp_avg_sq.clone(), opt.state.clone())
+        else:
+            ostate = ("torch", {id(p): {k: v.detach().clone() for k, v in st.items() if torch.is_tensor(v)}
+                                for p, st in opt.state.items()})
+        return {k: v.detach().clone() for k, v in self.model.state_dict().items()}, ostate
+
+    @torch.no_grad()
+    def _restore(self, saved):
+        msd, ostate = saved
+        for k, v in self.model.state_dict().items():
+            v.copy_(msd[k])
+        opt = self.optimizer
+        if ostate[0] == "flat":
+            opt.exp_avg.copy_(ostate[1])
+            opt.exp_avg_sq.copy_(ostate[2])
+            opt.state.copy_(ostate[3])
+        else:
+            for p, st in opt.state.items():
+                old = ostate[1].get(id(p), {})
+                for k, v in st.items():
+                    if torch.is_tensor(v):                 # lazily created by the warm-up: back to its initial zero
+                        v.copy_(old[k]) if k in old else v.zero_()
+        torch.cuda.synchronize()
 
     def _body(self):
         self._fwd_bwd()
