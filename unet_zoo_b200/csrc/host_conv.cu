@@ -84,9 +84,16 @@ static int make_act_map(CUtensorMap* m, const void* ptr, int C, int ld, int N, i
                            (cuuint64_t)H * W * ld * 2};
   cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
   cuuint32_t estr[4] = {1, 1, 1, 1};
+  // L2 promotion widens every 128-byte request to 256 bytes.  On a channel SLICE of a wider buffer the other 128 bytes
+  // belong to a different tensor (the skip half of a concat buffer): measured 2x DRAM reads for the transposed
+  // convolution's data / weight gradient (profiles/r02_g_unet_per_launch.md).  Promote only where the neighbour is ours.
+  const bool whole_rows = C == ld || ((C * 2) % 256 == 0 && (reinterpret_cast<uintptr_t>(base) & 255u) == 0);
+  static const int promo_env = getenv("UZ_TMA_PROMO") ? atoi(getenv("UZ_TMA_PROMO")) : -1;
+  const CUtensorMapL2promotion promo = (promo_env == 256 || (promo_env < 0 && whole_rows))
+                                           ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<char*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, box_c == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled(activation C=%d ld=%d N=%d H=%d W=%d) failed: %d", C, ld,
                      N, H, W, (int)r);
@@ -344,7 +351,10 @@ extern "C" int uz_device_sm_count(void) {
   return n;
 }
 // rows of the per-channel statistics partials: one per CTA of the persistent conv kernels
-extern "C" int uz_conv_stats_rows(void) { return uz_device_sm_count(); }
+extern "C" int uz_conv_stats_rows(void) {
+  const int n = uz_device_sm_count();
+  return n < 0 ? n : 2 * n;   // two epilogue groups per CTA, each flushes its own row
+}
 
 namespace uz {
 static int env_int(const char* name, int dflt) {
@@ -462,13 +472,13 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const bool pair_auto = p.b_items >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
   p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 ? 1 : 0;
   int b_item = bn * 128 / (p.pair ? 2 : 1);     // bytes of one weight tile per CTA
-  const int kTail = 1536;              // barriers (512) + bias vector (1024)
+  const int kTail = 2560;              // barriers (512) + one bias vector per epilogue group (2 x 1024)
   const long long b_all = (long long)p.b_items * b_item;
   int cluster = p.pair ? 2 : 1;
   bool stationary = false;
   if (p.num_n_tiles == 1 && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
     // weights resident for the whole launch, provided at least four halo stages still fit (TMA latency cover)
-    for (int nbuf = 2; nbuf >= 1 && !stationary; --nbuf) {
+    for (int nbuf = 2; nbuf >= 2 && !stationary; --nbuf) {   // one staging tile per epilogue group
       const long long left = (long long)kMaxSmem - kTail - nbuf * 16384 - b_all;
       if (left >= (long long)env_int("UZ_FWD2_MIN_A", 2) * a_slot) {
         stationary = true;
@@ -500,7 +510,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
       if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
       if (bn / cluster < 16) cluster = 1;
     }
-    p.stg_bufs = bn == 256 ? 1 : 2;
+    p.stg_bufs = 2;                      // one staging tile per epilogue group
     p.a_stages = env_int("UZ_FWD2_A_STAGES", p.mp == 2 ? (a_slot > 40000 ? 2 : 3) : bn == 256 ? 2 : bn == 128 ? 3 : 4);
     if (p.a_stages < 1 || p.a_stages > 6) p.a_stages = 2;
     int bs = (kMaxSmem - kTail - p.stg_bufs * 16384 - p.a_stages * a_slot) / b_item;
@@ -508,8 +518,10 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     if (p.b_stages < 2) return 0;
   }
   p.cluster = cluster;
+  p.n_minor = (convt && env_int("UZ_FWD2_N_MINOR", 1)) ? 1 : 0;
   p.m_tiles = ((p.m_tiles_real + p.mp - 1) / p.mp + cluster - 1) / cluster * cluster;
   p.total_tiles = p.m_tiles * p.num_n_tiles;
+  p.ragged = ((H % 16) != 0 || (W % 8) != 0 || p.m_tiles * p.mp != p.m_tiles_real) ? 1 : 0;
   p.a_off = 0;
   p.b_off = p.a_stages * a_slot;
   const long long b_bytes = p.b_stages ? (long long)p.b_stages * b_item : b_all;
@@ -608,7 +620,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 
   if (flags & UZ_FLAG_STATS) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * sms, st);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * uz_conv_stats_rows(), st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
   if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2) {

@@ -134,6 +134,13 @@ struct alignas(64) Igemm2Params {
                                // streamed-weight layers were capped at ~72 % tensor-active by SM ingest (~50 B/clk)
   int nt_per_phase;            // 0: N tiles walk the output columns.  > 0 (ConvTranspose2d k2s2 as four 1x1 GEMMs): N tile
                                // = (phase, column tile); the phase selects the weight "tap" coordinate and the output view
+  int ragged;                  // 1: some tile is partial (H % 16, W % 8) or a dummy (M tiles rounded up to the work-item
+                               // size).  0: every tile is full - the epilogue threads then skip the tile decode (five
+                               // integer divisions per tile; ncu showed the epilogue of the 64-channel 512^2 layers
+                               // instruction-bound with ~30 % of its instructions in division sequences)
+  int n_minor;                 // 1: consecutive work items walk the N tiles of ONE pixel tile (transposed conv: the four
+                               // output phases re-read the same input tile - adjacent CTAs then share it through L2
+                               // instead of streaming the input four times from HBM); 0: all pixel tiles of an N tile first
   int ncols;                   // valid output columns (Cout)
   const float* bias;
   float* stats;                // [8*gridDim.x][2][ncols] partial sums (kFlagStats), zeroed by the host

@@ -11,7 +11,7 @@
 //     accumulates), and takes the BatchNorm column sums from the staged bf16 tile (conflict-free column reads).
 //
 // Warp roles (384 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2 = B producer, 3 = idle,
-// 4..11 = epilogue (two warps per TMEM lane quarter, each owning 32 of the 64 columns of a chunk).
+// 4..11 = epilogue: two groups of four warps (one per TMEM lane quarter), the groups take alternate tiles.
 #include <string.h>
 
 #include "host_util.h"
@@ -45,10 +45,23 @@ struct F2Tile {
   int n_tile, n, x0, y0;
   bool dummy;
 };
+// work item -> (N tile, first pixel tile).  n_minor: items of one cluster-sized group of pixel tiles are adjacent
+// (group-major, N tile, rank) so that the CTAs of a cluster / pair still share their N tile.
+__device__ __forceinline__ void f2_item(const Igemm2Params& p, int tile, int* n_tile, int* m_item) {
+  if (p.n_minor) {
+    const int grp = tile / p.cluster, r = tile - grp * p.cluster;
+    *n_tile = grp % p.num_n_tiles;
+    *m_item = (grp / p.num_n_tiles) * p.cluster + r;
+  } else {
+    *n_tile = tile / p.m_tiles;
+    *m_item = tile - *n_tile * p.m_tiles;
+  }
+}
 __device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile, int sub = 0) {
   F2Tile t;
-  t.n_tile = tile / p.m_tiles;
-  const int m = (tile - t.n_tile * p.m_tiles) * p.mp + sub;
+  int m_item;
+  f2_item(p, tile, &t.n_tile, &m_item);
+  const int m = m_item * p.mp + sub;
   t.dummy = m >= p.m_tiles_real;
   const int xb = m % p.xb;
   const int r = m / p.xb;
@@ -106,7 +119,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     }
     for (int s = 0; s < kAcc; ++s) {
       mbar_init(tfull(s), 1);
-      mbar_init(tempty(s), 8 * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
+      mbar_init(tempty(s), 4 * CG);   // one epilogue group (four warps) drains a tile; pair: the leader's barrier
+                                      // collects both CTAs' groups
     }
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
@@ -187,7 +201,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         uint32_t phase = 0;
         const int rows = BN / cs;
         for (int g = cidx; g < ngroups; g += nclusters) {
-          const int n_tile = (g * cs) / p.m_tiles;
+          int n_tile, m_unused;
+          f2_item(p, g * cs, &n_tile, &m_unused);
           const int b_phase = p.nt_per_phase ? n_tile / p.nt_per_phase : -1;
           const int b_row0 = (p.nt_per_phase ? n_tile % p.nt_per_phase : n_tile) * BN;
           for (int seg = 0; seg < p.num_segs; ++seg) {
@@ -306,123 +321,143 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       }
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue warps (4..11)
+    // ------------------------------------------------------------------ epilogue warps (4..11): TWO groups of four
+    // Group g (warps 4+4g .. 7+4g, one per TMEM lane quarter) drains the CTA's tiles with local index parity g, so two
+    // tiles are in flight: ncu showed the single 8-warp epilogue latency-bound (IPC 1.7 of 4, 17 % of the samples in the
+    // 256-thread barrier) and the 64-channel 512^2 layers capped by it at half of the HBM roof.  Each group owns one
+    // staging tile, one bias vector, one named barrier and one row of statistics partials.
     const int ew = warp - 4;           // 0..7
-    const int q = warp & 3;            // TMEM lane quarter of this warp
-    const int hcol = ew >> 2;          // which 32-column half of a 64-column chunk this warp converts
-    const int et = threadIdx.x - 128;  // 0..255
+    const int grp = ew >> 2;           // epilogue group
+    const int gw = ew & 3;             // warp inside the group
+    const int q = warp & 3;            // TMEM lane quarter of this warp (== gw)
+    const int gt = threadIdx.x - 128 - grp * 128;   // 0..127 inside the group
     const int row = q * 32 + lane;     // accumulator row = pixel (y = row >> 3, x = row & 7) of the tile
     const bool do_stats = (p.flags & kFlagStats) != 0;
     const bool do_relu = (p.flags & kFlagRelu) != 0;
     const bool do_acc = (p.flags & kFlagAccumulate) != 0;
-    const int nbuf = p.stg_bufs;
-    const uint32_t bias_s = bars + 512u;  // BN floats (zero beyond ncols / without bias)
+    const uint32_t sbuf = stg_base + grp * kF2StgBytes;
+    const uint32_t bias_s = bars + 512u + grp * (BN * 4);  // BN floats (zero beyond ncols / without bias)
     constexpr int kChunks = BN / 64;
     float run_s[kChunks][2], run_q[kChunks][2];
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) run_s[c][0] = run_s[c][1] = run_q[c][0] = run_q[c][1] = 0.f;
-    int run_ntile = -1;
-    // column-sum reads: this warp sums rows [ew*16, ew*16+16) of the staged chunk, lane owns columns 2*lane, 2*lane+1
+    int run_ntile = -1, run_row0 = -1;
+    auto gbar = [&]() {
+      if (grp == 0)
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      else
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+    };
+    // column-sum reads: this warp sums rows [gw*32, gw*32+32) of the staged chunk, lane owns columns 2*lane, 2*lane+1
     uint32_t st_off[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) st_off[j] = ((((lane >> 2) ^ j) << 4) + (lane & 3) * 4) + (ew * 16 + j) * 128;
-    // One row of partials per CTA: the eight epilogue warps (16 tile rows each, all columns) are summed through the (idle)
-    // first staging tile before the flush - rare (n-tile change / end of kernel), deterministic order.
-    auto flush_stats = [&]() {   // called by all 256 epilogue threads
+    for (int j = 0; j < 8; ++j) st_off[j] = ((((lane >> 2) ^ j) << 4) + (lane & 3) * 4) + (gw * 32 + j) * 128;
+    // One row of partials per (CTA, group): the four warps (32 tile rows each, all columns) are summed through the
+    // group's (idle) staging tile before the flush - rare (n-tile change / end of kernel), deterministic order.
+    auto flush_stats = [&]() {   // called by all 128 threads of the group
       if (run_ntile < 0) return;
-      if (et == 0) tma_store_wait_read0();   // a TMA store may still be reading the staging tile
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (gt == 0) tma_store_wait_read0();   // a TMA store may still be reading the staging tile
+      gbar();
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int col = c * 64 + 2 * lane + h;   // each warp holds all columns of its 16 tile rows
-          st_shared_f32(stg_base + ((ew * 2 + 0) * BN + col) * 4, run_s[c][h]);
-          st_shared_f32(stg_base + ((ew * 2 + 1) * BN + col) * 4, run_q[c][h]);
+          const int col = c * 64 + 2 * lane + h;   // each warp holds all columns of its 32 tile rows
+          st_shared_f32(sbuf + ((gw * 2 + 0) * BN + col) * 4, run_s[c][h]);
+          st_shared_f32(sbuf + ((gw * 2 + 1) * BN + col) * 4, run_q[c][h]);
           run_s[c][h] = run_q[c][h] = 0.f;
         }
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      float* dst = p.stats + static_cast<size_t>(blockIdx.x) * 2 * p.ncols;
-      for (int i = et; i < 2 * BN; i += 256) {
+      gbar();
+      float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 2 + grp) * 2 * p.ncols;
+      for (int i = gt; i < 2 * BN; i += 128) {
         const int which = i / BN, c = i - which * BN;
         const int col = run_ntile * BN + c;
         if (col < p.ncols) {
           float v = 0.f;
 #pragma unroll
-          for (int w8 = 0; w8 < 8; ++w8) v += __uint_as_float(ld_shared_u32(stg_base + ((w8 * 2 + which) * BN + c) * 4));
+          for (int w4 = 0; w4 < 4; ++w4) v += __uint_as_float(ld_shared_u32(sbuf + ((w4 * 2 + which) * BN + c) * 4));
           dst[which * p.ncols + col] += v;
         }
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");   // the staging tile is free for the next chunk
+      gbar();   // the staging tile is free for the next chunk
     };
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    uint32_t it = 0;  // staging buffer toggle
-    for (int g = cidx; g < ngroups; g += nclusters) {
-      const int item_ntile = (g * cs + rank) / p.m_tiles;
+    int lt = 0;   // local tile counter of this CTA (both groups count every tile)
+    for (int g = cidx; g < ngroups; g += nclusters, ++lt) {
+      if ((lt & 1) != grp) continue;
+      const int acc = lt % kAcc;
+      const uint32_t acc_phase = static_cast<uint32_t>(lt / kAcc) & 1u;
+      int item_ntile = 0, m_unused;
+      if (p.num_n_tiles > 1) f2_item(p, g * cs + rank, &item_ntile, &m_unused);
       const int o_phase = p.nt_per_phase ? item_ntile / p.nt_per_phase : 0;
       const int row0 = (p.nt_per_phase ? item_ntile % p.nt_per_phase : item_ntile) * BN;   // first output column of the tile
       if (item_ntile != run_ntile) {
         if (do_stats) flush_stats();
         run_ntile = item_ntile;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (et < BN) {
-          const int col = row0 + et;
-          st_shared_f32(bias_s + et * 4, (p.bias != nullptr && col < p.ncols) ? __ldg(p.bias + col) : 0.f);
+      }
+      if (row0 != run_row0) {   // the bias vector depends on the column range only (not on the output phase)
+        run_row0 = row0;
+        gbar();
+        for (int c = gt; c < BN; c += 128) {
+          const int col = row0 + c;
+          st_shared_f32(bias_s + c * 4, (p.bias != nullptr && col < p.ncols) ? __ldg(p.bias + col) : 0.f);
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        gbar();
       }
       mbar_wait(tfull(acc), acc_phase);
       tc_fence_after();
 #pragma unroll 1
       for (int sub = 0; sub < MP; ++sub) {
-      const F2Tile t = f2_decode(p, g * cs + rank, sub);
-      const bool tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
-      const bool valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
-      const uint32_t t_addr =
-          tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (MP * BN) + sub * BN + hcol * 32;
+      // only the thread that issues the TMA store needs the tile coordinates when every tile is full
+      F2Tile t;
+      t.n = t.x0 = t.y0 = 0;
+      bool tile_full = true, valid = true;
+      if (p.ragged || gt == 0) {
+        t = f2_decode(p, g * cs + rank, sub);
+        tile_full = !t.dummy && (t.x0 + 8 <= p.W) && (t.y0 + 16 <= p.H);
+        valid = !t.dummy && (t.x0 + (row & 7) < p.W) && (t.y0 + (row >> 3) < p.H);
+      }
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (MP * BN) + sub * BN;
 #pragma unroll 1
       for (int ch = 0; ch < kChunks; ++ch) {
         const int col0 = row0 + ch * 64;
         if (col0 >= p.ncols) break;  // uniform over the CTA
-        const uint32_t sbuf = stg_base + (nbuf == 2 ? (it & 1u) * kF2StgBytes : 0u);
-        ++it;
-        uint32_t v[32];
-        tmem_ld32(t_addr + ch * 64, v);
-        if (nbuf == 1) {
-          if (et == 0) tma_store_wait_read0();  // the single staging tile is free again
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-        }
+        uint32_t v[2][32];
+        tmem_ld32(t_addr + ch * 64, v[0]);
+        tmem_ld32(t_addr + ch * 64 + 32, v[1]);
+        if (gt == 0) tma_store_wait_read0();  // the group's staging tile is free again
+        gbar();                               // (also: every thread has finished the column sums of the previous chunk)
         tmem_ld_wait();
-        float f[32];
 #pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 b4 = ld_shared_f4(bias_s + (ch * 64 + hcol * 32 + j4 * 4) * 4);
-          f[j4 * 4 + 0] = __uint_as_float(v[j4 * 4 + 0]) + b4.x;
-          f[j4 * 4 + 1] = __uint_as_float(v[j4 * 4 + 1]) + b4.y;
-          f[j4 * 4 + 2] = __uint_as_float(v[j4 * 4 + 2]) + b4.z;
-          f[j4 * 4 + 3] = __uint_as_float(v[j4 * 4 + 3]) + b4.w;
-        }
-        if (do_relu) {
+        for (int hcol = 0; hcol < 2; ++hcol) {
+          float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (!tile_full && !valid) {
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = ld_shared_f4(bias_s + (ch * 64 + hcol * 32 + j4 * 4) * 4);
+            f[j4 * 4 + 0] = __uint_as_float(v[hcol][j4 * 4 + 0]) + b4.x;
+            f[j4 * 4 + 1] = __uint_as_float(v[hcol][j4 * 4 + 1]) + b4.y;
+            f[j4 * 4 + 2] = __uint_as_float(v[hcol][j4 * 4 + 2]) + b4.z;
+            f[j4 * 4 + 3] = __uint_as_float(v[hcol][j4 * 4 + 3]) + b4.w;
+          }
+          if (do_relu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = 0.f;  // keeps out-of-image rows out of the column sums
-        }
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          if (!tile_full && !valid) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int chunk16 = hcol * 4 + c;  // 16-byte chunk index inside the 128-byte row
-          st_shared_v4(sbuf + row * 128 + ((chunk16 ^ (row & 7)) << 4), pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]),
-                       pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]), pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]),
-                       pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]));
+            for (int j = 0; j < 32; ++j) f[j] = 0.f;  // keeps out-of-image rows out of the column sums
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int chunk16 = hcol * 4 + c;  // 16-byte chunk index inside the 128-byte row
+            st_shared_v4(sbuf + row * 128 + ((chunk16 ^ (row & 7)) << 4), pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]),
+                         pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]), pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]),
+                         pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]));
+          }
         }
         fence_proxy_async_smem();
-        if (nbuf == 2 && et == 0) tma_store_wait_read0();  // the previous store has left the other buffer
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (et == 0) {
+        gbar();
+        if (gt == 0) {
           if (do_acc)
             tma_reduce_add_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
           else
@@ -432,7 +467,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         if (do_stats) {
           float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-          for (int rr = 0; rr < 16; ++rr) {
+          for (int rr = 0; rr < 32; ++rr) {
             const uint32_t w = ld_shared_u32(sbuf + st_off[rr & 7] + (rr >> 3) * 1024);
             const float lo = bf16_lo(w), hi = bf16_hi(w);
             s0 += lo;
@@ -455,13 +490,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         else
           mbar_arrive(tempty(acc));
       }
-      if (++acc == kAcc) {
-        acc = 0;
-        acc_phase ^= 1u;
-      }
     }
     if (do_stats) flush_stats();
-    if (et == 0) tma_store_wait_all();
+    if (gt == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
