@@ -94,3 +94,55 @@ def test_checkpoint_manager_roundtrip_and_module_prefix(tmp_path, capsys):
     assert "not found" in capsys.readouterr().out
     wrapped = nn.DataParallel(fresh) if False else fresh
     assert mgr.get_model_for_inference(wrapped, "cpu").training is False
+
+
+def test_train_model_epoch_driver_and_checkpoints(tmp_path):
+    """train_model (training_loop.py:182-285): same return tuple, last checkpoint every epoch, best checkpoint on
+    improvement (the reference never writes it), injected early stopping / scheduler objects with the reference's call
+    shapes are honoured."""
+    class Cfg:
+        EPOCHS, DEVICE = 4, torch.device("cpu")
+
+    class Stop:                                              # early_stopping.py call shape
+        def __init__(self):
+            self.calls, self.early_stop = [], False
+
+        def __call__(self, score, model, epoch):
+            self.calls.append((round(score, 6), epoch))
+            self.early_stop = epoch >= 3
+
+        def get_best_score(self):
+            return max(c[0] for c in self.calls)
+
+    class Sched:                                             # lr_scheduler.py call shape
+        def __init__(self, opt):
+            self.opt, self.calls = opt, []
+
+        def step(self, score, epoch):
+            self.calls.append(epoch)
+            self.opt.param_groups[0]["lr"] *= 0.5
+
+    torch.manual_seed(0)
+    model = _Tiny()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=1e-5)
+    stop, sched = Stop(), Sched(opt)
+    best, last = str(tmp_path / "best.pth"), str(tmp_path / "last.pth")
+    mgr = T.MultiGPUManager(device="cpu")
+    out = T.train_model(model, _batches(3), _batches(2, seed=1), opt, nn.BCEWithLogitsLoss(), Cfg, "tiny", best, last,
+                        logger=None, gpu_manager=mgr, early_stopping=stop, lr_scheduler=sched)
+    tl, td, vl, vd, early = out
+    assert early and len(tl) == len(td) == len(vl) == len(vd) == 3       # stopped by the injected object at epoch 3
+    assert sched.calls == [1, 2, 3] and abs(opt.param_groups[0]["lr"] - 1e-2 / 8) < 1e-12
+    assert [c[1] for c in stop.calls] == [1, 2, 3] and abs(stop.calls[-1][0] - round(vd[-1], 6)) < 1e-6
+    sd_last, sd_best = torch.load(last), torch.load(best)
+    assert set(sd_last) == set(model.state_dict()) == set(sd_best)
+    for k, v in model.state_dict().items():
+        assert torch.equal(sd_last[k], v)                                # last = the final weights
+    fresh = _Tiny()
+    mgr.load_model_state(fresh, best)
+    assert abs(T.validate_one_epoch(fresh, _batches(2, seed=1), nn.BCEWithLogitsLoss(), torch.device("cpu"))[1] - max(vd)) < 1e-6
+
+
+def test_init_distributed_single_process():
+    rank, world, device = T.init_distributed()
+    assert (rank, world) == (0, 1) and device.type in ("cpu", "cuda")

@@ -135,6 +135,87 @@ def validate_one_epoch(model: nn.Module, dataloader, criterion, device, model_na
     return float(run_loss) / n, float(run_dc) / n
 
 
+def init_distributed(backend: Optional[str] = None) -> Tuple[int, int, torch.device]:
+    """One process per GPU under ``torchrun`` (replaces the reference's single-process ``nn.DataParallel`` setup,
+    multi_gpu.py:20-37 / scripts/train.py:60-75): reads RANK / WORLD_SIZE / LOCAL_RANK, binds the process to its GPU and
+    brings up the process group.  Returns (rank, world size, device); a plain ``python`` launch gives (0, 1, cuda:0)."""
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local)
+        device = torch.device("cuda", local)
+    else:
+        device = torch.device("cpu")
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        # the step graph captures the bucketed NCCL all-reduces (train_step.GraphedTrainStep(capture_nccl=True))
+        os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
+        backend = backend or ("nccl" if device.type == "cuda" else "gloo")
+        if backend == "nccl":
+            dist.init_process_group(backend, device_id=device)
+        else:
+            dist.init_process_group(backend)
+    return rank, world, device
+
+
+def train_model(model: nn.Module, train_dataloader, val_dataloader, optimizer, criterion, config, model_name: str,
+                best_checkpoint_path: str, last_checkpoint_path: str, logger=None, gpu_manager=None, writer=None,
+                early_stopping=None, lr_scheduler=None):
+    """The reference's epoch driver (training_loop.py:182-285) on the drop-in loops above: per epoch
+    ``train_one_epoch -> validate_one_epoch -> scheduler / early stopping -> save last checkpoint`` and the same return
+    value ``(train_losses, train_dcs, val_losses, val_dcs, early_stopped)``.
+
+    ``config`` needs ``EPOCHS`` and ``DEVICE``.  The reference builds its ``EarlyStopping``, ``DiceScheduler`` and
+    TensorBoard ``SummaryWriter`` inside this function (:204-224); they are not part of the hot path, so here they are
+    optional injected objects with the reference's call shapes (``early_stopping(val_dc, model, epoch)`` /
+    ``.early_stop`` / ``.get_best_score()``, ``lr_scheduler.step(val_dc, epoch)``, ``writer.add_scalar(tag, v, step)``)
+    - pass the reference's own instances, or nothing.  One fix over the reference: the BEST checkpoint is written
+    whenever the validation Dice improves (the reference computes ``best_checkpoint_path`` but never writes it,
+    training_loop.py:252 vs scripts/train_all.py:125)."""
+    gpu_manager = gpu_manager or MultiGPUManager(config)
+    device = getattr(config, "DEVICE", None) or next(model.parameters()).device
+    epochs = int(getattr(config, "EPOCHS"))
+    log = (lambda m: logger.log_both(m)) if logger is not None and hasattr(logger, "log_both") else (lambda m: None)
+    train_losses, train_dcs, val_losses, val_dcs = [], [], [], []
+    early_stopped, best = False, float("-inf")
+    log(f"\nStarting training for {model_name} - {epochs} epochs on {device}")
+    for epoch in range(epochs):
+        sampler = getattr(train_dataloader, "sampler", None)
+        if hasattr(sampler, "set_epoch"):                       # DistributedSampler: reshuffle per epoch
+            sampler.set_epoch(epoch)
+        tl, td = train_one_epoch(model, train_dataloader, optimizer, criterion, device, writer, epoch, model_name, logger)
+        vl, vd = validate_one_epoch(model, val_dataloader, criterion, device, model_name, logger)
+        train_losses.append(tl)
+        train_dcs.append(td)
+        val_losses.append(vl)
+        val_dcs.append(vd)
+        if lr_scheduler is not None:
+            lr_scheduler.step(vd, epoch + 1)
+            if hasattr(optimizer, "sync_hyper"):               # FlatAdamW keeps its hyper-parameters on the device
+                optimizer.sync_hyper()
+        if early_stopping is not None:
+            early_stopping(vd, model, epoch + 1)
+        gpu_manager.save_model_state(model, last_checkpoint_path)
+        if vd > best:
+            best = vd
+            gpu_manager.save_model_state(model, best_checkpoint_path)
+        if writer is not None:
+            for tag, v in (("Train_Loss", tl), ("Train_Dice", td), ("Val_Loss", vl), ("Val_Dice", vd)):
+                writer.add_scalar(f"Epoch/{model_name}_{tag}", v, epoch + 1)
+            writer.add_scalar(f"{model_name}_Learning_Rate", optimizer.param_groups[0]["lr"], epoch + 1)
+        log(f"{'-' * 60}\n{model_name} - Epoch {epoch + 1}/{epochs}\n  Train Loss: {tl:.6f} | Train DICE: {td:.6f}"
+            f"\n  Val Loss:   {vl:.6f} | Val DICE:   {vd:.6f}\n  Learning Rate: {optimizer.param_groups[0]['lr']:.8f}"
+            f"\n  Best Val Dice: {best:.6f}\n{'-' * 60}")
+        if early_stopping is not None and getattr(early_stopping, "early_stop", False):
+            log(f"\nEarly stopping triggered for {model_name} at epoch {epoch + 1}")
+            early_stopped = True
+            break
+    log(f"Training {'stopped early' if early_stopped else 'completed'} for {model_name} after {len(train_losses)} epochs")
+    return train_losses, train_dcs, val_losses, val_dcs, early_stopped
+
+
 class MultiGPUManager:
     """multi_gpu.py:8-97 for one process per GPU.  ``config`` needs ``DEVICE`` only; when ``torch.distributed`` is
     initialised with more than one rank the model is wrapped in the bucketed-all-reduce data-parallel wrapper."""
