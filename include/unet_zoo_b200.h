@@ -149,6 +149,13 @@ int uz_gate_bwd(const void* x, int x_ld, const void* dout, int dout_ld, const fl
  *  fwd: x [N,H,W,C] -> out [N,2H,2W,C] written at (out, out_ld) - typically a channel slice of a concat buffer.
  *  bwd: dx [N,H,W,C] (+)= gather of dout [N,2H,2W,C]; H, W are the LOW-resolution sizes in both calls. */
 int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);
+/* F.pad with zeros on the bottom / right, or its backward (crop), between two NHWC pixel grids: replaces the
+ * `F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])` of common_layers.py:110-113 / :173-178 (dx, dy in {0, 1} for
+ * the odd input sizes the reference accepts).  dst[n,y,x,:] = (y < Hs && x < Ws) ? src[n,y,x,:] : 0 over (Hd, Wd);
+ * `row_bytes` bytes per pixel are moved (multiple of 16), pixel strides in bytes - bf16 and fp32 tensors alike. */
+int uz_pad_copy(const void* src, long long src_pixel_bytes, int Hs, int Ws, void* dst, long long dst_pixel_bytes, int Hd,
+                int Wd, int N, int row_bytes, void* stream);
+
 /* nn.Upsample(scale_factor=2) (nearest, common_layers.py:70) materialised: out [N,2H,2W,C] = x[n, y>>1, x>>1, :].
  * Used only for the weight gradient of UpConvBlock's convolution (3x3 wgrad kernel on the upsampled operand). */
 int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);

@@ -88,7 +88,9 @@ def test_train_step_edge_shapes_match_oracle(name, kw, shape):
 def test_bad_inputs_raise_like_the_contract_says():
     model = seeded_model("unet").cuda()
     with pytest.raises(RuntimeError):
-        model(torch.randn(1, 3, 40, 40, device="cuda"))            # H, W must be multiples of 16
+        model(torch.randn(1, 3, 8, 40, device="cuda"))             # four poolings need H, W >= 16
+    with pytest.raises(RuntimeError, match="multiples of 16"):      # the reference's attention_unet fails here too
+        seeded_model("attention_unet").cuda()(torch.randn(1, 3, 40, 40, device="cuda"))
     with pytest.raises(RuntimeError):
         model(torch.randn(1, 4, 32, 32, device="cuda"))            # wrong channel count
     with pytest.raises(RuntimeError):

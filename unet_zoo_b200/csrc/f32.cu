@@ -260,7 +260,9 @@ __global__ void f32_affine_act_kernel(const float* __restrict__ z, int z_ld, int
                                       const float* __restrict__ scale, const float* __restrict__ shift, int relu,
                                       const float* __restrict__ res, int res_ld, float* __restrict__ y, int y_ld,
                                       float* __restrict__ pooled, int pooled_ld) {
-  const int Hi = POOL ? H / 2 : H, Wi = POOL ? W / 2 : W;
+  // POOL: quads incl. the partial ones of an odd last row / column (written to y, part of no pooling window)
+  const int Hi = POOL ? (H + 1) / 2 : H, Wi = POOL ? (W + 1) / 2 : W;
+  const int Hp = H / 2, Wp = W / 2;
   const long long total = static_cast<long long>(N) * Hi * Wi * C;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -279,12 +281,13 @@ __global__ void f32_affine_act_kernel(const float* __restrict__ z, int z_ld, int
       float m = 0.f;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
+        if (2 * py + (k >> 1) >= H || 2 * px + (k & 1) >= W) continue;
         const long long q = (n * H + 2 * py + (k >> 1)) * W + 2 * px + (k & 1);
         const float v = f32_act(__ldg(z + q * z_ld + c), sc, sh, 0.f, relu);
         if (y) y[q * y_ld + c] = v;
         m = (k == 0 || v > m) ? v : m;
       }
-      pooled[p * pooled_ld + c] = m;
+      if (py < Hp && px < Wp) pooled[((n * Hp + py) * Wp + px) * pooled_ld + c] = m;
     }
   }
 }
@@ -458,9 +461,9 @@ extern "C" int uz_f32_affine_act(const float* z, int z_ld, int N, int H, int W, 
     return set_error(UZ_ERR_INVALID, "f32_affine_act: scale/shift must both be given");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (pooled) {
-    if ((H & 1) || (W & 1)) return set_error(UZ_ERR_INVALID, "f32_affine_act: pooling needs even H, W");
+    if (H < 2 || W < 2) return set_error(UZ_ERR_INVALID, "f32_affine_act: pooling needs H, W >= 2");
     if (residual) return set_error(UZ_ERR_UNSUPPORTED, "f32_affine_act: residual + pool not supported");
-    const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * C;
+    const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * C;
     f32_affine_act_kernel<true><<<ew_grid(total), 256, 0, st>>>(z, z_ld, N, H, W, C, scale, shift, relu, nullptr, 0, y,
                                                                 y_ld, pooled, pooled_ld);
   } else {

@@ -331,7 +331,10 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, i
       sh[j] = 0.f;
     }
   }
-  const int Hq = POOL ? H / 2 : H, Wq = POOL ? W / 2 : W;
+  // POOL: items are 2x2 quads INCLUDING the partial ones of an odd last row / column (MaxPool2d(2,2) floors: those
+  // pixels get their activation but belong to no pooling window - common_layers.py:94 on odd sizes)
+  const int Hq = POOL ? (H + 1) / 2 : H, Wq = POOL ? (W + 1) / 2 : W;
+  const int Hp = H / 2, Wp = W / 2;   // pooled extent
   const long long items = static_cast<long long>(N) * Hq * Wq;
   for (long long it = static_cast<long long>(blockIdx.x) * ppb + pl; it < items;
        it += static_cast<long long>(gridDim.x) * ppb * (POOL ? 1 : kApplyUnroll)) {
@@ -376,9 +379,11 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, i
       const int n = static_cast<int>(r0 / Hq);
       const long long p00 = (static_cast<long long>(n) * H + 2 * qy) * W + 2 * qx;
       const long long pix[4] = {p00, p00 + 1, p00 + W, p00 + W + 1};
+      const bool full = qy < Hp && qx < Wp;
+      const bool ok[4] = {true, 2 * qx + 1 < W, 2 * qy + 1 < H, full};
       uint4 raw[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) raw[i] = ldg16(z + pix[i] * z_ld + g * 8);
+      for (int i = 0; i < 4; ++i) raw[i] = ok[i] ? ldg16(z + pix[i] * z_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
       float m[8];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -390,12 +395,13 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ z, int z_ld, i
           if (relu) f[j] = fmaxf(f[j], 0.f);
         }
         const uint4 o = pack8(f);
-        if (y) *reinterpret_cast<uint4*>(y + pix[i] * y_ld + g * 8) = o;
+        if (y && ok[i]) *reinterpret_cast<uint4*>(y + pix[i] * y_ld + g * 8) = o;
         unpack8(o, f);  // pool the values as stored
 #pragma unroll
         for (int j = 0; j < 8; ++j) m[j] = i == 0 ? f[j] : fmaxf(m[j], f[j]);
       }
-      *reinterpret_cast<uint4*>(pooled + it * pooled_ld + g * 8) = pack8(m);
+      if (full)
+        *reinterpret_cast<uint4*>(pooled + ((static_cast<long long>(n) * Hp + qy) * Wp + qx) * pooled_ld + g * 8) = pack8(m);
     }
   }
 }
@@ -416,111 +422,38 @@ struct BwdArgs {
   int relu;
 };
 
-template <bool POOL>
-__device__ __forceinline__ void bwd_item_grad(const BwdArgs& a, long long it, int g, const float (&sc)[8],
-                                              const float (&sh)[8], float (&zv)[POOL ? 4 : 1][8],
-                                              float (&gv)[POOL ? 4 : 1][8], long long (&pix)[POOL ? 4 : 1]) {
-  if (!POOL) {
-    pix[0] = it;
-    unpack8(ldg16(a.z + it * a.z_ld + g * 8), zv[0]);
-    if (a.dy) {
-      unpack8(ldg16(a.dy + it * a.dy_ld + g * 8), gv[0]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) gv[0][j] = 0.f;
-    }
-    if (a.relu) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (!(fmaf(zv[0][j], sc[j], sh[j]) > 0.f)) gv[0][j] = 0.f;
-    }
-  } else {
-    const int Hq = a.H / 2, Wq = a.W / 2;
-    const int qx = static_cast<int>(it % Wq);
-    const long long r0 = it / Wq;
-    const int qy = static_cast<int>(r0 % Hq);
-    const int n = static_cast<int>(r0 / Hq);
-    const long long p00 = (static_cast<long long>(n) * a.H + 2 * qy) * a.W + 2 * qx;
-    pix[0] = p00;
-    pix[1] = p00 + 1;
-    pix[2] = p00 + a.W;
-    pix[3] = p00 + a.W + 1;
-    uint4 zr[4], dr[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) zr[i] = ldg16(a.z + pix[i] * a.z_ld + g * 8);
-    if (a.dy) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) dr[i] = ldg16(a.dy + pix[i] * a.dy_ld + g * 8);
-    }
-    float dp[8];
-    if (a.dpool) {
-      unpack8(ldg16(a.dpool + it * a.dpool_ld + g * 8), dp);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) dp[j] = 0.f;
-    }
-    float yv[4][8];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      unpack8(zr[i], zv[i]);
-      if (a.dy) {
-        unpack8(dr[i], gv[i]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) gv[i][j] = 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float u = fmaf(zv[i][j], sc[j], sh[j]);
-        if (a.relu) u = fmaxf(u, 0.f);
-        yv[i][j] = bf16_round(u);  // the forward pooled the stored (bf16) activations
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      // first maximum in row-major window order wins (nn.MaxPool2d index semantics)
-      int am = 0;
-      float mv = yv[0][j];
-#pragma unroll
-      for (int i = 1; i < 4; ++i)
-        if (yv[i][j] > mv) {
-          mv = yv[i][j];
-          am = i;
-        }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        if (i == am) gv[i][j] += dp[j];
-        if (a.relu && !(yv[i][j] > 0.f)) gv[i][j] = 0.f;
-      }
-    }
-  }
-}
-
 // Pooled path, register-lean form: the nine 16-byte words of one 2x2 quad (4 z, 4 dy, 1 dpool) stay raw; the gradient
 // is rebuilt two channels at a time and handed to `sink(word, pixel, z_lo, z_hi, g_lo, g_hi)`.
 struct QuadRaw {
   uint32_t z[4][4], d[4][4], dp[4];
   long long pix[4];
 };
+// Quads include the partial ones of an odd last row / column: their missing pixels read as z = dy = 0 and are marked
+// pix = -1 (never stored), and they receive no pooled gradient - MaxPool2d(2,2) floors, so those pixels are in no window.
 __device__ __forceinline__ void quad_load(const BwdArgs& a, long long it, int g, QuadRaw& r) {
-  const int Hq = a.H / 2, Wq = a.W / 2;
+  const int Hq = (a.H + 1) / 2, Wq = (a.W + 1) / 2, Hp = a.H / 2, Wp = a.W / 2;
   const int qx = static_cast<int>(it % Wq);
   const long long r0 = it / Wq;
   const int qy = static_cast<int>(r0 % Hq);
   const int n = static_cast<int>(r0 / Hq);
   const long long p00 = (static_cast<long long>(n) * a.H + 2 * qy) * a.W + 2 * qx;
+  const bool full = qy < Hp && qx < Wp;
+  const bool okx = 2 * qx + 1 < a.W, oky = 2 * qy + 1 < a.H;
   r.pix[0] = p00;
-  r.pix[1] = p00 + 1;
-  r.pix[2] = p00 + a.W;
-  r.pix[3] = p00 + a.W + 1;
+  r.pix[1] = okx ? p00 + 1 : -1;
+  r.pix[2] = oky ? p00 + a.W : -1;
+  r.pix[3] = full ? p00 + a.W + 1 : -1;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const uint4 v = ldg16(a.z + r.pix[i] * a.z_ld + g * 8);
+    const bool ok = r.pix[i] >= 0;
+    const uint4 v = ok ? ldg16(a.z + r.pix[i] * a.z_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
     r.z[i][0] = v.x; r.z[i][1] = v.y; r.z[i][2] = v.z; r.z[i][3] = v.w;
-    const uint4 d = a.dy ? ldg16(a.dy + r.pix[i] * a.dy_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+    const uint4 d = (a.dy && ok) ? ldg16(a.dy + r.pix[i] * a.dy_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
     r.d[i][0] = d.x; r.d[i][1] = d.y; r.d[i][2] = d.z; r.d[i][3] = d.w;
   }
-  const uint4 p = a.dpool ? ldg16(a.dpool + it * a.dpool_ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+  const uint4 p = (a.dpool && full)
+                      ? ldg16(a.dpool + ((static_cast<long long>(n) * Hp + qy) * Wp + qx) * a.dpool_ld + g * 8)
+                      : make_uint4(0u, 0u, 0u, 0u);
   r.dp[0] = p.x; r.dp[1] = p.y; r.dp[2] = p.z; r.dp[3] = p.w;
 }
 template <typename Sink>
@@ -592,7 +525,7 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 3) bn_bwd_reduce_kernel(const 
   float s[8], q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
+  const long long items = POOL ? static_cast<long long>(a.N) * ((a.H + 1) / 2) * ((a.W + 1) / 2)
                                : static_cast<long long>(a.N) * a.H * a.W;
   const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
   if (POOL) {
@@ -690,7 +623,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BwdArgs a, c
   load8f(a.bn + 3 * a.C + g * 8, sh);
   load8f(coef + g * 8, ca);
   load8f(coef + a.C + g * 8, cb);
-  const long long items = POOL ? static_cast<long long>(a.N) * (a.H / 2) * (a.W / 2)
+  const long long items = POOL ? static_cast<long long>(a.N) * ((a.H + 1) / 2) * ((a.W + 1) / 2)
                                : static_cast<long long>(a.N) * a.H * a.W;
   const long long stride = static_cast<long long>(gridDim.x) * a.ppb;
   auto emit = [&](long long p, const float (&zv)[8], const float (&gv)[8]) {
@@ -720,6 +653,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BwdArgs a, c
       });
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
+        if (r.pix[i] < 0) continue;     // outside the image (partial quad of an odd last row / column)
         __nv_bfloat16* dst = dz + r.pix[i] * dz_ld + g * 8;
         uint4 v = make_uint4(out[i][0], out[i][1], out[i][2], out[i][3]);
         if (dz_accumulate) {
@@ -935,9 +869,9 @@ extern "C" int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (pooled) {
     if ((rc = check_act("bn_apply(pooled)", pooled, C, pooled_ld))) return rc;
-    if ((H & 1) || (W & 1)) return set_error(UZ_ERR_INVALID, "bn_apply: pooling needs even H, W (got %dx%d)", H, W);
+    if (H < 2 || W < 2) return set_error(UZ_ERR_INVALID, "bn_apply: pooling needs H, W >= 2 (got %dx%d)", H, W);
     if (residual) return set_error(UZ_ERR_UNSUPPORTED, "bn_apply: residual + pool not supported");
-    const Geo g = make_geo(C, static_cast<long long>(N) * (H / 2) * (W / 2), 8);
+    const Geo g = make_geo(C, static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2), 8);
     bn_apply_kernel<true><<<g.grid, g.block, 0, st>>>(
         static_cast<const __nv_bfloat16*>(z), z_ld, N, H, W, C, g.cv, g.ppb, scale, shift, relu, nullptr, 0,
         static_cast<__nv_bfloat16*>(y), y_ld, static_cast<__nv_bfloat16*>(pooled), pooled_ld);
@@ -971,7 +905,7 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   if (dy && (rc = check_act("bn_bwd(dy)", dy, C, dy_ld))) return rc;
   if (dpool && (rc = check_act("bn_bwd(dpool)", dpool, C, dpool_ld))) return rc;
   if (!dy && !dpool) return set_error(UZ_ERR_INVALID, "bn_bwd: no incoming gradient");
-  if (dpool && ((H & 1) || (W & 1))) return set_error(UZ_ERR_INVALID, "bn_bwd: pooling needs even H, W");
+  if (dpool && (H < 2 || W < 2)) return set_error(UZ_ERR_INVALID, "bn_bwd: pooling needs H, W >= 2");
   if (workspace_bytes < uz_bn_bwd_workspace_bytes(C) || !a16(workspace))
     return set_error(UZ_ERR_WORKSPACE, "bn_bwd: workspace too small (%zu < %zu)", workspace_bytes,
                      uz_bn_bwd_workspace_bytes(C));
@@ -979,7 +913,8 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   const int dz_acc = (accumulate & 2) ? 1 : 0;
   accumulate &= 1;
   const bool pool = dpool != nullptr;
-  const long long items = pool ? static_cast<long long>(N) * (H / 2) * (W / 2) : static_cast<long long>(N) * H * W;
+  const long long items = pool ? static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2)
+                               : static_cast<long long>(N) * H * W;
   Geo g = make_geo(C, items, 4);
   const size_t smem = static_cast<size_t>(g.block) * 16 * sizeof(float);
   const long long need = (items + g.ppb - 1) / g.ppb;

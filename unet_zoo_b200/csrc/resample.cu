@@ -299,6 +299,49 @@ nearest2x_fwd_rows_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, 
 }
 }  // namespace uz
 
+namespace uz {
+// dst[n, y, x, :] = (y < Hs && x < Ws) ? src[n, y, x, :] : 0 over the dst extent, 16 bytes per thread
+__global__ void pad_copy_kernel(const uint8_t* __restrict__ src, long long src_px, int Hs, int Ws,
+                                uint8_t* __restrict__ dst, long long dst_px, int Hd, int Wd, int N, int vecs) {
+  const long long total = static_cast<long long>(N) * Hd * Wd * vecs;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(i % vecs);
+    long long p = i / vecs;
+    const int x = static_cast<int>(p % Wd);
+    p /= Wd;
+    const int y = static_cast<int>(p % Hd);
+    const long long n = p / Hd;
+    uint4 val = make_uint4(0u, 0u, 0u, 0u);
+    if (y < Hs && x < Ws)
+      val = __ldg(reinterpret_cast<const uint4*>(src + ((n * Hs + y) * Ws + x) * src_px) + v);
+    reinterpret_cast<uint4*>(dst + ((n * Hd + y) * Wd + x) * dst_px)[v] = val;
+  }
+}
+}  // namespace uz
+
+// F.pad (bottom / right, zeros) or crop of an NHWC tensor between two pixel grids: the reference centre-pads the
+// upsampled tensor to the skip tensor's size when H or W is odd (common_layers.py:110-113, :173-178: pad = [0, dx, 0, dy]
+// for dx, dy in {0, 1}); its backward is the crop.  Element-type agnostic: `row_bytes` bytes per pixel (multiple of
+// 16) are moved, pixel strides are given in bytes.
+extern "C" int uz_pad_copy(const void* src, long long src_pixel_bytes, int Hs, int Ws, void* dst,
+                           long long dst_pixel_bytes, int Hd, int Wd, int N, int row_bytes, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!src || !dst || N < 1 || Hs < 1 || Ws < 1 || Hd < 1 || Wd < 1)
+    return set_error(UZ_ERR_INVALID, "pad_copy: bad extents");
+  if (row_bytes < 16 || (row_bytes & 15) || (src_pixel_bytes & 15) || (dst_pixel_bytes & 15) ||
+      src_pixel_bytes < row_bytes || dst_pixel_bytes < row_bytes ||
+      (reinterpret_cast<uintptr_t>(src) & 15u) || (reinterpret_cast<uintptr_t>(dst) & 15u))
+    return set_error(UZ_ERR_INVALID, "pad_copy: rows / strides / pointers must be multiples of 16 bytes");
+  const int vecs = row_bytes / 16;
+  const long long total = static_cast<long long>(N) * Hd * Wd * vecs;
+  pad_copy_kernel<<<rs_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(src), src_pixel_bytes, Hs, Ws, static_cast<uint8_t*>(dst), dst_pixel_bytes, Hd, Wd, N,
+      vecs);
+  PW_CHECK_LAUNCH("pad_copy launch");
+  return UZ_OK;
+}
+
 extern "C" int uz_nearest2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
                                 void* stream) {
   PW_REQUIRE_DEVICE();

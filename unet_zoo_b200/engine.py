@@ -567,12 +567,40 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
             weight_gradient()
 
 
+def pad_into(ctx: Ctx, src: Act, dst: Act) -> Act:
+    """F.pad(src, [0, dx, 0, dy]) written into `dst` (a channel slice of the concat buffer) - the reference's centre
+    padding of the upsampled tensor when the skip tensor has an odd size (common_layers.py:110-113, :173-178: the pad is
+    [d // 2, d - d // 2] = [0, 1] per axis).  Backward = crop of the gradient."""
+    if src.N != dst.N or src.C != dst.C or not (0 <= dst.H - src.H <= 1 and 0 <= dst.W - src.W <= 1):
+        raise RuntimeError(f"unet_zoo_b200: cannot pad {(src.N, src.C, src.H, src.W)} into {(dst.N, dst.C, dst.H, dst.W)}")
+    es = src.buf.esize
+    L.check(ctx.lib.uz_pad_copy(src.ptr, src.ld * es, src.H, src.W, dst.ptr, dst.ld * es, dst.H, dst.W, src.N,
+                                src.C * es, ctx.stream), "uz_pad_copy")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            if not dst.has_grad():
+                raise RuntimeError("unet_zoo_b200: padded tensor has no gradient")
+            runs = src.grad_writes()
+            if any(acc for _, _, acc in runs):
+                raise NotImplementedError("pad_into: source already has a gradient")
+            L.check(c.lib.uz_pad_copy(dst.gptr(), dst.ld * 2, dst.H, dst.W, src.gptr(), src.ld * 2, src.H, src.W, src.N,
+                                      src.C * 2, c.stream), "uz_pad_copy")
+            c.launches += 1
+        ctx.tape.append(backward)
+    return dst
+
+
 def conv_transpose2x2(ctx: Ctx, x: Act, up, out: Act) -> Act:
     """ConvTranspose2d(k=2, s=2) written straight into a channel slice of the concat buffer.
 
     Reference: UpSample_UNet.up (common_layers.py:104,108) / UpsampleResUnet (common_layers.py:201-207).
     Four 1x1 GEMMs (one per output phase) with a pixel-shuffle scatter epilogue.
     """
+    if (out.H, out.W) != (2 * x.H, 2 * x.W):
+        # odd skip size: the reference pads the upsampled tensor (common_layers.py:110-113) - one extra copy on this
+        # (rare) path instead of a pitched scatter epilogue
+        return pad_into(ctx, conv_transpose2x2(ctx, x, up, ctx.new_act(x.N, 2 * x.H, 2 * x.W, up.out_channels)), out)
     if ctx.fp32:
         return _F32.conv_transpose2x2(ctx, x, up, out)
     cout = up.out_channels
@@ -796,6 +824,8 @@ def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mod
 def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:
     """nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True) written into a concat slice
     (nested_unet.py:33,81-93)."""
+    if (out.H, out.W) != (2 * x.H, 2 * x.W):     # odd skip size: Up pads the upsampled tensor (common_layers.py:173-178)
+        return pad_into(ctx, bilinear_up2x(ctx, x, ctx.new_act(x.N, 2 * x.H, 2 * x.W, x.C)), out)
     if ctx.fp32:
         return _F32.bilinear_up2x(ctx, x, out)
     L.check(ctx.lib.uz_bilinear2x_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, ctx.stream), "uz_bilinear2x_fwd")

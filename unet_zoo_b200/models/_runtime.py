@@ -56,6 +56,12 @@ class HotPathModel(nn.Module):
     """Base class: input checks, train/eval dispatch, autograd wiring.  Subclasses implement ``_graph(ctx, x)``."""
 
     _spatial_multiple = 16
+    # True: any H, W >= _spatial_multiple is accepted, as by the reference (whose Up / UpSample_UNet blocks pad the
+    # upsampled tensor to an odd skip size, common_layers.py:110-113, :173-178).  False: H and W must be multiples of
+    # _spatial_multiple - the reference's own forward raises on anything else for these models (their decoders
+    # concatenate / add tensors of 2 * floor(s / 2) and s pixels without padding: attention_unet.py:90,
+    # nested_unet.py:82, resunet.py:63).
+    _any_size = False
     # "bf16": tensor-core kernels, forward + backward (default).  "fp32": forward-only parity mode on the FFMA kernels
     # of csrc/f32.cu (BASELINE.json: fp32 logits within 1e-4 of the reference) - see set_precision().
     precision = "bf16"
@@ -107,9 +113,12 @@ class HotPathModel(nn.Module):
         if x.shape[1] != self._in_channels:
             raise RuntimeError(f"{type(self).__name__}: expected {self._in_channels} input channels, got {x.shape[1]}")
         m = self._spatial_multiple
-        if x.shape[2] % m or x.shape[3] % m or x.shape[2] < m or x.shape[3] < m:
+        if x.shape[2] < m or x.shape[3] < m:
+            raise RuntimeError(f"{type(self).__name__}: H and W must be at least {m} (got {tuple(x.shape[2:])})")
+        if not self._any_size and (x.shape[2] % m or x.shape[3] % m):
             raise RuntimeError(f"{type(self).__name__}: H and W must be multiples of {m} (got {tuple(x.shape[2:])}); "
-                               "the reference's centre-padding of odd skip sizes is not implemented")
+                               "the reference's forward fails on such sizes too (its decoder joins tensors of "
+                               "2 * floor(s / 2) and s pixels without padding)")
         if x.requires_grad:
             raise RuntimeError(f"{type(self).__name__}: gradients w.r.t. the input image are not implemented")
         return x if x.dtype == torch.uint8 else x.float().contiguous()

@@ -110,6 +110,8 @@ class ScaledDotProductAttention(nn.Module):
 
 
 class TransAttUNet(HotPathModel):
+    _any_size = True      # UpSample_UNet / Up pad the upsampled tensor to odd skip sizes
+
     def __init__(self, in_channels=3, num_classes=1, bilinear=True, **kwargs):
         super().__init__()
         if not bilinear:

@@ -11,6 +11,8 @@ from .blocks import DoubleConv, DownSample, OutConv, UpSample_UNet
 
 
 class UNet(HotPathModel):
+    _any_size = True      # UpSample_UNet / Up pad the upsampled tensor to odd skip sizes
+
     def __init__(self, in_channels: int, num_classes: int):
         super().__init__()
         self._in_channels = in_channels
