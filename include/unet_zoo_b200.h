@@ -252,6 +252,14 @@ int uz_bce_dice(const float* logits, const float* target, long long n, float gra
 int uz_adamw_flat(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, const float* hyper,
                   float* state, void* workspace, size_t workspace_bytes, void* stream);
 
+/* transforms.Resize((H, W)) on the decoded uint8 image / mask (unet_zoo/data/datasets.py:41,47 -> PIL Image.resize,
+ * BILINEAR with Pillow's support scaling), bit-exact with Pillow's ImagingResample (8-bit fixed-point, two passes).
+ * src [N][Hin][Win][C] (C <= 4) -> dst [N][Hout][Wout][C]; tmp [N][Hin][Wout][C] when both axes change.  The window
+ * and coefficient tables come from unet_zoo_b200.data.resample_coeffs (device int32 arrays). */
+int uz_resize_bilinear_u8(const uint8_t* src, int N, int Hin, int Win, int C, uint8_t* tmp, uint8_t* dst, int Hout,
+                          int Wout, const int* bounds_h, const int* kk_h, int ksize_h, const int* bounds_v,
+                          const int* kk_v, int ksize_v, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Input pipeline tail on the device (datasets.py:40-44,59; training_loop.py:109-110): the decoded bytes travel
  * (3 + 1 bytes per pixel instead of 12 + 4) and the device normalises.

@@ -125,6 +125,63 @@ __global__ void mask_u8_to_f32_kernel(const uint8_t* __restrict__ m, long long n
     out[i] = __fdiv_rn(static_cast<float>(__ldg(m + i)), 255.f) > 0.5f ? 1.f : 0.f;
 }
 
+
+// ---------------------------------------------------------------------------------------------- PIL-exact resize
+// Pillow's ImagingResample for 8-bit images (libImaging/Resample.c), which is what transforms.Resize((512, 512)) runs
+// on the decoded PIL image (datasets.py:41,47): a horizontal pass into a uint8 intermediate, then a vertical pass, each
+// a fixed-point convolution  out = clip8((2^21 + sum_k in[x0 + k] * kk[k]) >> 22)  with per-output-pixel windows
+// [x0, x0 + n) and integer coefficients kk (built on the host exactly as Pillow builds them, data.py).  Integer
+// arithmetic: the device result is BIT-EXACT with Pillow.
+constexpr int kResizePrecisionBits = 32 - 8 - 2;
+
+__device__ __forceinline__ uint8_t clip8(int v) {
+  v >>= kResizePrecisionBits;
+  return static_cast<uint8_t>(v < 0 ? 0 : (v > 255 ? 255 : v));
+}
+
+// horizontal: src [N][H][Win][C] -> dst [N][H][Wout][C]; one thread per output (n, y, x), all C channels (C <= 4)
+__global__ void resize_h_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, long long rows, int Win,
+                                   int Wout, int C, const int* __restrict__ bounds, const int* __restrict__ kk,
+                                   int ksize) {
+  const long long total = rows * Wout;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % Wout);
+    const long long r = i / Wout;
+    const int x0 = __ldg(bounds + 2 * x), n = __ldg(bounds + 2 * x + 1);
+    const int* k = kk + static_cast<long long>(x) * ksize;
+    int acc[4] = {1 << (kResizePrecisionBits - 1), 1 << (kResizePrecisionBits - 1), 1 << (kResizePrecisionBits - 1),
+                  1 << (kResizePrecisionBits - 1)};
+    const uint8_t* p = src + (r * Win + x0) * C;
+    for (int t = 0; t < n; ++t) {
+      const int w = __ldg(k + t);
+      for (int c = 0; c < C; ++c) acc[c] += static_cast<int>(__ldg(p + t * C + c)) * w;
+    }
+    uint8_t* o = dst + i * C;
+    for (int c = 0; c < C; ++c) o[c] = clip8(acc[c]);
+  }
+}
+
+// vertical: src [N][Hin][W][C] -> dst [N][Hout][W][C]; one thread per output byte (coalesced along the row)
+__global__ void resize_v_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int N, int Hin, int Hout,
+                                   long long rowbytes, const int* __restrict__ bounds, const int* __restrict__ kk,
+                                   int ksize) {
+  const long long total = static_cast<long long>(N) * Hout * rowbytes;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i % rowbytes;
+    const long long r = i / rowbytes;
+    const int y = static_cast<int>(r % Hout);
+    const long long n = r / Hout;
+    const int y0 = __ldg(bounds + 2 * y), cnt = __ldg(bounds + 2 * y + 1);
+    const int* k = kk + static_cast<long long>(y) * ksize;
+    int acc = 1 << (kResizePrecisionBits - 1);
+    const uint8_t* p = src + (n * Hin + y0) * rowbytes + b;
+    for (int t = 0; t < cnt; ++t) acc += static_cast<int>(__ldg(p + t * rowbytes)) * __ldg(k + t);
+    dst[i] = clip8(acc);
+  }
+}
+
 }  // namespace
 }  // namespace uz
 
@@ -178,5 +235,46 @@ extern "C" int uz_mask_u8_to_f32(const uint8_t* mask, long long n, float* out, v
   if (blocks > 148 * 16) blocks = 148 * 16;
   mask_u8_to_f32_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(mask, n, out);
   PW_CHECK_LAUNCH("mask_u8_to_f32 launch");
+  return UZ_OK;
+}
+
+
+// transforms.Resize on a decoded uint8 image (datasets.py:41,47), bit-exact with Pillow: horizontal pass (skipped when
+// Wout == Win) into `tmp` [N][Hin][Wout][C], vertical pass (skipped when Hout == Hin) into `dst` [N][Hout][Wout][C].
+// bounds_* [out][2] = {first input index, count}, kk_* [out][ksize_*] fixed-point coefficients (22 fractional bits) as
+// built by unet_zoo_b200.data.resample_coeffs (Pillow's precompute_coeffs + normalize_coeffs_8bpc), device memory.
+extern "C" int uz_resize_bilinear_u8(const uint8_t* src, int N, int Hin, int Win, int C, uint8_t* tmp, uint8_t* dst,
+                                     int Hout, int Wout, const int* bounds_h, const int* kk_h, int ksize_h,
+                                     const int* bounds_v, const int* kk_v, int ksize_v, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!src || !dst || N < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || C < 1 || C > 4)
+    return set_error(UZ_ERR_INVALID, "resize_bilinear_u8: bad extents (1 <= C <= 4)");
+  const bool do_h = Wout != Win, do_v = Hout != Hin;
+  if ((do_h && (!bounds_h || !kk_h || ksize_h < 1)) || (do_v && (!bounds_v || !kk_v || ksize_v < 1)))
+    return set_error(UZ_ERR_INVALID, "resize_bilinear_u8: missing coefficient tables");
+  if (do_h && do_v && !tmp) return set_error(UZ_ERR_INVALID, "resize_bilinear_u8: two passes need the intermediate");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int sms_ = uz_device_sm_count();
+  auto grid = [&](long long total) {
+    long long g = (total + 255) / 256, cap = static_cast<long long>(sms_ > 0 ? sms_ : 148) * 16;
+    return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+  };
+  const uint8_t* vin = src;
+  if (do_h) {
+    uint8_t* hout = do_v ? tmp : dst;
+    const long long rows = static_cast<long long>(N) * Hin;
+    resize_h_u8_kernel<<<grid(rows * Wout), 256, 0, st>>>(src, hout, rows, Win, Wout, C, bounds_h, kk_h, ksize_h);
+    PW_CHECK_LAUNCH("resize_h launch");
+    vin = hout;
+  }
+  if (do_v) {
+    const long long rowbytes = static_cast<long long>(Wout) * C;
+    resize_v_u8_kernel<<<grid(static_cast<long long>(N) * Hout * rowbytes), 256, 0, st>>>(vin, dst, N, Hin, Hout, rowbytes,
+                                                                                          bounds_v, kk_v, ksize_v);
+    PW_CHECK_LAUNCH("resize_v launch");
+  } else if (!do_h) {
+    cudaError_t e = cudaMemcpyAsync(dst, src, static_cast<size_t>(N) * Hin * Win * C, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_error(e, "resize copy");
+  }
   return UZ_OK;
 }
