@@ -194,3 +194,37 @@ def test_transatt_unet_graphed_step_with_fused_tail_matches_eager_steps():
     for k in s0:
         if s0[k].dtype.is_floating_point:
             assert torch.allclose(s0[k], s1[k], rtol=0, atol=2e-5), k
+
+
+def test_inference_memo_of_folded_weights_tracks_weight_changes():
+    """Eval-mode forwards keep their packed / BatchNorm-folded weights (engine.Ctx.cached): the second forward issues far
+    fewer launches and returns the same bits; an in-place weight change (version counter), a load_state_dict and a
+    training step in between (train() drops the memo; FlatAdamW bypasses version counters) are all picked up."""
+    from unet_zoo_b200.loss import BCEDiceWithLogits
+    from unet_zoo_b200.optim import FlatAdamW
+    model = seeded_model("resunet").cuda().eval()
+    x, m = O.synthetic_batch(2, 3, 64, 64)
+    with torch.no_grad():
+        a = model(x.cuda())
+        n_first = model._last_launches
+        b = model(x.cuda())
+        n_second = model._last_launches
+    assert torch.equal(a, b) and n_second < n_first and n_second <= 60, (n_first, n_second)
+
+    def oracle():
+        sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+        with torch.no_grad():
+            return O.resunet_forward(sd, x, False)
+    with torch.no_grad():
+        model.bridge.conv_block[2].weight.mul_(1.5)          # in place: version counter
+        model.input_layer[1].running_var.add_(0.3)
+        c = model(x.cuda()).cpu()
+    assert rel_err(c, oracle()) < LOGIT_TOL_BF16 and rel_err(c, a.cpu()) > 1e-3
+    opt = FlatAdamW(list(model.parameters()), lr=1e-2, weight_decay=0.0, max_norm=None)
+    model.train()
+    BCEDiceWithLogits()(model(x.cuda()), m.cuda()).backward()
+    opt.step()                                               # raw-pointer update: no version bump
+    model.eval()
+    with torch.no_grad():
+        d = model(x.cuda()).cpu()
+    assert rel_err(d, oracle()) < LOGIT_TOL_BF16 and rel_err(d, c) > 1e-3

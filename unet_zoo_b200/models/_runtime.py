@@ -74,6 +74,14 @@ class HotPathModel(nn.Module):
         return self
 
     _input_norm = None
+    _eval_cache = None          # engine.Ctx.cached: inference memo of packed / BatchNorm-folded weights
+
+    def train(self, mode: bool = True):
+        """nn.Module.train; entering train mode drops the inference memo (the optimizer is about to change the weights -
+        FlatAdamW and CUDA-graph replays do so without touching torch's version counters)."""
+        if mode:
+            self._eval_cache = None
+        return super().train(mode)
 
     def set_input_normalization(self, mean, std):
         """Let ``forward`` take the DECODED image bytes: a uint8 tensor [N, H, W, C] (as PIL / the dataset's Resize
@@ -141,6 +149,10 @@ class HotPathModel(nn.Module):
                 with torch.no_grad():
                     ctx = E.Ctx(x.device, training=self.training, record=False)
                     ctx.input_norm = self._input_norm
+                    if not self.training:           # packed / folded weights are constants of an eval-mode forward
+                        if self._eval_cache is None:
+                            self._eval_cache = {}
+                        ctx.eval_cache = self._eval_cache
                     outs = self._graph(ctx, x)
                     self._last_launches = ctx.launches
         return self._pack_outputs(list(outs))
