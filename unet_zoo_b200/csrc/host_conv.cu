@@ -447,6 +447,11 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   }
   p.num_segs = nseg;
   p.kblocks = kblocks;
+  for (int sg = 0; sg < nseg; ++sg) {
+    const int c = (convt_d || s2c) ? seg_c[0] : seg_c[sg];
+    const int rem = c - (p.seg_cblocks[sg] - 1) * 64;   // channels of the last block: 8..64
+    p.seg_klast[sg] = env_int("UZ_FWD2_KSKIP", 1) ? (rem + 15) / 16 : 4;
+  }
   p.b_items = 0;
   for (int sg = 0; sg < nseg; ++sg) {
     if (!s2c) p.seg_taps[sg] = (1 << p.num_taps) - 1;

@@ -107,6 +107,8 @@ struct alignas(64) Igemm2Params {
   int seg_cblocks[kMaxSegs];
   int seg_k0[kMaxSegs];
   int num_taps;
+  int seg_klast[kMaxSegs];     // K steps (of 16 channels) in the LAST 64-channel block of the segment: 1..4.  A 32-channel
+                               // segment (nested_unet level 0) would otherwise spend half of its MMAs on zero padding
   int seg_taps[kMaxSegs];      // bit t set: segment uses tap t (all taps except for the stride-2 3x3 convolution, whose
                                // four segments are the four parity lattices of ONE input, each with its own taps)
   int b_items;                 // weight tiles per output tile = sum over segments of cblocks x taps used

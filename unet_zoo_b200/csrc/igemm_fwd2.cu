@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         for (int seg = 0; seg < p.num_segs; ++seg) {
         const uint32_t seg_mask = static_cast<uint32_t>(p.seg_taps[seg]);
         for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb) {
+          const int ksteps = cb + 1 == p.seg_cblocks[seg] ? p.seg_klast[seg] : 4;
           mbar_wait(afull(astage), aphase);
           tc_fence_after();
           const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
@@ -278,6 +279,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 const uint32_t a_tap = a_lo + sub * (a_half >> 4) + tap_lo[tap];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
+                  if (k >= ksteps) break;
                   if (kPair)
                     umma2_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_lo + 2u * k, b_hi, idesc, k == 0 ? fresh : 1u);
                   else
