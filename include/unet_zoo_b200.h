@@ -188,6 +188,15 @@ int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void* const* se
                   int out_h, int out_w, float* stats, int flags, void* stream);
 int uz_conv_stats_rows(void);
 
+/* Nearest-x2 upsample + conv3x3 (UpConvBlock, common_layers.py:69-73) runs in PHASE form on images of at least 16 x 8
+ * low-resolution pixels with cout a multiple of 64: each of the four output phases is a 2x2 convolution of the
+ * low-resolution input with pre-summed weights (16 tap-pixels per input pixel instead of 36; the 4x upsampled tensor
+ * never exists).  uz_up2x_phase_form tells which weight packing UZ_UP2X_CONV3X3 / _DGRAD expect for a layer:
+ * 1 -> uz_pack_up2x ([cout][16][cin], transpose = 0; data gradient [cin][16][cout], transpose = 1),
+ * 0 -> uz_pack_weight with nine taps (first-generation kernel, small images). */
+int uz_up2x_phase_form(int H_low, int W_low, int cout);
+int uz_pack_up2x(const float* w_oihw, void* dst_bf16, int cout, int cin, int transpose, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Weight gradients on tcgen05 (reduction over pixels).  dY / X are NHWC bf16.
  *   UZ_CONV3X3 / UZ_CONV1X1 / *_S2 / UZ_UP2X_CONV3X3 : dW[co, c_off + ci, r, s] (OIHW fp32, full Cin = cin_total)

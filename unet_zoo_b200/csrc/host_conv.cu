@@ -370,8 +370,18 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   static const int disabled = env_int("UZ_DISABLE_FWD2", 0);
   if (disabled) return 0;
   if (!(mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || mode == UZ_CONV1X1 || mode == UZ_CONVT2X2 ||
-        mode == UZ_CONVT2X2_DGRAD || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2))
+        mode == UZ_CONVT2X2_DGRAD || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2 || mode == UZ_UP2X_CONV3X3 ||
+        mode == UZ_UP2X_CONV3X3_DGRAD))
     return 0;
+  // nearest-x2 upsample + conv3x3 (UpConvBlock, common_layers.py:69-73) in PHASE form: output pixel (2y+py, 2x+px) reads
+  // rows y + floor((py + r - 1) / 2), r = 0..2, of the low-resolution input - two distinct rows per phase, likewise two
+  // columns - so each of the four output phases is a 2x2 convolution of the low-resolution image whose weights are sums
+  // of the 3x3 taps (uz_pack_up2x): 16 tap-pixels per low-resolution pixel instead of 36.  The packed weights carry
+  // 16 "taps" = phase * 4 + a * 2 + b, tap (a, b) of phase (py, px) at low-resolution offset (a - 1 + py, b - 1 + px).
+  const bool up2x = mode == UZ_UP2X_CONV3X3, up2x_d = mode == UZ_UP2X_CONV3X3_DGRAD;
+  // (the caller packs 16-tap phase weights exactly when uz_up2x_phase_form() says so - same predicate here)
+  if (up2x && (nseg != 1 || !uz_up2x_phase_form(H, W, cout))) return 0;
+  if (up2x_d && (nseg != 1 || (H & 1) || (W & 1) || !uz_up2x_phase_form(H / 2, W / 2, seg_c[0]))) return 0;
   // 1x1 stride 2 (ResidualConv.conv_skip, common_layers.py:194) = a 1x1 GEMM over the even-pixel lattice of the input
   // 3x3 stride 2 (ResidualConv.conv_block, common_layers.py:188): the input splits into its four parity lattices; tap
   // (r, s) reads lattice (r != 1, s != 1) shifted by (r == 0 ? -1 : 0, s == 0 ? -1 : 0) - four segments over the SAME
@@ -386,23 +396,29 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   // ConvTranspose2d k2s2 forward = four 1x1 GEMMs (one per output phase) stored through strided output views;
   // its data gradient = one 1x1 GEMM whose K runs over the four strided views of dY (K = 4*Cout).
   const bool convt = mode == UZ_CONVT2X2, convt_d = mode == UZ_CONVT2X2_DGRAD;
-  if (convt_d) {
+  if (convt_d || up2x_d) {
     if ((H & 1) || (W & 1) || nseg != 1) return 0;
     H /= 2;
     W /= 2;  // tile space = the low-resolution gradient
   }
   if (H < 16 || W < 8 || nseg > kMaxSegs) return 0;
-  if (convt && (cout % 64) != 0) return 0;
+  if ((convt || up2x) && (cout % 64) != 0) return 0;
   Igemm2Params p;
   memset(&p, 0, sizeof(p));
-  const int pad = (mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || s2c) ? 0 + 1 : 0;
+  const int pad = (mode == UZ_CONV3X3 || mode == UZ_CONV3X3_DGRAD || s2c || up2x || up2x_d) ? 0 + 1 : 0;
   p.pad = pad;
   p.halo_w = 8 + 2 * pad;
   p.halo_bytes = p.halo_w * (16 + 2 * pad) * 128;
-  p.num_taps = pad ? 9 : 1;
+  p.num_taps = up2x ? 4 : pad ? 9 : 1;
+  if (up2x) {
+    p.ph_ntaps = 4;
+    for (int ph = 0; ph < 4; ++ph)
+      for (int t = 0; t < 4; ++t)   // tap (a, b) = (t >> 1, t & 1) of phase (py, px): halo position (a + py, b + px)
+        p.ph_row[ph][t] = (int8_t)(((t >> 1) + (ph >> 1)) * p.halo_w + (t & 1) + (ph & 1));
+  }
   for (int t = 0; t < p.num_taps; ++t) {
     const int r = t / 3, s = t % 3;
-    if (mode == UZ_CONV3X3) p.tap_row[t] = r * p.halo_w + s;
+    if (mode == UZ_CONV3X3 || up2x_d) p.tap_row[t] = r * p.halo_w + s;
     else if (mode == UZ_CONV3X3_DGRAD) p.tap_row[t] = (2 - r) * p.halo_w + (2 - s);
     else if (s2c) p.tap_row[t] = (r == 0 ? 0 : 1) * p.halo_w + (s == 0 ? 0 : 1);
     else p.tap_row[t] = 0;
@@ -411,7 +427,25 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   int bn = cout <= 64 ? 64 : cout <= 128 ? 128 : 256;
   int ctot = 0, kblocks = 0;
   const Lattice full = {0, 0, 1};
-  if (convt_d) {
+  if (up2x_d) {
+    // four segments = the four output phases of dZ (strided views with a halo), all over the SAME K range (the conv's
+    // output channels); phase (py, px) contributes through its taps (a, b) at halo position (2 - a - py, 2 - b - px)
+    for (int l = 0; l < 4; ++l) {
+      p.seg_cblocks[l] = (seg_c[0] + 63) / 64;
+      p.seg_k0[l] = 0;
+      kblocks += p.seg_cblocks[l];
+      int rc = make_act_map(&p.amap[l], seg_ptr[0], seg_c[0], seg_ld[0], N, 2 * H, 2 * W, Lattice{l >> 1, l & 1, 2}, p.halo_w,
+                            16 + 2 * pad, 1);
+      if (rc != UZ_OK) return rc;
+      for (int t4 = 0; t4 < 4; ++t4) {
+        const int hp = (2 - (t4 >> 1) - (l >> 1)) * 3 + (2 - (t4 & 1) - (l & 1));
+        p.seg_taps[l] |= 1 << hp;
+        p.seg_tap_b[l][hp] = (int8_t)(l * 4 + t4);
+      }
+    }
+    ctot = seg_c[0];
+    nseg = 4;
+  } else if (convt_d) {
     for (int l = 0; l < 4; ++l) {
       p.seg_cblocks[l] = (seg_c[0] + 63) / 64;
       p.seg_k0[l] = ctot;
@@ -448,13 +482,18 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.num_segs = nseg;
   p.kblocks = kblocks;
   for (int sg = 0; sg < nseg; ++sg) {
-    const int c = (convt_d || s2c) ? seg_c[0] : seg_c[sg];
+    const int c = (convt_d || s2c || up2x_d) ? seg_c[0] : seg_c[sg];
     const int rem = c - (p.seg_cblocks[sg] - 1) * 64;   // channels of the last block: 8..64
     p.seg_klast[sg] = env_int("UZ_FWD2_KSKIP", 1) ? (rem + 15) / 16 : 4;
   }
   p.b_items = 0;
   for (int sg = 0; sg < nseg; ++sg) {
-    if (!s2c) p.seg_taps[sg] = (1 << p.num_taps) - 1;
+    if (!s2c && !up2x_d) {
+      p.seg_taps[sg] = (1 << p.num_taps) - 1;
+      for (int t = 0; t < p.num_taps; ++t) p.seg_tap_b[sg][t] = (int8_t)p.tap_b[t];
+    } else if (s2c) {
+      for (int t = 0; t < 9; ++t) p.seg_tap_b[sg][t] = (int8_t)p.tap_b[t];
+    }
     p.b_items += p.seg_cblocks[sg] * __builtin_popcount(p.seg_taps[sg]);
   }
   p.N = N; p.H = H; p.W = W;
@@ -462,7 +501,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.yb = (H + 15) / 16;
   p.m_tiles_real = N * p.xb * p.yb;
   p.num_n_tiles = (cout + bn - 1) / bn;
-  if (convt) {
+  if (convt || up2x) {
     p.nt_per_phase = p.num_n_tiles;
     p.num_n_tiles *= 4;
   }
@@ -504,7 +543,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     b_item = bn * 128;
     a_slot *= 2;
     p.num_n_tiles = (cout + bn - 1) / bn;
-    if (convt) {
+    if (convt || up2x) {
       p.nt_per_phase = p.num_n_tiles;
       p.num_n_tiles *= 4;
     }
@@ -523,7 +562,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     if (p.b_stages < 2) return 0;
   }
   p.cluster = cluster;
-  p.n_minor = (convt && env_int("UZ_FWD2_N_MINOR", 1)) ? 1 : 0;
+  p.n_minor = ((convt || up2x) && env_int("UZ_FWD2_N_MINOR", 1)) ? 1 : 0;
   p.m_tiles = ((p.m_tiles_real + p.mp - 1) / p.mp + cluster - 1) / cluster * cluster;
   p.total_tiles = p.m_tiles * p.num_n_tiles;
   p.ragged = ((H % 16) != 0 || (W % 8) != 0 || p.m_tiles * p.mp != p.m_tiles_real) ? 1 : 0;
@@ -535,9 +574,9 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const int smem_bytes = p.bar_off + kTail + 1024;
   // packed weights: conv [Cout][taps][Ctot]; ConvT fwd [Cout][4 phases][Cin] (the phase is the "tap" coordinate);
   // ConvT dgrad [Cin][4][Cout] read as rows of K = 4*Cout
-  int rc = make_weight_map(&p.bmap, w_packed, ctot, convt ? 4 : p.num_taps, cout, bn / cluster);
+  int rc = make_weight_map(&p.bmap, w_packed, ctot, convt ? 4 : (up2x || up2x_d) ? 16 : p.num_taps, cout, bn / cluster);
   if (rc != UZ_OK) return rc;
-  if (convt) {
+  if (convt || up2x) {
     for (int l = 0; l < 4 && rc == UZ_OK; ++l)
       rc = make_act_map(&p.omap[l], out, cout, out_ld, N, 2 * H, 2 * W, Lattice{l >> 1, l & 1, 2}, 8, 16, 1);
   } else {
@@ -628,7 +667,8 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * uz_conv_stats_rows(), st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
-  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2) {
+  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2 ||
+      mode == UZ_UP2X_CONV3X3 || mode == UZ_UP2X_CONV3X3_DGRAD) {
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }

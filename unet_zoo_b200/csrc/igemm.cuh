@@ -114,6 +114,13 @@ struct alignas(64) Igemm2Params {
   int b_items;                 // weight tiles per output tile = sum over segments of cblocks x taps used
   int tap_row[9];              // halo row (pixel index in the box) of each tap's first pixel
   int tap_b[9];                // tap coordinate in the packed weights
+  int8_t seg_tap_b[kMaxSegs][9];  // tap coordinate in the packed weights per (segment, halo position).  Equal to tap_b
+                               // for every mode but the nearest-x2 conv's data gradient, whose four segments (the output
+                               // phases of dZ) each use four of the nine halo positions with their own pre-summed weights
+  int ph_ntaps;                // 0, or 4: nearest-x2 conv forward - N tile = (output phase, column tile) like the transposed
+                               // conv, and each phase reads a 2x2 window of the LOW-resolution halo (the nine taps of the
+                               // 3x3 filter on the upsampled image collapse onto it; weights pre-summed per phase):
+  int8_t ph_row[4][4];         //   halo row (pixel index in the box) of tap t of phase p; weight tap coordinate p*4 + t
   int pad;                     // 1 for 3x3, 0 for 1x1
   int halo_w;                  // 8 + 2*pad
   int halo_bytes;              // halo_w * (16 + 2*pad) * 128

@@ -190,10 +190,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
             for (int tap = 0; tap < p.num_taps; ++tap) {
               if (!((p.seg_taps[seg] >> tap) & 1)) continue;
               if (kPair)   // this CTA's half of the weight rows
-                tma_load_3d_pair(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap],
-                                 rank * (BN / 2));
+                tma_load_3d_pair(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64,
+                                 p.seg_tap_b[seg][tap], rank * (BN / 2));
               else
-                tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.tap_b[tap], 0);
+                tma_load_3d(b_base + item * kBItem, &p.bmap, bfull(0), p.seg_k0[seg] + cb * 64, p.seg_tap_b[seg][tap], 0);
               ++item;
             }
       } else {
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 mbar_wait(bempty(stage), phase ^ 1u);
                 if (leader) mbar_expect_tx(bfull(stage), kBItem * CG);
                 const uint32_t dst = b_base + stage * kBItem;
-                const int btap = b_phase >= 0 ? b_phase : p.tap_b[tap];
+                const int btap = b_phase >= 0 ? (p.ph_ntaps ? b_phase * 4 + tap : b_phase) : p.seg_tap_b[seg][tap];
                 if (kPair)
                   tma_load_3d_pair(dst, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows);
                 else if (cs == 1)
@@ -250,6 +250,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         tc_fence_after();
       }
       for (int g = cidx; g < ngroups; g += nclusters) {
+        if (p.ph_ntaps) {   // nearest-x2 conv: the tile's output phase selects its 2x2 window of the halo
+          int n_tile, m_unused;
+          f2_item(p, g * cs, &n_tile, &m_unused);
+          const int ph = n_tile / p.nt_per_phase;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) tap_lo[t] = static_cast<uint32_t>(p.ph_row[ph][t]) * 8u;
+        }
         mbar_wait(tempty(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (MP * BN);
@@ -343,7 +350,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     float run_s[kChunks][2], run_q[kChunks][2];
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) run_s[c][0] = run_s[c][1] = run_q[c][0] = run_q[c][1] = 0.f;
-    int run_ntile = -1, run_row0 = -1;
+    int run_row0 = -1;
     auto gbar = [&]() {
       if (grp == 0)
         asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -357,7 +364,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     // One row of partials per (CTA, group): the four warps (32 tile rows each, all columns) are summed through the
     // group's (idle) staging tile before the flush - rare (n-tile change / end of kernel), deterministic order.
     auto flush_stats = [&]() {   // called by all 128 threads of the group
-      if (run_ntile < 0) return;
+      if (run_row0 < 0) return;
       if (gt == 0) tma_store_wait_read0();   // a TMA store may still be reading the staging tile
       gbar();
 #pragma unroll
@@ -374,7 +381,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       float* dst = p.stats + (static_cast<size_t>(blockIdx.x) * 2 + grp) * 2 * p.ncols;
       for (int i = gt; i < 2 * BN; i += 128) {
         const int which = i / BN, c = i - which * BN;
-        const int col = run_ntile * BN + c;
+        const int col = run_row0 + c;
         if (col < p.ncols) {
           float v = 0.f;
 #pragma unroll
@@ -393,11 +400,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       if (p.num_n_tiles > 1) f2_item(p, g * cs + rank, &item_ntile, &m_unused);
       const int o_phase = p.nt_per_phase ? item_ntile / p.nt_per_phase : 0;
       const int row0 = (p.nt_per_phase ? item_ntile % p.nt_per_phase : item_ntile) * BN;   // first output column of the tile
-      if (item_ntile != run_ntile) {
+      if (row0 != run_row0) {   // statistics and bias belong to the column range (not to the output phase)
         if (do_stats) flush_stats();
-        run_ntile = item_ntile;
-      }
-      if (row0 != run_row0) {   // the bias vector depends on the column range only (not on the output phase)
         run_row0 = row0;
         gbar();
         for (int c = gt; c < BN; c += 128) {

@@ -93,6 +93,41 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, __nv_bfloat16*
   }
 }
 
+// Pre-summed weights of the nearest-x2 conv in phase form (host_conv.cu, UZ_UP2X_CONV3X3): for output phase (py, px) the
+// rows r of the 3x3 filter that read low-resolution row offset a - 1 + py are  R(0,0) = {0}, R(0,1) = {1,2},
+// R(1,0) = {0,1}, R(1,1) = {2}  (same for columns):  dst[x][ph*4 + a*2 + b][y] = bf16(sum_{r in R(py,a), s in R(px,b)} w[co][ci][r][s])
+// with (x, y) = (co, ci) for the forward layout and (ci, co) for the data-gradient layout.  Sums in fp32, one rounding.
+__global__ void pack_up2x_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Co, int Ci,
+                                 int transpose) {
+  const long long total = static_cast<long long>(Co) * Ci;
+  const int X = transpose ? Ci : Co, Y = transpose ? Co : Ci;
+  (void)X;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int y = static_cast<int>(i % Y);
+    const int x = static_cast<int>(i / Y);
+    const int co = transpose ? y : x, ci = transpose ? x : y;
+    float t[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) t[k] = __ldg(w + (static_cast<long long>(co) * Ci + ci) * 9 + k);
+    __nv_bfloat16* d = dst + static_cast<long long>(x) * 16 * Y + y;
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph) {
+      const int py = ph >> 1, px = ph & 1;
+#pragma unroll
+      for (int ab = 0; ab < 4; ++ab) {
+        const int a = ab >> 1, b = ab & 1;
+        const int r0 = py == 0 ? (a == 0 ? 0 : 1) : (a == 0 ? 0 : 2), r1 = py == 0 ? (a == 0 ? 0 : 2) : (a == 0 ? 1 : 2);
+        const int s0 = px == 0 ? (b == 0 ? 0 : 1) : (b == 0 ? 0 : 2), s1 = px == 0 ? (b == 0 ? 0 : 2) : (b == 0 ? 1 : 2);
+        float acc = 0.f;
+        for (int r = r0; r <= r1; ++r)
+          for (int c = s0; c <= s1; ++c) acc += t[r * 3 + c];
+        d[static_cast<long long>(ph * 4 + ab) * Y] = __float2bfloat16_rn(acc);
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- stem im2col
 // out[n, y, x, t*cin + ci] = x[n, ci, y + r - 1, x + s - 1] (t = r*3 + s), zero outside the image and for columns
 // >= 9*cin.  One thread per pixel; reads are coalesced along W and served mostly by L1 (each input is used 9 times).
@@ -772,6 +807,23 @@ extern "C" int uz_pack_weight(const float* src, void* dst_bf16, int A, int T, in
   pack_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       src, static_cast<__nv_bfloat16*>(dst_bf16), A, T, B, sa, sb, st, dst_pitch, row_scale);
   UZ_CHECK_LAUNCH("pack_weight launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_up2x_phase_form(int H_low, int W_low, int cout) {
+  static const bool gen1 = std::getenv("UZ_UP2X_GEN1") != nullptr && std::atoi(std::getenv("UZ_UP2X_GEN1")) != 0;
+  return (!gen1 && H_low >= 16 && W_low >= 8 && cout >= 64 && (cout % 64) == 0) ? 1 : 0;
+}
+
+extern "C" int uz_pack_up2x(const float* w, void* dst_bf16, int Co, int Ci, int transpose, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  if (!w || !dst_bf16 || Co < 1 || Ci < 1) return set_error(UZ_ERR_INVALID, "pack_up2x: bad extents");
+  const long long total = static_cast<long long>(Co) * Ci;
+  int blocks = static_cast<int>((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  pack_up2x_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, static_cast<__nv_bfloat16*>(dst_bf16), Co,
+                                                                           Ci, transpose);
+  UZ_CHECK_LAUNCH("pack_up2x launch");
   return UZ_OK;
 }
 

@@ -300,6 +300,16 @@ class Ctx:
         self.launches += 1
         return out
 
+    def pack_up2x(self, w: torch.Tensor, transpose: bool) -> torch.Tensor:
+        """Pre-summed phase weights of the nearest-x2 conv (uz_pack_up2x): [Co][16][Ci], or [Ci][16][Co] for the data
+        gradient."""
+        w = w.detach().contiguous()
+        co, ci = w.shape[0], w.shape[1]
+        out = torch.empty((ci, 16, co) if transpose else (co, 16, ci), dtype=torch.bfloat16, device=w.device)
+        L.check(self.lib.uz_pack_up2x(w.data_ptr(), out.data_ptr(), co, ci, int(transpose), self.stream), "uz_pack_up2x")
+        self.launches += 1
+        return out
+
     def conv(self, mode: int, segs: Sequence[Act], wp: torch.Tensor, cout: int, bias: Optional[torch.Tensor],
              out_ptr: int, out_ld: int, out_h: int, out_w: int, stats: Optional[torch.Tensor] = None, flags: int = 0,
              in_grad: bool = False):
@@ -481,10 +491,15 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
     is_stem = stem == "im2col"
     conv_mode = L.CONV1X1 if is_stem else mode
     cin_total = sum(a.C for a in xs)
+    # nearest-x2 conv: phase form (2x2 windows of the low-resolution input, pre-summed weights) where the kernel takes it
+    phase_form = mode == L.UP2X_CONV3X3 and len(xs) == 1 and bool(ctx.lib.uz_up2x_phase_form(H, W, cout))
 
     if not ctx.training:
         def folded():
             scale, bias = _fold_bn(conv.bias, bn) if bn is not None else (None, conv.bias)
+            if phase_form:      # fold the BatchNorm scale into the fp32 weights, then pre-sum per phase
+                w = conv.weight.detach() * scale.view(-1, 1, 1, 1) if scale is not None else conv.weight
+                return ctx.pack_up2x(w, False), bias
             return ctx.pack(conv.weight if is_stem else _weight_for(conv, cin_total), "stem" if is_stem else "conv_fwd",
                             row_scale=scale, kp=a0.C if is_stem else 0), bias
         deps = [conv.weight, conv.bias] + ([bn.weight, bn.bias, bn.running_mean, bn.running_var] if bn is not None else [])
@@ -494,8 +509,9 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
             ctx.bn_apply(out, None, None, False, None, pooled)
         return out
 
-    wp = ctx.pack(conv.weight if is_stem else _weight_for(conv, cin_total), "stem" if is_stem else "conv_fwd",
-                  kp=a0.C if is_stem else 0)
+    wp = ctx.pack_up2x(conv.weight, False) if phase_form else \
+        ctx.pack(conv.weight if is_stem else _weight_for(conv, cin_total), "stem" if is_stem else "conv_fwd",
+                 kp=a0.C if is_stem else 0)
     z = ctx.new_act(N, Ho, Wo, cout)
     stats = ctx.f32(ctx.stats_rows, 2, cout)
     ctx.conv(conv_mode, xs, wp, cout, conv.bias, z.ptr, z.ld, Ho, Wo, stats, L.FLAG_STATS)
@@ -562,7 +578,8 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
                       L.CONV1X1_S2: L.CONV1X1_S2_DGRAD, L.UP2X_CONV3X3: L.UP2X_CONV3X3_DGRAD}.get(mode)
         if dgrad_mode is None:
             raise NotImplementedError(f"data gradient for conv mode {mode}")
-        wpd = c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
+        up2x_phase = mode == L.UP2X_CONV3X3 and len(xs) == 1 and bool(c.lib.uz_up2x_phase_form(a0.H, a0.W, cout))
+        wpd = c.pack_up2x(conv.weight, True) if up2x_phase else c.pack(conv.weight, "conv_dgrad")  # [Cin][T][Cout]
         off = 0
         for a in xs:
             for (r0, rc, acc) in a.grad_writes():
