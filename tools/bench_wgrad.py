@@ -14,6 +14,9 @@ ctx = E.Ctx(dev, training=True, record=False)
 LAYERS = [(512, 64, 64), (512, 128, 64), (256, 64, 128), (256, 128, 128), (256, 256, 128), (128, 128, 256),
           (128, 256, 256), (128, 512, 256), (64, 256, 512), (64, 512, 512), (64, 1024, 512), (32, 512, 1024),
           (32, 1024, 1024)]
+only = os.environ.get("ONLY")        # e.g. ONLY=128,256,256 (H, cin, cout)
+if only:
+    LAYERS = [tuple(int(v) for v in only.split(","))]
 tot = 0.0
 for H, cin, cout in LAYERS:
     x = E.Act(ctx.new_buf(N, H, H, cin))
