@@ -72,7 +72,7 @@ __device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile, int
   return t;
 }
 
-template <int BN, int MP, int CG>
+template <int BN, int MP, int CG, bool KSKIP>
 __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_constant__ Igemm2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         for (int seg = 0; seg < p.num_segs; ++seg) {
         const uint32_t seg_mask = static_cast<uint32_t>(p.seg_taps[seg]);
         for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb) {
-          const int ksteps = cb + 1 == p.seg_cblocks[seg] ? p.seg_klast[seg] : 4;
+          const int ksteps = (KSKIP && cb + 1 == p.seg_cblocks[seg]) ? p.seg_klast[seg] : 4;
           mbar_wait(afull(astage), aphase);
           tc_fence_after();
           const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
@@ -286,7 +286,11 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 const uint32_t a_tap = a_lo + sub * (a_half >> 4) + tap_lo[tap];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  if (k >= ksteps) break;
+                  // KSKIP instantiation only (some segment ends in a channel block of < 64 channels): stop after the
+                  // block's last 16-channel step.  The common instantiation has NO test here - the issue loop of an
+                  // N = 64 tile has 32 cycles per MMA, a predicate + branch per UTCHMMA cost 14 % on 64->64 @512^2,
+                  // and any less regular loop shape made the compiler drop the uniform-register descriptors (+65 %).
+                  if (KSKIP && k >= ksteps) break;
                   if (kPair)
                     umma2_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_lo + 2u * k, b_hi, idesc, k == 0 ? fresh : 1u);
                   else
@@ -513,13 +517,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   }
 }
 
-template <int BN, int MP, int CG>
-static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
+template <int BN, int MP, int CG, bool KSKIP>
+static cudaError_t launch_fwd2_ks(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
   static int configured[kMaxDevices] = {0};   // the attribute is per device
   int& conf = configured[device_slot()];
   if (conf < smem_bytes) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG, KSKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
     conf = smem_bytes;
   }
@@ -540,7 +544,15 @@ static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_byte
   }
   cfg.attrs = attr;
   cfg.numAttrs = nattr;
-  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP, CG>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP, CG, KSKIP>, p);
+}
+
+template <int BN, int MP, int CG>
+static cudaError_t launch_fwd2_bn(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
+  bool kskip = false;   // any segment whose last channel block holds fewer than 64 channels
+  for (int s = 0; s < p.num_segs; ++s) kskip = kskip || p.seg_klast[s] < 4;
+  return kskip ? launch_fwd2_ks<BN, MP, CG, true>(p, grid, smem_bytes, stream)
+               : launch_fwd2_ks<BN, MP, CG, false>(p, grid, smem_bytes, stream);
 }
 
 cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_bytes, cudaStream_t stream) {
