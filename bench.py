@@ -476,6 +476,10 @@ def main():
                     fam, _ = _families(q["profile"], pk, 1)
                     v = b * 1000.0 / q["ms_per_step"]
                     tf = v * FWD_BWD_GFLOP_PER_IMG_512[name] * (S / 512.0) ** 2 / 1000.0
+                    if name == "attention_unet":
+                        # its four nearest-x2 convs run in phase form (16 instead of 36 tap-pixels): the families' TFLOP/s
+                        # count EXECUTED FLOPs, step_tflops the reference's algorithmic FLOPs (what img/s is worth)
+                        fam["note"] = "families: executed FLOPs (up-convs in phase form); step_tflops: reference FLOPs"
                     secondary[name] = {"workload": workload_name(name, b, S), "value": v, "unit": "images/sec",
                                        "ms_per_step": q["ms_per_step"], "steps": 5, "step_tflops": tf,
                                        "frac_tensor": tf / pk["tflops"], "launch": q["launch"], "families": fam}

@@ -751,15 +751,17 @@ static WgPlan plan_wgrad(int mode, int N, int H, int W, int cin, int cout) {
 
 namespace uz {
 // second-generation kernel: 3x3 stride-1 on images of at least one 8x16 chunk
-static bool use_wgrad2(int mode, int H, int W) {
+static bool use_wgrad2(int mode, int H, int W, int cout = 64) {
   static const bool disabled = getenv("UZ_DISABLE_WGRAD2") != nullptr;
-  return !disabled && mode == UZ_CONV3X3 && H >= 16 && W >= 8;
+  if (disabled || H < 16 || W < 8) return false;
+  // nearest-x2 conv (H, W = the LOW-resolution image): phase form under the predicate the forward pass uses
+  return mode == UZ_CONV3X3 || (mode == UZ_UP2X_CONV3X3 && uz_up2x_phase_form(H, W, cout));
 }
 struct Wg2Plan {
   int xb, yb, chunks, co_blocks, ci_blocks, splits, pair, ci_units, wide;
   size_t ws_bytes;
 };
-static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
+static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout, bool up2x = false) {
   Wg2Plan pl;
   pl.xb = (W + 7) / 8;
   pl.yb = (H + 15) / 16;
@@ -769,7 +771,7 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   pl.ci_blocks = (cin + 63) / 64;
   // measured per layer (tools/bench_wgrad.py): WIDE wins 2-19 % wherever the CTA pair applies; a single WIDE CTA
   // (64 input channels) is 4 % slower than the N = 64 tile (its 4-stage ring of 55 KB stages is shallower)
-  pl.wide = (cout >= 128 && pl.ci_blocks >= 2 && env_int("UZ_WGRAD2_WIDE", 1)) ? 1 : 0;
+  pl.wide = (!up2x && cout >= 128 && pl.ci_blocks >= 2 && env_int("UZ_WGRAD2_WIDE", 1)) ? 1 : 0;
   pl.co_blocks = pl.wide ? (cout + 127) / 128 : (cout + 63) / 64;
   int sms = sm_count();
   if (sms < 1) sms = 148;
@@ -801,13 +803,13 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout) {
   }
   pl.splits = splits;
   // tile-major partials: one contiguous 9 x (64 | 128) x 64 fp32 region per (split, co block, ci block)
-  pl.ws_bytes = sizeof(float) * (size_t)splits * pl.co_blocks * pl.ci_blocks * 9 * (pl.wide ? 128 : 64) * 64;
+  pl.ws_bytes = sizeof(float) * (size_t)splits * pl.co_blocks * pl.ci_blocks * (up2x ? 16 : 9) * (pl.wide ? 128 : 64) * 64;
   return pl;
 }
 }  // namespace uz
 
 extern "C" size_t uz_conv_wgrad_workspace_bytes(int mode, int N, int H, int W, int cin, int cout) {
-  if (use_wgrad2(mode, H, W)) return plan_wgrad2(N, H, W, cin, cout).ws_bytes;
+  if (use_wgrad2(mode, H, W, cout)) return plan_wgrad2(N, H, W, cin, cout, mode == UZ_UP2X_CONV3X3).ws_bytes;
   WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
   return pl.rc == UZ_OK ? pl.ws_bytes : 0;
 }
@@ -821,16 +823,26 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
     return set_error(UZ_ERR_INVALID, "wgrad: channel counts / strides must be multiples of 8");
   if (!aligned16(x) || !aligned16(dy) || !aligned16(workspace))
     return set_error(UZ_ERR_INVALID, "wgrad: pointers must be 16-byte aligned");
-  if (use_wgrad2(mode, H, W)) {
-    const Wg2Plan p2 = plan_wgrad2(N, H, W, cin, cout);
+  if (use_wgrad2(mode, H, W, cout)) {
+    const bool up2x = mode == UZ_UP2X_CONV3X3;
+    const Wg2Plan p2 = plan_wgrad2(N, H, W, cin, cout, up2x);
     if (workspace_bytes < p2.ws_bytes)
       return set_error(UZ_ERR_WORKSPACE, "wgrad: workspace %zu < required %zu bytes", workspace_bytes, p2.ws_bytes);
     Wgrad2Params q;
     memset(&q, 0, sizeof(q));
     const Lattice full2 = {0, 0, 1};
     int rc2 = make_act_map(&q.xmap, x, cin, x_ld, N, H, W, full2, 10, 18, 1);
-    if (rc2 == UZ_OK) rc2 = make_act_map(&q.dzmap, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1);
-    if (rc2 == UZ_OK && p2.pair) rc2 = make_act_map(&q.dzmap_half, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1, 32);
+    if (up2x) {   // dy is the HIGH-resolution gradient (2H x 2W): one strided view per output phase
+      for (int ph = 0; ph < 4 && rc2 == UZ_OK; ++ph) {
+        const Lattice lat = {ph >> 1, ph & 1, 2};
+        rc2 = make_act_map(&q.dzmap_ph[ph], dy, cout, dy_ld, N, 2 * H, 2 * W, lat, 8, 16, 1);
+        if (rc2 == UZ_OK && p2.pair) rc2 = make_act_map(&q.dzmap_half_ph[ph], dy, cout, dy_ld, N, 2 * H, 2 * W, lat, 8, 16, 1, 32);
+      }
+      q.up2x = 1;
+    } else {
+      if (rc2 == UZ_OK) rc2 = make_act_map(&q.dzmap, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1);
+      if (rc2 == UZ_OK && p2.pair) rc2 = make_act_map(&q.dzmap_half, dy, cout, dy_ld, N, H, W, full2, 8, 16, 1, 32);
+    }
     if (rc2 != UZ_OK) return rc2;
     q.pair = p2.pair;
     q.wide = p2.wide;

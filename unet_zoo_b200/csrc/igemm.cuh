@@ -92,6 +92,14 @@ struct alignas(64) Wgrad2Params {
   // WIDE mode: output-channel blocks of 128 (co_blocks = ceil(cp/128)), N = 128 MMAs, two passes over the chunk range
   // (tap pairs 0..2, then 3..4) because five 128-column accumulators exceed the 512 TMEM columns.
   int wide;                // 0 / 1
+  // Nearest-x2 conv weight gradient in PHASE form (see host_conv.cu, UZ_UP2X_CONV3X3): the pixel space is the
+  // LOW-resolution image; per 8x16 chunk one X halo box and FOUR dZ boxes (the four output phases = strided views of the
+  // high-resolution gradient); phase (py, px) pairs its dZ with the 2x2 window of the halo at (a + py, b + px) - two tap
+  // pairs per phase, eight 64-column accumulators = all 512 TMEM columns in ONE pass.  Partials carry 16 "taps"
+  // (phase * 4 + a * 2 + b); the reduce kernel folds them onto the 3x3 filter.
+  int up2x;                // 0 / 1 (narrow tiles only)
+  CUtensorMap dzmap_ph[4];       // dZ phase views, box (64, 8, 16, 1)
+  CUtensorMap dzmap_half_ph[4];  // pair mode: box (32, 8, 16, 1), SWIZZLE_64B
 };
 
 // Second-generation forward-type implicit GEMM (igemm_fwd2.cu): conv3x3 / its data gradient / conv1x1 on 8x16-pixel

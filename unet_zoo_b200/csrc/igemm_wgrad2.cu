@@ -36,11 +36,17 @@ constexpr int kW2HaloSlot = 23552;                       // rounded up to 1024
 constexpr int kW2DzBytes = 128 * 128;                    // 8x16 pixels x 64 channels bf16
 constexpr int kW2TmemCols = 512;
 // per (CG, WIDE): bytes of dZ one CTA keeps per stage, stage size, ring depth
-__host__ __device__ constexpr int w2_dz_slot(int cg, int wide) { return (wide && cg == 1) ? 2 * kW2DzBytes : kW2DzBytes; }
-__host__ __device__ constexpr int w2_stage_bytes(int cg, int wide) { return kW2HaloSlot + w2_dz_slot(cg, wide); }
-__host__ __device__ constexpr int w2_stages(int cg, int wide) { return (wide && cg == 1) ? 4 : 5; }
-__host__ __device__ constexpr int w2_smem_bytes(int cg, int wide) {
-  return w2_stages(cg, wide) * w2_stage_bytes(cg, wide) + 256 + 1024;
+// (UP: four dZ phase boxes per stage - 8 KB halves in a pair, 16 KB otherwise)
+__host__ __device__ constexpr int w2_dz_phase(int cg) { return cg == 2 ? kW2DzBytes / 2 : kW2DzBytes; }
+__host__ __device__ constexpr int w2_dz_slot(int cg, int wide, int up = 0) {
+  return up ? 4 * w2_dz_phase(cg) : (wide && cg == 1) ? 2 * kW2DzBytes : kW2DzBytes;
+}
+__host__ __device__ constexpr int w2_stage_bytes(int cg, int wide, int up = 0) { return kW2HaloSlot + w2_dz_slot(cg, wide, up); }
+__host__ __device__ constexpr int w2_stages(int cg, int wide, int up = 0) {
+  return up ? (cg == 2 ? 4 : 2) : (wide && cg == 1) ? 4 : 5;
+}
+__host__ __device__ constexpr int w2_smem_bytes(int cg, int wide, int up = 0) {
+  return w2_stages(cg, wide, up) * w2_stage_bytes(cg, wide, up) + 256 + 1024;
 }
 
 struct W2Item {
@@ -61,11 +67,14 @@ __device__ __forceinline__ W2Item w2_decode(const Wgrad2Params& p, int item, int
   return w;
 }
 
-template <int CG, int WIDE>
+template <int CG, int WIDE, int UP = 0>
 __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __grid_constant__ Wgrad2Params p) {
+  static_assert(!(UP && WIDE), "the phase form of the nearest-x2 conv uses narrow tiles (8 x 64 TMEM columns)");
   constexpr bool kPair = CG == 2;
-  constexpr int kW2StageBytes = w2_stage_bytes(CG, WIDE);
-  constexpr int kW2Stages = w2_stages(CG, WIDE);
+  constexpr int kW2StageBytes = w2_stage_bytes(CG, WIDE, UP);
+  constexpr int kW2Stages = w2_stages(CG, WIDE, UP);
+  constexpr int kDzPh = w2_dz_phase(CG);      // UP: bytes of one phase's dZ box in this CTA
+  constexpr int kTaps = UP ? 16 : 9;          // taps of the partial layout
   constexpr int kBN = WIDE ? 128 : 64;        // output channels per work unit = accumulator columns per tap pair
   constexpr int kPasses = WIDE ? 2 : 1;       // WIDE: tap pairs 0..2 in the first pass over the chunks, 3..4 in the second
   constexpr int kCoBlk = kBN;
@@ -97,7 +106,11 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
     mbar_init(tempty_bar, 4 * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&p.xmap);
-    tma_prefetch_desc((kPair && !WIDE) ? &p.dzmap_half : &p.dzmap);
+    if (UP) {
+      for (int ph = 0; ph < 4; ++ph) tma_prefetch_desc(kPair ? &p.dzmap_half_ph[ph] : &p.dzmap_ph[ph]);
+    } else {
+      tma_prefetch_desc((kPair && !WIDE) ? &p.dzmap_half : &p.dzmap);
+    }
   }
   if (warp == 1) {
     if (kPair) {
@@ -131,7 +144,21 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t halo_dst = base + stage * kW2StageBytes;
           const uint32_t dz_dst = halo_dst + kW2HaloSlot;
-          if (kPair && WIDE) {   // own halo + own 64 of the 128 dZ channels; completes on the leader's barrier
+          if (UP) {   // one X halo + the four dZ phase boxes of the chunk
+            if (kPair) {
+              if (leader) mbar_expect_tx(full_bar(stage), 2 * kW2HaloBytes + 4 * kW2DzBytes);
+              tma_load_4d_pair(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+#pragma unroll
+              for (int ph = 0; ph < 4; ++ph)
+                tma_load_4d_pair(dz_dst + ph * kDzPh, &p.dzmap_half_ph[ph], full_bar(stage), w.co_blk * 64 + rank * 32, x0, y0, n);
+            } else {
+              mbar_expect_tx(full_bar(stage), kW2HaloBytes + 4 * kW2DzBytes);
+              tma_load_4d(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
+#pragma unroll
+              for (int ph = 0; ph < 4; ++ph)
+                tma_load_4d(dz_dst + ph * kDzPh, &p.dzmap_ph[ph], full_bar(stage), w.co_blk * 64, x0, y0, n);
+            }
+          } else if (kPair && WIDE) {   // own halo + own 64 of the 128 dZ channels; completes on the leader's barrier
             if (leader) mbar_expect_tx(full_bar(stage), 2 * kW2HaloBytes + 2 * kW2DzBytes);
             tma_load_4d_pair(halo_dst, &p.xmap, full_bar(stage), w.ci_blk * 64, x0 - 1, y0 - 1, n);
             tma_load_4d_pair(dz_dst, &p.dzmap, full_bar(stage), w.co_blk * kCoBlk + rank * 64, x0, y0, n);
@@ -189,6 +216,26 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
           constexpr bool kHalfRows = kPair && !WIDE;
           constexpr uint32_t b_hi = kHalfRows ? (((512u >> 4) & 0x3FFFu) | (1u << 14) | (4u << 29)) : umma_desc_hi(1024);
           constexpr uint32_t b_kstep = (kHalfRows ? 1024u : 2048u) >> 4;   // 16 pixels further, in 16-byte units
+          if (UP) {
+            uint32_t bz[4];
+#pragma unroll
+            for (int ph = 0; ph < 4; ++ph) bz[ph] = dz_lo + ((ph * kDzPh) >> 4);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+#pragma unroll
+              for (int blk = 0; blk < 8; ++blk) {   // (phase, a): taps (a, 0), (a, 1) of the phase stacked along M
+                constexpr uint32_t kLbo = (128u >> 4) << 16;
+                const int ph = blk >> 1, a = blk & 1;
+                const uint32_t a_lo = halo_lo + ((((a + (ph >> 1)) * kW2HaloW + (ph & 1)) * 128 + j * 2 * kW2HaloW * 128) >> 4) + kLbo;
+                const uint32_t bz_lo = bz[ph];
+                const uint32_t d_col = tmem_base + blk * 64;
+                if (kPair)
+                  umma2_bf16_words(d_col, a_lo, a_hi, bz_lo + j * b_kstep, b_hi, idesc, (first && j == 0) ? 0u : 1u);
+                else
+                  umma_bf16_words(d_col, a_lo, a_hi, bz_lo + j * b_kstep, b_hi, idesc, (first && j == 0) ? 0u : 1u);
+              }
+            }
+          } else {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 16 pixels = image rows 2j, 2j+1 of the chunk
 #pragma unroll
@@ -202,6 +249,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
               else
                 umma_bf16_words(d_col, a_lo, a_hi, dz_lo + j * b_kstep, b_hi, idesc, (first && j == 0) ? 0u : 1u);
             }
+          }
           }
           first = false;
           if (kPair)
@@ -238,18 +286,18 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
       // per work unit.  (With the parameter layout [co][tap][ci] a unit scattered 256-byte pieces over a 9*cq*4-byte
       // pitch: the epilogue of the weight-heavy layers ran at < 1 TB/s, 23-28 us per unit.)
       float* pbase = p.partial + ((static_cast<size_t>(w.split) * p.co_blocks + w.co_blk) * p.ci_blocks + w.ci_blk) *
-                                     (9 * kBN * 64) + ci_l;
+                                     (kTaps * kBN * 64) + ci_l;
 #pragma unroll 1
       for (int pass = 0; pass < kPasses; ++pass) {
       const int b_begin = WIDE ? (pass == 0 ? 0 : 3) : 0;
-      const int b_end = WIDE ? (pass == 0 ? 3 : 5) : 5;
+      const int b_end = UP ? 8 : WIDE ? (pass == 0 ? 3 : 5) : 5;
       if (has_work) {
         mbar_wait(tfull_bar, acc_phase);
         tc_fence_after();
       }
 #pragma unroll 1
       for (int b = b_begin; b < b_end; ++b) {
-        const int tap = pair_tap[b][half];
+        const int tap = UP ? (b >> 1) * 4 + (b & 1) * 2 + half : pair_tap[b < 5 ? b : 0][half];
 #pragma unroll 1
         for (int h = 0; h < kBN / 32; ++h) {
           uint32_t v[32];
@@ -341,8 +389,53 @@ __global__ void __launch_bounds__(288) wgrad2_reduce_kernel(const float* __restr
   }
 }
 
+// Phase form of the nearest-x2 conv: partial[split][co block][ci block][16 = phase*4 + a*2 + b][64 co][64 ci] -> OIHW.
+// Filter row r of output phase py reads low-resolution row offset a - 1 + py with a = a_of(py, r): a_of(0, .) = {0, 1, 1},
+// a_of(1, .) = {0, 0, 1} (same for columns), so dW[r][s] = sum over the four phases of partial tap (py, px, a_of(py, r), a_of(px, s)).
+__global__ void __launch_bounds__(288) wgrad2_up2x_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dst,
+                                                                 int splits, int cp, int cq, int co_blocks, int ci_blocks,
+                                                                 long long s_row, int accumulate) {
+  __shared__ float stage[9 * 65];
+  const int co = blockIdx.x / ci_blocks, ci_blk = blockIdx.x % ci_blocks;
+  const int tap = threadIdx.x >> 5, lane = threadIdx.x & 31;   // tap = r * 3 + s of the 3x3 filter
+  const int r = tap / 3, sx = tap - r * 3;
+  const int co_blk = co / 64, co_l = co % 64;
+  const size_t tile = static_cast<size_t>(16) * 64 * 64;
+  const size_t split_stride = static_cast<size_t>(co_blocks) * ci_blocks * tile;
+  const float* base = partial + (static_cast<size_t>(co_blk) * ci_blocks + ci_blk) * tile + static_cast<size_t>(co_l) * 64 + lane;
+  float a0 = 0.f, b0 = 0.f;
+#pragma unroll
+  for (int ph = 0; ph < 4; ++ph) {
+    const int py = ph >> 1, px = ph & 1;
+    const int a = py == 0 ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
+    const int b = px == 0 ? (sx == 0 ? 0 : 1) : (sx == 2 ? 1 : 0);
+    const float* q = base + static_cast<size_t>(ph * 4 + a * 2 + b) * 64 * 64;
+    for (int k = 0; k < splits; ++k) {
+      a0 += __ldg(q + k * split_stride);
+      b0 += __ldg(q + k * split_stride + 32);
+    }
+  }
+  stage[tap * 65 + lane] = a0;
+  stage[tap * 65 + lane + 32] = b0;
+  __syncthreads();
+  const int ncol = min(64, cq - ci_blk * 64);
+  float* o = dst + co * s_row + static_cast<long long>(ci_blk) * 64 * 9;
+  for (int i = threadIdx.x; i < ncol * 9; i += 288) {
+    const int c = i / 9, t = i - c * 9;
+    const float v = stage[t * 65 + c];
+    o[i] = accumulate ? o[i] + v : v;
+  }
+}
+
 cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_row, int accumulate,
                                  cudaStream_t stream) {
+  if (p.up2x) {
+    const long long blocks_u = static_cast<long long>(p.cp) * p.ci_blocks;
+    if (blocks_u < 1 || blocks_u > 0x7fffffffLL) return cudaErrorInvalidValue;
+    wgrad2_up2x_reduce_kernel<<<static_cast<int>(blocks_u), 288, 0, stream>>>(p.partial, dst, p.splits, p.cp, p.cq,
+                                                                             p.co_blocks, p.ci_blocks, s_row, accumulate);
+    return cudaGetLastError();
+  }
   const long long blocks = static_cast<long long>(p.cp) * p.ci_blocks;
   if (blocks < 1 || blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
   wgrad2_reduce_kernel<<<static_cast<int>(blocks), 288, 0, stream>>>(p.partial, dst, p.splits, p.cp, p.cq, p.co_blocks,
@@ -350,13 +443,13 @@ cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_
   return cudaGetLastError();
 }
 
-template <int CG, int WIDE>
+template <int CG, int WIDE, int UP = 0>
 static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_t stream) {
-  constexpr int kW2SmemBytes = w2_smem_bytes(CG, WIDE);
+  constexpr int kW2SmemBytes = w2_smem_bytes(CG, WIDE, UP);
   static bool configured_dev[kMaxDevices] = {false};   // the attribute is per device
   bool& configured = configured_dev[device_slot()];
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_wgrad2_kernel<CG, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_wgrad2_kernel<CG, WIDE, UP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kW2SmemBytes);
     if (e != cudaSuccess) return e;
     configured = true;
@@ -374,10 +467,11 @@ static cudaError_t launch_wgrad2_cg(const Wgrad2Params& p, int grid, cudaStream_
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = CG > 1 ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, igemm_wgrad2_kernel<CG, WIDE>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_wgrad2_kernel<CG, WIDE, UP>, p);
 }
 
 cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream) {
+  if (p.up2x) return p.pair ? launch_wgrad2_cg<2, 0, 1>(p, grid, stream) : launch_wgrad2_cg<1, 0, 1>(p, grid, stream);
   if (p.wide) return p.pair ? launch_wgrad2_cg<2, 1>(p, grid, stream) : launch_wgrad2_cg<1, 1>(p, grid, stream);
   return p.pair ? launch_wgrad2_cg<2, 0>(p, grid, stream) : launch_wgrad2_cg<1, 0>(p, grid, stream);
 }

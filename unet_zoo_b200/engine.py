@@ -322,6 +322,8 @@ class Ctx:
         # algorithmic FLOPs: 2 * output pixels * cout * cin * taps (per output pixel; convT has one tap per output)
         opix = a.N * out_h * out_w
         taps = {L.CONVT2X2: 1, L.CONV3X3_S2_DGRAD: 2.25}.get(mode, _TAPS[mode])
+        if wp.dim() == 3 and wp.shape[1] == 16:   # nearest-x2 conv in phase form: EXECUTED FLOPs (4 of 9 / 16 of 36 taps)
+            taps = 4 if mode == L.UP2X_CONV3X3 else 16
         cin = sum(s.C for s in segs)
         flops = 2.0 * opix * cout * cin * taps
         # algorithmic HBM bytes: every operand once (input pixels, packed weights, output (read too when accumulating))
@@ -340,8 +342,8 @@ class Ctx:
             flops = 2.0 * N * H * W * cin * cout * 4
         elif mode in (L.CONV3X3_S2, L.CONV1X1_S2):
             flops = 2.0 * N * ((H - 1) // 2 + 1) * ((W - 1) // 2 + 1) * cin * cout * _TAPS[mode]
-        elif mode == L.UP2X_CONV3X3:
-            flops = 2.0 * N * 4 * H * W * cin * cout * 9
+        elif mode == L.UP2X_CONV3X3:   # executed FLOPs: 16 tap-pixels per low-resolution pixel in phase form, else 36
+            flops = 2.0 * N * H * W * cin * cout * (16 if self.lib.uz_up2x_phase_form(H, W, cout) else 36)
         else:
             flops = 2.0 * N * H * W * cin * cout * _TAPS[mode]
         if mode in (L.CONVT2X2, L.UP2X_CONV3X3):
@@ -555,7 +557,12 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
             tgt = c.f32(cout, cin_total, *conv.weight.shape[2:]) if padded else dw
             off = 0
             for a in xs:
-                if mode == L.UP2X_CONV3X3 and os.environ.get("UZ_UP2X_WGRAD_GEN1") is None:
+                if mode == L.UP2X_CONV3X3 and len(xs) == 1 and bool(c.lib.uz_up2x_phase_form(a.H, a.W, cout)) \
+                        and os.environ.get("UZ_UP2X_WGRAD_MATERIALISE") is None:
+                    # phase form on the halo-box kernel: the low-resolution operand against the four output phases of
+                    # dZ (16 tap-pixels per input pixel instead of 36, no upsampled tensor)
+                    c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, tgt, cin_total, off)
+                elif mode == L.UP2X_CONV3X3 and os.environ.get("UZ_UP2X_WGRAD_GEN1") is None:
                     # materialise the nearest-x2 operand (one bandwidth pass) so that the weight gradient runs on the
                     # halo-box 3x3 kernel instead of the first-generation per-tap kernel (measured 2.5x faster)
                     up = c.new_act(a.N, 2 * a.H, 2 * a.W, a.C)
