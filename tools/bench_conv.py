@@ -30,6 +30,11 @@ LAYERS = [
     ("c3 512->1024 @32", L.CONV3X3, 32, 512, 1024, True),
     ("c3 1024->1024 @32", L.CONV3X3, 32, 1024, 1024, True),
 ]
+spec = os.environ.get("SPEC")        # e.g. SPEC=c3,512,32,32 (kind c3|dg|c1, H, cin, cout) with BATCH=8: one custom layer
+if spec:
+    kind, hh, ci, co = spec.split(",")
+    LAYERS = [(f"{kind} {ci}->{co} @{hh}", {"c3": L.CONV3X3, "dg": L.CONV3X3_DGRAD, "c1": L.CONV1X1}[kind], int(hh), int(ci),
+               int(co), kind != "dg")]
 only = os.environ.get("ONLY")
 tot = 0.0
 for name, mode, H, cin, cout, stats in LAYERS:

@@ -71,16 +71,24 @@ def main():
             E.PROFILE = []
             model(x)
             torch.cuda.synchronize()
-        rows = [(tag, flops, e0.elapsed_time(e1)) for kind, flops, e0, e1, tag, _nb in E.PROFILE if kind == "igemm_fwd"]
+        rows = [(kind, tag or kind, flops if kind.startswith("igemm") else 0.0, e0.elapsed_time(e1), nb)
+                for kind, flops, e0, e1, tag, nb in E.PROFILE]
         E.PROFILE = None
-        tot_ms = sum(r[2] for r in rows)
-        print(f"# {a.model} inference, batch {b}, {sz}x{sz}: convolution launches (eval mode, BatchNorm folded)\n")
-        print(f"sum of conv launches {tot_ms:.3f} ms, {sum(r[1] for r in rows) / tot_ms / 1e9:.0f} TFLOP/s; "
-              f"denominator: sustained bf16 peak {peak:.0f} TFLOP/s (MEASURED_PEAKS.json)\n")
-        print("| layer | GFLOP | ms | TFLOP/s | frac of tensor peak |\n|---|---|---|---|---|")
-        for tag, flops, ms in rows:
+        try:
+            hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+        except Exception:
+            hbm = 6650.0
+        tot_ms = sum(r[3] for r in rows)
+        print(f"# {a.model} inference, batch {b}, {sz}x{sz}: every profiled launch of one eval-mode forward (BatchNorm folded), "
+              "CUDA events around each launch\n")
+        print(f"sum {tot_ms:.3f} ms, {sum(r[2] for r in rows) / tot_ms / 1e9:.0f} TFLOP/s; roofs: sustained bf16 peak "
+              f"{peak:.0f} TFLOP/s, HBM copy {hbm:.0f} GB/s (MEASURED_PEAKS.json).  A layer is bound by the roof it is "
+              "closer to: 3x3 layers with >= 128 channels by the tensor pipe, 1x1 / transposed / 64-channel layers by HBM.\n")
+        print("| launch | GFLOP | algorithmic MB | ms | TFLOP/s | of tensor roof | GB/s | of HBM roof |\n|---|---|---|---|---|---|---|---|")
+        for kind, tag, flops, ms, nb in rows:
             tf = flops / ms / 1e9
-            print(f"| {tag} | {flops / 1e9:.1f} | {ms:.3f} | {tf:.0f} | {tf / peak:.2f} |")
+            gbs = nb / ms / 1e6
+            print(f"| {tag} | {flops / 1e9:.1f} | {nb / 1e6:.0f} | {ms:.3f} | {tf:.0f} | {tf / peak:.2f} | {gbs:.0f} | {gbs / hbm:.2f} |")
         return
     for s in [int(v) for v in a.sizes.split(",")]:
         for b in [int(v) for v in a.batches.split(",")]:
