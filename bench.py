@@ -202,13 +202,18 @@ def train_leg(args, model_name, B, S, steps, warmup, dev, world, rank, e2e=True,
 
     torch.manual_seed(0)
     model = unet_zoo_b200.create_model(model_name, in_channels=3, num_classes=1).to(dev).train()
-    if world > 1:
+    # UZ_DP_MODE=replicas: N independent single-GPU steps with NO gradient exchange (not a training mode - it measures what
+    # the GPUs of the box do on their own, so that max-over-ranks power-cap spread can be told from exposed communication)
+    replicas = world > 1 and os.environ.get("UZ_DP_MODE", "") == "replicas"
+    if world > 1 and not replicas:
         model = P.DataParallel(model, bucket_mb=float(os.environ.get("UZ_BUCKET_MB", "25")))
     params = [p for p in model.parameters() if p.requires_grad]
     # N > 1 launch modes (UZ_DP_MODE): "overlap" (default) = ONE CUDA graph per step with the bucketed NCCL all-reduces
     # captured on the communication stream (they overlap the rest of backward); "split" = two graphs around one eager
     # all-reduce of the flat gradient buffer (round 1's default); "eager" = eager launches + bucketed all-reduces
     dp_mode = os.environ.get("UZ_DP_MODE", "overlap") if world > 1 else "single"
+    if replicas:
+        dp_mode = "single"
     if args.no_graph:
         dp_mode = "eager" if world > 1 else "single"
     use_graph = not args.no_graph
@@ -282,6 +287,8 @@ def train_leg(args, model_name, B, S, steps, warmup, dev, world, rank, e2e=True,
             else:
                 step = GraphedTrainStep(model, crit, opt, x_d, m_d, max_norm=clip, params=params)
                 graph_note = "one CUDA graph per step (unet_zoo_b200.train_step.GraphedTrainStep)"
+                if replicas:
+                    graph_note += "; UZ_DP_MODE=replicas: independent replicas, NO gradient exchange (diagnostic)"
         except Exception as e:   # report, never hide: the JSON line says which mode was measured
             graph_note = f"eager (graph capture failed: {type(e).__name__}: {e})"[:300]
             if world > 1:
