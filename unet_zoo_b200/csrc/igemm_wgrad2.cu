@@ -343,48 +343,46 @@ __global__ void __launch_bounds__(kW2Threads, 1) igemm_wgrad2_kernel(const __gri
 }
 
 // dst[co][c_off + ci][tap] (OIHW, row pitch s_row floats) (+)= sum over splits of the tile-major partials.
-// block = (output channel, input-channel block): thread = (tap, lane) sums two columns over the splits (256-byte
-// contiguous reads per tap), the sums are transposed through shared memory and leave as ONE contiguous run of
-// 64 * 9 floats.
-__global__ void __launch_bounds__(288) wgrad2_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dst,
+// block = (output channel, input-channel block): thread = (split group, tap, lane) sums two columns over every
+// kRedGroups-th split (256-byte contiguous reads per tap, four loads in flight), the groups are combined through shared
+// memory in a fixed order (deterministic), the sums are transposed there and leave as ONE contiguous run of 64 * 9 floats.
+// (Three split groups per block: the layers with few work units - nested_unet's 32-channel convolutions, 32 blocks -
+// take up to ~300 splits and were bound by the serial chain of dependent loads: 24 us per launch, 5 % of that model's step.)
+constexpr int kRedGroups = 3;
+__global__ void __launch_bounds__(288 * kRedGroups) wgrad2_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dst,
                                                             int splits, int cp, int cq, int co_blocks, int ci_blocks,
                                                             int bn, long long s_row, int accumulate) {
-  __shared__ float stage[9 * 65];
+  __shared__ float stage[kRedGroups][9 * 65];
   const int co = blockIdx.x / ci_blocks, ci_blk = blockIdx.x % ci_blocks;
-  const int tap = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int grp = threadIdx.x / 288, t288 = threadIdx.x - grp * 288;
+  const int tap = t288 >> 5, lane = t288 & 31;
   const int co_blk = co / bn, co_l = co % bn;
   const size_t tile = static_cast<size_t>(9) * bn * 64;
   const size_t split_stride = static_cast<size_t>(co_blocks) * ci_blocks * tile;
   const float* q = partial + (static_cast<size_t>(co_blk) * ci_blocks + ci_blk) * tile +
                    (static_cast<size_t>(tap) * bn + co_l) * 64 + lane;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
-  int k = 0;
-  for (; k + 4 <= splits; k += 4) {   // eight independent loads in flight per thread
-    a0 += __ldg(q + (k + 0) * split_stride);
-    b0 += __ldg(q + (k + 0) * split_stride + 32);
-    a1 += __ldg(q + (k + 1) * split_stride);
-    b1 += __ldg(q + (k + 1) * split_stride + 32);
-    a2 += __ldg(q + (k + 2) * split_stride);
-    b2 += __ldg(q + (k + 2) * split_stride + 32);
-    a3 += __ldg(q + (k + 3) * split_stride);
-    b3 += __ldg(q + (k + 3) * split_stride + 32);
+  float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+  int k = grp;
+  for (; k + kRedGroups < splits; k += 2 * kRedGroups) {   // four independent loads in flight per thread
+    a0 += __ldg(q + k * split_stride);
+    b0 += __ldg(q + k * split_stride + 32);
+    a1 += __ldg(q + (k + kRedGroups) * split_stride);
+    b1 += __ldg(q + (k + kRedGroups) * split_stride + 32);
   }
-  for (; k < splits; ++k) {
+  if (k < splits) {
     a0 += __ldg(q + k * split_stride);
     b0 += __ldg(q + k * split_stride + 32);
   }
-  a0 = (a0 + a1) + (a2 + a3);
-  b0 = (b0 + b1) + (b2 + b3);
-  a1 = 0.f;
-  b1 = 0.f;
-  stage[tap * 65 + lane] = a0 + a1;
-  stage[tap * 65 + lane + 32] = b0 + b1;
+  stage[grp][tap * 65 + lane] = a0 + a1;
+  stage[grp][tap * 65 + lane + 32] = b0 + b1;
   __syncthreads();
   const int ncol = min(64, cq - ci_blk * 64);
   float* o = dst + co * s_row + static_cast<long long>(ci_blk) * 64 * 9;
-  for (int i = threadIdx.x; i < ncol * 9; i += 288) {
+  for (int i = threadIdx.x; i < ncol * 9; i += 288 * kRedGroups) {
     const int c = i / 9, t = i - c * 9;
-    const float v = stage[t * 65 + c];
+    float v = stage[0][t * 65 + c];
+#pragma unroll
+    for (int g = 1; g < kRedGroups; ++g) v += stage[g][t * 65 + c];
     o[i] = accumulate ? o[i] + v : v;
   }
 }
@@ -438,7 +436,7 @@ cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_
   }
   const long long blocks = static_cast<long long>(p.cp) * p.ci_blocks;
   if (blocks < 1 || blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
-  wgrad2_reduce_kernel<<<static_cast<int>(blocks), 288, 0, stream>>>(p.partial, dst, p.splits, p.cp, p.cq, p.co_blocks,
+  wgrad2_reduce_kernel<<<static_cast<int>(blocks), 288 * kRedGroups, 0, stream>>>(p.partial, dst, p.splits, p.cp, p.cq, p.co_blocks,
                                                                      p.ci_blocks, p.wide ? 128 : 64, s_row, accumulate);
   return cudaGetLastError();
 }
