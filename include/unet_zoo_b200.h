@@ -149,6 +149,22 @@ int uz_gate_bwd(const void* x, int x_ld, const void* dout, int dout_ld, const fl
  *  fwd: x [N,H,W,C] -> out [N,2H,2W,C] written at (out, out_ld) - typically a channel slice of a concat buffer.
  *  bwd: dx [N,H,W,C] (+)= gather of dout [N,2H,2W,C]; H, W are the LOW-resolution sizes in both calls. */
 int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, void* stream);
+/* Attention bottlenecks of the neighbouring models (transatt_unet.py:26-107, unet_transformer.py:115-229).
+ * uz_bmm_tn: C[n][m][j] = sum_k A[n][m][k] * B[n][j][k], bf16 operands (both K-contiguous: A rows lda, B rows K), fp32
+ *   accumulation, bf16 output rows ldc - replaces torch.bmm / torch.matmul.  Image strides in elements.  Shapes with
+ *   M >= 128 and M, K, J multiples of 8 run on the tcgen05 1x1 kernel with a per-image B operand; others on a plain kernel.
+ * uz_softmax_rows / _bwd: y = softmax(scale * x) over the last axis (F.softmax(dim=-1), the temperature division folded in
+ *   as `scale`) and dx = scale * y * (dy - sum(dy * y)).
+ * uz_transpose_bf16: dst[n][c][r] = src[n][r][c] (the TN product wants K-contiguous operands). */
+int uz_bmm_tn(const void* A, long long lda, long long a_img, const void* B, long long b_img, void* C, long long ldc,
+              long long c_img, int N, int M, int K, int J, void* stream);
+int uz_softmax_rows(const void* x, long long x_ld, void* y, long long y_ld, long long rows, int cols, float scale,
+                    void* stream);
+int uz_softmax_rows_bwd(const void* y, long long y_ld, const void* dy, long long dy_ld, void* dx, long long dx_ld,
+                        long long rows, int cols, float scale, void* stream);
+int uz_transpose_bf16(const void* src, long long src_ld, long long src_img, void* dst, long long dst_ld, long long dst_img,
+                      int N, int R, int C, void* stream);
+
 /* F.pad with zeros on the bottom / right, or its backward (crop), between two NHWC pixel grids: replaces the
  * `F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])` of common_layers.py:110-113 / :173-178 (dx, dy in {0, 1} for
  * the odd input sizes the reference accepts).  dst[n,y,x,:] = (y < Hs && x < Ws) ? src[n,y,x,:] : 0 over (Hd, Wd);

@@ -1,0 +1,171 @@
+// Attention bottleneck pieces of the neighbouring models: transatt_unet's PAM / channel
+// self-attention (transatt_unet.py:26-107) and unet_transformer's MHSA / MHCA (unet_transformer.py:115-229) are batched
+// matrix products with a softmax in between.  The products run on the tcgen05 1x1 kernel in its batched-B mode
+// (uz_bmm_tn in host_conv.cu); this file holds what surrounds them: the row softmax and its backward, a batched
+// transpose (the TN kernel wants both operands K-contiguous), and a plain CUDA-core batched GEMM for shapes below one
+// 128-row tile (bottlenecks of small test images) - never a library call.
+#include <cstdint>
+
+#include "pw.cuh"
+
+namespace uz {
+namespace {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float block_reduce(float v, bool is_max, float* red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  __syncthreads();                 // red may still be read by the previous reduction
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = red[0];
+  for (int i = 1; i < nw; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  return r;
+}
+
+// y[r][c] = softmax_c(scale * x[r][c]); one block per row, fp32 arithmetic, bf16 storage
+__global__ void softmax_rows_kernel(const __nv_bfloat16* __restrict__ x, long long x_ld, __nv_bfloat16* __restrict__ y,
+                                    long long y_ld, int cols, float scale) {
+  __shared__ float red[32];
+  const __nv_bfloat16* xr = x + static_cast<long long>(blockIdx.x) * x_ld;
+  __nv_bfloat16* yr = y + static_cast<long long>(blockIdx.x) * y_ld;
+  float m = -INFINITY;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) m = fmaxf(m, scale * __bfloat162float(xr[c]));
+  m = block_reduce(m, true, red);
+  float s = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) s += __expf(scale * __bfloat162float(xr[c]) - m);
+  s = block_reduce(s, false, red);
+  const float inv = 1.f / s;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x)
+    yr[c] = __float2bfloat16_rn(__expf(scale * __bfloat162float(xr[c]) - m) * inv);
+}
+
+// dx[r][c] = scale * y[r][c] * (dy[r][c] - sum_j dy[r][j] * y[r][j])
+__global__ void softmax_rows_bwd_kernel(const __nv_bfloat16* __restrict__ y, long long y_ld,
+                                        const __nv_bfloat16* __restrict__ dy, long long dy_ld,
+                                        __nv_bfloat16* __restrict__ dx, long long dx_ld, int cols, float scale) {
+  __shared__ float red[32];
+  const __nv_bfloat16* yr = y + static_cast<long long>(blockIdx.x) * y_ld;
+  const __nv_bfloat16* gr = dy + static_cast<long long>(blockIdx.x) * dy_ld;
+  __nv_bfloat16* dr = dx + static_cast<long long>(blockIdx.x) * dx_ld;
+  float s = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) s += __bfloat162float(yr[c]) * __bfloat162float(gr[c]);
+  s = block_reduce(s, false, red);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    const float yv = __bfloat162float(yr[c]);
+    dr[c] = __float2bfloat16_rn(scale * yv * (__bfloat162float(gr[c]) - s));
+  }
+}
+
+// dst[n][c][r] = src[n][r][c]  (32 x 32 tiles through shared memory)
+__global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_img,
+                                      __nv_bfloat16* __restrict__ dst, long long dst_ld, long long dst_img, int R, int C) {
+  __shared__ __nv_bfloat16 tile[32][33];
+  const int n = blockIdx.z, r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  const __nv_bfloat16* s = src + n * src_img;
+  __nv_bfloat16* d = dst + n * dst_img;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    if (r < R && c < C) tile[i][threadIdx.x] = s[static_cast<long long>(r) * src_ld + c];
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < C) d[static_cast<long long>(c) * dst_ld + r] = tile[threadIdx.x][i];
+  }
+}
+
+// C[n][m][j] = sum_k A[n][m][k] * B[n][j][k]   (small shapes only: 32 x 32 output tile per block, K in steps of 32)
+__global__ void bmm_tn_small_kernel(const __nv_bfloat16* __restrict__ A, long long lda, long long a_img,
+                                    const __nv_bfloat16* __restrict__ B, long long ldb, long long b_img,
+                                    __nv_bfloat16* __restrict__ Cm, long long ldc, long long c_img, int M, int K, int J) {
+  __shared__ float as[32][33], bs[32][33];
+  const int n = blockIdx.z, m0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const __nv_bfloat16* a = A + n * a_img;
+  const __nv_bfloat16* b = B + n * b_img;
+  const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k0 = 0; k0 < K; k0 += 32) {
+    for (int i = ty; i < 32; i += 8) {
+      const int k = k0 + tx;
+      as[i][tx] = (m0 + i < M && k < K) ? __bfloat162float(a[static_cast<long long>(m0 + i) * lda + k]) : 0.f;
+      bs[i][tx] = (j0 + i < J && k < K) ? __bfloat162float(b[static_cast<long long>(j0 + i) * ldb + k]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int mi = ty + 8 * q;
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) s = fmaf(as[mi][k], bs[tx][k], s);
+      acc[q] += s;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int m = m0 + ty + 8 * q, j = j0 + tx;
+    if (m < M && j < J) Cm[n * c_img + static_cast<long long>(m) * ldc + j] = __float2bfloat16_rn(acc[q]);
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_bmm_tn_small(const void* A, long long lda, long long a_img, const void* B, long long ldb,
+                                long long b_img, void* C, long long ldc, long long c_img, int N, int M, int K, int J,
+                                cudaStream_t st) {
+  dim3 grid((J + 31) / 32, (M + 31) / 32, N), block(32, 8);
+  bmm_tn_small_kernel<<<grid, block, 0, st>>>(static_cast<const __nv_bfloat16*>(A), lda, a_img,
+                                              static_cast<const __nv_bfloat16*>(B), ldb, b_img,
+                                              static_cast<__nv_bfloat16*>(C), ldc, c_img, M, K, J);
+  return cudaGetLastError();
+}
+}  // namespace uz
+
+using namespace uz;
+
+extern "C" int uz_softmax_rows(const void* x, long long x_ld, void* y, long long y_ld, long long rows, int cols,
+                               float scale, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!x || !y || rows < 1 || cols < 1 || rows > 0x7fffffffLL || x_ld < cols || y_ld < cols)
+    return set_error(UZ_ERR_INVALID, "softmax_rows: bad extents rows=%lld cols=%d", rows, cols);
+  const int threads = cols >= 1024 ? 256 : cols >= 256 ? 128 : 64;
+  softmax_rows_kernel<<<static_cast<int>(rows), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_ld, static_cast<__nv_bfloat16*>(y), y_ld, cols, scale);
+  PW_CHECK_LAUNCH("softmax_rows launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_softmax_rows_bwd(const void* y, long long y_ld, const void* dy, long long dy_ld, void* dx,
+                                   long long dx_ld, long long rows, int cols, float scale, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!y || !dy || !dx || rows < 1 || cols < 1 || rows > 0x7fffffffLL || y_ld < cols || dy_ld < cols || dx_ld < cols)
+    return set_error(UZ_ERR_INVALID, "softmax_rows_bwd: bad extents rows=%lld cols=%d", rows, cols);
+  const int threads = cols >= 1024 ? 256 : cols >= 256 ? 128 : 64;
+  softmax_rows_bwd_kernel<<<static_cast<int>(rows), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(y), y_ld, static_cast<const __nv_bfloat16*>(dy), dy_ld,
+      static_cast<__nv_bfloat16*>(dx), dx_ld, cols, scale);
+  PW_CHECK_LAUNCH("softmax_rows_bwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_transpose_bf16(const void* src, long long src_ld, long long src_img, void* dst, long long dst_ld,
+                                 long long dst_img, int N, int R, int C, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!src || !dst || N < 1 || R < 1 || C < 1 || src_ld < C || dst_ld < R || N > 65535)
+    return set_error(UZ_ERR_INVALID, "transpose_bf16: bad extents N=%d R=%d C=%d", N, R, C);
+  dim3 grid((C + 31) / 32, (R + 31) / 32, N), block(32, 8);
+  transpose_bf16_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(src), src_ld, src_img, static_cast<__nv_bfloat16*>(dst), dst_ld, dst_img, R, C);
+  PW_CHECK_LAUNCH("transpose_bf16 launch");
+  return UZ_OK;
+}

@@ -17,6 +17,9 @@ cudaError_t launch_igemm_fwd2(const Igemm2Params& p, int bn, int grid, int smem_
 cudaError_t launch_igemm_wgrad(const WgradParams& p, int grid, cudaStream_t stream);
 cudaError_t launch_igemm_wgrad2(const Wgrad2Params& p, int grid, cudaStream_t stream);
 cudaError_t launch_wgrad2_reduce(const Wgrad2Params& p, float* dst, long long s_row, int accumulate, cudaStream_t stream);
+cudaError_t launch_bmm_tn_small(const void* A, long long lda, long long a_img, const void* B, long long ldb,
+                                long long b_img, void* C, long long ldc, long long c_img, int N, int M, int K, int J,
+                                cudaStream_t st);
 cudaError_t launch_wgrad_reduce(const float* partial, float* dst, int splits, int rows, int taps, int cols,
                                 long long s_row, long long s_col, long long s_tap, int accumulate,
                                 cudaStream_t stream);
@@ -694,6 +697,87 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   const int grid = p.total_tiles < sms ? p.total_tiles : sms;
   cudaError_t e = launch_igemm_fwd(p, bn, grid, st);
   if (e != cudaSuccess) return cuda_error(e, "igemm_fwd launch");
+  return UZ_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ batched TN GEMM
+// C[n][m][j] = sum_k A[n][m][k] * B[n][j][k]  (bf16, fp32 accumulation) - the matrix products of the attention
+// bottlenecks (torch.bmm / matmul in transatt_unet.py:49-53,99-105, unet_transformer.py:131-135,214-217).  A is read like
+// an NHWC activation whose "image" n has M pixels of K channels (W = 8, H = M / 8: a 128-pixel tile is 128 consecutive
+// rows), B is the 1x1 kernel's weight operand with one matrix PER IMAGE (Igemm2Params::b_batched), C its output.
+// Shapes below one tile, or not multiples of 8, run on a plain CUDA-core kernel (csrc/attention.cu).
+extern "C" int uz_bmm_tn(const void* A, long long lda, long long a_img, const void* B, long long b_img, void* C,
+                         long long ldc, long long c_img, int N, int M, int K, int J, void* stream) {
+  const int sms = uz_device_sm_count();
+  if (sms < 0) return sms;
+  if (!A || !B || !C || N < 1 || M < 1 || K < 1 || J < 1 || lda < K || ldc < J)
+    return set_error(UZ_ERR_INVALID, "bmm_tn: bad extents N=%d M=%d K=%d J=%d", N, M, K, J);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool fast = M >= 128 && (M % 8) == 0 && (K % 8) == 0 && (J % 8) == 0 && (lda % 8) == 0 && (ldc % 8) == 0 &&
+                    a_img == static_cast<long long>(M) * lda && c_img == static_cast<long long>(M) * ldc &&
+                    (b_img % 8) == 0 && b_img >= static_cast<long long>(J) * K && aligned16(A) && aligned16(B) &&
+                    aligned16(C) && N < 65536 && !env_int("UZ_BMM_SMALL", 0);
+  if (!fast) {
+    cudaError_t e = launch_bmm_tn_small(A, lda, a_img, B, K, b_img, C, ldc, c_img, N, M, K, J, st);
+    if (e != cudaSuccess) return cuda_error(e, "bmm_tn_small launch");
+    return UZ_OK;
+  }
+  Igemm2Params p;
+  memset(&p, 0, sizeof(p));
+  const int H = M / 8, W = 8;
+  p.pad = 0;
+  p.halo_w = 8;
+  p.halo_bytes = 8 * 16 * 128;
+  p.num_taps = 1;
+  p.num_segs = 1;
+  p.seg_cblocks[0] = (K + 63) / 64;
+  p.seg_klast[0] = (K - (p.seg_cblocks[0] - 1) * 64 + 15) / 16;
+  p.seg_taps[0] = 1;
+  p.kblocks = p.b_items = p.seg_cblocks[0];
+  p.N = N; p.H = H; p.W = W;
+  p.xb = 1;
+  p.yb = (H + 15) / 16;
+  p.m_tiles_real = N * p.yb;
+  const int bn = J <= 64 ? 64 : J <= 128 ? 128 : 256;
+  p.num_n_tiles = (J + bn - 1) / bn;
+  p.mp = 1;
+  p.cluster = 1;
+  p.b_batched = 1;
+  p.m_tiles = p.m_tiles_real;
+  p.total_tiles = p.m_tiles * p.num_n_tiles;
+  p.ragged = (H % 16) != 0 ? 1 : 0;
+  const int kMaxSmem = 232448 - 1024, kTail = 2560;
+  const int a_slot = p.halo_bytes, b_item = bn * 128;
+  p.stg_bufs = 2;
+  p.a_stages = 4;
+  int bs = (kMaxSmem - kTail - p.stg_bufs * 16384 - p.a_stages * a_slot) / b_item;
+  p.b_stages = bs > 8 ? 8 : bs;
+  p.a_off = 0;
+  p.b_off = p.a_stages * a_slot;
+  p.stg_off = p.b_off + p.b_stages * b_item;
+  p.bar_off = p.stg_off + p.stg_bufs * 16384;
+  const int smem_bytes = p.bar_off + kTail + 1024;
+  const Lattice full = {0, 0, 1};
+  int rc = make_act_map(&p.amap[0], A, K, (int)lda, N, H, W, full, 8, 16, 1);
+  if (rc != UZ_OK) return rc;
+  rc = make_act_map(&p.omap[0], C, J, (int)ldc, N, H, W, full, 8, 16, 1);
+  if (rc != UZ_OK) return rc;
+  {   // B: 3-D (K, image, row) - the image index takes the place of the filter tap
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)N, (cuuint64_t)J};
+    cuuint64_t strides[2] = {(cuuint64_t)b_img * 2, (cuuint64_t)K * 2};
+    cuuint32_t box[3] = {64, 1, (cuuint32_t)bn};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(&p.bmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(B), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(UZ_ERR_CUDA, "cuTensorMapEncodeTiled(bmm B K=%d N=%d J=%d) failed: %d", K, N, J, (int)r);
+  }
+  p.ncols = J;
+  int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  cudaError_t e = launch_igemm_fwd2(p, bn, grid, smem_bytes, st);
+  if (e != cudaSuccess) return cuda_error(e, "bmm_tn (igemm_fwd2) launch");
   return UZ_OK;
 }
 

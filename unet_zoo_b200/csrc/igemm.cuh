@@ -151,6 +151,8 @@ struct alignas(64) Igemm2Params {
                                // streamed-weight layers were capped at ~72 % tensor-active by SM ingest (~50 B/clk)
   int nt_per_phase;            // 0: N tiles walk the output columns.  > 0 (ConvTranspose2d k2s2 as four 1x1 GEMMs): N tile
                                // = (phase, column tile); the phase selects the weight "tap" coordinate and the output view
+  int b_batched;               // 1: batched GEMM (uz_bmm_tn): the "weight" operand differs per image - the B tensor map's tap
+                               // coordinate is the image index of the tile (ring mode, no CTA pair, no stationary weights)
   int ragged;                  // 1: some tile is partial (H % 16, W % 8) or a dummy (M tiles rounded up to the work-item
                                // size).  0: every tile is full - the epilogue threads then skip the tile decode (five
                                // integer divisions per tile; ncu showed the epilogue of the 64-channel 512^2 layers

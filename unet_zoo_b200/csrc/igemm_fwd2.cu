@@ -203,6 +203,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         for (int g = cidx; g < ngroups; g += nclusters) {
           int n_tile, m_unused;
           f2_item(p, g * cs, &n_tile, &m_unused);
+          const int b_image = p.b_batched ? f2_decode(p, g * cs, 0).n : -1;   // batched GEMM: this image's B matrix
           const int b_phase = p.nt_per_phase ? n_tile / p.nt_per_phase : -1;
           const int b_row0 = (p.nt_per_phase ? n_tile % p.nt_per_phase : n_tile) * BN;
           for (int seg = 0; seg < p.num_segs; ++seg) {
@@ -214,7 +215,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 mbar_wait(bempty(stage), phase ^ 1u);
                 if (leader) mbar_expect_tx(bfull(stage), kBItem * CG);
                 const uint32_t dst = b_base + stage * kBItem;
-                const int btap = b_phase >= 0 ? (p.ph_ntaps ? b_phase * 4 + tap : b_phase) : p.seg_tap_b[seg][tap];
+                const int btap = b_image >= 0 ? b_image
+                                 : b_phase >= 0 ? (p.ph_ntaps ? b_phase * 4 + tap : b_phase) : p.seg_tap_b[seg][tap];
                 if (kPair)
                   tma_load_3d_pair(dst, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows);
                 else if (cs == 1)

@@ -914,6 +914,51 @@ def _island_math(tf32: bool):
             mm.fp32_precision, cd.conv.fp32_precision = saved
 
 
+def token_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],
+                 out: Optional[Act] = None) -> Act:
+    """A sub-graph that works on the activation as bf16 TOKENS: ``fn`` maps ``[N, H*W, C]`` (the NHWC buffer seen flat, no
+    layout change) to ``[N, H*W, C']``.  Used for the attention bottlenecks, whose matrix products / softmaxes are the
+    library's own kernels wrapped as autograd Functions (unet_zoo_b200/attention.py); torch's autograd only chains them
+    and supplies the elementwise glue.  Gradients of `params` land in the flat gradient buffer."""
+    src = x.buf.data[..., x.c0:x.c0 + x.C]
+    xin = src.reshape(x.N, x.H * x.W, x.C).detach()
+    if not xin.is_contiguous():
+        xin = xin.contiguous()
+    if ctx.record:
+        xin.requires_grad_(True)
+        with torch.enable_grad():
+            y = fn(xin)
+    else:
+        y = fn(xin)
+    if y.dim() != 3 or y.shape[0] != x.N or y.shape[1] != x.H * x.W or y.dtype != torch.bfloat16:
+        raise RuntimeError(f"unet_zoo_b200: token island returned {tuple(y.shape)} {y.dtype} for {(x.N, x.H * x.W, x.C)}")
+    if out is None:
+        out = ctx.new_act(x.N, x.H, x.W, y.shape[2])
+    out.buf.data[..., out.c0:out.c0 + out.C].copy_(y.detach().reshape(x.N, x.H, x.W, -1))
+    if ctx.record:
+        params = [p for p in params if p.requires_grad]
+
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: token island output has no gradient")
+            dy = out.buf.grad_buf()[..., out.c0:out.c0 + out.C].reshape(x.N, x.H * x.W, -1)
+            grads = torch.autograd.grad([y], [xin] + params, [dy.contiguous()], allow_unused=True)
+            gx = x.buf.grad_buf()
+            dx = grads[0].reshape(x.N, x.H, x.W, x.C)
+            for (r0, rc, acc) in x.grad_writes():
+                dst = gx[..., x.c0 + r0:x.c0 + r0 + rc]
+                if acc:
+                    dst.add_(dx[..., r0:r0 + rc])
+                else:
+                    dst.copy_(dx[..., r0:r0 + rc])
+            for p, g in zip(params, grads[1:]):
+                if g is not None:
+                    c.pgrad(p).copy_(g)
+            c.pready(*params)
+        ctx.tape.append(backward)
+    return out
+
+
 def torch_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],
                  out: Optional[Act] = None) -> Act:
     """A sub-graph of stock torch ops between two fused operators: ``fn`` maps the NCHW fp32 image of `x` to an NCHW

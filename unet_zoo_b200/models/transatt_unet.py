@@ -17,6 +17,8 @@ hold the reference's parameter names and restate its math.
 ``ConvTranspose2d(1536, 768)`` for a 1024-channel input and the 512-channel position embedding is added to a
 1024-channel map, transatt_unet.py:121-135).
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -141,9 +143,34 @@ class TransAttUNet(HotPathModel):
         return super()._check_input(x)
 
     def _bottleneck(self, x5):
-        """transatt_unet.py:143-154 on an NCHW fp32 tensor (stock torch)."""
+        """transatt_unet.py:143-154 on an NCHW fp32 tensor (stock torch): the fp32 parity mode's path."""
         x5 = x5 + self.pos(x5)
         return self.sdpa(x5) + self.pam(x5)
+
+    def _bottleneck_tokens(self, t, h, w):
+        """The same bottleneck on bf16 tokens t [N, h*w, 512] with the library's own kernels (attention.py): every
+        matrix product is uz_bmm_tn, both softmaxes uz_softmax_rows.
+        Position embedding (transatt_unet.py:69-82), channel self-attention with q = k = v (:91-107), PAM (:40-55)."""
+        from .. import attention as A
+        n, hw, d = t.shape
+        if h > self.pos.row_embed.num_embeddings or w > self.pos.col_embed.num_embeddings:
+            raise RuntimeError(f"TransAttUNet: the bottleneck map {h}x{w} exceeds the learned position table")
+        cols = self.pos.col_embed.weight[:w][None, :, :].expand(h, w, -1)           # [h, w, F], constant over rows
+        rows = self.pos.row_embed.weight[:h][:, None, :].expand(h, w, -1)           # constant over columns
+        pos = torch.cat([cols, rows], dim=-1).reshape(1, hw, d)
+        t = (t.float() + pos).to(torch.bfloat16)                                     # x5 + pos
+        # channel attention: att[a, b] = softmax_b(sum_p f[a, p] f[b, p] / sqrt(T)), out[p, a] = sum_b att[a, b] f[b, p]
+        f = A.transpose(t)                                                           # [N, d, hw]
+        att = A.softmax_rows(A.bmm_tn(f, f), 1.0 / self.sdpa.temperature)
+        att = self.sdpa.dropout(att)
+        sdpa = A.bmm_tn(t, att)                                                      # [N, hw, d]
+        # PAM: energy[i, j] = q_i . k_j, att = softmax_j, out[i, c] = sum_j att[i, j] v[j, c]
+        q = A.linear_tokens(t, self.pam.query_conv.weight, self.pam.query_conv.bias)
+        k = A.linear_tokens(t, self.pam.key_conv.weight, self.pam.key_conv.bias)
+        v = A.linear_tokens(t, self.pam.value_conv.weight, self.pam.value_conv.bias)
+        patt = A.softmax_rows(A.bmm_tn(q, k), 1.0)                                   # [N, hw, hw]
+        pam = A.bmm_tn(patt, A.transpose(v))                                         # [N, hw, d]
+        return (self.pam.gamma * pam.float() + t.float() + sdpa.float()).to(torch.bfloat16)
 
     def _graph(self, ctx: E.Ctx, x):
         N, _, H, W = x.shape
@@ -162,7 +189,10 @@ class TransAttUNet(HotPathModel):
         (c1, b1), (c2, b2) = self.down4.maxpool_conv[1].units()
         x5 = E.conv_bn_act(ctx, [E.conv_bn_act(ctx, [cur], c1, b1)], c2, b2)
         island = [p for m in (self.pos, self.pam) for p in m.parameters()]
-        cur = E.torch_island(ctx, x5, self._bottleneck, island)
+        if ctx.fp32 or os.environ.get("UZ_TRANSATT_TORCH_ISLAND"):
+            cur = E.torch_island(ctx, x5, self._bottleneck, island)      # fp32 parity mode: strict fp32 torch math
+        else:
+            cur = E.token_island(ctx, x5, lambda t: self._bottleneck_tokens(t, x5.H, x5.W), island)
         for j, up in enumerate((self.up1, self.up2, self.up3, self.up4)):
             lvl = 3 - j
             E.bilinear_up2x(ctx, cur, E.Act(cats[lvl], widths[lvl], below[lvl]))
