@@ -73,6 +73,24 @@ def test_linear_tokens_matches_conv1x1():
     assert relmax(y.float(), ref) < 1e-2
 
 
+@pytest.mark.parametrize("N,T,K,J", [(4, 1024, 512, 64), (2, 1024, 512, 512), (2, 16, 512, 64), (3, 256, 64, 256)])
+def test_linear_tokens_gradients(N, T, K, J):
+    """Input and weight gradient (per-image orientation with the larger of K, J as rows) against torch fp32."""
+    w = torch.nn.Parameter(bf16r(torch.randn(J, K, 1, 1, device=DEV) * 0.05))
+    bias = torch.nn.Parameter(torch.randn(J, device=DEV) * 0.1)
+    t = bf16r(torch.randn(N, T, K, device=DEV)).to(torch.bfloat16).requires_grad_(True)
+    y = A.linear_tokens(t, w, bias)
+    tr, wr, br = t.detach().float().requires_grad_(True), w.detach().clone().requires_grad_(True), bias.detach().clone().requires_grad_(True)
+    ref = tr @ wr.reshape(J, K).t() + br
+    g = bf16r(torch.randn_like(ref) * 0.1)
+    y.backward(g.to(torch.bfloat16))
+    ref.backward(g)
+    assert relmax(y.float(), ref.detach()) < 1e-2
+    assert rel_l2(t.grad.float(), tr.grad) < 1e-2
+    assert rel_l2(w.grad, wr.grad) < 1e-2 and w.grad.shape == w.shape
+    assert rel_l2(bias.grad, br.grad) < 1e-2
+
+
 def test_cpu_tensors_are_rejected():
     with pytest.raises(RuntimeError, match="no CPU path"):
         A.bmm_tn(torch.zeros(1, 128, 8, dtype=torch.bfloat16), torch.zeros(1, 8, 8, dtype=torch.bfloat16))

@@ -114,12 +114,42 @@ def softmax_rows(x, scale: float = 1.0):
     return _Softmax.apply(x, scale)
 
 
+class _LinearTokens(torch.autograd.Function):
+    """y[n, t, j] = sum_k x[n, t, k] * w[j, k] with ONE weight matrix for all tokens.  The weight gradient is taken per
+    image in the orientation whose row count is the larger of (K, J) - dW^T[n] = x[n]^T g[n] as a [K, J] product over the
+    image's tokens - so that it runs on the tensor-core path with N x (K / 128) tiles (a single [J, K] product over all
+    N * T tokens has J = 64 rows for the PAM query / key projections: below one tile, and no parallelism over K)."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        n, tok, k = x.shape
+        ctx.save_for_backward(x, w)
+        return bmm_tn_raw(x.reshape(1, n * tok, k), w[None]).reshape(n, tok, -1)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        n, tok, k = x.shape
+        g = _check(g, "grad")
+        j = g.shape[2]
+        dx = dw = None
+        if ctx.needs_input_grad[0]:            # dx[t, k] = sum_j g[t, j] * w[j, k]
+            dx = bmm_tn_raw(g.reshape(1, n * tok, j), transpose_raw(w[None])).reshape(n, tok, k)
+        if ctx.needs_input_grad[1]:
+            xt, gt = transpose_raw(x), transpose_raw(g)          # [N, K, T], [N, J, T]
+            if k >= j:
+                dw = bmm_tn_raw(xt, gt).float().sum(0).t()        # [N, K, J] -> [J, K]
+            else:
+                dw = bmm_tn_raw(gt, xt).float().sum(0)
+            dw = dw.to(w.dtype)
+        return dx, dw
+
+
 def linear_tokens(t, weight, bias=None):
     """``t @ weight.T + bias`` for tokens t [N, T, K] (bf16) and an fp32 parameter weight [J, K] (a 1x1 Conv2d's weight
     viewed as a matrix): one product over all N * T tokens with the weight as the single B matrix."""
-    n, tok, k = t.shape
-    w = weight.reshape(weight.shape[0], -1).to(torch.bfloat16)[None]
-    y = bmm_tn(t.reshape(1, n * tok, k), w).reshape(n, tok, -1)
+    w = weight.reshape(weight.shape[0], -1).to(torch.bfloat16)
+    y = _LinearTokens.apply(_check(t, "t"), w)
     if bias is not None:
         y = (y.float() + bias).to(torch.bfloat16)
     return y
