@@ -91,6 +91,15 @@ int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, const void* dp
 size_t uz_colsum_workspace_bytes(int C);
 int uz_colsum(const void* x, int ld, long long npix, int C, float* out, int accumulate, void* workspace,
               size_t workspace_bytes, void* stream);
+/* uz_colsum_static: uz_colsum WITHOUT a workspace argument, for callers that cannot allocate one (CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The per-block partial sums live in a file-scope device array inside the library (2.5 MiB per device that
+ * loads the library, held until exit); the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limit: C <= uz_colsum_static_max_channels() (1024); larger C returns UZ_ERR_WORKSPACE - use uz_colsum.
+ * All calls on one device share the array: calls that OVERLAP on the GPU (different streams, no ordering) race;
+ * calls ordered on one stream, or by events, are safe.  Nothing in the array needs to start at zero. */
+int uz_colsum_static_max_channels(void);
+int uz_colsum_static(const void* x, int ld, long long npix, int C, float* out, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * 1x1 classifier head: logits[n,k,h,w] (fp32, NCHW) = b[k] + sum_c w[k,c] * y[n,h,w,c]   (no activation)

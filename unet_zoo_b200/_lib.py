@@ -42,6 +42,8 @@ _PROTOS = {
                           c_int, _P, c_size_t, _P]),
     "uz_colsum_workspace_bytes": (c_size_t, [c_int]),
     "uz_colsum": (c_int, [_P, c_int, c_longlong, c_int, _P, c_int, _P, c_size_t, _P]),
+    "uz_colsum_static_max_channels": (c_int, []),
+    "uz_colsum_static": (c_int, [_P, c_int, c_longlong, c_int, _P, c_int, _P]),
     "uz_gate_psi_fwd": (c_int, [_P, c_int, _P, c_int, c_longlong, c_int, _P, _P, _P, _P, _P, _P, _P]),
     "uz_gate_apply": (c_int, [_P, c_int, _P, _P, c_longlong, c_int, _P, c_int, _P]),
     "uz_gate_bwd_workspace_bytes": (c_size_t, [c_longlong, c_int]),

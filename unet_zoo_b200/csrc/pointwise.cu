@@ -1028,3 +1028,55 @@ extern "C" int uz_colsum(const void* x, int ld, long long npix, int C, float* ou
   UZ_CHECK_LAUNCH("colsum reduce launch");
   return UZ_OK;
 }
+
+// ---------------------------------------------------------------------------------- uz_colsum without a workspace
+// Same two kernels as uz_colsum, with the per-block partial sums in a file-scope device array instead of a caller
+// buffer: for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// Every device that loads the library holds the array (kNoAllocRows x kNoAllocMaxC fp32 = 2.5 MiB) until exit.
+// All calls on a device share it; colsum_kernel writes every row reduce_rows_kernel reads (rows = the launch's grid),
+// so nothing has to start at zero, and the previous call's contents are never read.
+namespace {
+constexpr int kNoAllocMaxC = 1024;   // widest channel count of the hot-path models (bottle_neck)
+constexpr int kNoAllocRows = 640;    // >= 4 blocks per SM on 148 SMs (592); larger devices get a clamped grid
+static __device__ __align__(256) float g_colsum_scratch[static_cast<size_t>(kNoAllocRows) * kNoAllocMaxC];
+float* g_colsum_scratch_ptr[uz::kMaxDevices] = {};   // device address of the array above, per device (host-side cache)
+
+// `g_colsum_scratch` in HOST code is only a handle: its device address comes from cudaGetSymbolAddress, once per device,
+// with that device current.
+int colsum_scratch(float** out) {
+  const int slot = uz::device_slot();
+  if (!g_colsum_scratch_ptr[slot]) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_scratch);
+    if (e != cudaSuccess) return uz::cuda_error(e, "colsum_static: cudaGetSymbolAddress");
+    if (!p) return uz::set_error(UZ_ERR_CUDA, "colsum_static: null scratch address");
+    g_colsum_scratch_ptr[slot] = p;
+  }
+  *out = g_colsum_scratch_ptr[slot];
+  return UZ_OK;
+}
+}  // namespace
+
+extern "C" int uz_colsum_static_max_channels(void) { return kNoAllocMaxC; }
+
+extern "C" int uz_colsum_static(const void* x, int ld, long long npix, int C, float* out, int accumulate, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("colsum_static", x, C, ld);
+  if (rc) return rc;
+  if (!out || npix < 1) return set_error(UZ_ERR_INVALID, "colsum_static: bad arguments");
+  if (C > kNoAllocMaxC)
+    return set_error(UZ_ERR_WORKSPACE, "colsum_static: C=%d exceeds the built-in scratch (max %d channels); use uz_colsum",
+                     C, kNoAllocMaxC);
+  float* scratch = nullptr;
+  rc = colsum_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Geo g = make_geo(C, npix, 4);
+  if (g.grid > kNoAllocRows) g.grid = kNoAllocRows;   // grid-stride kernel: any grid covers all pixels
+  colsum_kernel<<<g.grid, g.block, g.block * 8 * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), ld, npix, C,
+                                                                      g.cv, g.ppb, scratch);
+  UZ_CHECK_LAUNCH("colsum_static launch");
+  reduce_rows_kernel<<<(C + 3) / 4, 128, 0, st>>>(scratch, g.grid, C, out, accumulate);
+  UZ_CHECK_LAUNCH("colsum_static reduce launch");
+  return UZ_OK;
+}
