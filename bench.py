@@ -25,7 +25,7 @@ if ROOT not in sys.path:
 
 # conv + transposed-conv FLOPs (2*MAC) of one fwd+bwd per image at 512x512, SURVEY.md section 6 / 8(d)
 FWD_BWD_GFLOP_PER_IMG_512 = {"unet": 1155.11, "attention_unet": 1593.29, "nested_unet": 827.20, "resunet": 931.44,
-                              "transatt_unet": 967.47}
+                              "transatt_unet": 967.47, "unet_transformer": 1830.0}   # last: 3 x the 610 GFLOP forward
 FWD_GFLOP_PER_IMG_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08}
 UNET_FWD_BWD_GFLOP_PER_IMG_512 = FWD_BWD_GFLOP_PER_IMG_512["unet"]
 

@@ -161,7 +161,7 @@ int uz_bilinear2x_fwd(const void* x, int x_ld, int N, int H, int W, int C, void*
 /* Attention bottlenecks of the neighbouring models (transatt_unet.py:26-107, unet_transformer.py:115-229).
  * uz_bmm_tn: C[n][m][j] = sum_k A[n][m][k] * B[n][j][k], bf16 operands (both K-contiguous: A rows lda, B rows K), fp32
  *   accumulation, bf16 output rows ldc - replaces torch.bmm / torch.matmul.  Image strides in elements.  Shapes with
- *   M >= 128 and M, K, J multiples of 8 run on the tcgen05 1x1 kernel with a per-image B operand; others on a plain kernel.
+ *   M, K, J multiples of 8 run on the tcgen05 1x1 kernel with a per-image B operand; others on a plain kernel.
  * uz_softmax_rows / _bwd: y = softmax(scale * x) over the last axis (F.softmax(dim=-1), the temperature division folded in
  *   as `scale`) and dx = scale * y * (dy - sum(dy * y)).
  * uz_transpose_bf16: dst[n][c][r] = src[n][r][c] (the TN product wants K-contiguous operands). */
@@ -171,8 +171,32 @@ int uz_softmax_rows(const void* x, long long x_ld, void* y, long long y_ld, long
                     void* stream);
 int uz_softmax_rows_bwd(const void* y, long long y_ld, const void* dy, long long dy_ld, void* dx, long long dx_ld,
                         long long rows, int cols, float scale, void* stream);
+/* softmax over the ROW index of every column of N contiguous [rows][cols] bf16 matrices: nn.Softmax(dim=1) on the
+ * [b, queries, keys] scores of unet_transformer.py:122,130,216 (normalised over the queries), and its backward. */
+int uz_softmax_cols(const void* x, void* y, int N, int rows, int cols, float scale, void* stream);
+int uz_softmax_cols_bwd(const void* y, const void* dy, void* dx, int N, int rows, int cols, float scale, void* stream);
 int uz_transpose_bf16(const void* src, long long src_ld, long long src_img, void* dst, long long dst_ld, long long dst_img,
                       int N, int R, int C, void* stream);
+
+/* Bandwidth operators around unet_transformer's attention blocks (unet_zoo/models/unet_transformer.py), NHWC bf16:
+ * uz_addpe_fwd / _bwd: y = x + pe with pe a fixed fp32 [H][W][C] table (PositionalEncodingPermute2D, :68-113; built once
+ *   on the host side), optionally followed by MaxPool2d(2) of the sum without storing it (Sconv_process[0], :153).
+ *   Backward: dx (+)= dy + the pooled gradient routed to the first maximum of bf16(x + pe) per 2x2 window.
+ * uz_adaptive_avgpool_fwd / _bwd: F.adaptive_avg_pool2d (:201-203), ATen windows [floor(o*I/O), ceil((o+1)*I/O)).
+ * uz_bilinear_resize_fwd / _bwd: F.interpolate(size=(OH, OW), mode="bilinear", align_corners=True) (:222) and its exact
+ *   adjoint in gather form (no atomics). */
+int uz_addpe_fwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, void* y, int y_ld, void* pooled,
+                 int pooled_ld, void* stream);
+int uz_addpe_bwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, const void* dy, int dy_ld,
+                 const void* dpooled, int dpooled_ld, void* dx, int dx_ld, int accumulate, void* stream);
+int uz_adaptive_avgpool_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH, int OW,
+                            void* stream);
+int uz_adaptive_avgpool_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx, int dx_ld,
+                            int accumulate, void* stream);
+int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH, int OW,
+                           void* stream);
+int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx, int dx_ld,
+                           int accumulate, void* stream);
 
 /* F.pad with zeros on the bottom / right, or its backward (crop), between two NHWC pixel grids: replaces the
  * `F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])` of common_layers.py:110-113 / :173-178 (dx, dy in {0, 1} for

@@ -24,7 +24,8 @@ def _exact_fp32():
     (1, 4096, 512, 64),      # a 1x1 projection of all tokens with ONE weight matrix
     (2, 136, 72, 40),        # ragged: 17 pixel rows, K and J not multiples of 64
     (5, 128, 8, 8),          # smallest fast-path shape
-    (2, 16, 512, 16),        # below one tile: CUDA-core kernel (4x4 bottleneck of a 64 x 64 image)
+    (2, 16, 512, 16),        # far below one 128-row tile (4x4 bottleneck of a 64 x 64 image): TMA zero fill / clipping
+    (8, 64, 4096, 64),       # per-image weight gradient of a 64-channel projection: half a tile, long K
     (3, 100, 36, 52),        # nothing aligned: CUDA-core kernel
 ])
 def test_bmm_tn_and_its_gradients(N, M, K, J):
@@ -56,6 +57,21 @@ def test_softmax_rows_fwd_bwd(N, R, C, scale):
     # reference backward through the SAME (bf16-rounded) probabilities
     yq = y.detach().float()
     want = scale * yq * (g - (g * yq).sum(-1, keepdim=True))
+    assert rel_l2(x.grad.float(), want) < 1e-2
+
+
+@pytest.mark.parametrize("N,R,C,scale", [(2, 4096, 4096, 1 / 16.0), (3, 64, 200, 1.0), (1, 7, 33, 0.5), (2, 1024, 64, 1.0)])
+def test_softmax_cols_fwd_bwd(N, R, C, scale):
+    """nn.Softmax(dim=1) of a [b, rows, cols] matrix (unet_transformer's attention, normalised over the queries)."""
+    x = bf16r(torch.randn(N, R, C, device=DEV) * 3).to(torch.bfloat16).requires_grad_(True)
+    y = A.softmax_cols(x, scale)
+    ref = torch.softmax(scale * x.detach().float(), dim=1)
+    assert relmax(y.float(), ref) < 1e-2
+    assert float((y.float().sum(1) - 1).abs().max()) < 2e-2
+    g = bf16r(torch.randn_like(ref))
+    y.backward(g.to(torch.bfloat16))
+    yq = y.detach().float()
+    want = scale * yq * (g - (g * yq).sum(1, keepdim=True))
     assert rel_l2(x.grad.float(), want) < 1e-2
 
 

@@ -21,13 +21,14 @@ pytestmark = pytest.mark.gpu
 LOGIT_TOL_BF16 = 2e-2
 MASK_AGREE = 0.999
 CASES = [("attention_unet", {}), ("nested_unet", {}), ("nested_unet_ds", {"deep_supervision": True}), ("resunet", {}),
-         ("transatt_unet", {"attn_dropout": 0.0})]     # SURVEY 8(f) rank 4; attention dropout off: CPU / CUDA RNGs differ
+         ("transatt_unet", {"attn_dropout": 0.0}),     # SURVEY 8(f) rank 4; attention dropout off: CPU / CUDA RNGs differ
+         ("unet_transformer", {})]
 # Fixed gradient bars on the conditioned state, rel. L2 vs the reference's fp32 gradients: (all conv weights
 # concatenated, worst single tensor).  What they absorb is bf16 rounding of the saved activations and of dL/dy at every
 # layer on the way down (torch's bf16 autocast of the reference: 0.04-0.22 per tensor, tools/parity_floor.py); a sign
 # error, a dropped term or a wrong tap gives >= 1.
 GRAD_BARS = {"attention_unet": (0.25, 0.4), "nested_unet": (0.2, 0.3), "nested_unet_ds": (0.2, 0.3),
-             "resunet": (0.08, 0.12), "transatt_unet": (0.2, 0.3)}
+             "resunet": (0.08, 0.12), "transatt_unet": (0.2, 0.3), "unet_transformer": (0.4, 0.7)}     # the latter: see the exception in the train test
 
 
 def _as_list(o):
@@ -64,7 +65,13 @@ def test_train_step_against_the_reference_fixture(tag, kw):
     parity_report("models64_train/" + tag, logits=errs, agree=agree, grad_all=e_all, grad_worst=per[:3])
     for o, g in zip(outs, cond["logits_train"]):
         assert o.shape == g.shape and o.dtype == torch.float32
-    if tag == "nested_unet_ds":
+    if tag == "unet_transformer":
+        # second fixed exception: at random weights the attention of every MHCA is near-uniform over the 4096 queries,
+        # so its output is almost constant over pixels and the BatchNorm of conv_after_attention (:168-171) normalises
+        # rounding noise - torch's bf16 autocast of the reference deviates 4.2 % (64^2) to 7 % (128^2) from fp32 on this
+        # state (tools/parity_floor.py), this path 6.6 %.  Eval mode (running statistics) meets the plain 2e-2 below.
+        assert max(errs) < 1e-1 and min(agree) >= 0.98, (errs, agree)
+    elif tag == "nested_unet_ds":
         # the one fixed exception of this file (same as at 512 x 512): the supervised heads 2-4 hang off shallow nodes
         # whose logits are centred ON the threshold (about half of the pixels positive) - 2.0 % / 99.5 % measured
         assert max(errs) < 3e-2 and errs[0] < LOGIT_TOL_BF16 and min(agree) >= 0.99, (errs, agree)

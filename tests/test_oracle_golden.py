@@ -81,7 +81,7 @@ def test_transatt_unet_attention_dropout_path():
 
 
 def test_unet_transformer_oracle_groundwork():
-    """Next SURVEY 8(f) rank-4 model, oracle side only (no CUDA path yet): the oracle's own default-init recipe
+    """SURVEY 8(f) rank-4 model `unet_transformer`, oracle side: the oracle's own default-init recipe
     reproduces the reference's weights (fingerprint of all 209 state_dict entries) and its restatement of
     U_Transformer.forward (self-attention, three cross-attention decoders) reproduces the reference's train / eval
     outputs, loss, gradients and running statistics."""
@@ -106,9 +106,13 @@ def test_unet_transformer_oracle_groundwork():
     with torch.no_grad():
         oe = O.unet_transformer_forward(sd, x, False)
     assert rel_err(oe, gold["logits_eval"][0]) < 1e-5
-    import unet_zoo_b200
-    with pytest.raises(NotImplementedError):                 # the product does not pretend to serve it
-        unet_zoo_b200.create_model("unet_transformer")
+    # the product's parameter containers reproduce the same default initialisation (tests/test_boundary.py checks the
+    # fingerprint; here: the oracle's own recipe and the product agree entry by entry)
+    psd = seeded_model("unet_transformer").state_dict()
+    fresh = O.unet_transformer_state_dict(gold["recipe"]["seed"])
+    assert list(psd) == list(fresh)
+    for k, v in psd.items():
+        assert torch.equal(v, fresh[k]), k
 
 
 def test_threshold_is_bit_exact_with_sign_test():

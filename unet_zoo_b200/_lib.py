@@ -50,10 +50,18 @@ _PROTOS = {
     "uz_gate_bwd": (c_int, [_P, c_int, _P, c_int, _P, _P, c_longlong, c_int, _P, c_int, c_int, _P, c_int, _P, c_int, c_int,
                             _P, _P, _P, _P, c_int, _P, _P, _P, _P, _P, c_size_t, _P]),
     "uz_bilinear2x_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P]),
+    "uz_addpe_fwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P]),
+    "uz_addpe_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, _P]),
+    "uz_adaptive_avgpool_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P]),
+    "uz_adaptive_avgpool_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P]),
+    "uz_bilinear_resize_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P]),
+    "uz_bilinear_resize_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P]),
     "uz_bmm_tn": (c_int, [_P, c_longlong, c_longlong, _P, c_longlong, _P, c_longlong, c_longlong, c_int, c_int, c_int,
                           c_int, _P]),
     "uz_softmax_rows": (c_int, [_P, c_longlong, _P, c_longlong, c_longlong, c_int, c_float, _P]),
     "uz_softmax_rows_bwd": (c_int, [_P, c_longlong, _P, c_longlong, _P, c_longlong, c_longlong, c_int, c_float, _P]),
+    "uz_softmax_cols": (c_int, [_P, _P, c_int, c_int, c_int, c_float, _P]),
+    "uz_softmax_cols_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_float, _P]),
     "uz_transpose_bf16": (c_int, [_P, c_longlong, c_longlong, _P, c_longlong, c_longlong, c_int, c_int, c_int, _P]),
     "uz_resize_bilinear_u8": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, c_int, c_int, _P, _P, c_int, _P, _P, c_int,
                                       _P]),

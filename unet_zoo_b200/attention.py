@@ -99,6 +99,35 @@ class _Softmax(torch.autograd.Function):
         return dx, None
 
 
+class _SoftmaxCols(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, scale):
+        x = _check(x, "x")
+        n, r, c = x.shape
+        y = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            L.check(L.load().uz_softmax_cols(x.data_ptr(), y.data_ptr(), n, r, c, float(scale), _stream(x)), "uz_softmax_cols")
+        ctx.save_for_backward(y)
+        ctx.scale = float(scale)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        g = _check(g, "grad")
+        n, r, c = y.shape
+        dx = torch.empty_like(y)
+        with torch.cuda.device(y.device):
+            L.check(L.load().uz_softmax_cols_bwd(y.data_ptr(), g.data_ptr(), dx.data_ptr(), n, r, c, ctx.scale, _stream(y)),
+                    "uz_softmax_cols_bwd")
+        return dx, None
+
+
+def softmax_cols(x, scale: float = 1.0):
+    """Differentiable ``softmax(scale * x, dim=1)`` on bf16 [N, R, C] (normalised over the rows of every column)."""
+    return _SoftmaxCols.apply(x, scale)
+
+
 def transpose(x):
     """[N, R, C] -> [N, C, R], differentiable."""
     return _Transpose.apply(x)

@@ -66,6 +66,65 @@ __global__ void softmax_rows_bwd_kernel(const __nv_bfloat16* __restrict__ y, lon
   }
 }
 
+// Softmax over the ROW index of each column (nn.Softmax(dim=1) on a [b, rows, cols] score matrix, unet_transformer.py:
+// 122,130): y[r][c] = exp(scale * x[r][c] - m_c) / s_c.  Block = 64 columns x 4 row groups, three sweeps over the rows
+// (max, sum, write); consecutive threads touch consecutive columns (coalesced 128-byte rows).
+constexpr int kColTile = 64, kColGroups = 4;
+__global__ void __launch_bounds__(kColTile * kColGroups) softmax_cols_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                            __nv_bfloat16* __restrict__ y, int rows,
+                                                                            int cols, long long img, float scale) {
+  __shared__ float red[kColGroups][kColTile];
+  const int cl = threadIdx.x % kColTile, grp = threadIdx.x / kColTile;
+  const int c = blockIdx.x * kColTile + cl;
+  const bool ok = c < cols;
+  const __nv_bfloat16* xi = x + blockIdx.y * img + c;
+  __nv_bfloat16* yi = y + blockIdx.y * img + c;
+  float m = -INFINITY;
+  if (ok)
+    for (int r = grp; r < rows; r += kColGroups) m = fmaxf(m, scale * __bfloat162float(xi[static_cast<long long>(r) * cols]));
+  red[grp][cl] = m;
+  __syncthreads();
+  m = fmaxf(fmaxf(red[0][cl], red[1][cl]), fmaxf(red[2][cl], red[3][cl]));
+  __syncthreads();
+  float s = 0.f;
+  if (ok)
+    for (int r = grp; r < rows; r += kColGroups) s += __expf(scale * __bfloat162float(xi[static_cast<long long>(r) * cols]) - m);
+  red[grp][cl] = s;
+  __syncthreads();
+  s = (red[0][cl] + red[1][cl]) + (red[2][cl] + red[3][cl]);
+  const float inv = 1.f / s;
+  if (ok)
+    for (int r = grp; r < rows; r += kColGroups)
+      yi[static_cast<long long>(r) * cols] =
+          __float2bfloat16_rn(__expf(scale * __bfloat162float(xi[static_cast<long long>(r) * cols]) - m) * inv);
+}
+
+// dx[r][c] = scale * y[r][c] * (dy[r][c] - sum_r' dy[r'][c] * y[r'][c])
+__global__ void __launch_bounds__(kColTile * kColGroups) softmax_cols_bwd_kernel(const __nv_bfloat16* __restrict__ y,
+                                                                                const __nv_bfloat16* __restrict__ dy,
+                                                                                __nv_bfloat16* __restrict__ dx, int rows,
+                                                                                int cols, long long img, float scale) {
+  __shared__ float red[kColGroups][kColTile];
+  const int cl = threadIdx.x % kColTile, grp = threadIdx.x / kColTile;
+  const int c = blockIdx.x * kColTile + cl;
+  const bool ok = c < cols;
+  const long long base = blockIdx.y * img + c;
+  float s = 0.f;
+  if (ok)
+    for (int r = grp; r < rows; r += kColGroups) {
+      const long long o = base + static_cast<long long>(r) * cols;
+      s += __bfloat162float(y[o]) * __bfloat162float(dy[o]);
+    }
+  red[grp][cl] = s;
+  __syncthreads();
+  s = (red[0][cl] + red[1][cl]) + (red[2][cl] + red[3][cl]);
+  if (ok)
+    for (int r = grp; r < rows; r += kColGroups) {
+      const long long o = base + static_cast<long long>(r) * cols;
+      dx[o] = __float2bfloat16_rn(scale * __bfloat162float(y[o]) * (__bfloat162float(dy[o]) - s));
+    }
+}
+
 // dst[n][c][r] = src[n][r][c]  (32 x 32 tiles through shared memory)
 __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_img,
                                       __nv_bfloat16* __restrict__ dst, long long dst_ld, long long dst_img, int R, int C) {
@@ -167,5 +226,28 @@ extern "C" int uz_transpose_bf16(const void* src, long long src_ld, long long sr
   transpose_bf16_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(src), src_ld, src_img, static_cast<__nv_bfloat16*>(dst), dst_ld, dst_img, R, C);
   PW_CHECK_LAUNCH("transpose_bf16 launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_softmax_cols(const void* x, void* y, int N, int rows, int cols, float scale, void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!x || !y || N < 1 || N > 65535 || rows < 1 || cols < 1) return set_error(UZ_ERR_INVALID, "softmax_cols: bad extents");
+  dim3 grid((cols + kColTile - 1) / kColTile, N);
+  softmax_cols_kernel<<<grid, kColTile * kColGroups, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, static_cast<long long>(rows) * cols, scale);
+  PW_CHECK_LAUNCH("softmax_cols launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_softmax_cols_bwd(const void* y, const void* dy, void* dx, int N, int rows, int cols, float scale,
+                                   void* stream) {
+  PW_REQUIRE_DEVICE();
+  if (!y || !dy || !dx || N < 1 || N > 65535 || rows < 1 || cols < 1)
+    return set_error(UZ_ERR_INVALID, "softmax_cols_bwd: bad extents");
+  dim3 grid((cols + kColTile - 1) / kColTile, N);
+  softmax_cols_bwd_kernel<<<grid, kColTile * kColGroups, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), rows, cols,
+      static_cast<long long>(rows) * cols, scale);
+  PW_CHECK_LAUNCH("softmax_cols_bwd launch");
   return UZ_OK;
 }

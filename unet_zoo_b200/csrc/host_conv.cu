@@ -713,7 +713,7 @@ extern "C" int uz_bmm_tn(const void* A, long long lda, long long a_img, const vo
   if (!A || !B || !C || N < 1 || M < 1 || K < 1 || J < 1 || lda < K || ldc < J)
     return set_error(UZ_ERR_INVALID, "bmm_tn: bad extents N=%d M=%d K=%d J=%d", N, M, K, J);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool fast = M >= 128 && (M % 8) == 0 && (K % 8) == 0 && (J % 8) == 0 && (lda % 8) == 0 && (ldc % 8) == 0 &&
+  const bool fast = M >= env_int("UZ_BMM_MIN_M", 8) && (M % 8) == 0 && (K % 8) == 0 && (J % 8) == 0 && (lda % 8) == 0 && (ldc % 8) == 0 &&
                     a_img == static_cast<long long>(M) * lda && c_img == static_cast<long long>(M) * ldc &&
                     (b_img % 8) == 0 && b_img >= static_cast<long long>(J) * K && aligned16(A) && aligned16(B) &&
                     aligned16(C) && N < 65536 && !env_int("UZ_BMM_SMALL", 0);

@@ -1,0 +1,428 @@
+// Bandwidth kernels around the attention blocks of unet_transformer (reference
+// unet_zoo/models/unet_transformer.py:68-229), NHWC bf16, 8 channels (16 bytes) per thread:
+//   uz_addpe_fwd / _bwd           x + positional encoding (a fixed [H, W, C] fp32 table, :68-113), optionally followed by
+//                                 MaxPool2d(2) of the sum (Sconv_process[0], :153) without storing the sum
+//   uz_adaptive_avgpool_fwd / _bwd  F.adaptive_avg_pool2d to the attention resolution (:201-203), ATen window arithmetic
+//   uz_bilinear_resize_fwd / _bwd   F.interpolate(size=..., mode="bilinear", align_corners=True) (:222), ATen index
+//                                 arithmetic; the backward is the exact adjoint in gather form (deterministic, no atomics)
+#include <cstdint>
+
+#include "pw.cuh"
+
+namespace uz {
+namespace {
+
+__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&f)[8]) { *reinterpret_cast<uint4*>(p) = pw_pack8(f); }
+__device__ __forceinline__ float bf16r(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+// y[n, h, w, :] = bf16(x + pe[h, w, :]); pooled = 2x2 max of y (floor), either output may be null
+__global__ void addpe_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, const float* __restrict__ pe, int N, int H,
+                                 int W, int C, __nv_bfloat16* __restrict__ y, int y_ld, __nv_bfloat16* __restrict__ pooled,
+                                 int pooled_ld) {
+  const int cv = C / 8;
+  if (pooled == nullptr) {
+    const long long total = static_cast<long long>(N) * H * W * cv;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+      const int g = static_cast<int>(i % cv);
+      const long long p = i / cv;
+      const long long hw = p % (static_cast<long long>(H) * W);
+      float f[8];
+      ld8(x + p * x_ld + g * 8, f);
+      const float* e = pe + hw * C + g * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += __ldg(e + j);
+      st8(y + p * y_ld + g * 8, f);
+    }
+    return;
+  }
+  const int Hq = (H + 1) / 2, Wq = (W + 1) / 2, Hp = H / 2, Wp = W / 2;
+  const long long total = static_cast<long long>(N) * Hq * Wq * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int qx = static_cast<int>(q % Wq);
+    q /= Wq;
+    const int qy = static_cast<int>(q % Hq);
+    const long long n = q / Hq;
+    float m[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int yy = 2 * qy + (k >> 1), xx = 2 * qx + (k & 1);
+      if (yy >= H || xx >= W) continue;
+      const long long p = (n * H + yy) * W + xx;
+      float f[8];
+      ld8(x + p * x_ld + g * 8, f);
+      const float* e = pe + (static_cast<long long>(yy) * W + xx) * C + g * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = bf16r(f[j] + __ldg(e + j));
+      if (y) st8(y + p * y_ld + g * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) m[j] = (k == 0 || f[j] > m[j]) ? f[j] : m[j];
+    }
+    if (qy < Hp && qx < Wp) st8(pooled + ((n * Hp + qy) * Wp + qx) * pooled_ld + g * 8, m);
+  }
+}
+
+// dx (+)= dy + route(dpooled): the pooled gradient goes to the FIRST maximum of bf16(x + pe) in row-major window order
+__global__ void addpe_bwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, const float* __restrict__ pe, int N, int H,
+                                 int W, int C, const __nv_bfloat16* __restrict__ dy, int dy_ld,
+                                 const __nv_bfloat16* __restrict__ dpooled, int dpooled_ld, __nv_bfloat16* __restrict__ dx,
+                                 int dx_ld, int accumulate) {
+  const int cv = C / 8;
+  const int Hq = (H + 1) / 2, Wq = (W + 1) / 2, Hp = H / 2, Wp = W / 2;
+  const long long total = static_cast<long long>(N) * Hq * Wq * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int qx = static_cast<int>(q % Wq);
+    q /= Wq;
+    const int qy = static_cast<int>(q % Hq);
+    const long long n = q / Hq;
+    const bool full = dpooled != nullptr && qy < Hp && qx < Wp;
+    float s[4][8], dp[8];
+    int am[8];
+    if (full) {
+      ld8(dpooled + ((n * Hp + qy) * Wp + qx) * dpooled_ld + g * 8, dp);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const long long p = (n * H + 2 * qy + (k >> 1)) * W + 2 * qx + (k & 1);
+        ld8(x + p * x_ld + g * 8, s[k]);
+        const float* e = pe + (static_cast<long long>(2 * qy + (k >> 1)) * W + 2 * qx + (k & 1)) * C + g * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[k][j] = bf16r(s[k][j] + __ldg(e + j));
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        am[j] = 0;
+        float mv = s[0][j];
+#pragma unroll
+        for (int k = 1; k < 4; ++k)
+          if (s[k][j] > mv) {
+            mv = s[k][j];
+            am[j] = k;
+          }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int yy = 2 * qy + (k >> 1), xx = 2 * qx + (k & 1);
+      if (yy >= H || xx >= W) continue;
+      const long long p = (n * H + yy) * W + xx;
+      float o[8];
+      if (dy) {
+        ld8(dy + p * dy_ld + g * 8, o);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = 0.f;
+      }
+      if (full) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (am[j] == k) o[j] += dp[j];
+      }
+      __nv_bfloat16* d = dx + p * dx_ld + g * 8;
+      if (accumulate) {
+        float old[8];
+        ld8(d, old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += old[j];
+      }
+      st8(d, o);
+    }
+  }
+}
+
+// ATen adaptive pooling windows: [floor(o * I / O), ceil((o + 1) * I / O))
+__device__ __forceinline__ int ap_start(int o, int I, int O) { return static_cast<int>((static_cast<long long>(o) * I) / O); }
+__device__ __forceinline__ int ap_end(int o, int I, int O) {
+  return static_cast<int>((static_cast<long long>(o + 1) * I + O - 1) / O);
+}
+
+__global__ void adaptive_avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int C,
+                                            __nv_bfloat16* __restrict__ out, int out_ld, int OH, int OW) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * OH * OW * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ox = static_cast<int>(q % OW);
+    q /= OW;
+    const int oy = static_cast<int>(q % OH);
+    const long long n = q / OH;
+    const int y0 = ap_start(oy, H, OH), y1 = ap_end(oy, H, OH), x0 = ap_start(ox, W, OW), x1 = ap_end(ox, W, OW);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int yy = y0; yy < y1; ++yy)
+      for (int xx = x0; xx < x1; ++xx) {
+        float f[8];
+        ld8(x + ((n * H + yy) * W + xx) * x_ld + g * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    const float inv = 1.f / static_cast<float>((y1 - y0) * (x1 - x0));
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    st8(out + ((n * OH + oy) * OW + ox) * out_ld + g * 8, acc);
+  }
+}
+
+// dx[iy, ix] (+)= sum over the output cells whose window contains (iy, ix) of dout / window area
+__global__ void adaptive_avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int C,
+                                            int OH, int OW, __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ix = static_cast<int>(q % W);
+    q /= W;
+    const int iy = static_cast<int>(q % H);
+    const long long n = q / H;
+    int oy_lo = static_cast<int>((static_cast<long long>(iy) * OH) / H) - 1;
+    int oy_hi = static_cast<int>((static_cast<long long>(iy + 1) * OH + H - 1) / H);
+    int ox_lo = static_cast<int>((static_cast<long long>(ix) * OW) / W) - 1;
+    int ox_hi = static_cast<int>((static_cast<long long>(ix + 1) * OW + W - 1) / W);
+    oy_lo = oy_lo < 0 ? 0 : oy_lo;
+    ox_lo = ox_lo < 0 ? 0 : ox_lo;
+    oy_hi = oy_hi > OH - 1 ? OH - 1 : oy_hi;
+    ox_hi = ox_hi > OW - 1 ? OW - 1 : ox_hi;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int oy = oy_lo; oy <= oy_hi; ++oy) {
+      const int y0 = ap_start(oy, H, OH), y1 = ap_end(oy, H, OH);
+      if (iy < y0 || iy >= y1) continue;
+      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+        const int x0 = ap_start(ox, W, OW), x1 = ap_end(ox, W, OW);
+        if (ix < x0 || ix >= x1) continue;
+        float f[8];
+        ld8(dout + ((n * OH + oy) * OW + ox) * dout_ld + g * 8, f);
+        const float inv = 1.f / static_cast<float>((y1 - y0) * (x1 - x0));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], inv, acc[j]);
+      }
+    }
+    __nv_bfloat16* d = dx + ((n * H + iy) * W + ix) * dx_ld + g * 8;
+    if (accumulate) {
+      float old[8];
+      ld8(d, old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += old[j];
+    }
+    st8(d, acc);
+  }
+}
+
+// ATen upsample_bilinear2d, align_corners = True: src = dst * (I - 1) / (O - 1) in fp32, i0 = floor, i1 = min(i0 + 1, I - 1)
+__device__ __forceinline__ void bl_src(int dst, float scale, int I, int* i0, int* i1, float* l1) {
+  const float src = scale * static_cast<float>(dst);
+  int a = static_cast<int>(src);
+  a = a > I - 1 ? I - 1 : a;
+  *i0 = a;
+  *i1 = a + (a < I - 1 ? 1 : 0);
+  *l1 = src - static_cast<float>(a);
+}
+
+__global__ void bilinear_resize_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int C,
+                                           __nv_bfloat16* __restrict__ out, int out_ld, int OH, int OW, float sy,
+                                           float sx) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * OH * OW * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ox = static_cast<int>(q % OW);
+    q /= OW;
+    const int oy = static_cast<int>(q % OH);
+    const long long n = q / OH;
+    int y0, y1, x0, x1;
+    float ly, lx;
+    bl_src(oy, sy, H, &y0, &y1, &ly);
+    bl_src(ox, sx, W, &x0, &x1, &lx);
+    float a[8], b[8], c[8], d[8], o[8];
+    ld8(x + ((n * H + y0) * W + x0) * x_ld + g * 8, a);
+    ld8(x + ((n * H + y0) * W + x1) * x_ld + g * 8, b);
+    ld8(x + ((n * H + y1) * W + x0) * x_ld + g * 8, c);
+    ld8(x + ((n * H + y1) * W + x1) * x_ld + g * 8, d);
+    const float hy = 1.f - ly, hx = 1.f - lx;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = hy * (hx * a[j] + lx * b[j]) + ly * (hx * c[j] + lx * d[j]);
+    st8(out + ((n * OH + oy) * OW + ox) * out_ld + g * 8, o);
+  }
+}
+
+// exact adjoint in gather form: input pixel (iy, ix) collects every output whose (i0, i1) pair contains it
+__global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int C,
+                                           int OH, int OW, float sy, float sx, __nv_bfloat16* __restrict__ dx, int dx_ld,
+                                           int accumulate) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  const float ry = sy > 0.f ? 1.f / sy : 0.f, rx = sx > 0.f ? 1.f / sx : 0.f;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ix = static_cast<int>(q % W);
+    q /= W;
+    const int iy = static_cast<int>(q % H);
+    const long long n = q / H;
+    // candidate outputs: src in (i - 1, i + 1)  ->  dst in ((i - 1) / scale, (i + 1) / scale), widened by one
+    int oy_lo = sy > 0.f ? static_cast<int>(floorf((iy - 1) * ry)) - 1 : 0;
+    int oy_hi = sy > 0.f ? static_cast<int>(ceilf((iy + 1) * ry)) + 1 : OH - 1;
+    int ox_lo = sx > 0.f ? static_cast<int>(floorf((ix - 1) * rx)) - 1 : 0;
+    int ox_hi = sx > 0.f ? static_cast<int>(ceilf((ix + 1) * rx)) + 1 : OW - 1;
+    oy_lo = oy_lo < 0 ? 0 : oy_lo;
+    ox_lo = ox_lo < 0 ? 0 : ox_lo;
+    oy_hi = oy_hi > OH - 1 ? OH - 1 : oy_hi;
+    ox_hi = ox_hi > OW - 1 ? OW - 1 : ox_hi;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int oy = oy_lo; oy <= oy_hi; ++oy) {
+      int y0, y1;
+      float ly;
+      bl_src(oy, sy, H, &y0, &y1, &ly);
+      const float wy = (y0 == iy ? 1.f - ly : 0.f) + (y1 == iy ? ly : 0.f);
+      if (wy == 0.f) continue;
+      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+        int x0, x1;
+        float lx;
+        bl_src(ox, sx, W, &x0, &x1, &lx);
+        const float wx = (x0 == ix ? 1.f - lx : 0.f) + (x1 == ix ? lx : 0.f);
+        if (wx == 0.f) continue;
+        float f[8];
+        ld8(dout + ((n * OH + oy) * OW + ox) * dout_ld + g * 8, f);
+        const float w = wy * wx;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], w, acc[j]);
+      }
+    }
+    __nv_bfloat16* d = dx + ((n * H + iy) * W + ix) * dx_ld + g * 8;
+    if (accumulate) {
+      float old[8];
+      ld8(d, old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += old[j];
+    }
+    st8(d, acc);
+  }
+}
+
+int ew_grid(long long total) {
+  const int sms = uz_device_sm_count();
+  long long g = (total + 255) / 256, cap = static_cast<long long>(sms > 0 ? sms : 148) * 16;
+  return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+}
+int chk(const char* what, const void* p, int C, int ld) {
+  if (p == nullptr || C < 8 || (C & 7) || (ld & 7) || ld < C || (reinterpret_cast<uintptr_t>(p) & 15u))
+    return set_error(UZ_ERR_INVALID, "%s: channels=%d ld=%d must be multiples of 8, pointer 16-byte aligned", what, C, ld);
+  return UZ_OK;
+}
+
+}  // namespace
+}  // namespace uz
+
+using namespace uz;
+
+extern "C" int uz_addpe_fwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, void* y, int y_ld,
+                            void* pooled, int pooled_ld, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("addpe_fwd(x)", x, C, x_ld);
+  if (rc) return rc;
+  if (!pe || (!y && !pooled) || N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "addpe_fwd: bad arguments");
+  if (y && (rc = chk("addpe_fwd(y)", y, C, y_ld))) return rc;
+  if (pooled && (rc = chk("addpe_fwd(pooled)", pooled, C, pooled_ld))) return rc;
+  if (pooled && (H < 2 || W < 2)) return set_error(UZ_ERR_INVALID, "addpe_fwd: pooling needs H, W >= 2");
+  const long long total = pooled ? static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8)
+                                 : static_cast<long long>(N) * H * W * (C / 8);
+  addpe_fwd_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_ld, pe, N, H, W, C, static_cast<__nv_bfloat16*>(y), y_ld,
+      static_cast<__nv_bfloat16*>(pooled), pooled_ld);
+  PW_CHECK_LAUNCH("addpe_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_addpe_bwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, const void* dy,
+                            int dy_ld, const void* dpooled, int dpooled_ld, void* dx, int dx_ld, int accumulate,
+                            void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("addpe_bwd(dx)", dx, C, dx_ld);
+  if (rc) return rc;
+  if (!dy && !dpooled) return set_error(UZ_ERR_INVALID, "addpe_bwd: no incoming gradient");
+  if (dy && (rc = chk("addpe_bwd(dy)", dy, C, dy_ld))) return rc;
+  if (dpooled && ((rc = chk("addpe_bwd(dpooled)", dpooled, C, dpooled_ld)) || (rc = chk("addpe_bwd(x)", x, C, x_ld)))) return rc;
+  if (dpooled && !pe) return set_error(UZ_ERR_INVALID, "addpe_bwd: the pooled path needs x and pe");
+  const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+  addpe_bwd_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_ld, pe, N, H, W, C, static_cast<const __nv_bfloat16*>(dy), dy_ld,
+      static_cast<const __nv_bfloat16*>(dpooled), dpooled_ld, static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate);
+  PW_CHECK_LAUNCH("addpe_bwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_adaptive_avgpool_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld,
+                                       int OH, int OW, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("adaptive_avgpool_fwd(x)", x, C, x_ld);
+  if (rc || (rc = chk("adaptive_avgpool_fwd(out)", out, C, out_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "adaptive_avgpool_fwd: bad extents");
+  adaptive_avgpool_fwd_kernel<<<ew_grid(static_cast<long long>(N) * OH * OW * (C / 8)), 256, 0,
+                                static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W,
+                                                                     C, static_cast<__nv_bfloat16*>(out), out_ld, OH, OW);
+  PW_CHECK_LAUNCH("adaptive_avgpool_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_adaptive_avgpool_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW,
+                                       void* dx, int dx_ld, int accumulate, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("adaptive_avgpool_bwd(dout)", dout, C, dout_ld);
+  if (rc || (rc = chk("adaptive_avgpool_bwd(dx)", dx, C, dx_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "adaptive_avgpool_bwd: bad extents");
+  adaptive_avgpool_bwd_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0,
+                                static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H,
+                                                                     W, C, OH, OW, static_cast<__nv_bfloat16*>(dx), dx_ld,
+                                                                     accumulate);
+  PW_CHECK_LAUNCH("adaptive_avgpool_bwd launch");
+  return UZ_OK;
+}
+
+static float bl_scale(int in, int out) { return out > 1 ? static_cast<float>(in - 1) / static_cast<float>(out - 1) : 0.f; }
+
+extern "C" int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH,
+                                      int OW, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("bilinear_resize_fwd(x)", x, C, x_ld);
+  if (rc || (rc = chk("bilinear_resize_fwd(out)", out, C, out_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "bilinear_resize_fwd: bad extents");
+  bilinear_resize_fwd_kernel<<<ew_grid(static_cast<long long>(N) * OH * OW * (C / 8)), 256, 0,
+                               static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C,
+                                                                    static_cast<__nv_bfloat16*>(out), out_ld, OH, OW,
+                                                                    bl_scale(H, OH), bl_scale(W, OW));
+  PW_CHECK_LAUNCH("bilinear_resize_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx,
+                                      int dx_ld, int accumulate, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = chk("bilinear_resize_bwd(dout)", dout, C, dout_ld);
+  if (rc || (rc = chk("bilinear_resize_bwd(dx)", dx, C, dx_ld))) return rc;
+  if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "bilinear_resize_bwd: bad extents");
+  bilinear_resize_bwd_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0,
+                               static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H,
+                                                                    W, C, OH, OW, bl_scale(H, OH), bl_scale(W, OW),
+                                                                    static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate);
+  PW_CHECK_LAUNCH("bilinear_resize_bwd launch");
+  return UZ_OK;
+}

@@ -914,22 +914,93 @@ def _island_math(tf32: bool):
             mm.fp32_precision, cd.conv.fp32_precision = saved
 
 
+def add_posenc(ctx: Ctx, x: Act, pe: torch.Tensor, out: Optional[Act] = None, pooled: Optional[Act] = None):
+    """x + positional encoding (`pe`: fixed fp32 [H, W, C] table, no gradient), unet_transformer.py:128,196,199;
+    `pooled`: MaxPool2d(2) of the sum (Sconv_process[0], :153) - when only `pooled` is given the sum is never stored.
+    Returns (out, pooled)."""
+    if ctx.fp32:
+        raise RuntimeError("unet_zoo_b200: add_posenc has no fp32 parity path")
+    if out is None and pooled is None:
+        out = ctx.new_act(x.N, x.H, x.W, x.C)
+    pe = pe.contiguous()
+    L.check(ctx.lib.uz_addpe_fwd(x.ptr, x.ld, pe.data_ptr(), x.N, x.H, x.W, x.C, out.ptr if out else None,
+                                 out.ld if out else 0, pooled.ptr if pooled else None, pooled.ld if pooled else 0,
+                                 ctx.stream), "uz_addpe_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            has_dy = out is not None and out.has_grad()
+            has_dp = pooled is not None and pooled.has_grad()
+            if not (has_dy or has_dp):
+                raise RuntimeError("unet_zoo_b200: add_posenc output has no gradient")
+            runs = x.grad_writes()
+            if len(runs) != 1:          # the table's row pitch is the full channel count
+                raise NotImplementedError("add_posenc: input gradient partly written by another consumer")
+            L.check(c.lib.uz_addpe_bwd(x.ptr, x.ld, pe.data_ptr(), x.N, x.H, x.W, x.C,
+                                       out.gptr() if has_dy else None, out.ld if has_dy else 0,
+                                       pooled.gptr() if has_dp else None, pooled.ld if has_dp else 0,
+                                       x.gptr(), x.ld, int(runs[0][2]), c.stream), "uz_addpe_bwd")
+            c.launches += 1
+        ctx.tape.append(backward)
+    return out, pooled
+
+
+def adaptive_avgpool(ctx: Ctx, x: Act, OH: int, OW: int) -> Act:
+    """F.adaptive_avg_pool2d(x, (OH, OW)) (unet_transformer.py:201-203)."""
+    out = ctx.new_act(x.N, OH, OW, x.C)
+    L.check(ctx.lib.uz_adaptive_avgpool_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, OH, OW, ctx.stream),
+            "uz_adaptive_avgpool_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: adaptive_avgpool output has no gradient")
+            for (r0, rc, acc) in x.grad_writes():
+                L.check(c.lib.uz_adaptive_avgpool_bwd(out.gptr() + 2 * r0, out.ld, x.N, x.H, x.W, rc, OH, OW,
+                                                      x.gptr() + 2 * r0, x.ld, int(acc), c.stream), "uz_adaptive_avgpool_bwd")
+                c.launches += 1
+        ctx.tape.append(backward)
+    return out
+
+
+def bilinear_resize(ctx: Ctx, x: Act, OH: int, OW: int, out: Optional[Act] = None) -> Act:
+    """F.interpolate(x, size=(OH, OW), mode="bilinear", align_corners=True) (unet_transformer.py:222)."""
+    if out is None:
+        out = ctx.new_act(x.N, OH, OW, x.C)
+    L.check(ctx.lib.uz_bilinear_resize_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, OH, OW, ctx.stream),
+            "uz_bilinear_resize_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: bilinear_resize output has no gradient")
+            for (r0, rc, acc) in x.grad_writes():
+                L.check(c.lib.uz_bilinear_resize_bwd(out.gptr() + 2 * r0, out.ld, x.N, x.H, x.W, rc, OH, OW,
+                                                     x.gptr() + 2 * r0, x.ld, int(acc), c.stream), "uz_bilinear_resize_bwd")
+                c.launches += 1
+        ctx.tape.append(backward)
+    return out
+
+
 def token_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],
                  out: Optional[Act] = None) -> Act:
     """A sub-graph that works on the activation as bf16 TOKENS: ``fn`` maps ``[N, H*W, C]`` (the NHWC buffer seen flat, no
     layout change) to ``[N, H*W, C']``.  Used for the attention bottlenecks, whose matrix products / softmaxes are the
     library's own kernels wrapped as autograd Functions (unet_zoo_b200/attention.py); torch's autograd only chains them
     and supplies the elementwise glue.  Gradients of `params` land in the flat gradient buffer."""
-    src = x.buf.data[..., x.c0:x.c0 + x.C]
-    xin = src.reshape(x.N, x.H * x.W, x.C).detach()
-    if not xin.is_contiguous():
-        xin = xin.contiguous()
+    xs = list(x) if isinstance(x, (list, tuple)) else [x]     # several inputs of the same spatial size (cross-attention)
+    x = xs[0]
+    xins = []
+    for a in xs:
+        t = a.buf.data[..., a.c0:a.c0 + a.C].reshape(a.N, a.H * a.W, a.C).detach()
+        xins.append(t if t.is_contiguous() else t.contiguous())
     if ctx.record:
-        xin.requires_grad_(True)
+        for t in xins:
+            t.requires_grad_(True)
         with torch.enable_grad():
-            y = fn(xin)
+            y = fn(*xins)
     else:
-        y = fn(xin)
+        y = fn(*xins)
     if y.dim() != 3 or y.shape[0] != x.N or y.shape[1] != x.H * x.W or y.dtype != torch.bfloat16:
         raise RuntimeError(f"unet_zoo_b200: token island returned {tuple(y.shape)} {y.dtype} for {(x.N, x.H * x.W, x.C)}")
     if out is None:
@@ -942,16 +1013,17 @@ def token_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], p
             if not out.has_grad():
                 raise RuntimeError("unet_zoo_b200: token island output has no gradient")
             dy = out.buf.grad_buf()[..., out.c0:out.c0 + out.C].reshape(x.N, x.H * x.W, -1)
-            grads = torch.autograd.grad([y], [xin] + params, [dy.contiguous()], allow_unused=True)
-            gx = x.buf.grad_buf()
-            dx = grads[0].reshape(x.N, x.H, x.W, x.C)
-            for (r0, rc, acc) in x.grad_writes():
-                dst = gx[..., x.c0 + r0:x.c0 + r0 + rc]
-                if acc:
-                    dst.add_(dx[..., r0:r0 + rc])
-                else:
-                    dst.copy_(dx[..., r0:r0 + rc])
-            for p, g in zip(params, grads[1:]):
+            grads = torch.autograd.grad([y], xins + params, [dy.contiguous()], allow_unused=True)
+            for a, g in zip(xs, grads[:len(xs)]):
+                ga = a.buf.grad_buf()
+                dx = (g if g is not None else torch.zeros_like(xins[0][..., :a.C])).reshape(a.N, a.H, a.W, a.C)
+                for (r0, rc, acc) in a.grad_writes():
+                    dst = ga[..., a.c0 + r0:a.c0 + r0 + rc]
+                    if acc:
+                        dst.add_(dx[..., r0:r0 + rc])
+                    else:
+                        dst.copy_(dx[..., r0:r0 + rc])
+            for p, g in zip(params, grads[len(xs):]):
                 if g is not None:
                     c.pgrad(p).copy_(g)
             c.pready(*params)

@@ -36,8 +36,14 @@ try:  # first neighbouring model on the same blocks
 except ImportError:  # pragma: no cover
     pass
 
+try:  # second neighbouring model: self- / cross-attention U-Net on the same blocks + the attention kernels
+    from .unet_transformer import U_Transformer
+    _model_entries["unet_transformer"] = U_Transformer
+except ImportError:  # pragma: no cover
+    pass
+
 # registry names of the reference that are deliberately not part of this build
-_OUT_OF_SCOPE = ("raunet", "da_transformer", "unet_transformer", "uctransnet", "multiresunet",
+_OUT_OF_SCOPE = ("raunet", "da_transformer", "uctransnet", "multiresunet",
                  "missformer", "vnet", "u2net", "u2netp", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
                  "mmunet", "axialunet", "gated", "medt", "logo")
 
@@ -75,6 +81,8 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth, deep_supervision=False)
     elif name == "transatt_unet":    # models/__init__.py:106-109: `depth` is passed on and swallowed by **kwargs
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
+    elif name == "unet_transformer":   # the reference factory's default branch (models/__init__.py:221-223)
+        args = dict(in_channels=in_channels, num_classes=num_classes)
     else:  # resunet
         args = dict(in_channels=in_channels, num_classes=num_classes, filters=[64, 128, 256, 512])
     args.update(kwargs)              # leftovers reach the constructor (TypeError if it does not know them)
