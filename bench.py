@@ -25,7 +25,8 @@ if ROOT not in sys.path:
 
 # conv + transposed-conv FLOPs (2*MAC) of one fwd+bwd per image at 512x512, SURVEY.md section 6 / 8(d)
 FWD_BWD_GFLOP_PER_IMG_512 = {"unet": 1155.11, "attention_unet": 1593.29, "nested_unet": 827.20, "resunet": 931.44,
-                              "transatt_unet": 967.47, "unet_transformer": 1830.0}   # last: 3 x the 610 GFLOP forward
+                              "transatt_unet": 967.47, "unet_transformer": 1830.0,   # last: 3 x the 610 GFLOP forward
+                              "u2net": 900.07, "u2netp": 303.45}       # 3 x the conv FLOPs of one forward (hooks on the reference)
 FWD_GFLOP_PER_IMG_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08}
 UNET_FWD_BWD_GFLOP_PER_IMG_512 = FWD_BWD_GFLOP_PER_IMG_512["unet"]
 
@@ -239,7 +240,10 @@ def train_leg(args, model_name, B, S, steps, warmup, dev, world, rank, e2e=True,
     def eager_step(x, m):
         opt.zero_grad(set_to_none=True)
         out = model(x)
-        loss = crit(out, m)
+        if isinstance(out, dict):      # U2NET: seven maps, weight 1.0 each (training_loop.py:23-31, :61-64)
+            loss = sum(crit(o, m) for o in out.values())
+        else:
+            loss = crit(out, m)
         loss.backward()
         if getattr(model, "defer_sync", False):
             model.sync_gradients()

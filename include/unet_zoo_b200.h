@@ -183,8 +183,8 @@ int uz_transpose_bf16(const void* src, long long src_ld, long long src_img, void
  *   on the host side), optionally followed by MaxPool2d(2) of the sum without storing it (Sconv_process[0], :153).
  *   Backward: dx (+)= dy + the pooled gradient routed to the first maximum of bf16(x + pe) per 2x2 window.
  * uz_adaptive_avgpool_fwd / _bwd: F.adaptive_avg_pool2d (:201-203), ATen windows [floor(o*I/O), ceil((o+1)*I/O)).
- * uz_bilinear_resize_fwd / _bwd: F.interpolate(size=(OH, OW), mode="bilinear", align_corners=True) (:222) and its exact
- *   adjoint in gather form (no atomics). */
+ * uz_bilinear_resize_fwd / _bwd: F.interpolate(size=(OH, OW), mode="bilinear", align_corners=...) and its exact adjoint in
+ *   gather form (no atomics): align_corners = 1 for unet_transformer.py:222, 0 for u2net.py:19-23 (_upsample_like). */
 int uz_addpe_fwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, void* y, int y_ld, void* pooled,
                  int pooled_ld, void* stream);
 int uz_addpe_bwd(const void* x, int x_ld, const float* pe, int N, int H, int W, int C, const void* dy, int dy_ld,
@@ -194,9 +194,19 @@ int uz_adaptive_avgpool_fwd(const void* x, int x_ld, int N, int H, int W, int C,
 int uz_adaptive_avgpool_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx, int dx_ld,
                             int accumulate, void* stream);
 int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH, int OW,
-                           void* stream);
+                           int align_corners, void* stream);
+size_t uz_bilinear_resize_bwd_workspace_bytes(int N, int H, int W, int C, int OH, int OW); /* 0 below 4x magnification */
 int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx, int dx_ld,
-                           int accumulate, void* stream);
+                           int accumulate, int align_corners, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Residual add of U^2-Net's RSU blocks, `return hx1d + hxin` (u2net.py:78,127,171,210,237), NHWC bf16:
+ * uz_residual_add_fwd: y = a + b; `pooled` (optional) receives MaxPool2d(2, stride 2) of the sum (u2net.py:222-232).
+ * uz_residual_add_bwd: g = dy + the pooled gradient routed to the first maximum of the stored y per 2x2 window;
+ *   da (+)= g and db (+)= g (acc_a / acc_b select accumulation; either incoming gradient may be NULL, not both). */
+int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b_ld, int N, int H, int W, int C, void* y, int y_ld,
+                        void* pooled, int pooled_ld, void* stream);
+int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, const void* dy, int dy_ld, const void* dpooled,
+                        int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld, int acc_b, void* stream);
 
 /* F.pad with zeros on the bottom / right, or its backward (crop), between two NHWC pixel grids: replaces the
  * `F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])` of common_layers.py:110-113 / :173-178 (dx, dy in {0, 1} for
@@ -224,6 +234,10 @@ int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, int W, int C,
 #define UZ_CONVT2X2_DGRAD 8
 #define UZ_UP2X_CONV3X3 9   /* nn.Upsample(scale 2, nearest) + Conv2d k3 p1   common_layers.py:70-73              */
 #define UZ_UP2X_CONV3X3_DGRAD 10 /* its data gradient w.r.t. the LOW-res input (weights packed with the dgrad strides) */
+
+/* Dilated 3x3 convolution, Conv2d(k3, padding = dilation = d) of REBNCONV (u2net.py:10): OR into UZ_CONV3X3 /
+ * UZ_CONV3X3_DGRAD (uz_conv_igemm) and UZ_CONV3X3 (uz_conv_wgrad, uz_conv_wgrad_workspace_bytes).  d = 1 is the plain mode. */
+#define UZ_DILATION(d) ((d) << 8)
 
 #define UZ_FLAG_RELU 1
 #define UZ_FLAG_ACCUMULATE 2 /* out += result (used when a tensor has several consumers in backward) */

@@ -29,7 +29,7 @@ def load_reference():
     pkg.__path__ = [REF]
     sys.modules["refmodels"] = pkg
     mods = {}
-    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet", "unet_transformer"):
+    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet", "unet_transformer", "u2net"):
         spec = importlib.util.spec_from_file_location(f"refmodels.{name}", os.path.join(REF, name + ".py"))
         m = importlib.util.module_from_spec(spec)
         sys.modules[f"refmodels.{name}"] = m
@@ -57,7 +57,18 @@ def build(mods, name, **kw):
         return model
     if name == "unet_transformer":   # oracle groundwork for the next model (no CUDA path yet)
         return mods["unet_transformer"].U_Transformer(in_channels=3, num_classes=1)
+    if name == "u2net":
+        return mods["u2net"].U2NET(in_ch=3, out_ch=1)        # the factory's arguments (models/__init__.py:156-158)
+    if name == "u2netp":
+        return mods["u2net"].U2NETP(in_ch=3, out_ch=1)
     raise ValueError(name)
+
+
+def as_list(out):
+    """Model output -> list of logit maps: U2NET returns a dict (u2net.py:287-295), kept in its own key order."""
+    if isinstance(out, dict):
+        return list(out.values())
+    return out if isinstance(out, list) else [out]
 
 
 def fingerprint(sd):
@@ -74,8 +85,7 @@ def conditioned_case(mods, name, kw, x, mask):
     model = build(mods, name, **kw)
     model.load_state_dict(randomize_bn_affine({k: v.clone() for k, v in model.state_dict().items()}))
     model.train()
-    out = model(x)
-    outs = out if isinstance(out, list) else [out]
+    outs = as_list(model(x))
     sum(gaussian_projection_loss(o, mask) for o in outs).backward()
     grads = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
     cond = {
@@ -89,7 +99,7 @@ def conditioned_case(mods, name, kw, x, mask):
     model.eval()
     with torch.no_grad():
         oe = model(x)
-    cond["logits_eval"] = [o.clone() for o in (oe if isinstance(oe, list) else [oe])]
+    cond["logits_eval"] = [o.clone() for o in as_list(oe)]
     return cond
 
 
@@ -99,7 +109,8 @@ def main():
     mods = load_reference()
     os.makedirs(OUT, exist_ok=True)
     cases = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
-             ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}), ("unet_transformer", {})]
+             ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}), ("unet_transformer", {}),
+             ("u2net", {}), ("u2netp", {})]
     only = sys.argv[1:]
     if only:
         cases = [c for c in cases if c[0] in only]
@@ -108,7 +119,9 @@ def main():
         torch.manual_seed(0)
         model = build(mods, name, **kw)
         fp = fingerprint(model.state_dict())
-        x, mask = synthetic_batch(2, 3, 64, 64)
+        # u2net: 128 x 128 so that the innermost maps (six poolings) are 4 x 4, not 2 x 2
+        size = 128 if name in ("u2net", "u2netp") else 64
+        x, mask = synthetic_batch(2, 3, size, size)
         model.train()
         extra = {}
         if name == "transatt_unet":            # the reference as is: attention dropout p = 0.1 under a fixed seed
@@ -120,14 +133,13 @@ def main():
             extra["dropout_seed"] = 77
             model.sdpa.dropout.p = kw["attn_dropout"]
             model.load_state_dict(sd0)         # undo that forward's running-statistics update
-        out = model(x)
-        outs = out if isinstance(out, list) else [out]
+        outs = as_list(model(x))
         crit = torch.nn.BCEWithLogitsLoss()
         loss = sum(crit(o, mask) for o in outs)
         loss.backward()
         grads = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
         gold = {
-            "recipe": {"seed": 0, "batch": [2, 3, 64, 64], "seed_x": 1234, "seed_m": 4321, "kwargs": kw,
+            "recipe": {"seed": 0, "batch": [2, 3, size, size], "seed_x": 1234, "seed_m": 4321, "kwargs": kw,
                        "torch": str(torch.__version__)},
             "fingerprint": fp,
             "logits_train": [o.detach().clone() for o in outs],
@@ -137,11 +149,13 @@ def main():
             "bn_after": {k: v.detach().clone() for k, v in model.state_dict().items()
                          if "running_" in k or "num_batches" in k},
         }
+        if name in ("u2net", "u2netp"):     # fixture size: the default-init case keeps main + side1 (the conditioned case
+            gold["logits_train"] = gold["logits_train"][:2]      # below keeps all seven maps); "loss" is over all seven
         gold.update(extra)
         model.eval()
         with torch.no_grad():
             oe = model(x)
-        gold["logits_eval"] = [o.clone() for o in (oe if isinstance(oe, list) else [oe])]
+        gold["logits_eval"] = [o.clone() for o in as_list(oe)][:2 if name in ("u2net", "u2netp") else None]
         gold["cond"] = conditioned_case(mods, name, kw, x, mask)
         # README example (README.md:74-90): eval forward on randn(1,3,256,256) -> shape only (fresh default weights)
         if tag == "unet":

@@ -353,9 +353,118 @@ def unet_transformer_state_dict(seed: int = 0) -> SD:
     return {k: v.detach().clone() for k, v in Net().state_dict().items()}
 
 
+# ------------------------------------------------------------------------------------------------ U^2-Net (u2net.py)
+U2NET_KEYS = ("main", "side1", "side2", "side3", "side4", "side5", "side6")     # u2net.py:287-295, dict order
+# (block kind, in, mid, out) per stage: u2net.py:219-236 (U2NET) and :303-320 (U2NETP)
+U2NET_STAGES = {
+    "u2net": {"stage1": (7, 3, 32, 64), "stage2": (6, 64, 32, 128), "stage3": (5, 128, 64, 256),
+              "stage4": (4, 256, 128, 512), "stage5": ("4F", 512, 256, 512), "stage6": ("4F", 512, 256, 512),
+              "stage5d": ("4F", 1024, 256, 512), "stage4d": (4, 1024, 128, 256), "stage3d": (5, 512, 64, 128),
+              "stage2d": (6, 256, 32, 64), "stage1d": (7, 128, 16, 64)},
+    "u2netp": {"stage1": (7, 3, 16, 64), "stage2": (6, 64, 16, 64), "stage3": (5, 64, 16, 64),
+               "stage4": (4, 64, 16, 64), "stage5": ("4F", 64, 16, 64), "stage6": ("4F", 64, 16, 64),
+               "stage5d": ("4F", 128, 16, 64), "stage4d": (4, 128, 16, 64), "stage3d": (5, 128, 16, 64),
+               "stage2d": (6, 128, 16, 64), "stage1d": (7, 128, 16, 64)},
+}
+
+
+def _rebnconv(r: Runner, x, prefix, dirate=1):
+    """REBNCONV (u2net.py:6-17): Conv2d(3, padding = dilation = dirate) -> BatchNorm2d -> ReLU."""
+    z = F.conv2d(x, r.sd[prefix + ".conv_s1.weight"], r.sd[prefix + ".conv_s1.bias"], padding=dirate, dilation=dirate)
+    return F.relu(r.bn(z, prefix + ".bn_s1"))
+
+
+def _upsample_like(src, tar):
+    """u2net.py:19-23: bilinear, align_corners=False, to the target's spatial size."""
+    return F.interpolate(src, size=tar.shape[2:], mode="bilinear", align_corners=False)
+
+
+def _rsu(r: Runner, x, prefix, L):
+    """RSU-L, L = 7 / 6 / 5 / 4 (u2net.py:26-78, :81-127, :130-171, :174-210): input conv, L - 1 encoder convs with a
+    ceil-mode MaxPool2d(2) after all but the last, one dilation-2 conv at the bottom, L - 1 decoder convs on
+    cat(previous, skip) with a bilinear upsample in between, residual add of the input conv's output."""
+    hxin = _rebnconv(r, x, prefix + ".rebnconvin")
+    enc = []
+    hx = hxin
+    for i in range(1, L):
+        hx = _rebnconv(r, hx, f"{prefix}.rebnconv{i}")
+        enc.append(hx)
+        if i < L - 1:
+            hx = F.max_pool2d(hx, 2, stride=2, ceil_mode=True)
+    hx = _rebnconv(r, enc[-1], f"{prefix}.rebnconv{L}", dirate=2)
+    for i in range(L - 1, 0, -1):
+        hx = _rebnconv(r, torch.cat((hx, enc[i - 1]), 1), f"{prefix}.rebnconv{i}d")
+        if i > 1:
+            hx = _upsample_like(hx, enc[i - 2])
+    return hx + hxin
+
+
+def _rsu4f(r: Runner, x, prefix):
+    """RSU-4F (u2net.py:213-237): no pooling, dilations 1, 2, 4, 8 on the way in and 4, 2, 1 on the way out."""
+    hxin = _rebnconv(r, x, prefix + ".rebnconvin")
+    hx1 = _rebnconv(r, hxin, prefix + ".rebnconv1", 1)
+    hx2 = _rebnconv(r, hx1, prefix + ".rebnconv2", 2)
+    hx3 = _rebnconv(r, hx2, prefix + ".rebnconv3", 4)
+    hx4 = _rebnconv(r, hx3, prefix + ".rebnconv4", 8)
+    hx3d = _rebnconv(r, torch.cat((hx4, hx3), 1), prefix + ".rebnconv3d", 4)
+    hx2d = _rebnconv(r, torch.cat((hx3d, hx2), 1), prefix + ".rebnconv2d", 2)
+    hx1d = _rebnconv(r, torch.cat((hx2d, hx1), 1), prefix + ".rebnconv1d", 1)
+    return hx1d + hxin
+
+
+def _u2net_forward(variant: str, sd: SD, x: torch.Tensor, training: bool) -> List[torch.Tensor]:
+    """U2NET.forward / U2NETP.forward (u2net.py:239-295, :323-379).  Returns the seven logit maps in the order of the
+    reference's dict: [main, side1, ..., side6] (U2NET_KEYS)."""
+    r = Runner(sd, training)
+    spec = U2NET_STAGES[variant]
+
+    def stage(name, t):
+        kind = spec[name][0]
+        return _rsu4f(r, t, name) if kind == "4F" else _rsu(r, t, name, kind)
+
+    enc = []
+    hx = x
+    for i in range(1, 7):
+        hx = stage(f"stage{i}", hx)
+        enc.append(hx)
+        if i < 6:
+            hx = F.max_pool2d(hx, 2, stride=2, ceil_mode=True)
+    dec = {6: enc[5]}
+    hx = enc[5]
+    for i in range(5, 0, -1):
+        up = _upsample_like(hx, enc[i - 1])
+        hx = stage(f"stage{i}d", torch.cat((up, enc[i - 1]), 1))
+        dec[i] = hx
+    sides = []
+    for i in range(1, 7):
+        d = F.conv2d(dec[i], sd[f"side{i}.weight"], sd[f"side{i}.bias"], padding=1)       # u2net.py:238-243
+        sides.append(d if i == 1 else _upsample_like(d, sides[0]))
+    d0 = F.conv2d(torch.cat(sides, 1), sd["outconv.weight"], sd["outconv.bias"])          # u2net.py:244, :285
+    return [d0] + sides
+
+
+def u2net_forward(sd: SD, x: torch.Tensor, training: bool) -> List[torch.Tensor]:
+    return _u2net_forward("u2net", sd, x, training)
+
+
+def u2netp_forward(sd: SD, x: torch.Tensor, training: bool) -> List[torch.Tensor]:
+    return _u2net_forward("u2netp", sd, x, training)
+
+
+def u2net_loss(outs: List[torch.Tensor], target: torch.Tensor, criterion=None):
+    """training_loop.py:61-64: sum over the seven outputs of weight (1.0 each, :23-31) x criterion(output, mask resized
+    to the output's size with bilinear / align_corners=False - the identity here, every output has the input's size)."""
+    criterion = criterion or bce_with_logits
+    total = 0.0
+    for o in outs:
+        m = F.interpolate(target, size=o.shape[2:], mode="bilinear", align_corners=False)
+        total = total + 1.0 * criterion(o, m)
+    return total
+
+
 FORWARDS = {"unet": unet_forward, "attention_unet": attention_unet_forward, "nested_unet": nested_unet_forward,
             "resunet": resunet_forward, "transatt_unet": transatt_unet_forward,
-            "unet_transformer": unet_transformer_forward}
+            "unet_transformer": unet_transformer_forward, "u2net": u2net_forward, "u2netp": u2netp_forward}
 
 
 def bce_with_logits(logits, target):
@@ -415,7 +524,7 @@ def train_step(name: str, sd: SD, x, target, loss_fn=None, **kw):
     out = FORWARDS[name](work, x, True, **kw)
     outs = out if isinstance(out, list) else [out]
     loss_fn = loss_fn or bce_with_logits
-    loss = sum(loss_fn(o, target) for o in outs)
+    loss = sum(loss_fn(o, target) for o in outs)     # u2net: training_loop.py:61-64 sums the seven outputs, weight 1.0
     loss.backward()
     grads = {k: (t.grad if t.grad is not None else torch.zeros_like(t)) for k, t in leaves.items()}
     return out, loss.detach(), grads

@@ -9,7 +9,8 @@ from conftest import load_golden, rel_err, seeded_model
 from oracle import reference_port as O
 
 CASES = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
-         ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0})]
+         ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}),
+         ("u2net", {}), ("u2netp", {})]      # seven outputs [main, side1..6]; the default-init fixture stores the first two
 
 
 @pytest.mark.parametrize("tag,kw", CASES)
@@ -22,7 +23,7 @@ def test_oracle_matches_reference_outputs(tag, kw):
     x, mask = O.synthetic_batch(n, c, h, w, gold["recipe"]["seed_x"], gold["recipe"]["seed_m"])
     out, loss, grads = O.train_step(name, sd, x, mask, **kw)
     outs = out if isinstance(out, list) else [out]
-    assert len(outs) == len(gold["logits_train"])
+    assert len(outs) == (7 if name.startswith("u2net") else len(gold["logits_train"]))
     for o, g in zip(outs, gold["logits_train"]):
         assert o.shape == g.shape
         assert rel_err(o.detach(), g) < 1e-5

@@ -38,7 +38,7 @@ def main():
             return
         model.zero_grad(set_to_none=True)
         out = model(x)
-        outs = out if isinstance(out, (list, tuple)) else [out]
+        outs = list(out.values()) if isinstance(out, dict) else (out if isinstance(out, (list, tuple)) else [out])
         sum(crit(o, m) for o in outs).backward()
 
     for _ in range(3):

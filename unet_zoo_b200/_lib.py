@@ -17,6 +17,11 @@ CONV1X1_S2, CONV1X1_S2_DGRAD, CONVT2X2, CONVT2X2_DGRAD, UP2X_CONV3X3 = 5, 6, 7, 
 UP2X_CONV3X3_DGRAD = 10
 FLAG_RELU, FLAG_ACCUMULATE, FLAG_STATS = 1, 2, 4
 
+
+def dilation(d: int) -> int:
+    """UZ_DILATION(d): OR into CONV3X3 / CONV3X3_DGRAD for Conv2d(3, padding = dilation = d); 0 for d = 1."""
+    return (int(d) << 8) if d > 1 else 0
+
 _P = c_void_p
 _PROTOS = {
     "uz_last_error": (c_char_p, []),
@@ -54,8 +59,13 @@ _PROTOS = {
     "uz_addpe_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, _P]),
     "uz_adaptive_avgpool_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P]),
     "uz_adaptive_avgpool_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P]),
-    "uz_bilinear_resize_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P]),
-    "uz_bilinear_resize_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, _P]),
+    "uz_bilinear_resize_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, c_int, _P]),
+    "uz_bilinear_resize_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
+    "uz_bilinear_resize_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P,
+                                       c_size_t, _P]),
+    "uz_residual_add_fwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P]),
+    "uz_residual_add_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, _P, c_int,
+                                    c_int, _P]),
     "uz_bmm_tn": (c_int, [_P, c_longlong, c_longlong, _P, c_longlong, _P, c_longlong, c_longlong, c_int, c_int, c_int,
                           c_int, _P]),
     "uz_softmax_rows": (c_int, [_P, c_longlong, _P, c_longlong, c_longlong, c_int, c_float, _P]),

@@ -169,7 +169,7 @@ struct ModeInfo {
   int btaps;         // tap extent of the packed weight tensor
 };
 
-static int build_mode(int mode, int H, int W, int out_h, int out_w, IgemmParams* p, ModeInfo* mi) {
+static int build_mode(int mode, int H, int W, int out_h, int out_w, IgemmParams* p, ModeInfo* mi, int dil = 1) {
   memset(mi, 0, sizeof(*mi));
   mi->oscale = 1;
   mi->num_lat = 1;
@@ -194,7 +194,7 @@ static int build_mode(int mode, int H, int W, int out_h, int out_w, IgemmParams*
     case UZ_CONV3X3_DGRAD: {
       const int sgn = (mode == UZ_CONV3X3) ? 1 : -1;
       for (int r = 0; r < 3; ++r)
-        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, sgn * (r - 1), sgn * (s - 1), r * 3 + s, 0);
+        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, sgn * dil * (r - 1), sgn * dil * (s - 1), r * 3 + s, 0);
       mi->ntaps[0] = 9;
       mi->btaps = 9;
       break;
@@ -604,6 +604,14 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
                              int out_ld, int out_h, int out_w, float* stats, int flags, void* stream) {
   const int sms = uz_device_sm_count();
   if (sms < 0) return sms;
+  // dilated 3x3 convolution (u2net.py:10: padding = dilation = dirate): UZ_CONV3X3 | UZ_DILATION(d).  Only the tap shifts
+  // change, so it runs on the per-tap kernel (one shifted TMA box per tap, zero fill outside the image); the halo-box
+  // kernel would need a (8 + 2d) x (16 + 2d) box per 64 channels - 98 KB at d = 8
+  const int dil = ((mode >> 8) & 0xff) > 1 ? ((mode >> 8) & 0xff) : 1;
+  mode &= 0xff;
+  if (dil > 1 && mode != UZ_CONV3X3 && mode != UZ_CONV3X3_DGRAD)
+    return set_error(UZ_ERR_UNSUPPORTED, "dilation %d is only supported for UZ_CONV3X3 / UZ_CONV3X3_DGRAD (mode %d)", dil, mode);
+  if (dil > 64) return set_error(UZ_ERR_UNSUPPORTED, "dilation %d > 64", dil);
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "bad activation size N=%d H=%d W=%d", N, H, W);
   if (nseg < 1 || nseg > kMaxSegs) return set_error(UZ_ERR_INVALID, "nseg=%d out of range [1,%d]", nseg, kMaxSegs);
   if (cout < 8 || (cout & 7) || (out_ld & 7) || out_ld < cout)
@@ -614,7 +622,7 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
   IgemmParams p;
   memset(&p, 0, sizeof(p));
   ModeInfo mi;
-  int rc = build_mode(mode, H, W, out_h, out_w, &p, &mi);
+  int rc = build_mode(mode, H, W, out_h, out_w, &p, &mi, dil);
   if (rc != UZ_OK) return rc;
   if (mi.num_phases > 1) {
     for (int ph = 1; ph < mi.num_phases; ++ph)
@@ -670,7 +678,9 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * cout * uz_conv_stats_rows(), st);
     if (e != cudaSuccess) return cuda_error(e, "cudaMemsetAsync(stats)");
   }
-  if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2 ||
+  if (dil > 1) {
+    // per-tap kernel below
+  } else if ((mi.num_phases == 1 && mi.oscale == 1) || mode == UZ_CONVT2X2 || mode == UZ_CONV1X1_S2 || mode == UZ_CONV3X3_S2 ||
       mode == UZ_UP2X_CONV3X3 || mode == UZ_UP2X_CONV3X3_DGRAD) {
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
@@ -893,7 +903,9 @@ static Wg2Plan plan_wgrad2(int N, int H, int W, int cin, int cout, bool up2x = f
 }  // namespace uz
 
 extern "C" size_t uz_conv_wgrad_workspace_bytes(int mode, int N, int H, int W, int cin, int cout) {
-  if (use_wgrad2(mode, H, W, cout)) return plan_wgrad2(N, H, W, cin, cout, mode == UZ_UP2X_CONV3X3).ws_bytes;
+  const int dil = ((mode >> 8) & 0xff) > 1 ? ((mode >> 8) & 0xff) : 1;
+  mode &= 0xff;
+  if (dil == 1 && use_wgrad2(mode, H, W, cout)) return plan_wgrad2(N, H, W, cin, cout, mode == UZ_UP2X_CONV3X3).ws_bytes;
   WgPlan pl = plan_wgrad(mode, N, H, W, cin, cout);
   return pl.rc == UZ_OK ? pl.ws_bytes : 0;
 }
@@ -903,11 +915,15 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
                              void* workspace, size_t workspace_bytes, void* stream) {
   const int sms = uz_device_sm_count();
   if (sms < 0) return sms;
+  const int dil = ((mode >> 8) & 0xff) > 1 ? ((mode >> 8) & 0xff) : 1;   // UZ_CONV3X3 | UZ_DILATION(d), see uz_conv_igemm
+  mode &= 0xff;
+  if (dil > 1 && mode != UZ_CONV3X3) return set_error(UZ_ERR_UNSUPPORTED, "wgrad: dilation needs UZ_CONV3X3 (mode %d)", mode);
+  if (dil > 64) return set_error(UZ_ERR_UNSUPPORTED, "wgrad: dilation %d > 64", dil);
   if ((cin & 7) || (cout & 7) || (x_ld & 7) || (dy_ld & 7) || cin < 8 || cout < 8)
     return set_error(UZ_ERR_INVALID, "wgrad: channel counts / strides must be multiples of 8");
   if (!aligned16(x) || !aligned16(dy) || !aligned16(workspace))
     return set_error(UZ_ERR_INVALID, "wgrad: pointers must be 16-byte aligned");
-  if (use_wgrad2(mode, H, W, cout)) {
+  if (dil == 1 && use_wgrad2(mode, H, W, cout)) {
     const bool up2x = mode == UZ_UP2X_CONV3X3;
     const Wg2Plan p2 = plan_wgrad2(N, H, W, cin, cout, up2x);
     if (workspace_bytes < p2.ws_bytes)
@@ -970,7 +986,7 @@ extern "C" int uz_conv_wgrad(int mode, int N, int H, int W, const void* x, int c
       rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
       if (rc == UZ_OK) rc = make_act_map(&p.qmap[0], x, cin, x_ld, N, H, W, full, pl.tw, pl.th, pl.tn);
       for (int r = 0; r < 3; ++r)
-        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, r - 1, s - 1, 0);
+        for (int s = 0; s < 3; ++s) set_tap(0, r * 3 + s, dil * (r - 1), dil * (s - 1), 0);
       break;
     case UZ_CONV1X1:
       rc = make_act_map(&p.pmap[0], dy, cout, dy_ld, N, H, W, full, pl.tw, pl.th, pl.tn);

@@ -224,9 +224,10 @@ __global__ void adaptive_avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ do
   }
 }
 
-// ATen upsample_bilinear2d, align_corners = True: src = dst * (I - 1) / (O - 1) in fp32, i0 = floor, i1 = min(i0 + 1, I - 1)
-__device__ __forceinline__ void bl_src(int dst, float scale, int I, int* i0, int* i1, float* l1) {
-  const float src = scale * static_cast<float>(dst);
+// ATen upsample_bilinear2d source index in fp32: align_corners = True: src = dst * (I - 1) / (O - 1) (off = 0);
+// align_corners = False: src = max((dst + 0.5) * I / O - 0.5, 0) (off = 0.5 * scale - 0.5); i0 = floor, i1 = min(i0 + 1, I - 1)
+__device__ __forceinline__ void bl_src(int dst, float scale, float off, int I, int* i0, int* i1, float* l1) {
+  const float src = fmaxf(fmaf(scale, static_cast<float>(dst), off), 0.f);
   int a = static_cast<int>(src);
   a = a > I - 1 ? I - 1 : a;
   *i0 = a;
@@ -236,7 +237,7 @@ __device__ __forceinline__ void bl_src(int dst, float scale, int I, int* i0, int
 
 __global__ void bilinear_resize_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int C,
                                            __nv_bfloat16* __restrict__ out, int out_ld, int OH, int OW, float sy,
-                                           float sx) {
+                                           float sx, float offy, float offx) {
   const int cv = C / 8;
   const long long total = static_cast<long long>(N) * OH * OW * cv;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -249,8 +250,8 @@ __global__ void bilinear_resize_fwd_kernel(const __nv_bfloat16* __restrict__ x, 
     const long long n = q / OH;
     int y0, y1, x0, x1;
     float ly, lx;
-    bl_src(oy, sy, H, &y0, &y1, &ly);
-    bl_src(ox, sx, W, &x0, &x1, &lx);
+    bl_src(oy, sy, offy, H, &y0, &y1, &ly);
+    bl_src(ox, sx, offx, W, &x0, &x1, &lx);
     float a[8], b[8], c[8], d[8], o[8];
     ld8(x + ((n * H + y0) * W + x0) * x_ld + g * 8, a);
     ld8(x + ((n * H + y0) * W + x1) * x_ld + g * 8, b);
@@ -265,8 +266,8 @@ __global__ void bilinear_resize_fwd_kernel(const __nv_bfloat16* __restrict__ x, 
 
 // exact adjoint in gather form: input pixel (iy, ix) collects every output whose (i0, i1) pair contains it
 __global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int C,
-                                           int OH, int OW, float sy, float sx, __nv_bfloat16* __restrict__ dx, int dx_ld,
-                                           int accumulate) {
+                                           int OH, int OW, float sy, float sx, float offy, float offx,
+                                           __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate) {
   const int cv = C / 8;
   const long long total = static_cast<long long>(N) * H * W * cv;
   const float ry = sy > 0.f ? 1.f / sy : 0.f, rx = sx > 0.f ? 1.f / sx : 0.f;
@@ -279,10 +280,10 @@ __global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dou
     const int iy = static_cast<int>(q % H);
     const long long n = q / H;
     // candidate outputs: src in (i - 1, i + 1)  ->  dst in ((i - 1) / scale, (i + 1) / scale), widened by one
-    int oy_lo = sy > 0.f ? static_cast<int>(floorf((iy - 1) * ry)) - 1 : 0;
-    int oy_hi = sy > 0.f ? static_cast<int>(ceilf((iy + 1) * ry)) + 1 : OH - 1;
-    int ox_lo = sx > 0.f ? static_cast<int>(floorf((ix - 1) * rx)) - 1 : 0;
-    int ox_hi = sx > 0.f ? static_cast<int>(ceilf((ix + 1) * rx)) + 1 : OW - 1;
+    int oy_lo = sy > 0.f ? static_cast<int>(floorf((iy - 1 - offy) * ry)) - 1 : 0;
+    int oy_hi = sy > 0.f ? static_cast<int>(ceilf((iy + 1 - offy) * ry)) + 1 : OH - 1;
+    int ox_lo = sx > 0.f ? static_cast<int>(floorf((ix - 1 - offx) * rx)) - 1 : 0;
+    int ox_hi = sx > 0.f ? static_cast<int>(ceilf((ix + 1 - offx) * rx)) + 1 : OW - 1;
     oy_lo = oy_lo < 0 ? 0 : oy_lo;
     ox_lo = ox_lo < 0 ? 0 : ox_lo;
     oy_hi = oy_hi > OH - 1 ? OH - 1 : oy_hi;
@@ -291,13 +292,13 @@ __global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dou
     for (int oy = oy_lo; oy <= oy_hi; ++oy) {
       int y0, y1;
       float ly;
-      bl_src(oy, sy, H, &y0, &y1, &ly);
+      bl_src(oy, sy, offy, H, &y0, &y1, &ly);
       const float wy = (y0 == iy ? 1.f - ly : 0.f) + (y1 == iy ? ly : 0.f);
       if (wy == 0.f) continue;
       for (int ox = ox_lo; ox <= ox_hi; ++ox) {
         int x0, x1;
         float lx;
-        bl_src(ox, sx, W, &x0, &x1, &lx);
+        bl_src(ox, sx, offx, W, &x0, &x1, &lx);
         const float wx = (x0 == ix ? 1.f - lx : 0.f) + (x1 == ix ? lx : 0.f);
         if (wx == 0.f) continue;
         float f[8];
@@ -306,6 +307,83 @@ __global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dou
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], w, acc[j]);
       }
+    }
+    __nv_bfloat16* d = dx + ((n * H + iy) * W + ix) * dx_ld + g * 8;
+    if (accumulate) {
+      float old[8];
+      ld8(d, old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += old[j];
+    }
+    st8(d, acc);
+  }
+}
+
+// Separable form of the same adjoint for large magnifications (the side maps of U^2-Net grow 4-32x, u2net.py:276-284: in
+// the one-pass gather every input pixel would walk (2 s + 2)^2 candidate outputs serially with a few thousand threads in
+// flight).  Bilinear weights factor as wy * wx, so: pass X reduces every output row onto the W input columns (fp32
+// intermediate [N][OH][W][C]), pass Y reduces the OH rows of the intermediate onto the H input rows.
+__global__ void bilinear_bwd_x_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int W, int C, int OH,
+                                      int OW, float sx, float offx, float* __restrict__ tmp) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * OH * W * cv;
+  const float rx = sx > 0.f ? 1.f / sx : 0.f;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ix = static_cast<int>(q % W);
+    q /= W;                                   // q = n * OH + oy
+    int ox_lo = sx > 0.f ? static_cast<int>(floorf((ix - 1 - offx) * rx)) - 1 : 0;
+    int ox_hi = sx > 0.f ? static_cast<int>(ceilf((ix + 1 - offx) * rx)) + 1 : OW - 1;
+    ox_lo = ox_lo < 0 ? 0 : ox_lo;
+    ox_hi = ox_hi > OW - 1 ? OW - 1 : ox_hi;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+      int x0, x1;
+      float lx;
+      bl_src(ox, sx, offx, W, &x0, &x1, &lx);
+      const float wx = (x0 == ix ? 1.f - lx : 0.f) + (x1 == ix ? lx : 0.f);
+      if (wx == 0.f) continue;
+      float f[8];
+      ld8(dout + (q * OW + ox) * dout_ld + g * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], wx, acc[j]);
+    }
+    float4* t = reinterpret_cast<float4*>(tmp + (q * W + ix) * C + g * 8);
+    t[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    t[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+
+__global__ void bilinear_bwd_y_kernel(const float* __restrict__ tmp, int N, int H, int W, int C, int OH, float sy, float offy,
+                                      __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  const float ry = sy > 0.f ? 1.f / sy : 0.f;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int ix = static_cast<int>(q % W);
+    q /= W;
+    const int iy = static_cast<int>(q % H);
+    const long long n = q / H;
+    int oy_lo = sy > 0.f ? static_cast<int>(floorf((iy - 1 - offy) * ry)) - 1 : 0;
+    int oy_hi = sy > 0.f ? static_cast<int>(ceilf((iy + 1 - offy) * ry)) + 1 : OH - 1;
+    oy_lo = oy_lo < 0 ? 0 : oy_lo;
+    oy_hi = oy_hi > OH - 1 ? OH - 1 : oy_hi;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int oy = oy_lo; oy <= oy_hi; ++oy) {
+      int y0, y1;
+      float ly;
+      bl_src(oy, sy, offy, H, &y0, &y1, &ly);
+      const float wy = (y0 == iy ? 1.f - ly : 0.f) + (y1 == iy ? ly : 0.f);
+      if (wy == 0.f) continue;
+      float f[8];
+      pw_load8f(tmp + ((n * OH + oy) * W + ix) * C + g * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], wy, acc[j]);
     }
     __nv_bfloat16* d = dx + ((n * H + iy) * W + ix) * dx_ld + g * 8;
     if (accumulate) {
@@ -397,10 +475,15 @@ extern "C" int uz_adaptive_avgpool_bwd(const void* dout, int dout_ld, int N, int
   return UZ_OK;
 }
 
-static float bl_scale(int in, int out) { return out > 1 ? static_cast<float>(in - 1) / static_cast<float>(out - 1) : 0.f; }
+// ATen area_pixel_compute_scale: align_corners -> (I - 1) / (O - 1) (0 for O = 1); else I / O (no scale_factor given)
+static float bl_scale(int in, int out, int align) {
+  if (align) return out > 1 ? static_cast<float>(in - 1) / static_cast<float>(out - 1) : 0.f;
+  return static_cast<float>(in) / static_cast<float>(out);
+}
+static float bl_off(float scale, int align) { return align ? 0.f : 0.5f * scale - 0.5f; }
 
 extern "C" int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH,
-                                      int OW, void* stream) {
+                                      int OW, int align_corners, void* stream) {
   PW_REQUIRE_DEVICE();
   int rc = chk("bilinear_resize_fwd(x)", x, C, x_ld);
   if (rc || (rc = chk("bilinear_resize_fwd(out)", out, C, out_ld))) return rc;
@@ -408,20 +491,49 @@ extern "C" int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int
   bilinear_resize_fwd_kernel<<<ew_grid(static_cast<long long>(N) * OH * OW * (C / 8)), 256, 0,
                                static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C,
                                                                     static_cast<__nv_bfloat16*>(out), out_ld, OH, OW,
-                                                                    bl_scale(H, OH), bl_scale(W, OW));
+                                                                    bl_scale(H, OH, align_corners), bl_scale(W, OW, align_corners),
+                                                                    bl_off(bl_scale(H, OH, align_corners), align_corners),
+                                                                    bl_off(bl_scale(W, OW, align_corners), align_corners));
   PW_CHECK_LAUNCH("bilinear_resize_fwd launch");
   return UZ_OK;
 }
 
+// separable two-pass backward from 4x magnification on (needs the fp32 intermediate [N][OH][W][C])
+static bool bl_separable(int H, int W, int OH, int OW) { return OH >= 4 * H && OW >= 4 * W; }
+
+extern "C" size_t uz_bilinear_resize_bwd_workspace_bytes(int N, int H, int W, int C, int OH, int OW) {
+  return bl_separable(H, W, OH, OW) ? sizeof(float) * static_cast<size_t>(N) * OH * W * C : 0;
+}
+
 extern "C" int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx,
-                                      int dx_ld, int accumulate, void* stream) {
+                                      int dx_ld, int accumulate, int align_corners, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
   PW_REQUIRE_DEVICE();
   int rc = chk("bilinear_resize_bwd(dout)", dout, C, dout_ld);
   if (rc || (rc = chk("bilinear_resize_bwd(dx)", dx, C, dx_ld))) return rc;
   if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "bilinear_resize_bwd: bad extents");
+  if (bl_separable(H, W, OH, OW)) {
+    const size_t need = uz_bilinear_resize_bwd_workspace_bytes(N, H, W, C, OH, OW);
+    if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 15u))
+      return set_error(UZ_ERR_WORKSPACE, "bilinear_resize_bwd: workspace %zu < required %zu bytes (16-byte aligned)",
+                       workspace_bytes, need);
+    const float sy = bl_scale(H, OH, align_corners), sx = bl_scale(W, OW, align_corners);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float* tmp = static_cast<float*>(workspace);
+    bilinear_bwd_x_kernel<<<ew_grid(static_cast<long long>(N) * OH * W * (C / 8)), 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(dout), dout_ld, N, W, C, OH, OW, sx, bl_off(sx, align_corners), tmp);
+    PW_CHECK_LAUNCH("bilinear_resize_bwd (x pass) launch");
+    bilinear_bwd_y_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0, st>>>(
+        tmp, N, H, W, C, OH, sy, bl_off(sy, align_corners), static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate);
+    PW_CHECK_LAUNCH("bilinear_resize_bwd (y pass) launch");
+    return UZ_OK;
+  }
   bilinear_resize_bwd_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0,
                                static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H,
-                                                                    W, C, OH, OW, bl_scale(H, OH), bl_scale(W, OW),
+                                                                    W, C, OH, OW, bl_scale(H, OH, align_corners),
+                                                                    bl_scale(W, OW, align_corners),
+                                                                    bl_off(bl_scale(H, OH, align_corners), align_corners),
+                                                                    bl_off(bl_scale(W, OW, align_corners), align_corners),
                                                                     static_cast<__nv_bfloat16*>(dx), dx_ld, accumulate);
   PW_CHECK_LAUNCH("bilinear_resize_bwd launch");
   return UZ_OK;

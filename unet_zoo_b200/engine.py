@@ -312,7 +312,7 @@ class Ctx:
 
     def conv(self, mode: int, segs: Sequence[Act], wp: torch.Tensor, cout: int, bias: Optional[torch.Tensor],
              out_ptr: int, out_ld: int, out_h: int, out_w: int, stats: Optional[torch.Tensor] = None, flags: int = 0,
-             in_grad: bool = False):
+             in_grad: bool = False, dilation: int = 1):
         """uz_conv_igemm over a virtual concat of `segs` (activations, or their gradients when in_grad)."""
         n = len(segs)
         ptrs = (_c_void_p * n)(*[(s.gptr() if in_grad else s.ptr) for s in segs])
@@ -328,15 +328,17 @@ class Ctx:
         flops = 2.0 * opix * cout * cin * taps
         # algorithmic HBM bytes: every operand once (input pixels, packed weights, output (read too when accumulating))
         nbytes = 2.0 * (a.npix * cin + opix * cout * (2 if flags & L.FLAG_ACCUMULATE else 1) + wp.numel())
-        with _Timed("igemm_fwd", flops, f"{_MODE_NAMES.get(mode, mode)} {cin}->{cout} @{out_h}x{out_w} n{a.N}", nbytes):
-            rc = self.lib.uz_conv_igemm(mode, a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
+        tag = f"{_MODE_NAMES.get(mode, mode)}{'' if dilation == 1 else f'.d{dilation}'} {cin}->{cout} @{out_h}x{out_w} n{a.N}"
+        with _Timed("igemm_fwd", flops, tag, nbytes):
+            rc = self.lib.uz_conv_igemm(mode | L.dilation(dilation), a.N, a.H, a.W, n, ptrs, cs, lds, wp.data_ptr(), cout, _ptr(bias), out_ptr,
                                         out_ld, out_h, out_w, _ptr(stats), flags, self.stream)
         L.check(rc, "uz_conv_igemm")
         self.launches += 1
 
     def wgrad(self, mode: int, x_ptr: int, N, H, W, cin: int, x_ld: int, dy_ptr: int, cout: int, dy_ld: int,
-              dw: torch.Tensor, cin_total: int, c_off: int, accumulate: bool = False):
-        need = self.lib.uz_conv_wgrad_workspace_bytes(mode, N, H, W, cin, cout)
+              dw: torch.Tensor, cin_total: int, c_off: int, accumulate: bool = False, dilation: int = 1):
+        lmode = mode | L.dilation(dilation)
+        need = self.lib.uz_conv_wgrad_workspace_bytes(lmode, N, H, W, cin, cout)
         ws = self.workspace(need)
         if mode == L.CONVT2X2:
             flops = 2.0 * N * H * W * cin * cout * 4
@@ -355,7 +357,7 @@ class Ctx:
         # algorithmic HBM bytes: x and dy once, the fp32 gradient block once (read too when accumulating)
         nbytes = 2.0 * (N * H * W * cin + dy_pix * cout) + 4.0 * cin * cout * (4 if mode == L.CONVT2X2 else _TAPS[mode]) * (2 if accumulate else 1)
         with _Timed("igemm_wgrad", flops, f"{_MODE_NAMES.get(mode, mode)}.wgrad {cin}->{cout} @{H}x{W} n{N}", nbytes):
-            rc = self.lib.uz_conv_wgrad(mode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total,
+            rc = self.lib.uz_conv_wgrad(lmode, N, H, W, x_ptr, cin, x_ld, dy_ptr, cout, dy_ld, dw.data_ptr(), cin_total,
                                         c_off, int(accumulate), ws.data_ptr(), ws.numel(), self.stream)
         L.check(rc, "uz_conv_wgrad")
         self.launches += 2
@@ -470,8 +472,10 @@ def _weight_for(conv, cin_total: int) -> torch.Tensor:
 
 
 def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None, pooled: Optional[Act] = None,
-                relu: bool = True, mode: int = L.CONV3X3, stem: Optional[str] = None, need_dx: bool = True) -> Act:
+                relu: bool = True, mode: int = L.CONV3X3, stem: Optional[str] = None, need_dx: bool = True,
+                dilation: int = 1) -> Act:
     """[ReLU](BatchNorm2d(Conv2d(cat(xs)))) with optional MaxPool2d(2,2) second output.
+    `dilation` > 1 (mode CONV3X3 only): Conv2d(3, padding = dilation = d), REBNCONV of u2net.py:10.
 
     Reference: DoubleConv / ConvBlock / VGGBlock halves (common_layers.py:28-33,47-57; nested_unet.py:13-22),
     UpConvBlock with mode=UP2X_CONV3X3 (common_layers.py:70-76), DownSample pooling (common_layers.py:92-95).
@@ -479,7 +483,11 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
     Inference: BatchNorm folded into the packed weights and bias, ReLU in the conv epilogue.
     """
     if ctx.fp32:
+        if dilation != 1:
+            raise RuntimeError("unet_zoo_b200: dilated convolutions have no fp32 parity path")
         return _F32.conv_bn_act(ctx, xs, conv, bn, out=out, pooled=pooled, relu=relu, mode=mode, stem=stem, need_dx=need_dx)
+    if dilation != 1 and (mode != L.CONV3X3 or stem == "im2col"):
+        raise ValueError("dilation needs a plain 3x3 convolution")
     a0 = xs[0]
     N, H, W = a0.N, a0.H, a0.W
     cout = conv.out_channels
@@ -506,7 +514,7 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
                             row_scale=scale, kp=a0.C if is_stem else 0), bias
         deps = [conv.weight, conv.bias] + ([bn.weight, bn.bias, bn.running_mean, bn.running_var] if bn is not None else [])
         wp, bias = ctx.cached(("conv_bn", id(conv), id(bn), cin_total, a0.C if is_stem else 0), deps, folded)
-        ctx.conv(conv_mode, xs, wp, cout, bias, out.ptr, out.ld, Ho, Wo, None, L.FLAG_RELU if relu else 0)
+        ctx.conv(conv_mode, xs, wp, cout, bias, out.ptr, out.ld, Ho, Wo, None, L.FLAG_RELU if relu else 0, dilation=dilation)
         if pooled is not None:
             ctx.bn_apply(out, None, None, False, None, pooled)
         return out
@@ -516,7 +524,7 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
                  kp=a0.C if is_stem else 0)
     z = ctx.new_act(N, Ho, Wo, cout)
     stats = ctx.f32(ctx.stats_rows, 2, cout)
-    ctx.conv(conv_mode, xs, wp, cout, conv.bias, z.ptr, z.ld, Ho, Wo, stats, L.FLAG_STATS)
+    ctx.conv(conv_mode, xs, wp, cout, conv.bias, z.ptr, z.ld, Ho, Wo, stats, L.FLAG_STATS, dilation=dilation)
     bnbuf = ctx.f32(4, cout)
     ctx.bn_finalize(stats, ctx.stats_rows, cout, N * Ho * Wo, bn, bnbuf)
     ctx.bn_apply(z, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out, pooled)
@@ -533,12 +541,13 @@ def conv_bn_act(ctx: Ctx, xs: Sequence[Act], conv, bn, out: Optional[Act] = None
             c.bn_bwd(z, out.gptr() if has_dy else None, out.ld, pooled.gptr() if has_dp else None,
                      pooled.ld if has_dp else 0, bnbuf, relu, z.ptr, z.ld, dgamma, dbeta, dbias)
             c.pready(bn.weight, bn.bias, conv.bias)
-            _conv_backward(c, xs, conv, z, mode, is_stem, cin_total, need_dx)
+            _conv_backward(c, xs, conv, z, mode, is_stem, cin_total, need_dx, dilation)
         ctx.tape.append(backward)
     return out
 
 
-def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem: bool, cin_total: int, need_dx: bool):
+def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem: bool, cin_total: int, need_dx: bool,
+                   dilation: int = 1):
     """Weight gradient (tcgen05 split-K) and data gradient (flipped-weight implicit GEMM) of one convolution;
     `dz` holds the gradient w.r.t. the convolution output (NHWC bf16)."""
     a0 = xs[0]
@@ -571,7 +580,8 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
                     c.launches += 1
                     c.wgrad(L.CONV3X3, up.ptr, up.N, up.H, up.W, up.C, up.ld, dz.ptr, cout, dz.ld, tgt, cin_total, off)
                 else:
-                    c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, tgt, cin_total, off)
+                    c.wgrad(mode, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, cout, dz.ld, tgt, cin_total, off,
+                            dilation=dilation)
                 off += a.C
             if padded:
                 dw.copy_(tgt[:, :conv.in_channels])
@@ -596,13 +606,13 @@ def _conv_backward(c: Ctx, xs: Sequence[Act], conv, dz: Act, mode: int, is_stem:
                     acc = True
                 w_rows = wpd[off + r0: off + r0 + rc]
                 stats = None
-                if a.buf.want_gsum and not acc and mode == L.CONV3X3:
+                if a.buf.want_gsum and not acc and mode == L.CONV3X3 and dilation == 1:
                     # the epilogue's per-channel sums of this gradient ARE the bias gradient of the ConvTranspose2d that
                     # produced (part of) the buffer: saves a full read of the gradient (uz_colsum)
                     stats = c.f32(c.stats_rows, 2, rc)
                     a.buf.gsum.append((a.c0 + r0, a.c0 + r0 + rc, stats))
                 c.conv(dgrad_mode, [dz], w_rows, rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W, stats,
-                       L.FLAG_STATS if stats is not None else (L.FLAG_ACCUMULATE if acc else 0))
+                       L.FLAG_STATS if stats is not None else (L.FLAG_ACCUMULATE if acc else 0), dilation=dilation)
             off += a.C
     if dw is not None and has_dgrad and c.overlap_wgrad:
         # after the data gradient in stream order: the data gradient is on the critical path, the weight gradient only
@@ -963,21 +973,173 @@ def adaptive_avgpool(ctx: Ctx, x: Act, OH: int, OW: int) -> Act:
     return out
 
 
-def bilinear_resize(ctx: Ctx, x: Act, OH: int, OW: int, out: Optional[Act] = None) -> Act:
-    """F.interpolate(x, size=(OH, OW), mode="bilinear", align_corners=True) (unet_transformer.py:222)."""
+def bilinear_resize(ctx: Ctx, x: Act, OH: int, OW: int, out: Optional[Act] = None, align_corners: bool = True) -> Act:
+    """F.interpolate(x, size=(OH, OW), mode="bilinear", align_corners=...): True for unet_transformer.py:222, False for
+    u2net.py:19-23 (`_upsample_like`)."""
     if out is None:
         out = ctx.new_act(x.N, OH, OW, x.C)
-    L.check(ctx.lib.uz_bilinear_resize_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, OH, OW, ctx.stream),
-            "uz_bilinear_resize_fwd")
+    L.check(ctx.lib.uz_bilinear_resize_fwd(x.ptr, x.ld, x.N, x.H, x.W, x.C, out.ptr, out.ld, OH, OW, int(align_corners),
+                                           ctx.stream), "uz_bilinear_resize_fwd")
     ctx.launches += 1
     if ctx.record:
         def backward(c: Ctx):
             if not out.has_grad():
                 raise RuntimeError("unet_zoo_b200: bilinear_resize output has no gradient")
             for (r0, rc, acc) in x.grad_writes():
+                need = c.lib.uz_bilinear_resize_bwd_workspace_bytes(x.N, x.H, x.W, rc, OH, OW)
+                ws = c.workspace(need) if need else None
                 L.check(c.lib.uz_bilinear_resize_bwd(out.gptr() + 2 * r0, out.ld, x.N, x.H, x.W, rc, OH, OW,
-                                                     x.gptr() + 2 * r0, x.ld, int(acc), c.stream), "uz_bilinear_resize_bwd")
+                                                     x.gptr() + 2 * r0, x.ld, int(acc), int(align_corners),
+                                                     ws.data_ptr() if need else None, need, c.stream),
+                        "uz_bilinear_resize_bwd")
                 c.launches += 1
+        ctx.tape.append(backward)
+    return out
+
+
+def conv_padded_out(ctx: Ctx, xs: Sequence[Act], conv, out: Act) -> Act:
+    """Conv2d(C, K, 3, padding=1) with K < 8 output channels (the side convolutions of U^2-Net, u2net.py:238-243) on the
+    tensor-core path: the filter bank is zero-padded to 8 output channels, `out` is an 8-channel slot whose channels
+    K..7 come out as exact zeros.  Backward: weight / bias gradients of the K real rows, data gradient as usual."""
+    if ctx.fp32:
+        raise RuntimeError("unet_zoo_b200: conv_padded_out has no fp32 parity path")
+    K = conv.out_channels
+    if out.C != 8 or K > 8:
+        raise ValueError("conv_padded_out: the output slot has 8 channels")
+    a0 = xs[0]
+    cin_total = sum(a.C for a in xs)
+
+    def padded():
+        w = torch.nn.functional.pad(conv.weight.detach(), (0, 0, 0, 0, 0, 0, 0, 8 - K))
+        b = torch.nn.functional.pad(conv.bias.detach(), (0, 8 - K)) if conv.bias is not None else None
+        return w, b
+    if ctx.training:
+        w8, b8 = padded()
+        wp = ctx.pack(w8, "conv_fwd")
+    else:
+        wp, b8 = ctx.cached(("conv_padded", id(conv)), [conv.weight, conv.bias],
+                            lambda: (lambda wb: (ctx.pack(wb[0], "conv_fwd"), wb[1]))(padded()))
+    ctx.conv(L.CONV3X3, xs, wp, 8, b8, out.ptr, out.ld, a0.H, a0.W, None, 0)
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: conv_padded_out output has no gradient")
+            dz = GradAct(out)
+            db = c.pgrad(conv.bias) if conv.bias is not None else None
+            if db is not None:
+                tmp = c.f32(8)
+                c.colsum(dz.ptr, dz.ld, out.npix, 8, tmp)
+                db.copy_(tmp[:K])
+            dw = c.pgrad(conv.weight)
+            if dw is not None:
+                tgt = c.f32(8, cin_total, 3, 3)
+                off = 0
+                for a in xs:
+                    c.wgrad(L.CONV3X3, a.ptr, a.N, a.H, a.W, a.C, a.ld, dz.ptr, 8, dz.ld, tgt, cin_total, off)
+                    off += a.C
+                dw.copy_(tgt[:K])
+            c.pready(conv.weight, conv.bias)
+            wpd = c.pack(padded()[0], "conv_dgrad")                 # [Cin][9][8]
+            off = 0
+            for a in xs:
+                for (r0, rc, acc) in a.grad_writes():
+                    c.conv(L.CONV3X3_DGRAD, [dz], wpd[off + r0: off + r0 + rc], rc, None, a.gptr() + 2 * r0, a.ld, a.H, a.W,
+                           None, L.FLAG_ACCUMULATE if acc else 0)
+                off += a.C
+        ctx.tape.append(backward)
+    return out
+
+
+def fused_side_head(ctx: Ctx, fuse: Act, outconv, K: int, nsides: int) -> torch.Tensor:
+    """The output stage of U^2-Net in ONE 1x1 head pass over the buffer of upsampled side maps (side i in channels
+    [8 i, 8 i + K)): logits[:, :K] = outconv(cat(sides)) (u2net.py:285), logits[:, K (1 + i) : K (2 + i)] = side i itself
+    (fp32 NCHW, the tensors the reference returns, :287-295).  Backward: one uz_head_bwd gives the gradient of every
+    side map (its own logit gradient + outconv's share) and outconv's weight / bias gradients."""
+    C = fuse.C
+    rows = K * (1 + nsides)
+    dev = ctx.device
+    w = _side_selector(K, nsides, C, dev).clone()
+    ow = outconv.weight.detach().reshape(K, nsides * K)
+    for i in range(nsides):
+        w[:K, 8 * i: 8 * i + K] = ow[:, i * K:(i + 1) * K]
+    b = torch.zeros(rows, dtype=torch.float32, device=dev)
+    if outconv.bias is not None:
+        b[:K] = outconv.bias.detach()
+    logits = torch.empty((fuse.N, rows, fuse.H, fuse.W), dtype=torch.float32, device=dev)
+    L.check(ctx.lib.uz_head_fwd(fuse.ptr, fuse.ld, fuse.N, fuse.H, fuse.W, C, rows, w.data_ptr(), b.data_ptr(),
+                                logits.data_ptr(), ctx.stream), "uz_head_fwd")
+    ctx.launches += (rows + 3) // 4
+    idx = len(ctx.outputs)
+    ctx.outputs.append(logits)
+    if ctx.record:
+        def backward(c: Ctx):
+            g = c.out_grads[idx] if idx < len(c.out_grads) else None
+            if g is None:
+                raise RuntimeError("unet_zoo_b200: fused_side_head output has no gradient")
+            dl = g.contiguous().float()
+            dwf, dbf = c.f32(rows, C), c.f32(rows)
+            ws = c.workspace(c.lib.uz_head_bwd_workspace_bytes(C))
+            if any(acc for _, _, acc in fuse.grad_writes()):
+                raise NotImplementedError("fused_side_head input already has a gradient")
+            L.check(c.lib.uz_head_bwd(fuse.ptr, fuse.ld, dl.data_ptr(), fuse.N, fuse.H, fuse.W, C, rows, w.data_ptr(),
+                                      fuse.gptr(), fuse.ld, dwf.data_ptr(), dbf.data_ptr(), 0, ws.data_ptr(), ws.numel(),
+                                      c.stream), "uz_head_bwd")
+            c.launches += 3 * ((rows + 3) // 4)
+            dw = c.pgrad(outconv.weight)
+            if dw is not None:
+                dwv = dw.view(K, nsides * K)
+                for i in range(nsides):
+                    dwv[:, i * K:(i + 1) * K] = dwf[:K, 8 * i: 8 * i + K]
+            db = c.pgrad(outconv.bias) if outconv.bias is not None else None
+            if db is not None:
+                db.copy_(dbf[:K])
+            c.pready(outconv.weight, outconv.bias)
+        ctx.tape.append(backward)
+    return logits
+
+
+_SIDE_SELECTORS: Dict[tuple, torch.Tensor] = {}
+
+
+def _side_selector(K: int, nsides: int, C: int, device) -> torch.Tensor:
+    """Constant rows K.. of the fused head's weight matrix (one-hot selectors of the side maps); built on the device with
+    scalar fills (no host-to-device copy: the first call may happen under CUDA graph capture) and kept per device."""
+    key = (K, nsides, C, str(device))
+    sel = _SIDE_SELECTORS.get(key)
+    if sel is None:
+        sel = torch.zeros(K * (1 + nsides), C, dtype=torch.float32, device=device)
+        for i in range(nsides):
+            for k in range(K):
+                sel[K * (1 + i) + k, 8 * i + k] = 1.0
+        _SIDE_SELECTORS[key] = sel
+    return sel
+
+
+def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Optional[Act] = None) -> Act:
+    """out = a + b with optional MaxPool2d(2, 2) of the sum as a second output: `return hx1d + hxin` of the RSU blocks
+    (u2net.py:78,127,171,210,237) followed by the stage pooling (u2net.py:222-232)."""
+    if ctx.fp32:
+        raise RuntimeError("unet_zoo_b200: residual_add has no fp32 parity path")
+    if out is None:
+        out = ctx.new_act(a.N, a.H, a.W, a.C)
+    L.check(ctx.lib.uz_residual_add_fwd(a.ptr, a.ld, b.ptr, b.ld, a.N, a.H, a.W, a.C, out.ptr, out.ld,
+                                        pooled.ptr if pooled else None, pooled.ld if pooled else 0, ctx.stream),
+            "uz_residual_add_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            has_dy = out.has_grad()
+            has_dp = pooled is not None and pooled.has_grad()
+            if not (has_dy or has_dp):
+                raise RuntimeError("unet_zoo_b200: residual_add output has no gradient")
+            ra, rb = a.grad_writes(), b.grad_writes()
+            if len(ra) != 1 or len(rb) != 1:
+                raise NotImplementedError("residual_add: input gradient partly written by another consumer")
+            L.check(c.lib.uz_residual_add_bwd(out.ptr, out.ld, a.N, a.H, a.W, a.C, out.gptr() if has_dy else None,
+                                              out.ld if has_dy else 0, pooled.gptr() if has_dp else None,
+                                              pooled.ld if has_dp else 0, a.gptr(), a.ld, int(ra[0][2]), b.gptr(), b.ld,
+                                              int(rb[0][2]), c.stream), "uz_residual_add_bwd")
+            c.launches += 1
         ctx.tape.append(backward)
     return out
 

@@ -42,9 +42,16 @@ try:  # second neighbouring model: self- / cross-attention U-Net on the same blo
 except ImportError:  # pragma: no cover
     pass
 
+try:  # third neighbouring family: U^2-Net (RSU blocks = conv-BN-ReLU with dilation, nested encoder-decoders)
+    from .u2net import U2NET, U2NETP
+    _model_entries["u2net"] = U2NET
+    _model_entries["u2netp"] = U2NETP
+except ImportError:  # pragma: no cover
+    pass
+
 # registry names of the reference that are deliberately not part of this build
 _OUT_OF_SCOPE = ("raunet", "da_transformer", "uctransnet", "multiresunet",
-                 "missformer", "vnet", "u2net", "u2netp", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
+                 "missformer", "vnet", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
                  "mmunet", "axialunet", "gated", "medt", "logo")
 
 
@@ -83,6 +90,8 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
     elif name == "unet_transformer":   # the reference factory's default branch (models/__init__.py:221-223)
         args = dict(in_channels=in_channels, num_classes=num_classes)
+    elif name in ("u2net", "u2netp"):  # models/__init__.py:156-158
+        args = dict(in_ch=in_channels, out_ch=num_classes)
     else:  # resunet
         args = dict(in_channels=in_channels, num_classes=num_classes, filters=[64, 128, 256, 512])
     args.update(kwargs)              # leftovers reach the constructor (TypeError if it does not know them)

@@ -113,7 +113,10 @@ class GraphedTrainStep:
     def _fwd_bwd(self):
         self.optimizer.zero_grad(set_to_none=True)
         self.out = self.model(self.x)
-        outs = self.out if isinstance(self.out, (list, tuple)) else [self.out]
+        if isinstance(self.out, dict):                     # U2NET: seven maps, loss weights 1.0 (training_loop.py:23-31)
+            outs = list(self.out.values())
+        else:
+            outs = self.out if isinstance(self.out, (list, tuple)) else [self.out]
         loss = self.criterion(outs[0], self.target)
         for o in outs[1:]:                                 # deep supervision: the reference sums the per-head losses
             loss = loss + self.criterion(o, self.target)

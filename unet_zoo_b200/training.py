@@ -68,12 +68,26 @@ def _unwrap(model: nn.Module) -> nn.Module:
 def _loss_and_dice(outputs, masks, criterion) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """training_loop.py:43-83 for the hot-path models (plain tensor; NestedUNet deep supervision returns a list whose
     per-head losses are summed and whose last head is the main prediction, nested_unet.py:95-102)."""
-    outs = list(outputs) if isinstance(outputs, (list, tuple)) else [outputs]
-    main = outs[-1]
+    if isinstance(outputs, dict):
+        # U2NET / U2NETP (training_loop.py:23-31, :61-64): every map against the mask (resized to the map's size - the
+        # identity for these models), weights U2NET_LOSS_WEIGHTS = 1.0 for all seven keys; 'main' is the prediction
+        outs = list(outputs.values())
+        main = outputs["main"]
+        sized = {}
+    else:
+        outs = list(outputs) if isinstance(outputs, (list, tuple)) else [outputs]
+        main = outs[-1]
+        sized = None
     loss = None
     dice = None
     for o in outs:
-        term = criterion(o, masks)
+        tgt = masks
+        if sized is not None and o.shape[2:] != masks.shape[2:]:
+            key = tuple(o.shape[2:])
+            if key not in sized:
+                sized[key] = torch.nn.functional.interpolate(masks, size=key, mode="bilinear", align_corners=False)
+            tgt = sized[key]
+        term = criterion(o, tgt)
         loss = term if loss is None else loss + term
         if o is main and getattr(criterion, "last_dice", None) is not None:
             dice = criterion.last_dice              # uz_bce_dice already produced it in the same pass
