@@ -208,6 +208,18 @@ int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b_ld, int N,
 int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, const void* dy, int dy_ld, const void* dpooled,
                         int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld, int acc_b, void* stream);
 
+/* Output stage of U2NET / U2NETP (u2net.py:273-295).  `fuse`: NHWC bf16, side map i (already at full resolution) in
+ * channels [8 i, 8 i + K), i < nsides <= 8, K <= 4 classes; w = outconv.weight [K][nsides * K], b = outconv.bias [K].
+ * uz_side_head_fwd: logits fp32 NCHW [N][(1 + nsides) K][H][W]: rows [0, K) = outconv(cat(sides)) ('main'), rows
+ *   [K (1 + i), K (2 + i)) = side map i ('side<i+1>').
+ * uz_side_head_bwd: dfuse slot i = dlogits[side i] + outconv^T dlogits[main] (channels K..7 of a slot: 0),
+ *   dw [K][nsides * K], db [K] (overwritten). */
+size_t uz_side_head_bwd_workspace_bytes(int nsides, int K);
+int uz_side_head_fwd(const void* fuse, int ld, int N, int H, int W, int nsides, int K, const float* w, const float* b,
+                     float* logits, void* stream);
+int uz_side_head_bwd(const void* fuse, int ld, const float* dlogits, int N, int H, int W, int nsides, int K, const float* w,
+                     void* dfuse, int dfuse_ld, float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
+
 /* F.pad with zeros on the bottom / right, or its backward (crop), between two NHWC pixel grids: replaces the
  * `F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])` of common_layers.py:110-113 / :173-178 (dx, dy in {0, 1} for
  * the odd input sizes the reference accepts).  dst[n,y,x,:] = (y < Hs && x < Ws) ? src[n,y,x,:] : 0 over (Hd, Wd);

@@ -6,6 +6,7 @@
 //   uz_bilinear_resize_fwd / _bwd   F.interpolate(size=..., mode="bilinear", align_corners=True) (:222), ATen index
 //                                 arithmetic; the backward is the exact adjoint in gather form (deterministic, no atomics)
 #include <cstdint>
+#include <cstdlib>
 
 #include "pw.cuh"
 
@@ -319,6 +320,93 @@ __global__ void bilinear_resize_bwd_kernel(const __nv_bfloat16* __restrict__ dou
   }
 }
 
+// Exact 2x magnification with align_corners = False (every _upsample_like inside the RSU blocks and between the stages of
+// U^2-Net, u2net.py:19-23): out[2 i] = 0.25 in[i - 1] + 0.75 in[i], out[2 i + 1] = 0.75 in[i] + 0.25 in[i + 1] per axis,
+// indices clamped at the borders - the same fp32 weights ATen computes (src = i -+ 0.25).  One thread per INPUT pixel and
+// 8-channel group: 3 x 3 neighbourhood in, 2 x 2 quad out; 32-bit index arithmetic.
+__global__ void bilinear2x_half_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, int N, int H, int W, int C,
+                                           __nv_bfloat16* __restrict__ out, int out_ld) {
+  const int cv = C / 8;
+  const unsigned total = static_cast<unsigned>(N) * H * W * cv;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int g = i % cv;
+    unsigned q = i / cv;
+    const int ix = q % W;
+    q /= W;
+    const int iy = q % H;
+    const int n = q / H;
+    const int ys[3] = {iy > 0 ? iy - 1 : 0, iy, iy < H - 1 ? iy + 1 : H - 1};
+    const int xs[3] = {ix > 0 ? ix - 1 : 0, ix, ix < W - 1 ? ix + 1 : W - 1};
+    float v[3][3][8];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int b = 0; b < 3; ++b)
+        ld8(x + (static_cast<long long>(n * H + ys[a]) * W + xs[b]) * x_ld + g * 8, v[a][b]);
+    // along x first: h[a][px] = 0.25 * (left | right neighbour) + 0.75 * centre; then the same along y
+    float h[3][2][8];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        h[a][0][j] = 0.25f * v[a][0][j] + 0.75f * v[a][1][j];
+        h[a][1][j] = 0.75f * v[a][1][j] + 0.25f * v[a][2][j];
+      }
+#pragma unroll
+    for (int py = 0; py < 2; ++py)
+#pragma unroll
+      for (int px = 0; px < 2; ++px) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          o[j] = py == 0 ? 0.25f * h[0][px][j] + 0.75f * h[1][px][j] : 0.75f * h[1][px][j] + 0.25f * h[2][px][j];
+        st8(out + (static_cast<long long>(n * 2 * H + 2 * iy + py) * (2 * W) + 2 * ix + px) * out_ld + g * 8, o);
+      }
+  }
+}
+
+// exact adjoint: din[i] = wa d[2 i - 1] + wb d[2 i] + wc d[2 i + 1] + wd d[2 i + 2] per axis with (0.25, 0.75, 0.75, 0.25),
+// border pixels take the weight of the clamped neighbour as well (wb = 1 at i = 0, wc = 1 at i = I - 1)
+__global__ void bilinear2x_half_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int dout_ld, int N, int H, int W, int C,
+                                           __nv_bfloat16* __restrict__ dx, int dx_ld, int accumulate) {
+  const int cv = C / 8;
+  const unsigned total = static_cast<unsigned>(N) * H * W * cv;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int g = i % cv;
+    unsigned q = i / cv;
+    const int ix = q % W;
+    q /= W;
+    const int iy = q % H;
+    const int n = q / H;
+    const float wy[4] = {iy > 0 ? 0.25f : 0.f, iy > 0 ? 0.75f : 1.f, iy < H - 1 ? 0.75f : 1.f, iy < H - 1 ? 0.25f : 0.f};
+    const float wx[4] = {ix > 0 ? 0.25f : 0.f, ix > 0 ? 0.75f : 1.f, ix < W - 1 ? 0.75f : 1.f, ix < W - 1 ? 0.25f : 0.f};
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      if (wy[a] == 0.f) continue;
+      const int oy = 2 * iy - 1 + a;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        if (wx[b] == 0.f) continue;
+        const int ox = 2 * ix - 1 + b;
+        float f[8];
+        ld8(dout + (static_cast<long long>(n * 2 * H + oy) * (2 * W) + ox) * dout_ld + g * 8, f);
+        const float w = wy[a] * wx[b];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], w, acc[j]);
+      }
+    }
+    __nv_bfloat16* d = dx + (static_cast<long long>(n * H + iy) * W + ix) * dx_ld + g * 8;
+    if (accumulate) {
+      float old[8];
+      ld8(d, old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += old[j];
+    }
+    st8(d, acc);
+  }
+}
+
 // Separable form of the same adjoint for large magnifications (the side maps of U^2-Net grow 4-32x, u2net.py:276-284: in
 // the one-pass gather every input pixel would walk (2 s + 2)^2 candidate outputs serially with a few thousand threads in
 // flight).  Bilinear weights factor as wy * wx, so: pass X reduces every output row onto the W input columns (fp32
@@ -481,6 +569,11 @@ static float bl_scale(int in, int out, int align) {
   return static_cast<float>(in) / static_cast<float>(out);
 }
 static float bl_off(float scale, int align) { return align ? 0.f : 0.5f * scale - 0.5f; }
+// the specialised 2x kernels: align_corners = False, exact doubling, index space below 2^31 (32-bit arithmetic)
+static bool bl_exact2x(int N, int H, int W, int C, int OH, int OW, int align) {
+  return !align && OH == 2 * H && OW == 2 * W && H >= 2 && W >= 2 &&
+         static_cast<long long>(N) * OH * OW * (C / 8) < 0x7fffffffLL && getenv("UZ_BILINEAR_GENERIC") == nullptr;
+}
 
 extern "C" int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int W, int C, void* out, int out_ld, int OH,
                                       int OW, int align_corners, void* stream) {
@@ -488,6 +581,13 @@ extern "C" int uz_bilinear_resize_fwd(const void* x, int x_ld, int N, int H, int
   int rc = chk("bilinear_resize_fwd(x)", x, C, x_ld);
   if (rc || (rc = chk("bilinear_resize_fwd(out)", out, C, out_ld))) return rc;
   if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "bilinear_resize_fwd: bad extents");
+  if (bl_exact2x(N, H, W, C, OH, OW, align_corners)) {
+    bilinear2x_half_fwd_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0,
+                                 static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C,
+                                                                      static_cast<__nv_bfloat16*>(out), out_ld);
+    PW_CHECK_LAUNCH("bilinear_resize_fwd (2x) launch");
+    return UZ_OK;
+  }
   bilinear_resize_fwd_kernel<<<ew_grid(static_cast<long long>(N) * OH * OW * (C / 8)), 256, 0,
                                static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), x_ld, N, H, W, C,
                                                                     static_cast<__nv_bfloat16*>(out), out_ld, OH, OW,
@@ -512,6 +612,14 @@ extern "C" int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int 
   int rc = chk("bilinear_resize_bwd(dout)", dout, C, dout_ld);
   if (rc || (rc = chk("bilinear_resize_bwd(dx)", dx, C, dx_ld))) return rc;
   if (N < 1 || H < 1 || W < 1 || OH < 1 || OW < 1) return set_error(UZ_ERR_INVALID, "bilinear_resize_bwd: bad extents");
+  if (bl_exact2x(N, H, W, C, OH, OW, align_corners)) {
+    bilinear2x_half_bwd_kernel<<<ew_grid(static_cast<long long>(N) * H * W * (C / 8)), 256, 0,
+                                 static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout), dout_ld, N, H,
+                                                                      W, C, static_cast<__nv_bfloat16*>(dx), dx_ld,
+                                                                      accumulate);
+    PW_CHECK_LAUNCH("bilinear_resize_bwd (2x) launch");
+    return UZ_OK;
+  }
   if (bl_separable(H, W, OH, OW)) {
     const size_t need = uz_bilinear_resize_bwd_workspace_bytes(N, H, W, C, OH, OW);
     if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 15u))

@@ -5,6 +5,8 @@
 //                         ceil_mode changes nothing)
 //   uz_residual_add_bwd   g = dy + route(dpooled) (the pooled gradient goes to the FIRST maximum of the stored y in
 //                         row-major window order, as torch's max_pool2d backward does); da (+)= g, db (+)= g
+//   uz_side_head_fwd/_bwd the output stage: outconv over the six upsampled side maps + the side maps themselves as fp32
+//                         NCHW logits (u2net.py:273-295) in one pass over the slot buffer
 #include <cstdint>
 
 #include "pw.cuh"
@@ -123,6 +125,154 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
   }
 }
 
+// ------------------------------------------------------------------------------------------------ fused output stage
+// U2NET's last lines (u2net.py:273-295): d0 = outconv(cat(d1..d6)), returned together with d1..d6.  The upsampled side
+// maps live in 8-channel slots of one NHWC bf16 buffer (slot i = channels [8 i, 8 i + K), the rest of a slot is zero).
+// One thread per pixel: nsides 16-byte loads, (1 + nsides) * K fp32 stores into NCHW planes (coalesced over pixels).
+constexpr int kSideMax = 8;    // slots
+constexpr int kSideK = 4;      // classes per map handled by these kernels
+
+template <int K>
+__global__ void __launch_bounds__(256) side_head_fwd_kernel(const __nv_bfloat16* __restrict__ fuse, int ld, long long npix,
+                                                            long long plane, int nsides,
+                                                            const float* __restrict__ w /* [K][nsides*K] */,
+                                                            const float* __restrict__ b, float* __restrict__ logits) {
+  __shared__ float ws[K * kSideMax * K + K];
+  const int nw = K * nsides * K;
+  for (int i = threadIdx.x; i < nw + K; i += blockDim.x) ws[i] = i < nw ? w[i] : (b ? b[i - nw] : 0.f);
+  __syncthreads();
+  const int rows = (1 + nsides) * K;
+  for (long long p = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; p < npix;
+       p += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long n = p / plane, hw = p - n * plane;
+    float* out = logits + n * rows * plane + hw;
+    float mainv[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) mainv[j] = ws[nw + j];
+#pragma unroll
+    for (int i = 0; i < kSideMax; ++i) {
+      if (i < nsides) {
+        float f[8];
+        ra_ld8(fuse + p * ld + i * 8, f);
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          out[(static_cast<long long>(1 + i) * K + k) * plane] = f[k];
+#pragma unroll
+          for (int j = 0; j < K; ++j) mainv[j] = fmaf(ws[j * nsides * K + i * K + k], f[k], mainv[j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < K; ++j) out[j * plane] = mainv[j];
+  }
+}
+
+// dfuse[p][slot i][k] = dl[side i][k] + sum_j w[j][i K + k] dl[main j]   (channels K..7 of a slot: 0)
+// partial[block][(j * nsides + i) * K + k] = sum_p dl[main j] * side[i][k]  ;  partial[block][K*nsides*K + j] = sum_p dl[main j]
+template <int K>
+__global__ void __launch_bounds__(256) side_head_bwd_kernel(const __nv_bfloat16* __restrict__ fuse, int ld, long long npix,
+                                                            long long plane, int nsides, const float* __restrict__ w,
+                                                            const float* __restrict__ dl, __nv_bfloat16* __restrict__ dfuse,
+                                                            int dld, float* __restrict__ partial) {
+  __shared__ float ws[K * kSideMax * K];
+  __shared__ float red[8][K * kSideMax * K + K];
+  const int nw = K * nsides * K;
+  for (int i = threadIdx.x; i < nw; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  const int rows = (1 + nsides) * K;
+  float acc[K][kSideMax][K], accb[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    accb[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < kSideMax; ++i)
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc[j][i][k] = 0.f;
+  }
+  for (long long p = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; p < npix;
+       p += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long n = p / plane, hw = p - n * plane;
+    const float* g = dl + n * rows * plane + hw;
+    float gm[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      gm[j] = __ldg(g + j * plane);
+      accb[j] += gm[j];
+    }
+#pragma unroll
+    for (int i = 0; i < kSideMax; ++i) {
+      if (i < nsides) {
+        float f[8], o[8];
+        ra_ld8(fuse + p * ld + i * 8, f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = 0.f;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          float v = __ldg(g + (static_cast<long long>(1 + i) * K + k) * plane);
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            v = fmaf(ws[j * nsides * K + i * K + k], gm[j], v);
+            acc[j][i][k] = fmaf(gm[j], f[k], acc[j][i][k]);
+          }
+          o[k] = v;
+        }
+        ra_st8(dfuse + p * dld + i * 8, o);
+      }
+    }
+  }
+  // block reduction in a fixed order: warp shuffles, then the eight warps through shared memory
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    const float vb = pw_warp_sum(accb[j]);
+    if (lane == 0) red[warp][K * kSideMax * K + j] = vb;
+#pragma unroll
+    for (int i = 0; i < kSideMax; ++i)
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        const float v = pw_warp_sum(acc[j][i][k]);
+        if (lane == 0) red[warp][(j * kSideMax + i) * K + k] = v;
+      }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < nw + K; t += blockDim.x) {
+    int src;
+    if (t < nw) {
+      const int j = t / (nsides * K), r = t - j * nsides * K;
+      src = (j * kSideMax + r / K) * K + r % K;
+    } else {
+      src = K * kSideMax * K + (t - nw);
+    }
+    float v = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) v += red[wq][src];
+    partial[static_cast<size_t>(blockIdx.x) * (nw + K) + t] = v;
+  }
+}
+
+// out[c] = sum_r partial[r][c0 + c] for c < n (rows of `pitch` floats), fixed order, one warp per column
+__global__ void side_reduce_kernel(const float* __restrict__ partial, int rows, int pitch, int c0, int n,
+                                   float* __restrict__ out) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (c >= n) return;
+  double s = 0.0;
+  for (int r = lane; r < rows; r += 32) s += static_cast<double>(partial[static_cast<size_t>(r) * pitch + c0 + c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) out[c] = static_cast<float>(s);
+}
+cudaError_t launch_reduce_rows_strided(const float* partial, int rows, int pitch, int c0, int n, float* out,
+                                       cudaStream_t st) {
+  side_reduce_kernel<<<(n + 3) / 4, 128, 0, st>>>(partial, rows, pitch, c0, n, out);
+  return cudaGetLastError();
+}
+
+int side_rows() {
+  const int sms = uz_device_sm_count();
+  return sms < 0 ? sms : sms * 4;
+}
+
 int ra_grid(long long total) {
   const int sms = uz_device_sm_count();
   long long g = (total + 255) / 256, cap = static_cast<long long>(sms > 0 ? sms : 148) * 16;
@@ -172,5 +322,70 @@ extern "C" int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W,
       static_cast<const __nv_bfloat16*>(dpooled), dpooled_ld, static_cast<__nv_bfloat16*>(da), da_ld, acc_a,
       static_cast<__nv_bfloat16*>(db), db_ld, acc_b);
   PW_CHECK_LAUNCH("residual_add_bwd launch");
+  return UZ_OK;
+}
+
+extern "C" size_t uz_side_head_bwd_workspace_bytes(int nsides, int K) {
+  const int rows = side_rows();
+  return rows < 0 ? 0 : sizeof(float) * static_cast<size_t>(rows) * (K * nsides * K + K);
+}
+
+static int side_check(const char* who, const void* fuse, int ld, int N, int H, int W, int nsides, int K) {
+  if (nsides < 1 || nsides > kSideMax || K < 1 || K > kSideK)
+    return set_error(UZ_ERR_UNSUPPORTED, "%s: needs 1..%d side maps of 1..%d classes (got %d x %d)", who, kSideMax, kSideK,
+                     nsides, K);
+  if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "%s: bad extents", who);
+  return ra_chk(who, fuse, 8 * nsides, ld);
+}
+
+extern "C" int uz_side_head_fwd(const void* fuse, int ld, int N, int H, int W, int nsides, int K, const float* w,
+                                const float* b, float* logits, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = side_check("side_head_fwd", fuse, ld, N, H, W, nsides, K);
+  if (rc) return rc;
+  if (!w || !logits) return set_error(UZ_ERR_INVALID, "side_head_fwd: null weights / output");
+  const long long plane = static_cast<long long>(H) * W, npix = plane * N;
+  const long long need = (npix + 255) / 256;
+  const int grid = static_cast<int>(need < side_rows() * 2 ? need : side_rows() * 2);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* fp = static_cast<const __nv_bfloat16*>(fuse);
+  switch (K) {
+    case 1: side_head_fwd_kernel<1><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, b, logits); break;
+    case 2: side_head_fwd_kernel<2><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, b, logits); break;
+    case 3: side_head_fwd_kernel<3><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, b, logits); break;
+    default: side_head_fwd_kernel<4><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, b, logits); break;
+  }
+  PW_CHECK_LAUNCH("side_head_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_side_head_bwd(const void* fuse, int ld, const float* dlogits, int N, int H, int W, int nsides, int K,
+                                const float* w, void* dfuse, int dfuse_ld, float* dw, float* db, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = side_check("side_head_bwd", fuse, ld, N, H, W, nsides, K);
+  if (rc || (rc = ra_chk("side_head_bwd(dfuse)", dfuse, 8 * nsides, dfuse_ld))) return rc;
+  if (!w || !dlogits || !dw || !db) return set_error(UZ_ERR_INVALID, "side_head_bwd: null argument");
+  if (!workspace || workspace_bytes < uz_side_head_bwd_workspace_bytes(nsides, K))
+    return set_error(UZ_ERR_WORKSPACE, "side_head_bwd: workspace too small");
+  const long long plane = static_cast<long long>(H) * W, npix = plane * N;
+  const long long need = (npix + 255) / 256;
+  const int grid = static_cast<int>(need < side_rows() ? need : side_rows());
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* partial = static_cast<float*>(workspace);
+  const int nw = K * nsides * K;
+  const __nv_bfloat16* fp = static_cast<const __nv_bfloat16*>(fuse);
+  __nv_bfloat16* dfp = static_cast<__nv_bfloat16*>(dfuse);
+  switch (K) {
+    case 1: side_head_bwd_kernel<1><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, dlogits, dfp, dfuse_ld, partial); break;
+    case 2: side_head_bwd_kernel<2><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, dlogits, dfp, dfuse_ld, partial); break;
+    case 3: side_head_bwd_kernel<3><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, dlogits, dfp, dfuse_ld, partial); break;
+    default: side_head_bwd_kernel<4><<<grid, 256, 0, st>>>(fp, ld, npix, plane, nsides, w, dlogits, dfp, dfuse_ld, partial); break;
+  }
+  PW_CHECK_LAUNCH("side_head_bwd launch");
+  // partial rows are [nw weights | K biases]: reduce the two column ranges into dw and db
+  cudaError_t e = launch_reduce_rows_strided(partial, grid, nw + K, 0, nw, dw, st);
+  if (e == cudaSuccess) e = launch_reduce_rows_strided(partial, grid, nw + K, nw, K, db, st);
+  if (e != cudaSuccess) return cuda_error(e, "side_head_bwd reduce launch");
   return UZ_OK;
 }

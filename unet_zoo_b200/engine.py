@@ -1051,24 +1051,19 @@ def conv_padded_out(ctx: Ctx, xs: Sequence[Act], conv, out: Act) -> Act:
 
 
 def fused_side_head(ctx: Ctx, fuse: Act, outconv, K: int, nsides: int) -> torch.Tensor:
-    """The output stage of U^2-Net in ONE 1x1 head pass over the buffer of upsampled side maps (side i in channels
-    [8 i, 8 i + K)): logits[:, :K] = outconv(cat(sides)) (u2net.py:285), logits[:, K (1 + i) : K (2 + i)] = side i itself
-    (fp32 NCHW, the tensors the reference returns, :287-295).  Backward: one uz_head_bwd gives the gradient of every
-    side map (its own logit gradient + outconv's share) and outconv's weight / bias gradients."""
-    C = fuse.C
+    """The output stage of U^2-Net in ONE pass over the buffer of upsampled side maps (side i in channels [8 i, 8 i + K)):
+    logits[:, :K] = outconv(cat(sides)) (u2net.py:285), logits[:, K (1 + i) : K (2 + i)] = side i itself (fp32 NCHW, the
+    tensors the reference returns, :287-295).  Backward: one pass gives the gradient of every side map (its own logit
+    gradient + outconv's share) and outconv's weight / bias gradients (uz_side_head_fwd / _bwd)."""
     rows = K * (1 + nsides)
     dev = ctx.device
-    w = _side_selector(K, nsides, C, dev).clone()
-    ow = outconv.weight.detach().reshape(K, nsides * K)
-    for i in range(nsides):
-        w[:K, 8 * i: 8 * i + K] = ow[:, i * K:(i + 1) * K]
-    b = torch.zeros(rows, dtype=torch.float32, device=dev)
-    if outconv.bias is not None:
-        b[:K] = outconv.bias.detach()
+    if fuse.C < 8 * nsides:
+        raise ValueError("fused_side_head: the slot buffer is too narrow")
+    w = outconv.weight.detach().reshape(K, nsides * K).contiguous()
     logits = torch.empty((fuse.N, rows, fuse.H, fuse.W), dtype=torch.float32, device=dev)
-    L.check(ctx.lib.uz_head_fwd(fuse.ptr, fuse.ld, fuse.N, fuse.H, fuse.W, C, rows, w.data_ptr(), b.data_ptr(),
-                                logits.data_ptr(), ctx.stream), "uz_head_fwd")
-    ctx.launches += (rows + 3) // 4
+    L.check(ctx.lib.uz_side_head_fwd(fuse.ptr, fuse.ld, fuse.N, fuse.H, fuse.W, nsides, K, w.data_ptr(), _ptr(outconv.bias),
+                                     logits.data_ptr(), ctx.stream), "uz_side_head_fwd")
+    ctx.launches += 1
     idx = len(ctx.outputs)
     ctx.outputs.append(logits)
     if ctx.record:
@@ -1077,42 +1072,20 @@ def fused_side_head(ctx: Ctx, fuse: Act, outconv, K: int, nsides: int) -> torch.
             if g is None:
                 raise RuntimeError("unet_zoo_b200: fused_side_head output has no gradient")
             dl = g.contiguous().float()
-            dwf, dbf = c.f32(rows, C), c.f32(rows)
-            ws = c.workspace(c.lib.uz_head_bwd_workspace_bytes(C))
+            dw = c.pgrad(outconv.weight)
+            db = c.pgrad(outconv.bias) if outconv.bias is not None else None
+            dw = dw if dw is not None else c.f32(K, nsides * K)
+            db = db if db is not None else c.f32(K)
+            ws = c.workspace(c.lib.uz_side_head_bwd_workspace_bytes(nsides, K))
             if any(acc for _, _, acc in fuse.grad_writes()):
                 raise NotImplementedError("fused_side_head input already has a gradient")
-            L.check(c.lib.uz_head_bwd(fuse.ptr, fuse.ld, dl.data_ptr(), fuse.N, fuse.H, fuse.W, C, rows, w.data_ptr(),
-                                      fuse.gptr(), fuse.ld, dwf.data_ptr(), dbf.data_ptr(), 0, ws.data_ptr(), ws.numel(),
-                                      c.stream), "uz_head_bwd")
-            c.launches += 3 * ((rows + 3) // 4)
-            dw = c.pgrad(outconv.weight)
-            if dw is not None:
-                dwv = dw.view(K, nsides * K)
-                for i in range(nsides):
-                    dwv[:, i * K:(i + 1) * K] = dwf[:K, 8 * i: 8 * i + K]
-            db = c.pgrad(outconv.bias) if outconv.bias is not None else None
-            if db is not None:
-                db.copy_(dbf[:K])
+            L.check(c.lib.uz_side_head_bwd(fuse.ptr, fuse.ld, dl.data_ptr(), fuse.N, fuse.H, fuse.W, nsides, K, w.data_ptr(),
+                                           fuse.gptr(), fuse.ld, dw.data_ptr(), db.data_ptr(), ws.data_ptr(), ws.numel(),
+                                           c.stream), "uz_side_head_bwd")
+            c.launches += 3
             c.pready(outconv.weight, outconv.bias)
         ctx.tape.append(backward)
     return logits
-
-
-_SIDE_SELECTORS: Dict[tuple, torch.Tensor] = {}
-
-
-def _side_selector(K: int, nsides: int, C: int, device) -> torch.Tensor:
-    """Constant rows K.. of the fused head's weight matrix (one-hot selectors of the side maps); built on the device with
-    scalar fills (no host-to-device copy: the first call may happen under CUDA graph capture) and kept per device."""
-    key = (K, nsides, C, str(device))
-    sel = _SIDE_SELECTORS.get(key)
-    if sel is None:
-        sel = torch.zeros(K * (1 + nsides), C, dtype=torch.float32, device=device)
-        for i in range(nsides):
-            for k in range(K):
-                sel[K * (1 + i) + k, 8 * i + k] = 1.0
-        _SIDE_SELECTORS[key] = sel
-    return sel
 
 
 def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Optional[Act] = None) -> Act:

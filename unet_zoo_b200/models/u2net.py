@@ -12,16 +12,14 @@ ones run on the per-tap kernel (``UZ_DILATION``).  Nothing is concatenated or po
 * the block's residual ``hx1d + hxin`` (:78) is one pass that also emits the stage's MaxPool2d (:222) and lands in
   the skip half of the OUTER decoder's buffer;
 * the six side convolutions (Conv2d(C, out_ch, 3), :238-243) run with their output channels zero-padded to 8, are
-  upsampled into 8-channel slots of ONE 64-channel full-resolution buffer, and a single 1x1 head pass produces all seven
-  logit maps: row 0 carries ``outconv``'s weights (:244), rows 1-6 select the side maps themselves.
+  upsampled into 8-channel slots of ONE 48-channel full-resolution buffer, and a single pass over it (``uz_side_head_fwd``)
+  produces all seven fp32 logit maps: ``outconv`` (:244) over the six side maps, and the side maps themselves.
 
 Input sizes: multiples of 32 (five 2x poolings at every nesting level; the reference's ceil-mode pooling and
 size-matching upsample also accept other sizes - not implemented, raises).  bf16 mode only.
 """
-import torch
 import torch.nn as nn
 
-from .. import _lib as L
 from .. import engine as E
 from ._runtime import HotPathModel
 from .blocks import _Container
@@ -119,8 +117,8 @@ class _U2NetBase(HotPathModel):
         super().__init__()
         self._in_channels = in_ch
         self.out_ch = out_ch
-        if out_ch > 8:
-            raise NotImplementedError("U2NET: more than 8 classes (the side maps are stored in 8-channel slots)")
+        if out_ch > 4:
+            raise NotImplementedError("U2NET: more than 4 classes (uz_side_head_fwd handles K <= 4 per side map)")
         for name, (kind, cin, mid, cout) in self._spec:
             cin = in_ch if name == "stage1" else cin
             setattr(self, name, RSU4F(cin, mid, cout) if kind == "4F" else RSU(kind, cin, mid, cout))
@@ -163,8 +161,7 @@ class _U2NetBase(HotPathModel):
                               align_corners=False)
             prev = dec[i] = self._stage(ctx, f"stage{i}d", [E.Act(cats[i - 1])])
         # side outputs (u2net.py:273-284) into 8-channel slots of one full-resolution buffer, then one head pass
-        fuse = ctx.new_buf(N, H, W, 64)
-        fuse.data[..., 48:].zero_()
+        fuse = ctx.new_buf(N, H, W, 48)
         for i in range(1, 7):
             slot = E.Act(fuse, 8 * (i - 1), 8)
             conv = getattr(self, f"side{i}")
