@@ -481,7 +481,9 @@ def main():
     if not args.no_secondary and args.model == "unet":
         secondary = {}
         if world == 1:
-            for name, b in (("attention_unet", 16), ("nested_unet", 8)):
+            # BASELINE configs[2], [3], then the neighbouring models of SURVEY 8(f) rank 4 (not BASELINE configs: batch 32)
+            for name, b in (("attention_unet", 16), ("nested_unet", 8), ("transatt_unet", 32), ("unet_transformer", 32),
+                            ("u2net", 32), ("u2netp", 32)):
                 try:
                     q = train_leg(args, name, b, S, 5, 3, dev, world, rank, e2e=False, profile_steps=1)
                     fam, _ = _families(q["profile"], pk, 1)
