@@ -254,6 +254,12 @@ int uz_bilinear2x_bwd(const void* dout, int dout_ld, int N, int H, int W, int C,
 #define UZ_FLAG_RELU 1
 #define UZ_FLAG_ACCUMULATE 2 /* out += result (used when a tensor has several consumers in backward) */
 #define UZ_FLAG_STATS 4      /* also emit per-channel sum / sum-of-squares partials for BatchNorm */
+/* Inference form of ResidualConv (common_layers.py:182-199): with UZ_CONV3X3 and >= 2 segments, the LAST segment is the
+ * operand of the block's 1x1 skip convolution - only the centre tap of its weight columns is read; _S2: that segment is a
+ * 2H x 2W tensor sampled at its even pixels (stride-2 skip, common_layers.py:194).  out = conv3x3(first segments) +
+ * conv1x1(last segment) + bias in one accumulator.  Halo-box kernel only (output >= 16 x 8 pixels). */
+#define UZ_FLAG_RES1X1 8
+#define UZ_FLAG_RES1X1_S2 16
 
 /* out[n, oy, ox, 0:cout] (bf16, pixel stride out_ld) = conv(concat(segments), w_packed) [+ bias] [ReLU].
  * N,H,W: batch and spatial size of the INPUT activation(s).  Output spatial size follows from `mode`.

@@ -16,6 +16,7 @@ CONV3X3, CONV3X3_DGRAD, CONV1X1, CONV3X3_S2, CONV3X3_S2_DGRAD = 0, 1, 2, 3, 4
 CONV1X1_S2, CONV1X1_S2_DGRAD, CONVT2X2, CONVT2X2_DGRAD, UP2X_CONV3X3 = 5, 6, 7, 8, 9
 UP2X_CONV3X3_DGRAD = 10
 FLAG_RELU, FLAG_ACCUMULATE, FLAG_STATS = 1, 2, 4
+FLAG_RES1X1, FLAG_RES1X1_S2 = 8, 16
 
 
 def dilation(d: int) -> int:

@@ -390,6 +390,12 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   // (r, s) reads lattice (r != 1, s != 1) shifted by (r == 0 ? -1 : 0, s == 0 ? -1 : 0) - four segments over the SAME
   // channels, each with its own subset of the nine taps (1 + 2 + 2 + 4), one halo box per lattice and channel block
   const bool s2 = mode == UZ_CONV1X1_S2, s2c = mode == UZ_CONV3X3_S2;
+  // UZ_FLAG_RES1X1 / _S2 (inference form of ResidualConv, common_layers.py:182-199): the LAST segment is the operand of the
+  // block's 1x1 skip convolution - it contributes through the centre tap only (its other eight weight taps are never
+  // read), and with _S2 it is the even-pixel lattice of a 2H x 2W tensor (the stride-2 skip of the encoder blocks).  The
+  // residual sum then forms in ONE accumulator: no separate skip launch, no read-modify-write of the output.
+  const bool res1 = (flags & (UZ_FLAG_RES1X1 | UZ_FLAG_RES1X1_S2)) != 0;
+  if (res1 && (mode != UZ_CONV3X3 || nseg < 2)) return set_error(UZ_ERR_INVALID, "UZ_FLAG_RES1X1 needs UZ_CONV3X3 and >= 2 segments");
   const int Hin = H, Win = W;
   if (s2c && nseg != 1) return 0;
   if (s2 || s2c) {
@@ -478,7 +484,10 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
       ctot += seg_c[s];
       kblocks += p.seg_cblocks[s];
       int rc = s2 ? make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, Hin, Win, Lattice{0, 0, 2}, 8, 16, 1)
-                  : make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
+               : (res1 && s == nseg - 1 && (flags & UZ_FLAG_RES1X1_S2))
+                   ? make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, 2 * H, 2 * W, Lattice{0, 0, 2}, p.halo_w,
+                                  16 + 2 * pad, 1)
+                   : make_act_map(&p.amap[s], seg_ptr[s], seg_c[s], seg_ld[s], N, H, W, full, p.halo_w, 16 + 2 * pad, 1);
       if (rc != UZ_OK) return rc;
     }
   }
@@ -497,6 +506,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     } else if (s2c) {
       for (int t = 0; t < 9; ++t) p.seg_tap_b[sg][t] = (int8_t)p.tap_b[t];
     }
+    if (res1 && sg == nseg - 1) p.seg_taps[sg] = 1 << 4;   // centre tap only
     p.b_items += p.seg_cblocks[sg] * __builtin_popcount(p.seg_taps[sg]);
   }
   p.N = N; p.H = H; p.W = W;
@@ -518,6 +528,10 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   // to 1690 TFLOP/s); with fewer the tile is epilogue bound and pair mode adds ~1 us per tile pair
   const bool pair_auto = p.b_items >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
   p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 ? 1 : 0;
+  // 3x3 + 1x1 in one GEMM with 65..128 output channels: the 1x1 segment's halo boxes feed four MMAs each instead of 36, and
+  // the pair's cross-SM handshake per box then dominates (384->128 @256^2: 0.916 ms as a pair, 0.615 ms as one CTA with
+  // two pixel tiles per weight tile, 0.622 ms as two separate launches - tools/bench_res_tail.py)
+  if (res1 && bn == 128 && !env_int("UZ_FWD2_RES_PAIR", 0)) p.pair = 0;
   int b_item = bn * 128 / (p.pair ? 2 : 1);     // bytes of one weight tile per CTA
   const int kTail = 2560;              // barriers (512) + one bias vector per epilogue group (2 x 1024)
   const long long b_all = (long long)p.b_items * b_item;
@@ -589,7 +603,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.ncols = cout;
   p.bias = bias;
   p.stats = stats;
-  p.flags = flags;
+  p.flags = flags & (UZ_FLAG_RELU | UZ_FLAG_ACCUMULATE | UZ_FLAG_STATS);
   int grid = p.total_tiles < sms ? p.total_tiles : sms;
   grid = grid / cluster * cluster;
   if (grid < cluster) return 0;
@@ -685,6 +699,8 @@ extern "C" int uz_conv_igemm(int mode, int N, int H, int W, int nseg, const void
     rc = try_fwd2(mode, N, H, W, nseg, seg_ptr, seg_c, seg_ld, w_packed, cout, bias, out, out_ld, stats, flags, sms, st);
     if (rc != 0) return rc < 0 ? rc : UZ_OK;
   }
+  if (flags & (UZ_FLAG_RES1X1 | UZ_FLAG_RES1X1_S2))
+    return set_error(UZ_ERR_UNSUPPORTED, "UZ_FLAG_RES1X1 needs the halo-box kernel (output of at least 16 x 8 pixels, no dilation)");
   if (mode == UZ_CONV3X3_S2_DGRAD) {
     // ragged tap counts per phase: one launch per phase (each is a 1-phase problem with its own tap table)
     if (flags & UZ_FLAG_STATS) return set_error(UZ_ERR_UNSUPPORTED, "stats not supported for stride-2 dgrad");

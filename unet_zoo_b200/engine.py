@@ -326,6 +326,8 @@ class Ctx:
             taps = 4 if mode == L.UP2X_CONV3X3 else 16
         cin = sum(s.C for s in segs)
         flops = 2.0 * opix * cout * cin * taps
+        if flags & (L.FLAG_RES1X1 | L.FLAG_RES1X1_S2):    # last segment: 1x1 skip operand (one tap)
+            flops = 2.0 * opix * cout * ((cin - segs[-1].C) * taps + segs[-1].C)
         # algorithmic HBM bytes: every operand once (input pixels, packed weights, output (read too when accumulating))
         nbytes = 2.0 * (a.npix * cin + opix * cout * (2 if flags & L.FLAG_ACCUMULATE else 1) + wp.numel())
         tag = f"{_MODE_NAMES.get(mode, mode)}{'' if dilation == 1 else f'.d{dilation}'} {cin}->{cout} @{out_h}x{out_w} n{a.N}"
@@ -875,6 +877,59 @@ def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mod
             _conv_backward(c, xs, conv, GradAct(out), mode, is_stem, cin_total, need_dx)
         ctx.tape.append(backward)
     return out
+
+
+def conv3x3_plus_1x1_fused(ctx: Ctx, h: Act, x: Act, conv2, skip: Callable, deps: Sequence, key, out: Optional[Act],
+                           stride2: bool = False) -> Optional[Act]:
+    """Inference only: ``conv2(h) + M x + bias`` as ONE implicit GEMM - the operand `x` of a 1x1 branch rides along as an
+    extra K segment that only the centre tap reads (UZ_FLAG_RES1X1; stride-2 branch: the even-pixel lattice of `x`,
+    UZ_FLAG_RES1X1_S2).  `skip()` returns the branch as (fp32 matrix M [Cout, x.C], fp32 bias [Cout] or None) with any
+    BatchNorm already folded in.  Replaces the separate 1x1 launch and the read-modify-write of the output by the
+    accumulating 3x3 launch.  Returns None when the halo-box kernel does not take the layer (tiny images): the caller
+    falls back to the two-launch form."""
+    if ctx.training or ctx.fp32 or h.H < 16 or h.W < 8 or os.environ.get("UZ_RESUNET_UNFUSED") is not None:
+        return None
+    if (stride2 and (x.H != 2 * h.H or x.W != 2 * h.W)) or (not stride2 and (x.H != h.H or x.W != h.W)):
+        return None
+    cout = conv2.out_channels
+    if out is None:
+        out = ctx.new_act(h.N, h.H, h.W, cout)
+
+    def folded():
+        m, bias = skip()
+        w = torch.zeros((cout, h.C + x.C, 3, 3), dtype=torch.float32, device=ctx.device)
+        w[:, :h.C] = conv2.weight.detach()
+        w[:, h.C:, 1, 1] = m
+        if conv2.bias is not None:
+            bias = conv2.bias.detach() if bias is None else bias + conv2.bias.detach()
+        return ctx.pack(w, "conv_fwd"), (bias.float().contiguous() if bias is not None else None)
+    wp, bias = ctx.cached(key, [conv2.weight, conv2.bias] + list(deps), folded)
+    ctx.conv(L.CONV3X3, [h, x], wp, cout, bias, out.ptr, out.ld, h.H, h.W, None,
+             L.FLAG_RES1X1_S2 if stride2 else L.FLAG_RES1X1)
+    return out
+
+
+def residual_conv_tail_fused(ctx: Ctx, h: Act, x: Act, conv2, conv_s, bn_s, out: Optional[Act], stride2: bool) -> Optional[Act]:
+    """The end of ResidualConv.forward (common_layers.py:196-199), ``conv2(h) + bn_s(conv_s(x))``, in inference mode:
+    BatchNorm of the skip branch folded into its weight columns and the bias (conv3x3_plus_1x1_fused)."""
+    def skip():
+        scale, bias = _fold_bn(conv_s.bias, bn_s)
+        return conv_s.weight.detach()[:, :, 0, 0] * scale.view(-1, 1), bias
+    deps = [conv_s.weight, conv_s.bias, bn_s.weight, bn_s.bias, bn_s.running_mean, bn_s.running_var]
+    return conv3x3_plus_1x1_fused(ctx, h, x, conv2, skip, deps, ("res_tail", id(conv2), id(conv_s), id(bn_s)), out, stride2)
+
+
+def stem_pair_fused(ctx: Ctx, h: Act, conv2, im2col: Act, conv_stem, out: Optional[Act]) -> Optional[Act]:
+    """ResUnet's input stage in inference mode (resunet.py:29-33,56): ``input_layer[3](h) + input_skip(image)`` - the second
+    term is a 1x1 GEMM over the stem's im2col operand (k = tap * Cin + ci, zero-padded to `im2col.C` columns)."""
+    def skip():
+        w = conv_stem.weight.detach()
+        co, ci = w.shape[0], w.shape[1]
+        m = torch.zeros((co, im2col.C), dtype=torch.float32, device=ctx.device)
+        m[:, :9 * ci] = w.permute(0, 2, 3, 1).reshape(co, 9 * ci)
+        return m, (conv_stem.bias.detach() if conv_stem.bias is not None else None)
+    return conv3x3_plus_1x1_fused(ctx, h, im2col, conv2, skip, [conv_stem.weight, conv_stem.bias],
+                                  ("stem_pair", id(conv2), id(conv_stem)), out)
 
 
 def bilinear_up2x(ctx: Ctx, x: Act, out: Act) -> Act:

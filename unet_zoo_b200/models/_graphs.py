@@ -81,6 +81,14 @@ def _residual_conv(ctx: E.Ctx, x: E.Act, blk, out=None) -> E.Act:
     s2 = blk.stride == 2
     bn1, _, conv1, bn2, _, conv2 = blk.conv_block
     conv_s, bn_s = blk.conv_skip
+    if not ctx.training and not ctx.fp32:
+        # inference: the skip branch rides along in the last convolution's GEMM (engine.residual_conv_tail_fused)
+        hh = E.conv_bn_act(ctx, [E.bn_act(ctx, x, bn1)], conv1, bn2, mode=L.CONV3X3_S2 if s2 else L.CONV3X3)
+        fused = E.residual_conv_tail_fused(ctx, hh, x, conv2, conv_s, bn_s, out, s2)
+        if fused is not None:
+            return fused
+        out = E.conv_bn_act(ctx, [x], conv_s, bn_s, out=out, relu=False, mode=L.CONV1X1_S2 if s2 else L.CONV1X1)
+        return E.conv_plain(ctx, [hh], conv2, out=out, accumulate=True)
     out = E.conv_bn_act(ctx, [x], conv_s, bn_s, out=out, relu=False, mode=L.CONV1X1_S2 if s2 else L.CONV1X1)
     h = E.bn_act(ctx, x, bn1)
     h = E.conv_bn_act(ctx, [h], conv1, bn2, mode=L.CONV3X3_S2 if s2 else L.CONV3X3)
@@ -96,8 +104,12 @@ def resunet_graph(m, ctx: E.Ctx, x):
     cur, stem = E.stem_input(ctx, x)
     h = E.conv_bn_act(ctx, [cur], m.input_layer[0], m.input_layer[1], stem=stem, need_dx=False)
     x1 = E.Act(cats[0], f[0], f[0])
-    E.conv_plain(ctx, [h], m.input_layer[3], out=x1)                                        # resunet.py:56
-    E.conv_plain(ctx, [cur], m.input_skip[0], out=x1, accumulate=True, stem=stem, need_dx=False)
+    fused = None
+    if not ctx.training and not ctx.fp32 and stem == "im2col":      # inference: both stem convolutions in one GEMM
+        fused = E.stem_pair_fused(ctx, h, m.input_layer[3], cur, m.input_skip[0], x1)
+    if fused is None:
+        E.conv_plain(ctx, [h], m.input_layer[3], out=x1)                                    # resunet.py:56
+        E.conv_plain(ctx, [cur], m.input_skip[0], out=x1, accumulate=True, stem=stem, need_dx=False)
     x2 = _residual_conv(ctx, x1, m.residual_conv_1, E.Act(cats[1], f[1], f[1]))
     x3 = _residual_conv(ctx, x2, m.residual_conv_2, E.Act(cats[2], f[2], f[2]))
     x4 = _residual_conv(ctx, x3, m.bridge)
