@@ -3,6 +3,7 @@ stand-in module: same return values as the reference's loops (training_loop.py:8
 host every batch, and the reference's checkpoint key format (multi_gpu.py:39-87)."""
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from oracle import reference_port as O
 from unet_zoo_b200 import training as T
@@ -74,6 +75,22 @@ def test_deep_supervision_lists_sum_the_head_losses():
     loss, main, dice = T._loss_and_dice(outs, t, crit)
     assert abs(float(loss) - sum(float(crit(o, t)) for o in outs)) < 1e-6
     assert main is outs[-1] and abs(float(dice) - float(O.dice_coefficient(outs[-1], t))) < 1e-7
+
+
+def test_u2net_dict_outputs_sum_seven_losses_with_weight_one():
+    """training_loop.py:23-31,61-64: U2NET's dict - every map against the mask resized to the map's size (bilinear,
+    align_corners=False), all weights 1.0, 'main' is the prediction the Dice score is taken from."""
+    torch.manual_seed(3)
+    t = (torch.rand(2, 1, 16, 16) > 0.5).float()
+    keys = ["main"] + [f"side{i}" for i in range(1, 7)]
+    outs = {k: torch.randn(2, 1, 16, 16, requires_grad=True) for k in keys}
+    outs["side6"] = torch.randn(2, 1, 8, 8, requires_grad=True)          # a map at another size: the mask is resized
+    crit = nn.BCEWithLogitsLoss()
+    loss, main, dice = T._loss_and_dice(outs, t, crit)
+    want = sum(crit(o, F.interpolate(t, size=o.shape[2:], mode="bilinear", align_corners=False)) for o in outs.values())
+    assert abs(float(loss) - float(want)) < 1e-6
+    assert main is outs["main"]
+    assert abs(float(dice) - float(O.dice_coefficient(outs["main"].detach(), t))) < 1e-6
 
 
 def test_checkpoint_manager_roundtrip_and_module_prefix(tmp_path, capsys):
