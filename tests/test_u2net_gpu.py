@@ -278,3 +278,31 @@ def test_u2net_rejects_sizes_the_nesting_cannot_halve():
         model(torch.zeros(1, 3, 48, 64, device="cuda"))
     with pytest.raises(ValueError, match="bf16"):
         model.set_precision("fp32")
+
+
+def test_u2netp_non_square_eval_and_graph_replay():
+    """Eval forward at 64 x 96 (innermost maps 2 x 3), batch 3, against the oracle; the same forward replayed from one
+    CUDA graph returns the same dict bit for bit."""
+    from unet_zoo_b200.train_step import GraphedInference
+    model = seeded_model("u2netp")
+    sd = O.randomize_bn_affine({k: v.clone() for k, v in model.state_dict().items()})
+    with torch.no_grad():
+        for k, v in sd.items():
+            if k.endswith("running_mean"):
+                v.normal_(0.0, 0.2, generator=torch.Generator().manual_seed(len(k)))
+            if k.endswith("running_var"):
+                v.uniform_(0.5, 1.5, generator=torch.Generator().manual_seed(len(k) + 1))
+    model.load_state_dict(sd)
+    model.cuda().eval()
+    x, _ = O.synthetic_batch(3, 3, 64, 96)
+    with torch.no_grad():
+        out = model(x.cuda())
+        refs = O.u2netp_forward({k: v.clone() for k, v in sd.items()}, x, False)
+    assert list(out) == list(O.U2NET_KEYS)
+    for (k, o), r in zip(out.items(), refs):
+        assert o.shape == r.shape == (3, 1, 64, 96), k
+        assert rel_err(o.cpu(), r) < LOGIT_TOL, k
+    g = GraphedInference(model, x.cuda())
+    again = g(x.cuda())
+    for k in out:
+        assert torch.equal(again[k], out[k]), k
