@@ -75,7 +75,7 @@ def test_softmax_cols_fwd_bwd(N, R, C, scale):
     assert rel_l2(x.grad.float(), want) < 1e-2
 
 
-@pytest.mark.parametrize("N,R,C", [(2, 1024, 512), (3, 17, 40), (1, 1, 8), (4, 64, 64)])
+@pytest.mark.parametrize("N,R,C", [(2, 1024, 512), (3, 17, 40), (1, 1, 8), (4, 64, 64), (2, 4096, 4096), (3, 72, 200), (2, 64, 8), (1, 4096, 64)])
 def test_transpose(N, R, C):
     x = torch.randn(N, R, C, device=DEV).to(torch.bfloat16)
     assert torch.equal(A.transpose(x), x.transpose(1, 2).contiguous())
