@@ -12,6 +12,7 @@
 //
 // Warp roles (384 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2 = B producer, 3 = idle,
 // 4..11 = epilogue: two groups of four warps (one per TMEM lane quarter), the groups take alternate tiles.
+#include <stdlib.h>
 #include <string.h>
 
 #include "host_util.h"
@@ -20,6 +21,19 @@
 
 namespace uz {
 
+// Diagnostic knock-outs (compile-time, tools/build_variants.sh ... -DUZ_F2_KNOCK=<mask>; results are garbage, only the
+// timing is meaningful): 1 = the A producer stops issuing TMA loads once the ring has been filled once (barriers still
+// complete), 2 = the issuer skips the UTCHMMA instructions (commits stay), 4 = the epilogue only hands the accumulator
+// back, 8 = the epilogue skips the TMA store, 16 = the epilogue skips the BatchNorm column sums, 32 = no aempty commits
+// (the producer does not wait for free stages either; may deadlock - run under `timeout`), 64 = no tcgen05 fences in the
+// issuer, 128 = one EXTRA tcgen05.commit per tile onto a dummy barrier (prices a commit), 256 = the issuer does not wait
+// for a drained accumulator, 512 / 1024 = the tfull / aempty commit is issued BEFORE the tile's MMAs (the handshake then
+// does not wait for their completion).  0 (the product build)
+// compiles to exactly the code without them.
+#ifndef UZ_F2_KNOCK
+#define UZ_F2_KNOCK 0
+#endif
+constexpr int kF2Knock = UZ_F2_KNOCK;
 constexpr int kF2Threads = 384;
 constexpr int kF2EpiThreads = 256;
 constexpr int kF2StgBytes = 128 * 128;  // one staged 128-pixel x 64-channel bf16 chunk
@@ -72,7 +86,15 @@ __device__ __forceinline__ F2Tile f2_decode(const Igemm2Params& p, int tile, int
   return t;
 }
 
-template <int BN, int MP, int CG, bool KSKIP>
+// FAST: stationary weights, all nine taps of every segment, one CTA, one pixel tile per item - the issue loop of these
+// (short-K, <= 128 output channels) layers then carries no ring / tap-mask logic: the generic loop spends ~35 instructions
+// (six R2UR) per tap, ~150 cycles, where the four N = 64 MMAs of a tap last 128 - measured by knock-outs (UZ_F2_KNOCK): the
+// per-tile time did not move without TMA loads or without the epilogue, only without the MMAs.
+// FAST = 4: all four K steps; 1..3: EVERY channel block of the launch holds exactly FAST x 16 channels (single-block segments
+// of 16 / 32 / 48 channels: nested_unet level 0, the RSU interiors of u2net) - the K-step count is then a compile-time
+// constant and the MMAs of a tile are one straight line of UIADD3 / UTCHMMA (the dynamic K-skip loop needs an R2UR and a
+// branch per MMA: ~74 cycles per MMA where an N = 64 MMA lasts 32); 5: FAST loop with the dynamic K-skip; 0: generic loop.
+template <int BN, int MP, int CG, bool KSKIP, int FAST>
 __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_constant__ Igemm2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -84,10 +106,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   auto aempty = [&](int s) { return bars + 64u + 8u * s; };
   auto bfull = [&](int s) { return bars + 128u + 8u * s; };
   auto bempty = [&](int s) { return bars + 256u + 8u * s; };
-  auto tfull = [&](int s) { return bars + 384u + 8u * s; };
-  auto tempty = [&](int s) { return bars + 416u + 8u * s; };
-  const uint32_t tmem_slot = bars + 448u;
-  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + p.bar_off + 448);
+  auto tfull = [&](int s) { return bars + 384u + 8u * s; };     // up to 8 accumulator stages
+  auto tempty = [&](int s) { return bars + 448u + 8u * s; };
+  const uint32_t tmem_slot = bars + 56u;                        // the eighth afull slot (a_stages <= 6)
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + p.bar_off + 56);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -103,7 +125,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   const bool leader = !kPair || rank == 0;
   // accumulator stages: as many as TMEM holds, at most 4 (short-K layers are bound by the tfull -> epilogue -> tempty ->
   // MMA round trip, which crosses SMs in pair mode)
-  constexpr int kAcc = 512 / (MP * BN) > 4 ? 4 : 512 / (MP * BN);
+#ifndef UZ_F2_MAX_ACC
+#define UZ_F2_MAX_ACC 8
+#endif
+  constexpr int kAcc = 512 / (MP * BN) > UZ_F2_MAX_ACC ? UZ_F2_MAX_ACC : 512 / (MP * BN);
   constexpr uint32_t kTmemCols = kAcc * MP * BN;
   static_assert(kTmemCols <= 512, "accumulators exceed TMEM");
 
@@ -122,6 +147,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       mbar_init(tempty(s), 4 * CG);   // one epilogue group (four warps) drains a tile; pair: the leader's barrier
                                       // collects both CTAs' groups
     }
+    if (kF2Knock & 128) mbar_init(bars + 48u, 1);   // dummy barrier (seventh afull slot, unused: a_stages <= 6)
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
     tma_prefetch_desc(&p.bmap);
@@ -151,6 +177,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      [[maybe_unused]] int issued = 0;
       for (int g = cidx; g < ngroups; g += nclusters) {
         F2Tile t[MP];
 #pragma unroll
@@ -158,12 +185,15 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         for (int seg = 0; seg < p.num_segs; ++seg) {
           const int ncb = p.seg_cblocks[seg];
           for (int cb = 0; cb < ncb; ++cb) {
-            mbar_wait(aempty(stage), phase ^ 1u);
+            if (!(kF2Knock & 32)) mbar_wait(aempty(stage), phase ^ 1u);
             if (kPair) {   // both halos complete on the leader's barrier
               if (leader) mbar_expect_tx(afull(stage), p.halo_bytes * 2);
               tma_load_4d_pair(a_base + stage * a_slot, &p.amap[seg], afull(stage), cb * 64, t[0].x0 - p.pad,
                                t[0].y0 - p.pad, t[0].n);
+            } else if ((kF2Knock & 1) && issued >= p.a_stages) {
+              mbar_arrive(afull(stage));
             } else {
+              if (kF2Knock & 1) ++issued;
               mbar_expect_tx(afull(stage), p.halo_bytes * MP);
 #pragma unroll
               for (int sub = 0; sub < MP; ++sub)
@@ -259,8 +289,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
 #pragma unroll
           for (int t = 0; t < 4; ++t) tap_lo[t] = static_cast<uint32_t>(p.ph_row[ph][t]) * 8u;
         }
-        mbar_wait(tempty(acc), acc_phase ^ 1u);
-        tc_fence_after();
+        if (!(kF2Knock & 256)) mbar_wait(tempty(acc), acc_phase ^ 1u);
+        if (!(kF2Knock & 64)) tc_fence_after();
+        if ((kF2Knock & 512) && !kPair) umma_commit(tfull(acc));
         const uint32_t d_tmem = tmem_base + acc * (MP * BN);
         uint32_t b_item = (b_base >> 4) | (1u << 16);   // stationary weights: walks through the resident tiles
         uint32_t fresh = 0;   // 0 for the first MMA of the tile (overwrite the accumulator), 1 afterwards
@@ -269,8 +300,24 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         for (int cb = 0; cb < p.seg_cblocks[seg]; ++cb) {
           const int ksteps = (KSKIP && cb + 1 == p.seg_cblocks[seg]) ? p.seg_klast[seg] : 4;
           mbar_wait(afull(astage), aphase);
-          tc_fence_after();
+          if (!(kF2Knock & 64)) tc_fence_after();
           const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
+          if ((kF2Knock & 1024) && !kPair) umma_commit(aempty(astage));
+          if constexpr (FAST != 0) {
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              const uint32_t a_tap = a_lo + tap_lo[tap];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                if (FAST < 5 && k >= FAST) break;            // compile-time
+                if (FAST == 5 && k >= ksteps) break;
+                if (kF2Knock & 2) continue;
+                umma_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_item + 2u * k, b_hi, idesc, (tap == 0 && k == 0) ? fresh : 1u);
+              }
+              b_item += kBItem >> 4;
+            }
+            fresh = 1u;
+          } else {
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) {
             if (tap < ntaps && ((seg_mask >> tap) & 1u)) {
@@ -293,6 +340,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                   // N = 64 tile has 32 cycles per MMA, a predicate + branch per UTCHMMA cost 14 % on 64->64 @512^2,
                   // and any less regular loop shape made the compiler drop the uniform-register descriptors (+65 %).
                   if (KSKIP && k >= ksteps) break;
+                  if (kF2Knock & 2) continue;
                   if (kPair)
                     umma2_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_lo + 2u * k, b_hi, idesc, k == 0 ? fresh : 1u);
                   else
@@ -315,7 +363,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
               }
             }
           }
-          if (kPair)
+          }
+          if (kF2Knock & (32 | 1024)) {
+          } else if (kPair)
             umma2_commit_mc(aempty(astage));
           else
             umma_commit(aempty(astage));
@@ -325,7 +375,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
           }
         }
         }
-        if (kPair)
+        if ((kF2Knock & 128) && !kPair) umma_commit(bars + 48u);
+        if (kF2Knock & 512) {
+        } else if (kPair)
           umma2_commit_mc(tfull(acc));
         else
           umma_commit(tfull(acc));
@@ -419,7 +471,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       mbar_wait(tfull(acc), acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int sub = 0; sub < MP; ++sub) {
+      for (int sub = 0; sub < ((kF2Knock & 4) ? 0 : MP); ++sub) {
       // only the thread that issues the TMA store needs the tile coordinates when every tile is full
       F2Tile t;
       t.n = t.x0 = t.y0 = 0;
@@ -473,14 +525,14 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         }
         fence_proxy_async_smem();
         gbar();
-        if (gt == 0) {
+        if (gt == 0 && !(kF2Knock & 8)) {
           if (do_acc)
             tma_reduce_add_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
           else
             tma_store_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
           tma_store_commit();
         }
-        if (do_stats) {
+        if (do_stats && !(kF2Knock & 16)) {
           float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
           for (int rr = 0; rr < 32; ++rr) {
@@ -523,13 +575,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
   }
 }
 
-template <int BN, int MP, int CG, bool KSKIP>
-static cudaError_t launch_fwd2_ks(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
+template <int BN, int MP, int CG, bool KSKIP, int FAST>
+static cudaError_t launch_fwd2_fast(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
   static int configured[kMaxDevices] = {0};   // the attribute is per device
   int& conf = configured[device_slot()];
   if (conf < smem_bytes) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG, KSKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(igemm_fwd2_kernel<BN, MP, CG, KSKIP, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
     conf = smem_bytes;
   }
@@ -550,7 +602,32 @@ static cudaError_t launch_fwd2_ks(const Igemm2Params& p, int grid, int smem_byte
   }
   cfg.attrs = attr;
   cfg.numAttrs = nattr;
-  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP, CG, KSKIP>, p);
+  return cudaLaunchKernelEx(&cfg, igemm_fwd2_kernel<BN, MP, CG, KSKIP, FAST>, p);
+}
+
+template <int BN, int MP, int CG, bool KSKIP>
+static cudaError_t launch_fwd2_ks(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
+  if constexpr (MP == 1 && CG == 1 && BN <= 128) {
+    static const bool off = getenv("UZ_FWD2_NO_FAST") != nullptr && getenv("UZ_FWD2_NO_FAST")[0] == '1';
+    bool fast = !off && p.b_stages == 0 && p.num_taps == 9 && p.ph_ntaps == 0;
+    for (int sg = 0; sg < p.num_segs; ++sg) fast = fast && p.seg_taps[sg] == 0x1ff;
+    if (fast) {
+      if constexpr (!KSKIP) {
+        return launch_fwd2_fast<BN, MP, CG, KSKIP, 4>(p, grid, smem_bytes, stream);
+      } else {
+        int ks = p.seg_klast[0];     // static K-step count: every segment is ONE channel block of the same size
+        for (int sg = 0; sg < p.num_segs; ++sg)
+          if (p.seg_cblocks[sg] != 1 || p.seg_klast[sg] != ks) ks = 0;
+        switch (ks) {
+          case 1: return launch_fwd2_fast<BN, MP, CG, KSKIP, 1>(p, grid, smem_bytes, stream);
+          case 2: return launch_fwd2_fast<BN, MP, CG, KSKIP, 2>(p, grid, smem_bytes, stream);
+          case 3: return launch_fwd2_fast<BN, MP, CG, KSKIP, 3>(p, grid, smem_bytes, stream);
+          default: return launch_fwd2_fast<BN, MP, CG, KSKIP, 5>(p, grid, smem_bytes, stream);
+        }
+      }
+    }
+  }
+  return launch_fwd2_fast<BN, MP, CG, KSKIP, 0>(p, grid, smem_bytes, stream);
 }
 
 template <int BN, int MP, int CG>
