@@ -13,6 +13,8 @@
 // Warp roles (384 threads): 0 = A (halo) producer, 1 = TMEM allocator + MMA issuer, 2 = B producer, 3 = idle,
 // 4..11 = epilogue: two groups of four warps (one per TMEM lane quarter), the groups take alternate tiles.
 #include <stdlib.h>
+
+#include <type_traits>
 #include <string.h>
 
 #include "host_util.h"
@@ -304,17 +306,34 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
           const uint32_t a_lo = ((a_base + astage * a_slot) >> 4) | (1u << 16);
           if ((kF2Knock & 1024) && !kPair) umma_commit(aempty(astage));
           if constexpr (FAST != 0) {
+            // nine taps x KS K-steps of one channel block as one straight line (KS is a compile-time constant here)
+            auto issue_block = [&](auto ks_tag) {
+              constexpr int KS = decltype(ks_tag)::value;
 #pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const uint32_t a_tap = a_lo + tap_lo[tap];
+              for (int tap = 0; tap < 9; ++tap) {
+                const uint32_t a_tap = a_lo + tap_lo[tap];
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                if (FAST < 5 && k >= FAST) break;            // compile-time
-                if (FAST == 5 && k >= ksteps) break;
-                if (kF2Knock & 2) continue;
-                umma_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_item + 2u * k, b_hi, idesc, (tap == 0 && k == 0) ? fresh : 1u);
+                for (int k = 0; k < KS; ++k) {
+                  if (kF2Knock & 2) continue;
+                  if (kPair)
+                    umma2_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_item + 2u * k, b_hi, idesc,
+                                     (tap == 0 && k == 0) ? fresh : 1u);
+                  else
+                    umma_bf16_words(d_tmem, a_tap + 2u * k, a_hi, b_item + 2u * k, b_hi, idesc,
+                                    (tap == 0 && k == 0) ? fresh : 1u);
+                }
+                b_item += kBItem >> 4;
               }
-              b_item += kBItem >> 4;
+            };
+            if constexpr (FAST < 5) {
+              issue_block(std::integral_constant<int, FAST>{});
+            } else {   // some segment ends in a partial block: ONE branch per channel block picks its unrolled form
+              switch (ksteps) {
+                case 1: issue_block(std::integral_constant<int, 1>{}); break;
+                case 2: issue_block(std::integral_constant<int, 2>{}); break;
+                case 3: issue_block(std::integral_constant<int, 3>{}); break;
+                default: issue_block(std::integral_constant<int, 4>{}); break;
+              }
             }
             fresh = 1u;
           } else {
@@ -607,7 +626,7 @@ static cudaError_t launch_fwd2_fast(const Igemm2Params& p, int grid, int smem_by
 
 template <int BN, int MP, int CG, bool KSKIP>
 static cudaError_t launch_fwd2_ks(const Igemm2Params& p, int grid, int smem_bytes, cudaStream_t stream) {
-  if constexpr (MP == 1 && CG == 1 && BN <= 128) {
+  if constexpr (MP == 1 && BN <= 128) {
     static const bool off = getenv("UZ_FWD2_NO_FAST") != nullptr && getenv("UZ_FWD2_NO_FAST")[0] == '1';
     bool fast = !off && p.b_stages == 0 && p.num_taps == 9 && p.ph_ntaps == 0;
     for (int sg = 0; sg < p.num_segs; ++sg) fast = fast && p.seg_taps[sg] == 0x1ff;
