@@ -52,6 +52,10 @@ int uz_device_sm_count(void);
  * Replaces: the implicit weight reads of nn.Conv2d / nn.ConvTranspose2d (common_layers.py:28,31,104). */
 int uz_pack_weight(const float* src, void* dst_bf16, int A, int T, int B, long long sa, long long sb, long long st,
                    long long dst_pitch, const float* row_scale, void* stream);
+/* All weights of a model in one launch: jobs (DEVICE memory) = njobs x {src, dst, A, T, B, sa, sb, st, dst_pitch, first}
+ * as 64-bit integers - the arguments of uz_pack_weight (no row scale) plus `first`, the number of (a, b) pairs of all
+ * earlier jobs; total_pairs = sum of A * B.  A training step otherwise spends one ~5 us launch per convolution and layout. */
+int uz_pack_weights_batched(const long long* jobs_device, int njobs, long long total_pairs, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Input staging.  The reference feeds NCHW fp32 images (training_loop.py:109, unet.py:31).

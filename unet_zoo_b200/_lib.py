@@ -33,6 +33,7 @@ _PROTOS = {
     "uz_up2x_phase_form": (c_int, [c_int, c_int, c_int]),
     "uz_pack_up2x": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
     "uz_pack_weight": (c_int, [_P, _P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_longlong, _P, _P]),
+    "uz_pack_weights_batched": (c_int, [_P, c_int, c_longlong, _P]),
     "uz_stem_im2col": (c_int, [_P, c_int, c_int, c_int, c_int, _P, c_int, _P]),
     "uz_nchw_to_nhwc": (c_int, [_P, c_int, c_int, c_int, c_int, _P, c_int, _P]),
     "uz_conv_igemm": (c_int, [c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, _P, c_int, c_int, c_int,

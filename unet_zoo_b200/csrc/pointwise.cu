@@ -93,6 +93,33 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, __nv_bfloat16*
   }
 }
 
+// Every weight of a model in ONE launch (a training step re-packs each convolution's fp32 master weights twice - forward
+// and data-gradient layout - and every pack_weight launch costs ~5 us of a CUDA-graph step whatever its size: 235 launches
+// in u2net).  jobs[j] = {src, dst, A, T, B, sa, sb, st, dst_pitch, first}: `first` = number of (a, b) pairs of the jobs
+// before j; a thread finds its job by binary search.
+constexpr int kPackJobFields = 10;
+__global__ void pack_weights_batched_kernel(const long long* __restrict__ jobs, int njobs, long long total) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    int lo = 0, hi = njobs - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (__ldg(jobs + static_cast<size_t>(mid) * kPackJobFields + 9) <= i) lo = mid; else hi = mid - 1;
+    }
+    const long long* j = jobs + static_cast<size_t>(lo) * kPackJobFields;
+    const float* src = reinterpret_cast<const float*>(__ldg(j + 0));
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(__ldg(j + 1));
+    const int T = static_cast<int>(__ldg(j + 3)), B = static_cast<int>(__ldg(j + 4));
+    const long long sa = __ldg(j + 5), sb = __ldg(j + 6), st = __ldg(j + 7), pitch = __ldg(j + 8);
+    const long long e = i - __ldg(j + 9);
+    const int b = static_cast<int>(e % B);
+    const long long a = e / B;
+    const float* sp = src + a * sa + b * sb;
+    __nv_bfloat16* d = dst + a * pitch + b;
+    for (int t = 0; t < T; ++t) d[static_cast<long long>(t) * B] = __float2bfloat16_rn(__ldg(sp + t * st));
+  }
+}
+
 // Pre-summed weights of the nearest-x2 conv in phase form (host_conv.cu, UZ_UP2X_CONV3X3): for output phase (py, px) the
 // rows r of the 3x3 filter that read low-resolution row offset a - 1 + py are  R(0,0) = {0}, R(0,1) = {1,2},
 // R(1,0) = {0,1}, R(1,1) = {2}  (same for columns):  dst[x][ph*4 + a*2 + b][y] = bf16(sum_{r in R(py,a), s in R(px,b)} w[co][ci][r][s])
@@ -807,6 +834,17 @@ extern "C" int uz_pack_weight(const float* src, void* dst_bf16, int A, int T, in
   pack_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       src, static_cast<__nv_bfloat16*>(dst_bf16), A, T, B, sa, sb, st, dst_pitch, row_scale);
   UZ_CHECK_LAUNCH("pack_weight launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_pack_weights_batched(const long long* jobs_device, int njobs, long long total_pairs, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  if (!jobs_device || njobs < 1 || total_pairs < 1) return set_error(UZ_ERR_INVALID, "pack_weights_batched: bad arguments");
+  long long blocks = (total_pairs + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_weights_batched_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(jobs_device, njobs,
+                                                                                                      total_pairs);
+  UZ_CHECK_LAUNCH("pack_weights_batched launch");
   return UZ_OK;
 }
 

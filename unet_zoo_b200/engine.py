@@ -176,6 +176,44 @@ class ParamGrads:
             self.on_ready(p)
 
 
+class PackPlan:
+    """All weight packs of a model's training step in ONE launch (uz_pack_weights_batched).  Learned from the pack calls
+    of one complete step (Ctx.pack_log): only packs straight from a parameter's own fp32 storage qualify (no padded or
+    scaled temporaries).  `run` re-packs every operand into persistent buffers at the start of a forward and returns
+    the cache Ctx.pack consults; it declines (None) when a parameter has moved since the plan was made."""
+
+    def __init__(self, log, params, device):
+        own = {p.data_ptr(): p for p in params if p.dtype == torch.float32 and p.is_contiguous()}
+        jobs, self.entries, first, total_out = [], [], 0, 0
+        seen = set()
+        for (w, kind, A, T, B, sa, sb) in log:
+            key = (w.data_ptr(), kind)
+            p = own.get(w.data_ptr())
+            if p is None or key in seen or w.numel() != p.numel():
+                continue
+            seen.add(key)
+            self.entries.append((p, kind, A, T, B, sa, sb, total_out))
+            total_out += A * T * B
+        self.device = device
+        self.store = torch.empty(max(total_out, 1), dtype=torch.bfloat16, device=device)
+        rows = []
+        for (p, kind, A, T, B, sa, sb, off) in self.entries:
+            rows.append([p.data_ptr(), self.store.data_ptr() + 2 * off, A, T, B, sa, sb, 1, T * B, first])
+            first += A * B
+        self.total_pairs = first
+        self.jobs = torch.tensor(rows if rows else [[0] * 10], dtype=torch.int64).to(device)
+        self.ptrs = [p.data_ptr() for (p, *_r) in self.entries]
+
+    def run(self, ctx: "Ctx") -> Optional[Dict[tuple, torch.Tensor]]:
+        if not self.entries or any(p.data_ptr() != q for (p, *_r), q in zip(self.entries, self.ptrs)):
+            return None
+        L.check(ctx.lib.uz_pack_weights_batched(self.jobs.data_ptr(), len(self.entries), self.total_pairs, ctx.stream),
+                "uz_pack_weights_batched")
+        ctx.launches += 1
+        return {(p.data_ptr(), kind): self.store[off:off + A * T * B].view(A, T, B)
+                for (p, kind, A, T, B, sa, sb, off) in self.entries}
+
+
 class Ctx:
     """Per-forward execution context: stream, scratch memory, tape, parameter-gradient sink."""
 
@@ -211,6 +249,8 @@ class Ctx:
         # running-statistics affines are constants there - re-deriving them cost ~130 small launches (0.6 of 12.4 ms) per
         # resunet forward.  Entries are validated against (storage pointer, version counter) of their source tensors.
         self.eval_cache: Optional[dict] = None
+        self.pack_cache: Dict[tuple, torch.Tensor] = {}    # (weight data_ptr, kind) -> operand packed by a PackPlan
+        self.pack_log: Optional[list] = None               # not None: record the packs a PackPlan could batch
         self.outputs: List[torch.Tensor] = []     # logits tensors, in the order the model returns them
         self.out_grads: List[Optional[torch.Tensor]] = []
         self.launches = 0
@@ -290,6 +330,13 @@ class Ctx:
         else:
             raise ValueError(kind)
         pitch = T * B
+        batchable = kind != "stem" and row_scale is None and w.dtype == torch.float32
+        if batchable:
+            hit = self.pack_cache.get((w.data_ptr(), kind))
+            if hit is not None and hit.shape == (A, T, B):
+                return hit
+            if self.pack_log is not None:
+                self.pack_log.append((w, kind, A, T, B, sa, sb))
         if kind == "stem":
             pitch = kp
             out = torch.zeros((A, kp), dtype=torch.bfloat16, device=w.device)

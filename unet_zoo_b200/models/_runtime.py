@@ -5,6 +5,7 @@ network runs as one ``torch.autograd.Function``: forward launches the fused kern
 replays the tape and hands one fp32 gradient per ``nn.Parameter`` back to autograd, so ``loss.backward()``,
 ``clip_grad_norm_`` and any ``torch.optim`` optimizer work unchanged (training_loop.py:112-121).
 """
+import os
 from typing import List, Optional
 
 import torch
@@ -18,6 +19,12 @@ class _HotPathFn(torch.autograd.Function):
     def forward(fctx, model, x, *params):
         ctx = E.Ctx(x.device, training=True, record=True)
         ctx.input_norm = model._input_norm
+        plan = model._pack_plan
+        cache = plan.run(ctx) if plan is not None and plan.device == x.device else None
+        if cache is not None:
+            ctx.pack_cache = cache
+        elif os.environ.get("UZ_NO_PACK_PLAN") != "1":
+            ctx.pack_log = []              # learn the plan from this step (finished at the end of backward)
         outs = model._graph(ctx, x)
         fctx.ectx = ctx
         fctx.model = model
@@ -44,6 +51,9 @@ class _HotPathFn(torch.autograd.Function):
             step(ctx)
         ctx.join_side()                      # weight gradients ran on the side stream (engine.Ctx.on_side)
         ctx.tape.clear()
+        if ctx.pack_log is not None and not torch.cuda.is_current_stream_capturing():
+            model._pack_plan = E.PackPlan(ctx.pack_log, params, ctx.device)    # one launch packs them all from now on
+            ctx.pack_log = None
         model._last_launches_bwd = ctx.launches
         finish = getattr(ctx.pgrads, "finish", None)
         if finish is not None:
@@ -74,6 +84,7 @@ class HotPathModel(nn.Module):
         return self
 
     _input_norm = None
+    _pack_plan = None           # engine.PackPlan: every weight pack of a training step in one launch (learned in step 1)
     _eval_cache = None          # engine.Ctx.cached: inference memo of packed / BatchNorm-folded weights
 
     def train(self, mode: bool = True):
