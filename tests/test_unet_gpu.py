@@ -323,3 +323,38 @@ def test_overlapped_graph_data_parallel_step_matches_eager_steps():
             assert torch.allclose(s0[k], s1[k], rtol=0, atol=1e-6), k
         else:
             assert torch.equal(s0[k], s1[k]), k
+
+
+def test_batched_weight_packs_equal_per_layer_packs(monkeypatch):
+    """engine.PackPlan (all weight packs of a step in one launch, learned in step 1 and used from step 2 on) gives bit-identical
+    logits and gradients to the per-layer packs, follows in-place weight updates (optimizer steps, load_state_dict) and
+    is rebuilt when the parameters move."""
+    x, mask = O.synthetic_batch(2, 3, 64, 64)
+    x, mask = x.cuda(), mask.cuda()
+
+    def run(plan: bool):
+        monkeypatch.setenv("UZ_NO_PACK_PLAN", "0" if plan else "1")
+        model = seeded_model("unet").cuda().train()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05)
+        outs = []
+        for step in range(3):
+            opt.zero_grad(set_to_none=True)
+            out = model(x)
+            O.bce_with_logits(out, mask).backward()
+            outs.append((out.detach().clone(), model.out.conv.weight.grad.detach().clone(),
+                         model.down_convolution_2.conv.conv_op[0].weight.grad.detach().clone()))
+            opt.step()
+        assert (model._pack_plan is not None) == plan
+        if plan:
+            assert model._last_launches < 120          # one pack launch instead of one per convolution
+            sd = {k: v.clone() for k, v in seeded_model("unet").state_dict().items()}
+            model.load_state_dict(sd)                  # in place: same storage, the plan stays valid and sees the new values
+            a = model(x).detach().clone()
+            fresh = seeded_model("unet").cuda().train()
+            monkeypatch.setenv("UZ_NO_PACK_PLAN", "1")
+            b = fresh(x).detach()
+            assert torch.equal(a, b)
+        return outs
+
+    for (o1, g1, h1), (o2, g2, h2) in zip(run(True), run(False)):
+        assert torch.equal(o1, o2) and torch.equal(g1, g2) and torch.equal(h1, h2)
