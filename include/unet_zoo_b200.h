@@ -77,7 +77,9 @@ int uz_nchw_to_nhwc(const float* x, int N, int C, int H, int W, void* out, int o
 int uz_reduce_rows(void);
 int uz_bn_stats(const void* x, int ld, long long npix, int C, float* partial, void* stream);
 int uz_bn_finalize(const float* partial, int rows, int C, long long count, const float* gamma, const float* beta,
-                   float eps, float momentum, float* running_mean, float* running_var, float* bn, void* stream);
+                   float eps, float momentum, float* running_mean, float* running_var, float* bn,
+                   long long* num_batches_tracked /* int64 device scalar, += 1 (nn.BatchNorm2d's counter); may be NULL */,
+                   void* stream);
 int uz_bn_apply(const void* z, int z_ld, int N, int H, int W, int C, const float* scale, const float* shift, int relu,
                 const void* residual, int res_ld, void* y, int y_ld, void* pooled, int pooled_ld, void* stream);
 

@@ -42,7 +42,7 @@ _PROTOS = {
     "uz_conv_wgrad": (c_int, [c_int, c_int, c_int, c_int, _P, c_int, c_int, _P, c_int, c_int, _P, c_int, c_int, c_int,
                               _P, c_size_t, _P]),
     "uz_bn_stats": (c_int, [_P, c_int, c_longlong, c_int, _P, _P]),
-    "uz_bn_finalize": (c_int, [_P, c_int, c_int, c_longlong, _P, _P, c_float, c_float, _P, _P, _P, _P]),
+    "uz_bn_finalize": (c_int, [_P, c_int, c_int, c_longlong, _P, _P, c_float, c_float, _P, _P, _P, _P, _P]),
     "uz_bn_apply": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, _P, c_int, _P, c_int, _P, c_int, _P]),
     "uz_bn_bwd_workspace_bytes": (c_size_t, [c_int]),
     "uz_bn_bwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, _P, _P,

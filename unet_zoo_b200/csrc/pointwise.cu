@@ -341,10 +341,11 @@ __device__ __forceinline__ void partial_column_sums(const float* __restrict__ pa
 __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, int C, double count,
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                    float momentum, float* __restrict__ running_mean, float* __restrict__ running_var,
-                                   float* __restrict__ bn) {
+                                   float* __restrict__ bn, long long* __restrict__ num_batches_tracked) {
   // one warp per channel: lanes stride over the partial rows, fp64 shuffle reduction (deterministic)
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
+  if (num_batches_tracked != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
   partial_column_sums(partial, rows, C, c, lane, s, q);
@@ -938,11 +939,12 @@ extern "C" int uz_bn_stats(const void* x, int ld, long long npix, int C, float* 
 
 extern "C" int uz_bn_finalize(const float* partial, int rows, int C, long long count, const float* gamma,
                               const float* beta, float eps, float momentum, float* running_mean, float* running_var,
-                              float* bn, void* stream) {
+                              float* bn, long long* num_batches_tracked, void* stream) {
   UZ_REQUIRE_DEVICE();
   if (rows < 1 || C < 1 || count < 1) return set_error(UZ_ERR_INVALID, "bn_finalize: bad extents");
   bn_finalize_kernel<<<(C + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      partial, rows, C, static_cast<double>(count), gamma, beta, eps, momentum, running_mean, running_var, bn);
+      partial, rows, C, static_cast<double>(count), gamma, beta, eps, momentum, running_mean, running_var, bn,
+      num_batches_tracked);
   UZ_CHECK_LAUNCH("bn_finalize launch");
   return UZ_OK;
 }

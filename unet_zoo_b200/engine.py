@@ -414,14 +414,19 @@ class Ctx:
     def bn_finalize(self, stats: torch.Tensor, rows: int, C: int, count: int, bn_mod, bnbuf: torch.Tensor):
         track = bn_mod.track_running_stats and bn_mod.running_mean is not None
         mom = bn_mod.momentum
+        nbt = None
         if track:
-            bn_mod.num_batches_tracked += 1
-            if mom is None:  # cumulative moving average, as nn.BatchNorm2d does for momentum=None
-                mom = 1.0 / float(bn_mod.num_batches_tracked)
+            t = bn_mod.num_batches_tracked
+            if mom is None or t is None or not t.is_cuda or t.dtype != torch.int64:
+                bn_mod.num_batches_tracked += 1
+                if mom is None:  # cumulative moving average, as nn.BatchNorm2d does for momentum=None
+                    mom = 1.0 / float(bn_mod.num_batches_tracked)
+            else:
+                nbt = t.data_ptr()       # the counter is bumped inside the finalize kernel: no launch of its own
         rc = self.lib.uz_bn_finalize(stats.data_ptr(), rows, C, count, _ptr(bn_mod.weight), _ptr(bn_mod.bias),
                                      bn_mod.eps, mom if mom is not None else 0.0,
                                      _ptr(bn_mod.running_mean) if track else None,
-                                     _ptr(bn_mod.running_var) if track else None, bnbuf.data_ptr(), self.stream)
+                                     _ptr(bn_mod.running_var) if track else None, bnbuf.data_ptr(), nbt, self.stream)
         L.check(rc, "uz_bn_finalize")
         self.launches += 1
 
