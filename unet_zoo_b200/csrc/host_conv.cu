@@ -514,7 +514,18 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   p.yb = (H + 15) / 16;
   p.m_tiles_real = N * p.xb * p.yb;
   p.num_n_tiles = (cout + bn - 1) / bn;
-  if (convt || up2x) {
+  // ConvTranspose2d: all four output phases of a 64-column slice in ONE 256-wide item (Igemm2Params::ph_major) - the input
+  // tile is loaded once per slice instead of once per (phase, N tile), and a 128->64 layer issues N = 256 MMAs instead
+  // of four times N = 64
+  // (measured, tools/bench_convt.py, batch 32: 128->64 @256^2 0.561 -> 0.331 ms = 0.74 of the HBM roof; 256->128 @128^2
+  // 0.217 -> 0.234 ms and wider layers unchanged - their N = 128 / 256 tiles were fine already: 64 output channels only)
+  const int ph_env = env_int("UZ_CONVT_PH_MAJOR", 1);
+  const bool ph_major = convt && (ph_env == 2 || (ph_env == 1 && cout == 64));
+  if (ph_major) {
+    bn = 256;
+    p.ph_major = 1;
+    p.num_n_tiles = cout / 64;
+  } else if (convt || up2x) {
     p.nt_per_phase = p.num_n_tiles;
     p.num_n_tiles *= 4;
   }
@@ -527,7 +538,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   // measured per layer (tools/bench_conv.py): the pair wins when a tile carries >= 18 (cblock, tap) steps (+4..12 %, up
   // to 1690 TFLOP/s); with fewer the tile is epilogue bound and pair mode adds ~1 us per tile pair
   const bool pair_auto = p.b_items >= env_int("UZ_FWD2_PAIR_MIN_STEPS", 18);
-  p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 ? 1 : 0;
+  p.pair = (pair_env == 2 || (pair_env == 1 && pair_auto)) && sms >= 2 && !ph_major ? 1 : 0;
   // 3x3 + 1x1 in one GEMM with 65..128 output channels: the 1x1 segment's halo boxes feed four MMAs each instead of 36, and
   // the pair's cross-SM handshake per box then dominates (384->128 @256^2: 0.916 ms as a pair, 0.615 ms as one CTA with
   // two pixel tiles per weight tile, 0.622 ms as two separate launches - tools/bench_res_tail.py)
@@ -537,7 +548,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const long long b_all = (long long)p.b_items * b_item;
   int cluster = p.pair ? 2 : 1;
   bool stationary = false;
-  if (p.num_n_tiles == 1 && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
+  if (p.num_n_tiles == 1 && !ph_major && !env_int("UZ_FWD2_NO_STATIONARY", 0)) {
     // weights resident for the whole launch, provided at least four halo stages still fit (TMA latency cover)
     for (int nbuf = 2; nbuf >= 2 && !stationary; --nbuf) {   // one staging tile per epilogue group
       const long long left = (long long)kMaxSmem - kTail - nbuf * 16384 - b_all;
@@ -566,7 +577,7 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
     }
   }
   if (!stationary) {
-    if (!p.pair) {
+    if (!p.pair && !ph_major) {
       cluster = env_int("UZ_FWD2_CLUSTER", 1);
       if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
       if (bn / cluster < 16) cluster = 1;
@@ -591,7 +602,8 @@ static int try_fwd2(int mode, int N, int H, int W, int nseg, const void* const* 
   const int smem_bytes = p.bar_off + kTail + 1024;
   // packed weights: conv [Cout][taps][Ctot]; ConvT fwd [Cout][4 phases][Cin] (the phase is the "tap" coordinate);
   // ConvT dgrad [Cin][4][Cout] read as rows of K = 4*Cout
-  int rc = make_weight_map(&p.bmap, w_packed, ctot, convt ? 4 : (up2x || up2x_d) ? 16 : p.num_taps, cout, bn / cluster);
+  int rc = make_weight_map(&p.bmap, w_packed, ctot, convt ? 4 : (up2x || up2x_d) ? 16 : p.num_taps, cout,
+                           ph_major ? 64 : bn / cluster);
   if (rc != UZ_OK) return rc;
   if (convt || up2x) {
     for (int l = 0; l < 4 && rc == UZ_OK; ++l)

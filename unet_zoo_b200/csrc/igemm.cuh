@@ -151,6 +151,10 @@ struct alignas(64) Igemm2Params {
                                // streamed-weight layers were capped at ~72 % tensor-active by SM ingest (~50 B/clk)
   int nt_per_phase;            // 0: N tiles walk the output columns.  > 0 (ConvTranspose2d k2s2 as four 1x1 GEMMs): N tile
                                // = (phase, column tile); the phase selects the weight "tap" coordinate and the output view
+  int ph_major;                // 1 (ConvTranspose2d with cout a multiple of 64, BN = 256): ONE item covers all four output
+                               // phases of a 64-column slice - N tile = column slice, accumulator columns [64 ph, 64 ph + 64)
+                               // belong to phase ph: the input tile is loaded once instead of four times, the MMAs are 256 wide,
+                               // each epilogue chunk goes to its phase's output view.  nt_per_phase is 0 then
   int b_batched;               // 1: batched GEMM (uz_bmm_tn): the "weight" operand differs per image - the B tensor map's tap
                                // coordinate is the image index of the tile (ring mode, no CTA pair, no stationary weights)
   int ragged;                  // 1: some tile is partial (H % 16, W % 8) or a dummy (M tiles rounded up to the work-item

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
     mbar_fence_init();
     for (int s = 0; s < p.num_segs; ++s) tma_prefetch_desc(&p.amap[s]);
     tma_prefetch_desc(&p.bmap);
-    for (int i = 0; i < (p.nt_per_phase ? 4 : 1); ++i) tma_prefetch_desc(&p.omap[i]);
+    for (int i = 0; i < ((p.nt_per_phase || p.ph_major) ? 4 : 1); ++i) tma_prefetch_desc(&p.omap[i]);
   }
   if (warp == 1) {
     if (kPair) {
@@ -249,7 +249,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
                 const uint32_t dst = b_base + stage * kBItem;
                 const int btap = b_image >= 0 ? b_image
                                  : b_phase >= 0 ? (p.ph_ntaps ? b_phase * 4 + tap : b_phase) : p.seg_tap_b[seg][tap];
-                if (kPair)
+                if (p.ph_major) {   // four 64-row boxes (one per output phase = weight "tap") stacked into the 256-row tile
+#pragma unroll
+                  for (int ph = 0; ph < 4; ++ph) tma_load_3d(dst + ph * 64 * 128, &p.bmap, bfull(stage), k, ph, n_tile * 64);
+                } else if (kPair)
                   tma_load_3d_pair(dst, &p.bmap, bfull(stage), k, btap, b_row0 + rank * rows);
                 else if (cs == 1)
                   tma_load_3d(dst, &p.bmap, bfull(stage), k, btap, b_row0);
@@ -476,13 +479,14 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       int item_ntile = 0, m_unused;
       if (p.num_n_tiles > 1) f2_item(p, g * cs + rank, &item_ntile, &m_unused);
       const int o_phase = p.nt_per_phase ? item_ntile / p.nt_per_phase : 0;
-      const int row0 = (p.nt_per_phase ? item_ntile % p.nt_per_phase : item_ntile) * BN;   // first output column of the tile
+      const int row0 = p.ph_major ? item_ntile * 64                                          // first output column of the tile
+                                  : (p.nt_per_phase ? item_ntile % p.nt_per_phase : item_ntile) * BN;
       if (row0 != run_row0) {   // statistics and bias belong to the column range (not to the output phase)
         if (do_stats) flush_stats();
         run_row0 = row0;
         gbar();
         for (int c = gt; c < BN; c += 128) {
-          const int col = row0 + c;
+          const int col = row0 + (p.ph_major ? (c & 63) : c);   // phase-major: the same 64 biases for every phase
           st_shared_f32(bias_s + c * 4, (p.bias != nullptr && col < p.ncols) ? __ldg(p.bias + col) : 0.f);
         }
         gbar();
@@ -503,7 +507,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (MP * BN) + sub * BN;
 #pragma unroll 1
       for (int ch = 0; ch < kChunks; ++ch) {
-        const int col0 = row0 + ch * 64;
+        const int col0 = p.ph_major ? row0 : row0 + ch * 64;   // phase-major: chunk ch = phase ch of the same column slice
+        const int c_phase = p.ph_major ? ch : o_phase;
         if (col0 >= p.ncols) break;  // uniform over the CTA
         // 32-channel outputs (nested_unet level 0): the chunk's upper 32 columns are padding that the TMA store clips -
         // skip their TMEM load, conversion and staging (a third of this warp's instructions per tile)
@@ -546,9 +551,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) igemm_fwd2_kernel(const __grid_
         gbar();
         if (gt == 0 && !(kF2Knock & 8)) {
           if (do_acc)
-            tma_reduce_add_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
+            tma_reduce_add_4d(&p.omap[c_phase], sbuf, col0, t.x0, t.y0, t.n);
           else
-            tma_store_4d(&p.omap[o_phase], sbuf, col0, t.x0, t.y0, t.n);
+            tma_store_4d(&p.omap[c_phase], sbuf, col0, t.x0, t.y0, t.n);
           tma_store_commit();
         }
         if (do_stats && !(kF2Knock & 16)) {
