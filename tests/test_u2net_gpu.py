@@ -149,10 +149,11 @@ def test_residual_add_with_pooling(N, C, H, W, pool):
     assert relmax(get_grad(ba), br.grad + prev) < 1e-2
 
 
-def test_side_convolutions_and_fused_head():
+@pytest.mark.parametrize("K", [1, 3])
+def test_side_convolutions_and_fused_head(K):
     """Two side maps at different resolutions -> 8-channel slots -> one head pass: the three logit maps [main, side1,
-    side2] and every gradient against the reference arithmetic (u2net.py:273-285) in fp32."""
-    N, H, W, K = 2, 32, 32, 1
+    side2] (K classes each) and every gradient against the reference arithmetic (u2net.py:273-285) in fp32."""
+    N, H, W = 2, 32, 32
     s1 = nn.Conv2d(64, K, 3, padding=1).to(DEV)
     s2 = nn.Conv2d(32, K, 3, padding=1).to(DEV)
     outconv = nn.Conv2d(2 * K, K, 1).to(DEV)
@@ -306,3 +307,23 @@ def test_u2netp_non_square_eval_and_graph_replay():
     again = g(x.cuda())
     for k in out:
         assert torch.equal(again[k], out[k]), k
+
+
+def test_u2netp_two_classes_against_the_oracle():
+    """out_ch = 2 (the factory's num_classes): seven maps of two channels each, eval mode and one training step's gradients
+    of the output stage against the oracle."""
+    model = seeded_model("u2netp", num_classes=2)
+    sd = O.randomize_bn_affine({k: v.clone() for k, v in model.state_dict().items()})
+    model.load_state_dict(sd)
+    x, _ = O.synthetic_batch(2, 3, 64, 64)
+    model.cuda().train()
+    out = model(x.cuda())
+    assert all(o.shape == (2, 2, 64, 64) for o in out.values())
+    sum(O.gaussian_projection_loss(o, None) for o in out.values()).backward()
+    refs, _, ref_grads = O.train_step("u2netp", {k: v.clone() for k, v in sd.items()}, x, None,
+                                      loss_fn=O.gaussian_projection_loss)
+    for (k, o), r in zip(out.items(), refs):
+        assert rel_err(o.detach().cpu(), r.detach()) < LOGIT_TOL, k
+    grads = {k: p.grad.detach().cpu() for k, p in model.named_parameters()}
+    for k in ("outconv.weight", "outconv.bias", "side1.weight", "side1.bias", "side6.weight"):
+        assert float((grads[k] - ref_grads[k]).norm() / ref_grads[k].norm().clamp_min(1e-20)) < 5e-2, k
