@@ -26,7 +26,8 @@ if ROOT not in sys.path:
 # conv + transposed-conv FLOPs (2*MAC) of one fwd+bwd per image at 512x512, SURVEY.md section 6 / 8(d)
 FWD_BWD_GFLOP_PER_IMG_512 = {"unet": 1155.11, "attention_unet": 1593.29, "nested_unet": 827.20, "resunet": 931.44,
                               "transatt_unet": 967.47, "unet_transformer": 1830.0,   # last: 3 x the 610 GFLOP forward
-                              "u2net": 900.07, "u2netp": 303.45}       # 3 x the conv FLOPs of one forward (hooks on the reference)
+                              "u2net": 900.07, "u2netp": 303.45,       # 3 x the conv FLOPs of one forward (hooks on the reference)
+                              "multiresunet": 375.72}                  # ditto, on the reference's (unpadded) channel counts
 FWD_GFLOP_PER_IMG_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08}
 UNET_FWD_BWD_GFLOP_PER_IMG_512 = FWD_BWD_GFLOP_PER_IMG_512["unet"]
 
@@ -483,7 +484,7 @@ def main():
         if world == 1:
             # BASELINE configs[2], [3], then the neighbouring models of SURVEY 8(f) rank 4 (not BASELINE configs: batch 32)
             for name, b in (("attention_unet", 16), ("nested_unet", 8), ("transatt_unet", 32), ("unet_transformer", 32),
-                            ("u2net", 32), ("u2netp", 32)):
+                            ("u2net", 32), ("u2netp", 32), ("multiresunet", 32)):
                 try:
                     q = train_leg(args, name, b, S, 5, 3, dev, world, rank, e2e=False, profile_steps=1)
                     fam, _ = _families(q["profile"], pk, 1)

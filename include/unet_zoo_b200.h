@@ -205,14 +205,22 @@ size_t uz_bilinear_resize_bwd_workspace_bytes(int N, int H, int W, int C, int OH
 int uz_bilinear_resize_bwd(const void* dout, int dout_ld, int N, int H, int W, int C, int OH, int OW, void* dx, int dx_ld,
                            int accumulate, int align_corners, void* workspace, size_t workspace_bytes, void* stream);
 
-/* Residual add of U^2-Net's RSU blocks, `return hx1d + hxin` (u2net.py:78,127,171,210,237), NHWC bf16:
- * uz_residual_add_fwd: y = a + b; `pooled` (optional) receives MaxPool2d(2, stride 2) of the sum (u2net.py:222-232).
- * uz_residual_add_bwd: g = dy + the pooled gradient routed to the first maximum of the stored y per 2x2 window;
- *   da (+)= g and db (+)= g (acc_a / acc_b select accumulation; either incoming gradient may be NULL, not both). */
+/* Residual add of U^2-Net's RSU blocks, `return hx1d + hxin` (u2net.py:78,127,171,210,237), and - with relu = 1 - the
+ * `x = x + temp; x = F.relu(x)` of MultiResUnet's Multiresblock / Respath (multiresunet.py:82-83,125-126,132-133), NHWC bf16:
+ * uz_residual_add_fwd: y = [relu](a + b); `pooled` (optional) receives MaxPool2d(2, stride 2) of y (u2net.py:222-232).
+ * uz_residual_add_bwd: g = dy + the pooled gradient routed to the first maximum of the stored y per 2x2 window, masked
+ *   by y > 0 when relu; da (+)= g and db (+)= g (acc_a / acc_b select accumulation; either incoming gradient may be
+ *   NULL, not both; y is read when dpooled is given or relu is set). */
 int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b_ld, int N, int H, int W, int C, void* y, int y_ld,
-                        void* pooled, int pooled_ld, void* stream);
+                        void* pooled, int pooled_ld, int relu, void* stream);
 int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, const void* dy, int dy_ld, const void* dpooled,
-                        int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld, int acc_b, void* stream);
+                        int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld, int acc_b, int relu,
+                        void* stream);
+
+/* Channels [0, K), K <= 8, of an NHWC bf16 map as fp32 NCHW logits [N][K][H][W]: the output of MultiResUnet's conv_final
+ * (Conv2d 1x1 -> BatchNorm2d(affine=False), no activation; multiresunet.py:200-201,238), which runs as a conv-BN pair
+ * with the classes zero-padded to 8 channels.  The way back (fp32 NCHW gradient -> NHWC bf16) is uz_nchw_to_nhwc. */
+int uz_nhwc_to_nchw_f32(const void* x, int ld, int N, int H, int W, int K, float* out, void* stream);
 
 /* Output stage of U2NET / U2NETP (u2net.py:273-295).  `fuse`: NHWC bf16, side map i (already at full resolution) in
  * channels [8 i, 8 i + K), i < nsides <= 8, K <= 4 classes; w = outconv.weight [K][nsides * K], b = outconv.bias [K].

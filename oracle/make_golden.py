@@ -29,7 +29,7 @@ def load_reference():
     pkg.__path__ = [REF]
     sys.modules["refmodels"] = pkg
     mods = {}
-    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet", "unet_transformer", "u2net"):
+    for name in ("common_layers", "unet", "attention_unet", "nested_unet", "resunet", "transatt_unet", "unet_transformer", "u2net", "multiresunet"):
         spec = importlib.util.spec_from_file_location(f"refmodels.{name}", os.path.join(REF, name + ".py"))
         m = importlib.util.module_from_spec(spec)
         sys.modules[f"refmodels.{name}"] = m
@@ -61,6 +61,8 @@ def build(mods, name, **kw):
         return mods["u2net"].U2NET(in_ch=3, out_ch=1)        # the factory's arguments (models/__init__.py:156-158)
     if name == "u2netp":
         return mods["u2net"].U2NETP(in_ch=3, out_ch=1)
+    if name == "multiresunet":   # the factory's arguments (models/__init__.py:134-137; `depth` lands in **kwargs)
+        return mods["multiresunet"].MultiResUnet(in_channels=3, num_classes=1)
     raise ValueError(name)
 
 
@@ -110,7 +112,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     cases = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
              ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}), ("unet_transformer", {}),
-             ("u2net", {}), ("u2netp", {})]
+             ("u2net", {}), ("u2netp", {}), ("multiresunet", {})]
     only = sys.argv[1:]
     if only:
         cases = [c for c in cases if c[0] in only]

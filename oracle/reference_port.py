@@ -22,16 +22,33 @@ import torch.nn.functional as F
 SD = Dict[str, torch.Tensor]
 
 
+def _ste_round(t: torch.Tensor, dtype) -> torch.Tensor:
+    """Round to `dtype` and back with a straight-through gradient."""
+    return t + (t.detach().to(dtype).to(t.dtype) - t.detach())
+
+
 class Runner:
-    """Carries the parameters, the train/eval flag and (in train mode) updates BatchNorm running statistics in `sd`."""
+    """Carries the parameters, the train/eval flag and (in train mode) updates BatchNorm running statistics in `sd`.
+
+    `round_storage` (class attribute, default None = the reference's plain fp32 arithmetic) is a TEST mode: with
+    torch.bfloat16 every tensor the sm_100a executor stores in bf16 - convolution weights, inputs and outputs,
+    BatchNorm inputs and outputs - is rounded at the same point (straight-through gradient), everything else stays
+    fp32.  Networks whose train-mode outputs are ill-conditioned (MultiResUnet: no BatchNorm affine parameters, every
+    ReLU input zero-mean) can then be compared tightly: the ReLU masks of both sides see the same rounded values."""
+
+    round_storage = None
 
     def __init__(self, sd: SD, training: bool):
         self.sd = sd
         self.training = training
 
+    def _q(self, t):
+        return t if self.round_storage is None else _ste_round(t, self.round_storage)
+
     # nn.Conv2d defaults: stride 1, dilation 1, groups 1 (common_layers.py:28)
     def conv(self, x, key, stride=1, padding=0):
-        return F.conv2d(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"), stride=stride, padding=padding)
+        return self._q(F.conv2d(self._q(x), self._q(self.sd[key + ".weight"]), self.sd.get(key + ".bias"), stride=stride,
+                                padding=padding))
 
     # nn.BatchNorm2d defaults: eps 1e-5, momentum 0.1, affine, track_running_stats (common_layers.py:29).
     # Training: biased batch variance normalises, running_var gets the unbiased one; eval: running statistics.
@@ -39,8 +56,9 @@ class Runner:
         rm, rv = self.sd[key + ".running_mean"], self.sd[key + ".running_var"]
         if self.training:
             self.sd[key + ".num_batches_tracked"] += 1
-        return F.batch_norm(x, rm, rv, self.sd[key + ".weight"], self.sd[key + ".bias"], training=self.training,
-                            momentum=0.1, eps=1e-5)
+        # affine=False modules (multiresunet.py:22,68,106) have no weight / bias entries
+        return self._q(F.batch_norm(self._q(x), rm, rv, self.sd.get(key + ".weight"), self.sd.get(key + ".bias"),
+                                    training=self.training, momentum=0.1, eps=1e-5))
 
     def cbr(self, x, conv_key, bn_key, stride=1):
         return F.relu(self.bn(self.conv(x, conv_key, stride=stride, padding=1), bn_key))
@@ -52,7 +70,8 @@ class Runner:
 
     # nn.ConvTranspose2d(k=2, s=2): weight [Cin, Cout, 2, 2]  (common_layers.py:104)
     def conv_transpose(self, x, key):
-        return F.conv_transpose2d(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"), stride=2)
+        return self._q(F.conv_transpose2d(self._q(x), self._q(self.sd[key + ".weight"]), self.sd.get(key + ".bias"),
+                                          stride=2))
 
 
 def _pad_to(x1, x2):
@@ -461,10 +480,66 @@ def u2net_loss(outs: List[torch.Tensor], target: torch.Tensor, criterion=None):
         total = total + 1.0 * criterion(o, m)
     return total
 
+# ------------------------------------------------------------------------------------------------ MultiResUnet
+def multires_widths(f: int, alpha: float = 1.67):
+    """Multiresblock.__init__ (multiresunet.py:47-52): W = int(f * alpha); the 3x3 / "5x5" / "7x7" branch widths are
+    int(W * 0.167), int(W * 0.333), int(W * 0.5)."""
+    w = int(f * alpha)
+    return int(w * 0.167), int(w * 0.333), int(w * 0.5)
+
+
+def _conv2d_bn(r: Runner, x, prefix, relu: bool, padding: int):
+    """Conv2d_batchnorm.forward (multiresunet.py:24-30): conv1 -> BatchNorm2d(affine=False) -> ReLU or nothing."""
+    x = r.bn(r.conv(x, prefix + ".conv1", padding=padding), prefix + ".batchnorm")
+    return F.relu(x) if relu else x
+
+
+def _multiresblock(r: Runner, x, prefix):
+    """Multiresblock.forward (multiresunet.py:70-85).  batch_norm1 is applied TWICE: to the concatenation and, after
+    the residual add + ReLU, to the sum (in train mode each application normalises with its own batch statistics
+    and updates the same running buffers)."""
+    temp = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1", False, 0)
+    a = _conv2d_bn(r, x, prefix + ".conv2d_bn_3x3", True, 1)
+    b = _conv2d_bn(r, a, prefix + ".conv2d_bn_5x5", True, 1)
+    c = _conv2d_bn(r, b, prefix + ".conv2d_bn_7x7", True, 1)
+    x = r.bn(torch.cat([a, b, c], dim=1), prefix + ".batch_norm1")
+    x = F.relu(x + temp)
+    return r.bn(x, prefix + ".batch_norm1")
+
+
+def _respath(r: Runner, x, prefix, length: int):
+    """Respath.forward (multiresunet.py:121-135): `length` residual steps conv3x3-BN-ReLU + conv1x1-BN -> ReLU -> BN."""
+    shortcut = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1_initial", False, 0)
+    x = _conv2d_bn(r, x, prefix + ".conv2d_bn_3x3_initial", True, 1)
+    x = r.bn(F.relu(x + shortcut), prefix + ".batch_norm_initial")
+    for i in range(length - 1):
+        shortcut = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.0", False, 0)
+        x = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.1", True, 1)
+        x = r.bn(F.relu(x + shortcut), f"{prefix}.blocks.{i}.2")
+    return x
+
+
+def multiresunet_forward(sd: SD, x: torch.Tensor, training: bool) -> torch.Tensor:
+    """MultiResUnet.forward (multiresunet.py:203-240): four Multiresblock + MaxPool2d(2, 2) stages, each with a
+    Respath on its skip (lengths 4, 3, 2, 1), a fifth Multiresblock, four ConvTranspose2d(2, 2) -> cat([up, skip]) ->
+    Multiresblock steps, and conv_final = Conv2d(1x1) -> BatchNorm2d(affine=False) without activation."""
+    r = Runner(sd, training)
+    skips = []
+    for i in range(1, 5):
+        m = _multiresblock(r, x, f"multiresblock{i}")
+        skips.append(_respath(r, m, f"respath{i}", 5 - i))
+        x = F.max_pool2d(m, 2, 2)
+    x = _multiresblock(r, x, "multiresblock5")
+    for i in range(6, 10):
+        up = r.conv_transpose(x, f"upsample{i}")
+        x = _multiresblock(r, torch.cat([up, skips[9 - i]], dim=1), f"multiresblock{i}")
+    return _conv2d_bn(r, x, "conv_final", False, 0)
+
 
 FORWARDS = {"unet": unet_forward, "attention_unet": attention_unet_forward, "nested_unet": nested_unet_forward,
             "resunet": resunet_forward, "transatt_unet": transatt_unet_forward,
-            "unet_transformer": unet_transformer_forward, "u2net": u2net_forward, "u2netp": u2netp_forward}
+            "unet_transformer": unet_transformer_forward, "u2net": u2net_forward, "u2netp": u2netp_forward,
+            "multiresunet": multiresunet_forward}
 
 
 def bce_with_logits(logits, target):

@@ -13,18 +13,18 @@ from unet_zoo_b200.models import blocks
 
 
 def test_list_models_and_names():
-    assert unet_zoo_b200.list_models() == ["attention_unet", "nested_unet", "resunet", "transatt_unet", "u2net",
-                                           "u2netp", "unet", "unet_transformer"]
+    assert unet_zoo_b200.list_models() == ["attention_unet", "multiresunet", "nested_unet", "resunet", "transatt_unet",
+                                           "u2net", "u2netp", "unet", "unet_transformer"]
     names = {"unet": "UNet", "attention_unet": "AttentionUNet", "nested_unet": "NestedUNet", "resunet": "ResUnet",
              "transatt_unet": "TransAttUNet", "unet_transformer": "U_Transformer",
-             "u2net": "U2NET", "u2netp": "U2NETP"}
+             "u2net": "U2NET", "u2netp": "U2NETP", "multiresunet": "MultiResUnet"}
     for n, cls in names.items():
         assert type(unet_zoo_b200.create_model(n.upper())).__name__ == cls      # case-insensitive (__init__.py:82)
 
 
 @pytest.mark.parametrize("name,count", [("unet", 136), ("attention_unet", 240), ("nested_unet", 212), ("resunet", 127),
                                         ("transatt_unet", 137), ("unet_transformer", 209),
-                                        ("u2net", 798), ("u2netp", 798)])
+                                        ("u2net", 798), ("u2netp", 798), ("multiresunet", 350)])
 def test_default_init_matches_reference(name, count):
     """Same keys, shapes and - under the same seed - bit-identical default initialisation as the reference modules."""
     fp = load_golden(name)["fingerprint"]

@@ -10,7 +10,8 @@ from oracle import reference_port as O
 
 CASES = [("unet", {}), ("attention_unet", {}), ("nested_unet", {}), ("resunet", {}),
          ("nested_unet_ds", {"deep_supervision": True}), ("transatt_unet", {"attn_dropout": 0.0}),
-         ("u2net", {}), ("u2netp", {})]      # seven outputs [main, side1..6]; the default-init fixture stores the first two
+         ("u2net", {}), ("u2netp", {}),      # seven outputs [main, side1..6]; the default-init fixture stores the first two
+         ("multiresunet", {})]               # no BatchNorm affine parameters: the "conditioned" state is the default one
 
 
 @pytest.mark.parametrize("tag,kw", CASES)
@@ -58,7 +59,8 @@ def test_oracle_matches_reference_on_conditioned_state(tag, kw):
         assert rel_err(o.detach(), g) < 1e-5
     assert abs(float(sum(O.bce_with_logits(o.detach(), mask) for o in outs)) - cond["bce"]) < 1e-5
     for k, gn in cond["grad_norm"].items():
-        assert abs(float(grads[k].double().norm()) - gn) <= 5e-4 * gn + 1e-9, k
+        # + 1e-7: conv biases in front of a train-mode BatchNorm have an identically zero gradient (fp32 noise ~1e-8)
+        assert abs(float(grads[k].double().norm()) - gn) <= 5e-4 * gn + 1e-7, k
     for k, v in cond["bn_after"].items():
         assert torch.allclose(sd[k].double(), v.double(), rtol=1e-5, atol=1e-6), k
     with torch.no_grad():

@@ -65,12 +65,13 @@ _PROTOS = {
     "uz_bilinear_resize_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "uz_bilinear_resize_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_int, c_int, c_int, _P,
                                        c_size_t, _P]),
-    "uz_residual_add_fwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P]),
+    "uz_residual_add_fwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, c_int, _P]),
+    "uz_nhwc_to_nchw_f32": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P]),
     "uz_side_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int]),
     "uz_side_head_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "uz_side_head_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, _P, _P, _P, c_size_t, _P]),
     "uz_residual_add_bwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, _P, c_int,
-                                    c_int, _P]),
+                                    c_int, c_int, _P]),
     "uz_bmm_tn": (c_int, [_P, c_longlong, c_longlong, _P, c_longlong, _P, c_longlong, c_longlong, c_int, c_int, c_int,
                           c_int, _P]),
     "uz_softmax_rows": (c_int, [_P, c_longlong, _P, c_longlong, c_longlong, c_int, c_float, _P]),

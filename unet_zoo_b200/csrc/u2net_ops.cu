@@ -21,7 +21,7 @@ __device__ __forceinline__ float ra_bf16r(float v) { return __bfloat162float(__f
 // one thread per (2x2 quad, 8-channel group); partial quads of odd sizes get their sum but no pooling window
 __global__ void residual_add_fwd_kernel(const __nv_bfloat16* __restrict__ a, int a_ld, const __nv_bfloat16* __restrict__ b,
                                         int b_ld, int N, int H, int W, int C, __nv_bfloat16* __restrict__ y, int y_ld,
-                                        __nv_bfloat16* __restrict__ pooled, int pooled_ld) {
+                                        __nv_bfloat16* __restrict__ pooled, int pooled_ld, int relu) {
   const int cv = C / 8;
   const int Hq = (H + 1) / 2, Wq = (W + 1) / 2, Hp = H / 2, Wp = W / 2;
   const long long total = static_cast<long long>(N) * Hq * Wq * cv;
@@ -43,7 +43,7 @@ __global__ void residual_add_fwd_kernel(const __nv_bfloat16* __restrict__ a, int
       ra_ld8(a + p * a_ld + g * 8, f);
       ra_ld8(b + p * b_ld + g * 8, r);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = ra_bf16r(f[j] + r[j]);
+      for (int j = 0; j < 8; ++j) f[j] = ra_bf16r(relu ? fmaxf(f[j] + r[j], 0.f) : f[j] + r[j]);
       ra_st8(y + p * y_ld + g * 8, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) m[j] = (k == 0 || f[j] > m[j]) ? f[j] : m[j];
@@ -56,7 +56,7 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
                                         const __nv_bfloat16* __restrict__ dy, int dy_ld,
                                         const __nv_bfloat16* __restrict__ dpooled, int dpooled_ld,
                                         __nv_bfloat16* __restrict__ da, int da_ld, int acc_a,
-                                        __nv_bfloat16* __restrict__ db, int db_ld, int acc_b) {
+                                        __nv_bfloat16* __restrict__ db, int db_ld, int acc_b, int relu) {
   const int cv = C / 8;
   const int Hq = (H + 1) / 2, Wq = (W + 1) / 2, Hp = H / 2, Wp = W / 2;
   const long long total = static_cast<long long>(N) * Hq * Wq * cv;
@@ -69,14 +69,17 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
     const int qy = static_cast<int>(q % Hq);
     const long long n = q / Hq;
     const bool full = dpooled != nullptr && qy < Hp && qx < Wp;
-    float dp[8];
+    float dp[8], s[4][8];
     int am[8];
-    if (full) {
-      float s[4][8];
-      ra_ld8(dpooled + ((n * Hp + qy) * Wp + qx) * dpooled_ld + g * 8, dp);
+    if (full || relu) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        ra_ld8(y + ((n * H + 2 * qy + (k >> 1)) * W + 2 * qx + (k & 1)) * y_ld + g * 8, s[k]);
+      for (int k = 0; k < 4; ++k) {
+        const int yy = 2 * qy + (k >> 1), xx = 2 * qx + (k & 1);
+        if (yy < H && xx < W) ra_ld8(y + ((n * H + yy) * W + xx) * y_ld + g * 8, s[k]);
+      }
+    }
+    if (full) {
+      ra_ld8(dpooled + ((n * Hp + qy) * Wp + qx) * dpooled_ld + g * 8, dp);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         am[j] = 0;
@@ -106,6 +109,11 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
         for (int j = 0; j < 8; ++j)
           if (am[j] == k) o[j] += dp[j];
       }
+      if (relu) {      // ReLU after the add: the gradient passes where the stored sum is positive
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (!(s[k][j] > 0.f)) o[j] = 0.f;
+      }
       __nv_bfloat16* dst[2] = {da + p * da_ld + g * 8, db + p * db_ld + g * 8};
       const int acc[2] = {acc_a, acc_b};
 #pragma unroll
@@ -122,6 +130,23 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
         ra_st8(dst[t], v);
       }
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ logits extraction
+// The first K (<= 8) channels of an NHWC bf16 map as fp32 NCHW planes: MultiResUnet's conv_final (Conv2d 1x1 ->
+// BatchNorm2d(affine=False), multiresunet.py:200-201,238) runs as a conv-BN pair whose single class is padded to 8
+// channels.  One thread per pixel: one 16-byte load, K coalesced fp32 stores.
+__global__ void nhwc_to_nchw_f32_kernel(const __nv_bfloat16* __restrict__ x, int ld, long long npix, long long plane, int K,
+                                        float* __restrict__ out) {
+  for (long long p = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; p < npix;
+       p += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long n = p / plane, hw = p - n * plane;
+    float f[8];
+    ra_ld8(x + p * ld, f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (k < K) out[(n * K + k) * plane + hw] = f[k];
   }
 }
 
@@ -290,7 +315,7 @@ int ra_chk(const char* what, const void* p, int C, int ld) {
 using namespace uz;
 
 extern "C" int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b_ld, int N, int H, int W, int C, void* y,
-                                   int y_ld, void* pooled, int pooled_ld, void* stream) {
+                                   int y_ld, void* pooled, int pooled_ld, int relu, void* stream) {
   PW_REQUIRE_DEVICE();
   int rc = ra_chk("residual_add_fwd(a)", a, C, a_ld);
   if (rc || (rc = ra_chk("residual_add_fwd(b)", b, C, b_ld)) || (rc = ra_chk("residual_add_fwd(y)", y, C, y_ld))) return rc;
@@ -299,29 +324,42 @@ extern "C" int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b
   const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   residual_add_fwd_kernel<<<ra_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(a), a_ld, static_cast<const __nv_bfloat16*>(b), b_ld, N, H, W, C,
-      static_cast<__nv_bfloat16*>(y), y_ld, static_cast<__nv_bfloat16*>(pooled), pooled_ld);
+      static_cast<__nv_bfloat16*>(y), y_ld, static_cast<__nv_bfloat16*>(pooled), pooled_ld, relu);
   PW_CHECK_LAUNCH("residual_add_fwd launch");
   return UZ_OK;
 }
 
 extern "C" int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, const void* dy, int dy_ld,
                                    const void* dpooled, int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld,
-                                   int acc_b, void* stream) {
+                                   int acc_b, int relu, void* stream) {
   PW_REQUIRE_DEVICE();
   int rc = ra_chk("residual_add_bwd(da)", da, C, da_ld);
   if (rc || (rc = ra_chk("residual_add_bwd(db)", db, C, db_ld))) return rc;
   if (!dy && !dpooled) return set_error(UZ_ERR_INVALID, "residual_add_bwd: no incoming gradient");
   if (dy && (rc = ra_chk("residual_add_bwd(dy)", dy, C, dy_ld))) return rc;
-  if (dpooled && ((rc = ra_chk("residual_add_bwd(dpooled)", dpooled, C, dpooled_ld)) || (rc = ra_chk("residual_add_bwd(y)", y, C, y_ld))))
-    return rc;
+  if (dpooled && (rc = ra_chk("residual_add_bwd(dpooled)", dpooled, C, dpooled_ld))) return rc;
+  if ((dpooled || relu) && (rc = ra_chk("residual_add_bwd(y)", y, C, y_ld))) return rc;
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "residual_add_bwd: bad extents");
   if (da == db) return set_error(UZ_ERR_INVALID, "residual_add_bwd: da and db must be different buffers");
   const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   residual_add_bwd_kernel<<<ra_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(y), y_ld, N, H, W, C, static_cast<const __nv_bfloat16*>(dy), dy_ld,
       static_cast<const __nv_bfloat16*>(dpooled), dpooled_ld, static_cast<__nv_bfloat16*>(da), da_ld, acc_a,
-      static_cast<__nv_bfloat16*>(db), db_ld, acc_b);
+      static_cast<__nv_bfloat16*>(db), db_ld, acc_b, relu);
   PW_CHECK_LAUNCH("residual_add_bwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_nhwc_to_nchw_f32(const void* x, int ld, int N, int H, int W, int K, float* out, void* stream) {
+  PW_REQUIRE_DEVICE();
+  int rc = ra_chk("nhwc_to_nchw_f32(x)", x, 8, ld);
+  if (rc) return rc;
+  if (N < 1 || H < 1 || W < 1 || K < 1 || K > 8 || out == nullptr)
+    return set_error(UZ_ERR_INVALID, "nhwc_to_nchw_f32: bad extents (N=%d H=%d W=%d K=%d, K <= 8)", N, H, W, K);
+  const long long plane = static_cast<long long>(H) * W, npix = plane * N;
+  nhwc_to_nchw_f32_kernel<<<ra_grid(npix), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), ld, npix, plane, K, out);
+  PW_CHECK_LAUNCH("nhwc_to_nchw_f32 launch");
   return UZ_OK;
 }
 

@@ -164,13 +164,24 @@ class ParamGrads:
         self.flat = torch.zeros(total, dtype=torch.float32, device=device)
         self.done = set()
         self.on_ready = on_ready
+        # tensors that are NOT parameters but receive a gradient during backward: the zero-padded shadow operands of
+        # models whose channel counts are not multiples of 8 (models/multiresunet.py); id -> (offset, shape, buffer)
+        self.extern: Dict[int, Tuple[int, torch.Size, torch.Tensor]] = {}
+
+    def add_extern(self, t: torch.Tensor, off: int, flat: torch.Tensor):
+        self.extern[id(t)] = (off, t.shape, flat)
 
     def view(self, p) -> torch.Tensor:
+        ext = self.extern.get(id(p))
+        if ext is not None:
+            return ext[2][ext[0]:ext[0] + p.numel()].view(ext[1])
         off, shape = self.offsets[id(p)]
         return self.flat[off:off + p.numel()].view(shape)
 
     def ready(self, p):
         """Called by the tape when the gradient of `p` is complete on the compute stream."""
+        if id(p) in self.extern:     # the owner gathers these into the parameters' gradients and reports those
+            return
         self.done.add(id(p))
         if self.on_ready is not None:
             self.on_ready(p)
@@ -860,16 +871,21 @@ def conv_stats(ctx: Ctx, xs: Sequence[Act], conv, bn, mode: int = L.CONV3X3) -> 
     return z, bnbuf
 
 
-def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True) -> Act:
+def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True, out: Optional[Act] = None, pooled: Optional[Act] = None) -> Act:
     """[ReLU](BatchNorm2d(x)) on an existing activation - the pre-activation half of ResidualConv
-    (common_layers.py:185-186,189-190).  Training: one statistics pass + one apply pass; inference: apply only."""
+    (common_layers.py:185-186,189-190) and the stand-alone BatchNorm2d(affine=False) layers of MultiResUnet
+    (multiresunet.py:79,84,127,134); `pooled` receives MaxPool2d(2, 2) of the result (multiresunet.py:206).
+    Training: one statistics pass + one apply pass; inference: apply only."""
     if ctx.fp32:
+        if out is not None or pooled is not None:
+            raise RuntimeError("unet_zoo_b200: bn_act into a given buffer / with pooling has no fp32 parity path")
         return _F32.bn_act(ctx, x, bn, relu=relu)
-    out = ctx.new_act(x.N, x.H, x.W, x.C)
+    if out is None:
+        out = ctx.new_act(x.N, x.H, x.W, x.C)
     if not ctx.training:
         aff = ctx.cached(("affine", id(bn)), [bn.weight, bn.bias, bn.running_mean, bn.running_var],
                          lambda: _running_affine(bn, ctx.device))
-        ctx.bn_apply(x, aff[2].data_ptr(), aff[3].data_ptr(), relu, out)
+        ctx.bn_apply(x, aff[2].data_ptr(), aff[3].data_ptr(), relu, out, pooled)
         return out
     rows = ctx.reduce_rows
     stats = ctx.f32(rows, 2, x.C)
@@ -877,16 +893,19 @@ def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True) -> Act:
     ctx.launches += 1
     bnbuf = ctx.f32(4, x.C)
     ctx.bn_finalize(stats, rows, x.C, x.npix, bn, bnbuf)
-    ctx.bn_apply(x, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out)
+    ctx.bn_apply(x, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out, pooled)
     if ctx.record:
         def backward(c: Ctx):
-            if not out.has_grad():
+            has_dy = out.has_grad()
+            has_dp = pooled is not None and pooled.has_grad()
+            if not (has_dy or has_dp):
                 raise RuntimeError("unet_zoo_b200: bn_act output has no gradient")
             for (r0, rc, acc) in x.grad_writes():
                 xs_ = x.slice(r0, rc)
                 sub = bnbuf if rc == x.C else torch.stack([bnbuf[k, r0:r0 + rc] for k in range(4)]).contiguous()
                 dg, db = c.pgrad(bn.weight), c.pgrad(bn.bias)
-                c.bn_bwd(xs_, out.gptr() + 2 * r0, out.ld, None, 0, sub, relu, xs_.gptr(), x.ld,
+                c.bn_bwd(xs_, out.gptr() + 2 * r0 if has_dy else None, out.ld, pooled.gptr() + 2 * r0 if has_dp else None,
+                         pooled.ld if has_dp else 0, sub, relu, xs_.gptr(), x.ld,
                          dg[r0:r0 + rc] if dg is not None else None, db[r0:r0 + rc] if db is not None else None, None,
                          dz_accumulate=acc)
             c.pready(bn.weight, bn.bias)
@@ -1195,15 +1214,17 @@ def fused_side_head(ctx: Ctx, fuse: Act, outconv, K: int, nsides: int) -> torch.
     return logits
 
 
-def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Optional[Act] = None) -> Act:
-    """out = a + b with optional MaxPool2d(2, 2) of the sum as a second output: `return hx1d + hxin` of the RSU blocks
-    (u2net.py:78,127,171,210,237) followed by the stage pooling (u2net.py:222-232)."""
+def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Optional[Act] = None,
+                 relu: bool = False) -> Act:
+    """out = [ReLU](a + b) with optional MaxPool2d(2, 2) of the result as a second output: `return hx1d + hxin` of the
+    RSU blocks (u2net.py:78,127,171,210,237) followed by the stage pooling (u2net.py:222-232); with `relu` the
+    `x = x + temp; x = F.relu(x)` of Multiresblock / Respath (multiresunet.py:82-83,125-126,132-133)."""
     if ctx.fp32:
         raise RuntimeError("unet_zoo_b200: residual_add has no fp32 parity path")
     if out is None:
         out = ctx.new_act(a.N, a.H, a.W, a.C)
     L.check(ctx.lib.uz_residual_add_fwd(a.ptr, a.ld, b.ptr, b.ld, a.N, a.H, a.W, a.C, out.ptr, out.ld,
-                                        pooled.ptr if pooled else None, pooled.ld if pooled else 0, ctx.stream),
+                                        pooled.ptr if pooled else None, pooled.ld if pooled else 0, int(relu), ctx.stream),
             "uz_residual_add_fwd")
     ctx.launches += 1
     if ctx.record:
@@ -1218,10 +1239,38 @@ def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Op
             L.check(c.lib.uz_residual_add_bwd(out.ptr, out.ld, a.N, a.H, a.W, a.C, out.gptr() if has_dy else None,
                                               out.ld if has_dy else 0, pooled.gptr() if has_dp else None,
                                               pooled.ld if has_dp else 0, a.gptr(), a.ld, int(ra[0][2]), b.gptr(), b.ld,
-                                              int(rb[0][2]), c.stream), "uz_residual_add_bwd")
+                                              int(rb[0][2]), int(relu), c.stream), "uz_residual_add_bwd")
             c.launches += 1
         ctx.tape.append(backward)
     return out
+
+
+def nhwc_logits(ctx: Ctx, y: Act, K: int) -> torch.Tensor:
+    """Channels [0, K) of `y` as the model's fp32 NCHW output: MultiResUnet returns the BatchNorm2d(affine=False) of its
+    1x1 conv_final directly (multiresunet.py:238-240); that conv-BN pair runs with the classes padded to 8 channels.
+    Backward: the incoming fp32 gradient becomes the (zero-padded) bf16 gradient of `y`."""
+    if ctx.fp32:
+        raise RuntimeError("unet_zoo_b200: nhwc_logits has no fp32 parity path")
+    if y.C != 8 or not 1 <= K <= 8:
+        raise ValueError("nhwc_logits: an 8-channel activation and 1 <= K <= 8 classes")
+    logits = torch.empty((y.N, K, y.H, y.W), dtype=torch.float32, device=ctx.device)
+    L.check(ctx.lib.uz_nhwc_to_nchw_f32(y.ptr, y.ld, y.N, y.H, y.W, K, logits.data_ptr(), ctx.stream), "uz_nhwc_to_nchw_f32")
+    ctx.launches += 1
+    idx = len(ctx.outputs)
+    ctx.outputs.append(logits)
+    if ctx.record:
+        def backward(c: Ctx):
+            g = c.out_grads[idx] if idx < len(c.out_grads) else None
+            if g is None:
+                raise RuntimeError("unet_zoo_b200: the model output received no gradient")
+            runs = y.grad_writes()
+            if len(runs) != 1 or runs[0][2]:
+                raise NotImplementedError("nhwc_logits: the activation already has a gradient")
+            dl = g.contiguous().float()
+            L.check(c.lib.uz_nchw_to_nhwc(dl.data_ptr(), y.N, K, y.H, y.W, y.gptr(), y.ld, c.stream), "uz_nchw_to_nhwc")
+            c.launches += 1
+        ctx.tape.append(backward)
+    return logits
 
 
 def token_island(ctx: Ctx, x: Act, fn: Callable[[torch.Tensor], torch.Tensor], params: Sequence[torch.nn.Parameter],

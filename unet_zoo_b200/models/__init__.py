@@ -49,8 +49,14 @@ try:  # third neighbouring family: U^2-Net (RSU blocks = conv-BN-ReLU with dilat
 except ImportError:  # pragma: no cover
     pass
 
+try:  # fourth: MultiResUnet (channel counts that are not multiples of 8 run zero-padded, models/_padded.py)
+    from .multiresunet import MultiResUnet
+    _model_entries["multiresunet"] = MultiResUnet
+except ImportError:  # pragma: no cover
+    pass
+
 # registry names of the reference that are deliberately not part of this build
-_OUT_OF_SCOPE = ("raunet", "da_transformer", "uctransnet", "multiresunet",
+_OUT_OF_SCOPE = ("raunet", "da_transformer", "uctransnet",
                  "missformer", "vnet", "swin_unet_v2", "wranet", "egeunet", "unext", "unext_s",
                  "mmunet", "axialunet", "gated", "medt", "logo")
 
@@ -90,6 +96,8 @@ def create_model(model_name: str, pretrained: bool = False, **kwargs) -> nn.Modu
         args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
     elif name == "unet_transformer":   # the reference factory's default branch (models/__init__.py:221-223)
         args = dict(in_channels=in_channels, num_classes=num_classes)
+    elif name == "multiresunet":       # models/__init__.py:134-137: `depth` is passed on and swallowed by **kwargs
+        args = dict(in_channels=in_channels, num_classes=num_classes, depth=depth)
     elif name in ("u2net", "u2netp"):  # models/__init__.py:156-158
         args = dict(in_ch=in_channels, out_ch=num_classes)
     else:  # resunet

@@ -46,13 +46,19 @@ class _HotPathFn(torch.autograd.Function):
         make = getattr(model, "_uz_make_param_grads", None)
         ctx.pgrads = make(params, ctx.device) if make is not None else E.ParamGrads(params, ctx.device)
         model._last_param_grads = ctx.pgrads     # the flat gradient buffer of this step (parallel.sync_gradients)
+        shadow = model._uz_shadow      # zero-padded operands standing in for the parameters (models/multiresunet.py)
+        if shadow is not None:
+            shadow.begin_backward(ctx.pgrads)
         ctx.out_grads = list(douts)
         for step in reversed(ctx.tape):
             step(ctx)
         ctx.join_side()                      # weight gradients ran on the side stream (engine.Ctx.on_side)
         ctx.tape.clear()
+        if shadow is not None:
+            shadow.end_backward(ctx.pgrads, params)
         if ctx.pack_log is not None and not torch.cuda.is_current_stream_capturing():
-            model._pack_plan = E.PackPlan(ctx.pack_log, params, ctx.device)    # one launch packs them all from now on
+            sources = list(params) + (shadow.pack_sources() if shadow is not None else [])
+            model._pack_plan = E.PackPlan(ctx.pack_log, sources, ctx.device)    # one launch packs them all from now on
             ctx.pack_log = None
         model._last_launches_bwd = ctx.launches
         finish = getattr(ctx.pgrads, "finish", None)
@@ -84,6 +90,8 @@ class HotPathModel(nn.Module):
         return self
 
     _input_norm = None
+    _uz_shadow = None           # models whose tensors need zero-padding to multiples of 8 channels keep their padded
+                                # stand-ins here (refreshed from the parameters before every forward)
     _pack_plan = None           # engine.PackPlan: every weight pack of a training step in one launch (learned in step 1)
     _eval_cache = None          # engine.Ctx.cached: inference memo of packed / BatchNorm-folded weights
 
@@ -145,6 +153,7 @@ class HotPathModel(nn.Module):
     def forward(self, x):
         x = self._check_input(x)
         with torch.cuda.device(x.device):
+            self._before_forward(x.device)
             if self.precision == "fp32":
                 if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
                     raise RuntimeError(f"{type(self).__name__}: the fp32 mode is a forward-only parity mode - call it "
@@ -167,6 +176,9 @@ class HotPathModel(nn.Module):
                     outs = self._graph(ctx, x)
                     self._last_launches = ctx.launches
         return self._pack_outputs(list(outs))
+
+    def _before_forward(self, device):
+        """Hook that runs on the input's device before anything is launched (padded stand-ins of the parameters)."""
 
     def _pack_outputs(self, outs: List[torch.Tensor]):
         return outs[0]
