@@ -133,6 +133,62 @@ __global__ void residual_add_bwd_kernel(const __nv_bfloat16* __restrict__ y, int
   }
 }
 
+// Without pooling the quad structure buys nothing: one thread per (pixel, 8-channel group), consecutive threads on
+// consecutive 16-byte words of a pixel row (every residual add of MultiResUnet; the decoder RSU blocks of U^2-Net).
+__global__ void residual_add_lin_fwd_kernel(const __nv_bfloat16* __restrict__ a, int a_ld, const __nv_bfloat16* __restrict__ b,
+                                            int b_ld, long long npix, int C, __nv_bfloat16* __restrict__ y, int y_ld, int relu) {
+  const int cv = C / 8;
+  const long long total = npix * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long p = i / cv;
+    const int g = static_cast<int>(i - p * cv);
+    float f[8], r[8];
+    ra_ld8(a + p * a_ld + g * 8, f);
+    ra_ld8(b + p * b_ld + g * 8, r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = relu ? fmaxf(f[j] + r[j], 0.f) : f[j] + r[j];
+    ra_st8(y + p * y_ld + g * 8, f);
+  }
+}
+
+__global__ void residual_add_lin_bwd_kernel(const __nv_bfloat16* __restrict__ y, int y_ld, long long npix, int C,
+                                            const __nv_bfloat16* __restrict__ dy, int dy_ld, __nv_bfloat16* __restrict__ da,
+                                            int da_ld, int acc_a, __nv_bfloat16* __restrict__ db, int db_ld, int acc_b,
+                                            int relu) {
+  const int cv = C / 8;
+  const long long total = npix * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long p = i / cv;
+    const int g = static_cast<int>(i - p * cv);
+    float o[8];
+    ra_ld8(dy + p * dy_ld + g * 8, o);
+    if (relu) {
+      float s[8];
+      ra_ld8(y + p * y_ld + g * 8, s);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (!(s[j] > 0.f)) o[j] = 0.f;
+    }
+    __nv_bfloat16* dst[2] = {da + p * da_ld + g * 8, db + p * db_ld + g * 8};
+    const int acc[2] = {acc_a, acc_b};
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = o[j];
+      if (acc[t]) {
+        float old[8];
+        ra_ld8(dst[t], old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += old[j];
+      }
+      ra_st8(dst[t], v);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ logits extraction
 // The first K (<= 8) channels of an NHWC bf16 map as fp32 NCHW planes: MultiResUnet's conv_final (Conv2d 1x1 ->
 // BatchNorm2d(affine=False), multiresunet.py:200-201,238) runs as a conv-BN pair whose single class is padded to 8
@@ -321,6 +377,14 @@ extern "C" int uz_residual_add_fwd(const void* a, int a_ld, const void* b, int b
   if (rc || (rc = ra_chk("residual_add_fwd(b)", b, C, b_ld)) || (rc = ra_chk("residual_add_fwd(y)", y, C, y_ld))) return rc;
   if (pooled && (rc = ra_chk("residual_add_fwd(pooled)", pooled, C, pooled_ld))) return rc;
   if (N < 1 || H < 1 || W < 1 || (pooled && (H < 2 || W < 2))) return set_error(UZ_ERR_INVALID, "residual_add_fwd: bad extents");
+  if (!pooled) {
+    const long long npix = static_cast<long long>(N) * H * W;
+    residual_add_lin_fwd_kernel<<<ra_grid(npix * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(a), a_ld, static_cast<const __nv_bfloat16*>(b), b_ld, npix, C,
+        static_cast<__nv_bfloat16*>(y), y_ld, relu);
+    PW_CHECK_LAUNCH("residual_add_fwd launch");
+    return UZ_OK;
+  }
   const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   residual_add_fwd_kernel<<<ra_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(a), a_ld, static_cast<const __nv_bfloat16*>(b), b_ld, N, H, W, C,
@@ -341,6 +405,14 @@ extern "C" int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W,
   if ((dpooled || relu) && (rc = ra_chk("residual_add_bwd(y)", y, C, y_ld))) return rc;
   if (N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "residual_add_bwd: bad extents");
   if (da == db) return set_error(UZ_ERR_INVALID, "residual_add_bwd: da and db must be different buffers");
+  if (!dpooled) {
+    const long long npix = static_cast<long long>(N) * H * W;
+    residual_add_lin_bwd_kernel<<<ra_grid(npix * (C / 8)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(y), y_ld, npix, C, static_cast<const __nv_bfloat16*>(dy), dy_ld,
+        static_cast<__nv_bfloat16*>(da), da_ld, acc_a, static_cast<__nv_bfloat16*>(db), db_ld, acc_b, relu);
+    PW_CHECK_LAUNCH("residual_add_bwd launch");
+    return UZ_OK;
+  }
   const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   residual_add_bwd_kernel<<<ra_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(y), y_ld, N, H, W, C, static_cast<const __nv_bfloat16*>(dy), dy_ld,
