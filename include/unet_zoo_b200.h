@@ -217,6 +217,23 @@ int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, con
                         int dpooled_ld, void* da, int da_ld, int acc_a, void* db, int db_ld, int acc_b, int relu,
                         void* stream);
 
+/* Two train-mode BatchNorms, add and ReLU in one pass from the two RAW (pre-BatchNorm) tensors, NHWC bf16:
+ *   y = relu( actA(a * scaleA + shiftA) + (b * scaleB + shiftB) ),  actA = ReLU when relu_a.
+ * Replaces `x = self.batch_norm1(cat); x = x + temp; x = F.relu(x)` of Multiresblock (multiresunet.py:79-83; a = the
+ * concatenation, b = the 1x1 shortcut convolution's output) and `x = F.relu(conv3x3_bn_relu(x) + conv1x1_bn(x))` of
+ * Respath (multiresunet.py:122-126,130-133; relu_a = 1); neither normalised branch is stored.
+ * bnA / bnB: [4][C] {mean, invstd, scale, shift} of uz_bn_finalize.
+ * uz_dual_bn_add_relu_bwd: g = dy * [y > 0] (y recomputed from a and b), gA = g * [actA'], gB = g; both BatchNorm
+ *   backwards from one reduce pass and one apply pass: dA, dB (bf16; may alias a / b; accA / accB: += into the
+ *   destination), dbiasA / dbiasB (optional, overwritten): gradient of a convolution bias in front of the BatchNorm. */
+size_t uz_dual_bn_bwd_workspace_bytes(int C);
+int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
+                            const float* bnB, int N, int H, int W, int C, void* y, int y_ld, void* stream);
+int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
+                            const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld, void* dA, int dA_ld,
+                            int accA, float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB, void* workspace,
+                            size_t workspace_bytes, void* stream);
+
 /* Channels [0, K), K <= 8, of an NHWC bf16 map as fp32 NCHW logits [N][K][H][W]: the output of MultiResUnet's conv_final
  * (Conv2d 1x1 -> BatchNorm2d(affine=False), no activation; multiresunet.py:200-201,238), which runs as a conv-BN pair
  * with the classes zero-padded to 8 channels.  The way back (fp32 NCHW gradient -> NHWC bf16) is uz_nchw_to_nhwc. */

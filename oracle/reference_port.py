@@ -52,13 +52,16 @@ class Runner:
 
     # nn.BatchNorm2d defaults: eps 1e-5, momentum 0.1, affine, track_running_stats (common_layers.py:29).
     # Training: biased batch variance normalises, running_var gets the unbiased one; eval: running statistics.
-    def bn(self, x, key):
+    def bn(self, x, key, store=True):
+        """`store=False` (only meaningful in the round_storage test mode): the executor does not materialise this
+        normalised tensor - it is consumed in registers by a fused add (engine.dual_bn_add_relu) - so it is not rounded."""
         rm, rv = self.sd[key + ".running_mean"], self.sd[key + ".running_var"]
         if self.training:
             self.sd[key + ".num_batches_tracked"] += 1
         # affine=False modules (multiresunet.py:22,68,106) have no weight / bias entries
-        return self._q(F.batch_norm(self._q(x), rm, rv, self.sd.get(key + ".weight"), self.sd.get(key + ".bias"),
-                                    training=self.training, momentum=0.1, eps=1e-5))
+        y = F.batch_norm(self._q(x), rm, rv, self.sd.get(key + ".weight"), self.sd.get(key + ".bias"),
+                         training=self.training, momentum=0.1, eps=1e-5)
+        return self._q(y) if store or not self.training else y
 
     def cbr(self, x, conv_key, bn_key, stride=1):
         return F.relu(self.bn(self.conv(x, conv_key, stride=stride, padding=1), bn_key))
@@ -488,9 +491,9 @@ def multires_widths(f: int, alpha: float = 1.67):
     return int(w * 0.167), int(w * 0.333), int(w * 0.5)
 
 
-def _conv2d_bn(r: Runner, x, prefix, relu: bool, padding: int):
+def _conv2d_bn(r: Runner, x, prefix, relu: bool, padding: int, store: bool = True):
     """Conv2d_batchnorm.forward (multiresunet.py:24-30): conv1 -> BatchNorm2d(affine=False) -> ReLU or nothing."""
-    x = r.bn(r.conv(x, prefix + ".conv1", padding=padding), prefix + ".batchnorm")
+    x = r.bn(r.conv(x, prefix + ".conv1", padding=padding), prefix + ".batchnorm", store=store)
     return F.relu(x) if relu else x
 
 
@@ -498,23 +501,23 @@ def _multiresblock(r: Runner, x, prefix):
     """Multiresblock.forward (multiresunet.py:70-85).  batch_norm1 is applied TWICE: to the concatenation and, after
     the residual add + ReLU, to the sum (in train mode each application normalises with its own batch statistics
     and updates the same running buffers)."""
-    temp = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1", False, 0)
+    temp = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1", False, 0, store=False)
     a = _conv2d_bn(r, x, prefix + ".conv2d_bn_3x3", True, 1)
     b = _conv2d_bn(r, a, prefix + ".conv2d_bn_5x5", True, 1)
     c = _conv2d_bn(r, b, prefix + ".conv2d_bn_7x7", True, 1)
-    x = r.bn(torch.cat([a, b, c], dim=1), prefix + ".batch_norm1")
+    x = r.bn(torch.cat([a, b, c], dim=1), prefix + ".batch_norm1", store=False)
     x = F.relu(x + temp)
     return r.bn(x, prefix + ".batch_norm1")
 
 
 def _respath(r: Runner, x, prefix, length: int):
     """Respath.forward (multiresunet.py:121-135): `length` residual steps conv3x3-BN-ReLU + conv1x1-BN -> ReLU -> BN."""
-    shortcut = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1_initial", False, 0)
-    x = _conv2d_bn(r, x, prefix + ".conv2d_bn_3x3_initial", True, 1)
+    shortcut = _conv2d_bn(r, x, prefix + ".conv2d_bn_1x1_initial", False, 0, store=False)
+    x = _conv2d_bn(r, x, prefix + ".conv2d_bn_3x3_initial", True, 1, store=False)
     x = r.bn(F.relu(x + shortcut), prefix + ".batch_norm_initial")
     for i in range(length - 1):
-        shortcut = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.0", False, 0)
-        x = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.1", True, 1)
+        shortcut = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.0", False, 0, store=False)
+        x = _conv2d_bn(r, x, f"{prefix}.blocks.{i}.1", True, 1, store=False)
         x = r.bn(F.relu(x + shortcut), f"{prefix}.blocks.{i}.2")
     return x
 

@@ -113,6 +113,49 @@ def test_batchnorm_without_affine_into_a_slice_with_pooling(N, C, H, W, pool):
     assert rel_l2(get_grad(xa), xr.grad) < 1.5e-2
 
 
+@pytest.mark.parametrize("N,C,H,W,relu_a", [(2, 64, 16, 16, False), (2, 32, 16, 24, True), (1, 120, 8, 8, False), (3, 256, 8, 8, True)])
+def test_two_batchnorms_add_relu_in_one_pass(N, C, H, W, relu_a):
+    """relu([relu](BN(a)) + BN(b)) from the raw tensors (uz_dual_bn_add_relu_fwd/_bwd): a = a convolution output with a ReLU
+    behind its BatchNorm (Respath) or an existing activation (the concatenation of a Multiresblock), b = the 1x1 shortcut."""
+    from unet_zoo_b200 import _lib as L
+    cin = 24
+    convB, bnB = nn.Conv2d(cin, C, 1).to(DEV), nn.BatchNorm2d(C, affine=False).to(DEV)
+    convA, bnA = nn.Conv2d(cin, C, 3, padding=1).to(DEV), nn.BatchNorm2d(C, affine=False).to(DEV)
+    with torch.no_grad():
+        convA.weight.copy_(bf16r(convA.weight))
+        convB.weight.copy_(bf16r(convB.weight))
+    x = bf16r(torch.randn(N, cin, H, W, device=DEV))
+    a = bf16r(torch.randn(N, C, H, W, device=DEV) * 2.0 + 0.5)
+    params = [convA.weight, convA.bias, convB.weight, convB.bias]
+    ctx = new_ctx(params=params)
+    xa, aa = make_act(ctx, x), make_act(ctx, a)
+    A = E.bn_branch_conv(ctx, [xa], convA, bnA, relu=True) if relu_a else E.bn_branch_act(ctx, aa, bnA)
+    B = E.bn_branch_conv(ctx, [xa], convB, bnB, relu=False, mode=L.CONV1X1)
+    out = E.dual_bn_add_relu(ctx, A, B)
+    ste = lambda t: t + (bf16r(t.detach()) - t.detach())      # noqa: E731
+    xr, ar = x.clone().requires_grad_(True), a.clone().requires_grad_(True)
+    ps = [p.detach().clone().requires_grad_(True) for p in params]
+    bn = lambda t: F.batch_norm(t, None, None, None, None, training=True, eps=1e-5)      # noqa: E731
+    ya = F.relu(bn(ste(F.conv2d(xr, ps[0], ps[1], padding=1)))) if relu_a else bn(ar)
+    y = F.relu(ya + bn(ste(F.conv2d(xr, ps[2], ps[3]))))
+    torch.cuda.synchronize()
+    assert relmax(out.to_nchw(), y.detach()) < 1e-2
+    dy = bf16r(torch.randn_like(y) * 0.1)
+    (y * dy).sum().backward()
+    set_grad(out, dy)
+    run_tape(ctx)
+    ctx.join_side()
+    torch.cuda.synchronize()
+    assert rel_l2(get_grad(xa), xr.grad) < 1.5e-2
+    assert rel_l2(ctx.pgrads.view(convB.weight), ps[2].grad) < 1e-2
+    if relu_a:
+        assert rel_l2(ctx.pgrads.view(convA.weight), ps[0].grad) < 1e-2
+        assert int(bnA.num_batches_tracked) == 1
+    else:
+        assert rel_l2(get_grad(aa), ar.grad) < 1.5e-2
+    assert float(ctx.pgrads.view(convB.bias).abs().max()) < 2e-2 * float(dy.abs().sum() / C) + 1e-3
+
+
 @pytest.mark.parametrize("K", [1, 3, 8])
 def test_logits_extraction_and_its_gradient(K):
     N, H, W = 2, 16, 24

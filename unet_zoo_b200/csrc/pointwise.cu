@@ -750,6 +750,216 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BwdArgs a, c
   (void)dbias_partial;
 }
 
+// ---------------------------------------------------------------------------------------------- two BatchNorms + add + ReLU
+// y = relu( actA(a*scaleA + shiftA) + (b*scaleB + shiftB) ),  actA = ReLU when relu_a, straight from the two raw
+// (pre-BatchNorm) tensors: `x = F.relu(BN(cat) + BN(conv1x1(x)))` of Multiresblock (multiresunet.py:79-83) and
+// `F.relu(F.relu(BN(conv3x3(x))) + BN(conv1x1(x)))` of Respath (multiresunet.py:123-126,130-133).  Neither normalised
+// branch is ever stored.  Backward: g = dy * [y > 0] (recomputed from a and b), gA = g * [actA'], gB = g; one reduce pass
+// feeds both BatchNorm backward finalizes, one apply pass writes both input gradients.
+struct DualArgs {
+  const __nv_bfloat16* a;
+  const __nv_bfloat16* b;
+  int a_ld, b_ld;
+  const float* bnA;   // [4][C] mean, invstd, scale, shift
+  const float* bnB;
+  int relu_a;
+  long long npix;
+  int C, cv, ppb;
+};
+
+constexpr int kDualUnroll = 2;
+__global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, __nv_bfloat16* __restrict__ y, int y_ld) {
+  const int g = threadIdx.x % d.cv;
+  const int pl = threadIdx.x / d.cv;
+  float sa[8], ha[8], sb[8], hb[8];
+  load8f(d.bnA + 2 * d.C + g * 8, sa);
+  load8f(d.bnA + 3 * d.C + g * 8, ha);
+  load8f(d.bnB + 2 * d.C + g * 8, sb);
+  load8f(d.bnB + 3 * d.C + g * 8, hb);
+  constexpr int U = 4;
+  const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
+  for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
+    uint4 ra[U], rb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = it + u * stride;
+      if (p < d.npix) {
+        ra[u] = ldg16(d.a + p * d.a_ld + g * 8);
+        rb[u] = ldg16(d.b + p * d.b_ld + g * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = it + u * stride;
+      if (p < d.npix) {
+        float fa[8], fb[8];
+        unpack8(ra[u], fa);
+        unpack8(rb[u], fb);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float ua = fmaf(fa[j], sa[j], ha[j]);
+          if (d.relu_a) ua = fmaxf(ua, 0.f);
+          fa[j] = fmaxf(ua + fmaf(fb[j], sb[j], hb[j]), 0.f);
+        }
+        *reinterpret_cast<uint4*>(y + p * y_ld + g * 8) = pack8(fa);
+      }
+    }
+  }
+}
+
+// gradient of one pixel group w.r.t. the two normalised branches (before the BatchNorm backward proper)
+__device__ __forceinline__ void dual_grad(const DualArgs& d, const uint4& ra, const uint4& rb, const uint4& rd,
+                                          const float (&sa)[8], const float (&ha)[8], const float (&sb)[8],
+                                          const float (&hb)[8], float (&fa)[8], float (&fb)[8], float (&ga)[8],
+                                          float (&gb)[8]) {
+  unpack8(ra, fa);
+  unpack8(rb, fb);
+  unpack8(rd, gb);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float ua = fmaf(fa[j], sa[j], ha[j]);
+    const float ya = d.relu_a ? fmaxf(ua, 0.f) : ua;
+    if (!(ya + fmaf(fb[j], sb[j], hb[j]) > 0.f)) gb[j] = 0.f;
+    ga[j] = (d.relu_a && !(ua > 0.f)) ? 0.f : gb[j];
+  }
+}
+
+// partialA[block][2][C] = { sum gA, sum gA*a } ; partialB[block][2][C] = { sum gB, sum gB*b }
+__global__ void __launch_bounds__(256, 2) dual_bn_bwd_reduce_kernel(const DualArgs d, const __nv_bfloat16* __restrict__ dy,
+                                                                    int dy_ld, float* __restrict__ partialA,
+                                                                    float* __restrict__ partialB) {
+  extern __shared__ float red[];
+  const int g = threadIdx.x % d.cv;
+  const int pl = threadIdx.x / d.cv;
+  float sa[8], ha[8], sb[8], hb[8];
+  load8f(d.bnA + 2 * d.C + g * 8, sa);
+  load8f(d.bnA + 3 * d.C + g * 8, ha);
+  load8f(d.bnB + 2 * d.C + g * 8, sb);
+  load8f(d.bnB + 3 * d.C + g * 8, hb);
+  float s1[8], q1[8], s2[8], q2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1[j] = q1[j] = s2[j] = q2[j] = 0.f;
+  constexpr int U = kDualUnroll;
+  const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
+  for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
+    uint4 ra[U], rb[U], rd[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = it + u * stride;
+      if (p < d.npix) {
+        ra[u] = ldg16(d.a + p * d.a_ld + g * 8);
+        rb[u] = ldg16(d.b + p * d.b_ld + g * 8);
+        rd[u] = ldg16(dy + p * dy_ld + g * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (it + u * stride < d.npix) {
+        float fa[8], fb[8], ga[8], gb[8];
+        dual_grad(d, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          s1[j] += ga[j];
+          q1[j] = fmaf(ga[j], fa[j], q1[j]);
+          s2[j] += gb[j];
+          q2[j] = fmaf(gb[j], fb[j], q2[j]);
+        }
+      }
+    }
+  }
+  float* mine = red + static_cast<size_t>(threadIdx.x) * 32;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s1[j];
+    mine[8 + j] = q1[j];
+    mine[16 + j] = s2[j];
+    mine[24 + j] = q2[j];
+  }
+  __syncthreads();
+  if (pl == 0) {
+    for (int r = 1; r < d.ppb; ++r) {
+      const float* o = red + (static_cast<size_t>(r) * d.cv + g) * 32;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s1[j] += o[j];
+        q1[j] += o[8 + j];
+        s2[j] += o[16 + j];
+        q2[j] += o[24 + j];
+      }
+    }
+    float* da = partialA + static_cast<size_t>(blockIdx.x) * 2 * d.C;
+    float* db = partialB + static_cast<size_t>(blockIdx.x) * 2 * d.C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      da[g * 8 + j] = s1[j];
+      da[d.C + g * 8 + j] = q1[j];
+      db[g * 8 + j] = s2[j];
+      db[d.C + g * 8 + j] = q2[j];
+    }
+  }
+}
+
+// dA = scaleA*gA + coefA[0] + coefA[1]*a ; dB likewise (coef from bn_bwd_finalize_kernel); dA may alias a, dB may alias b
+__global__ void __launch_bounds__(256, 2) dual_bn_bwd_apply_kernel(const DualArgs d, const __nv_bfloat16* __restrict__ dy,
+                                                                   int dy_ld, const float* __restrict__ coefA,
+                                                                   const float* __restrict__ coefB,
+                                                                   __nv_bfloat16* __restrict__ dA, int dA_ld, int accA,
+                                                                   __nv_bfloat16* __restrict__ dB, int dB_ld, int accB) {
+  const int g = threadIdx.x % d.cv;
+  const int pl = threadIdx.x / d.cv;
+  float sa[8], ha[8], sb[8], hb[8];
+  load8f(d.bnA + 2 * d.C + g * 8, sa);
+  load8f(d.bnA + 3 * d.C + g * 8, ha);
+  load8f(d.bnB + 2 * d.C + g * 8, sb);
+  load8f(d.bnB + 3 * d.C + g * 8, hb);
+  constexpr int U = kDualUnroll;
+  const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
+  for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
+    uint4 ra[U], rb[U], rd[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = it + u * stride;
+      if (p < d.npix) {
+        ra[u] = ldg16(d.a + p * d.a_ld + g * 8);
+        rb[u] = ldg16(d.b + p * d.b_ld + g * 8);
+        rd[u] = ldg16(dy + p * dy_ld + g * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = it + u * stride;
+      if (p < d.npix) {
+        float fa[8], fb[8], ga[8], gb[8], c0[8], c1[8];
+        dual_grad(d, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
+        load8f(coefA + g * 8, c0);
+        load8f(coefA + d.C + g * 8, c1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ga[j] = fmaf(sa[j], ga[j], fmaf(c1[j], fa[j], c0[j]));
+        load8f(coefB + g * 8, c0);
+        load8f(coefB + d.C + g * 8, c1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gb[j] = fmaf(sb[j], gb[j], fmaf(c1[j], fb[j], c0[j]));
+        __nv_bfloat16* pa = dA + p * dA_ld + g * 8;
+        __nv_bfloat16* pb = dB + p * dB_ld + g * 8;
+        if (accA) {
+          float old[8];
+          unpack8(*reinterpret_cast<const uint4*>(pa), old);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ga[j] += old[j];
+        }
+        if (accB) {
+          float old[8];
+          unpack8(*reinterpret_cast<const uint4*>(pb), old);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) gb[j] += old[j];
+        }
+        *reinterpret_cast<uint4*>(pa) = pack8(ga);
+        *reinterpret_cast<uint4*>(pb) = pack8(gb);
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- column sums
 // partial[block][C] = per-channel sum over this block's pixels
 __global__ void colsum_kernel(const __nv_bfloat16* __restrict__ x, int ld, long long npix, int C, int cv, int ppb,
@@ -1045,6 +1255,82 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
                                                               dz_acc);
   UZ_CHECK_LAUNCH("bn_bwd_apply launch");
   (void)dbias_partial;
+  return UZ_OK;
+}
+
+extern "C" size_t uz_dual_bn_bwd_workspace_bytes(int C) {
+  const int rows = uz_reduce_rows();
+  if (rows < 0) return 0;
+  return sizeof(float) * static_cast<size_t>(rows) * 4 * C + sizeof(float) * 4 * C;
+}
+
+static int dual_args(DualArgs& d, Geo& g, const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
+                     const float* bnB, int N, int H, int W, int C, int blocks_per_sm) {
+  int rc = check_act("dual_bn(a)", a, C, a_ld);
+  if (rc || (rc = check_act("dual_bn(b)", b, C, b_ld))) return rc;
+  if (!bnA || !bnB || N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "dual_bn: missing statistics or bad extents");
+  d.a = static_cast<const __nv_bfloat16*>(a);
+  d.b = static_cast<const __nv_bfloat16*>(b);
+  d.a_ld = a_ld;
+  d.b_ld = b_ld;
+  d.bnA = bnA;
+  d.bnB = bnB;
+  d.relu_a = relu_a;
+  d.npix = static_cast<long long>(N) * H * W;
+  d.C = C;
+  g = make_geo(C, d.npix, blocks_per_sm);
+  d.cv = g.cv;
+  d.ppb = g.ppb;
+  return UZ_OK;
+}
+
+extern "C" int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
+                                       const float* bnB, int N, int H, int W, int C, void* y, int y_ld, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  DualArgs d;
+  Geo g;
+  int rc = dual_args(d, g, a, a_ld, bnA, relu_a, b, b_ld, bnB, N, H, W, C, 4);
+  if (rc || (rc = check_act("dual_bn(y)", y, C, y_ld))) return rc;
+  dual_bn_fwd_kernel<<<g.grid, g.block, 0, static_cast<cudaStream_t>(stream)>>>(d, static_cast<__nv_bfloat16*>(y), y_ld);
+  UZ_CHECK_LAUNCH("dual_bn_fwd launch");
+  return UZ_OK;
+}
+
+extern "C" int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
+                                       const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld, void* dA,
+                                       int dA_ld, int accA, float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  DualArgs d;
+  Geo g;
+  int rc = dual_args(d, g, a, a_ld, bnA, relu_a, b, b_ld, bnB, N, H, W, C, 4);
+  if (rc || (rc = check_act("dual_bn_bwd(dy)", dy, C, dy_ld)) || (rc = check_act("dual_bn_bwd(dA)", dA, C, dA_ld)) ||
+      (rc = check_act("dual_bn_bwd(dB)", dB, C, dB_ld)))
+    return rc;
+  if (workspace_bytes < uz_dual_bn_bwd_workspace_bytes(C) || !a16(workspace))
+    return set_error(UZ_ERR_WORKSPACE, "dual_bn_bwd: workspace too small (%zu < %zu)", workspace_bytes,
+                     uz_dual_bn_bwd_workspace_bytes(C));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = static_cast<size_t>(g.block) * 32 * sizeof(float);
+  const long long need = (d.npix + g.ppb - 1) / g.ppb;
+  const int grid_r = resident_grid(dual_bn_bwd_reduce_kernel, g.block, smem, need, 4);
+  const int grid_a = resident_grid(dual_bn_bwd_apply_kernel, g.block, 0, need, 4);
+  const size_t max_rows = static_cast<size_t>(uz_reduce_rows());
+  float* partialA = static_cast<float*>(workspace);
+  float* partialB = partialA + max_rows * 2 * C;
+  float* coefA = partialB + max_rows * 2 * C;
+  float* coefB = coefA + 2 * C;
+  const __nv_bfloat16* g_dy = static_cast<const __nv_bfloat16*>(dy);
+  dual_bn_bwd_reduce_kernel<<<grid_r, g.block, smem, st>>>(d, g_dy, dy_ld, partialA, partialB);
+  UZ_CHECK_LAUNCH("dual_bn_bwd_reduce launch");
+  const double count = static_cast<double>(d.npix);
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partialA, grid_r, C, count, bnA, nullptr, nullptr, 0, coefA, 1, dbiasA);
+  UZ_CHECK_LAUNCH("dual_bn_bwd finalize A launch");
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partialB, grid_r, C, count, bnB, nullptr, nullptr, 0, coefB, 1, dbiasB);
+  UZ_CHECK_LAUNCH("dual_bn_bwd finalize B launch");
+  dual_bn_bwd_apply_kernel<<<grid_a, g.block, 0, st>>>(d, g_dy, dy_ld, coefA, coefB, static_cast<__nv_bfloat16*>(dA), dA_ld,
+                                                       accA, static_cast<__nv_bfloat16*>(dB), dB_ld, accB);
+  UZ_CHECK_LAUNCH("dual_bn_bwd_apply launch");
   return UZ_OK;
 }
 

@@ -1245,6 +1245,84 @@ def residual_add(ctx: Ctx, a: Act, b: Act, out: Optional[Act] = None, pooled: Op
     return out
 
 
+class BnBranch:
+    """One operand of :func:`dual_bn_add_relu`: a raw (pre-BatchNorm) tensor, its batch statistics, whether a ReLU follows
+    the BatchNorm, and how its gradient travels on (into a convolution's backward, or into the tensor's gradient buffer)."""
+    __slots__ = ("z", "bnbuf", "relu", "conv", "xs", "mode", "need_dx", "cin_total")
+
+
+def bn_branch_conv(ctx: Ctx, xs: Sequence[Act], conv, bn, relu: bool, mode: int = L.CONV3X3, need_dx: bool = True) -> BnBranch:
+    """Convolution + train-mode BatchNorm statistics, the normalised tensor left to the consumer (no apply pass)."""
+    a0 = xs[0]
+    br = BnBranch()
+    br.conv, br.xs, br.mode, br.need_dx, br.relu = conv, list(xs), mode, need_dx, relu
+    br.cin_total = sum(a.C for a in xs)
+    cout = conv.out_channels
+    br.z = ctx.new_act(a0.N, a0.H, a0.W, cout)
+    wp = ctx.pack(_weight_for(conv, br.cin_total), "conv_fwd")
+    stats = ctx.f32(ctx.stats_rows, 2, cout)
+    ctx.conv(mode, xs, wp, cout, conv.bias, br.z.ptr, br.z.ld, a0.H, a0.W, stats, L.FLAG_STATS)
+    br.bnbuf = ctx.f32(4, cout)
+    ctx.bn_finalize(stats, ctx.stats_rows, cout, a0.npix, bn, br.bnbuf)
+    return br
+
+
+def bn_branch_act(ctx: Ctx, x: Act, bn) -> BnBranch:
+    """Train-mode BatchNorm statistics of an existing activation (no ReLU behind it), normalised tensor left to the consumer."""
+    br = BnBranch()
+    br.conv, br.xs, br.mode, br.need_dx, br.relu, br.cin_total = None, None, 0, True, False, 0
+    br.z = x
+    stats = ctx.f32(ctx.reduce_rows, 2, x.C)
+    L.check(ctx.lib.uz_bn_stats(x.ptr, x.ld, x.npix, x.C, stats.data_ptr(), ctx.stream), "uz_bn_stats")
+    ctx.launches += 1
+    br.bnbuf = ctx.f32(4, x.C)
+    ctx.bn_finalize(stats, ctx.reduce_rows, x.C, x.npix, bn, br.bnbuf)
+    return br
+
+
+def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = None) -> Act:
+    """out = ReLU([ReLU](BN(A.z)) + BN(B.z)) in one pass over the two raw tensors (uz_dual_bn_add_relu_fwd / _bwd): the
+    tails of Multiresblock and Respath (multiresunet.py:79-83,122-126).  Training mode only (batch statistics)."""
+    if ctx.fp32 or not ctx.training:
+        raise RuntimeError("unet_zoo_b200: dual_bn_add_relu is a train-mode bf16 operator")
+    a, b = A.z, B.z
+    if (a.N, a.H, a.W, a.C) != (b.N, b.H, b.W, b.C) or B.relu:
+        raise ValueError("dual_bn_add_relu: operands must have one shape and only the first may carry a ReLU")
+    if out is None:
+        out = ctx.new_act(a.N, a.H, a.W, a.C)
+    with _Timed("bn_apply", 2.0 * a.npix * a.C * 3):
+        L.check(ctx.lib.uz_dual_bn_add_relu_fwd(a.ptr, a.ld, A.bnbuf.data_ptr(), int(A.relu), b.ptr, b.ld, B.bnbuf.data_ptr(),
+                                                a.N, a.H, a.W, a.C, out.ptr, out.ld, ctx.stream), "uz_dual_bn_add_relu_fwd")
+    ctx.launches += 1
+    if ctx.record:
+        def backward(c: Ctx):
+            if not out.has_grad():
+                raise RuntimeError("unet_zoo_b200: dual_bn_add_relu output has no gradient")
+            dst = []
+            for br in (A, B):
+                if br.conv is not None:          # dz overwrites z in place, then the convolution's backward consumes it
+                    dst.append((br.z.ptr, br.z.ld, 0, c.pgrad(br.conv.bias) if br.conv.bias is not None else None))
+                else:
+                    runs = br.z.grad_writes()
+                    if len(runs) != 1:
+                        raise NotImplementedError("dual_bn_add_relu: operand gradient partly written by another consumer")
+                    dst.append((br.z.gptr(), br.z.ld, int(runs[0][2]), None))
+            ws = c.workspace(c.lib.uz_dual_bn_bwd_workspace_bytes(a.C))
+            with _Timed("bn_bwd", 2.0 * a.npix * a.C * 8):
+                L.check(c.lib.uz_dual_bn_add_relu_bwd(a.ptr, a.ld, A.bnbuf.data_ptr(), int(A.relu), b.ptr, b.ld,
+                                                      B.bnbuf.data_ptr(), a.N, a.H, a.W, a.C, out.gptr(), out.ld,
+                                                      dst[0][0], dst[0][1], dst[0][2], _ptr(dst[0][3]),
+                                                      dst[1][0], dst[1][1], dst[1][2], _ptr(dst[1][3]),
+                                                      ws.data_ptr(), ws.numel(), c.stream), "uz_dual_bn_add_relu_bwd")
+            c.launches += 4
+            for br in (A, B):
+                if br.conv is not None:
+                    c.pready(br.conv.bias)
+                    _conv_backward(c, br.xs, br.conv, br.z, br.mode, False, br.cin_total, br.need_dx)
+        ctx.tape.append(backward)
+    return out
+
+
 def nhwc_logits(ctx: Ctx, y: Act, K: int) -> torch.Tensor:
     """Channels [0, K) of `y` as the model's fp32 NCHW output: MultiResUnet returns the BatchNorm2d(affine=False) of its
     1x1 conv_final directly (multiresunet.py:238-240); that conv-BN pair runs with the classes padded to 8 channels.

@@ -17,6 +17,8 @@ shortcut conv-BN, BatchNorm of the concatenation, one add+ReLU pass, BatchNorm o
 MaxPool2d).  A Respath step: two conv-BN, one add+ReLU pass, BatchNorm.  Inputs: multiples of 16 (the reference's
 decoder concatenates a 2 * floor(s / 2) tensor with an s tensor, so it fails on other sizes too); bf16 mode only.
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -25,6 +27,11 @@ from .. import engine as E
 from ._padded import Lay, Shadow, ceil8
 from ._runtime import HotPathModel
 from .blocks import _Container
+
+
+# UZ_MULTIRES_UNFUSED=1: the training graph with every normalised branch materialised (conv-BN[-ReLU], add+ReLU as
+# separate passes) - the A/B arm of the measurements in DESIGN.md; eval mode always runs that way (BatchNorm folded).
+_UNFUSED = os.environ.get("UZ_MULTIRES_UNFUSED") == "1"
 
 
 class Conv2d_batchnorm(_Container):                       # multiresunet.py:7-30
@@ -176,6 +183,13 @@ class MultiResUnet(HotPathModel):                         # multiresunet.py:137-
         return E.conv_bn_act(ctx, xs, sh[id(m.conv1)], sh[id(m.batchnorm)], out=out, relu=m.activation == "relu",
                              mode=mode, need_dx=need_dx)
 
+    def _branch(self, ctx, xs, m: Conv2d_batchnorm, need_dx=True):
+        """Convolution + batch statistics of a unit whose normalised output only feeds an add (engine.dual_bn_add_relu)."""
+        sh = self._uz_shadow.of
+        mode = L.CONV3X3 if m.conv1.kernel_size[0] == 3 else L.CONV1X1
+        return E.bn_branch_conv(ctx, xs, sh[id(m.conv1)], sh[id(m.batchnorm)], relu=m.activation == "relu", mode=mode,
+                                need_dx=need_dx)
+
     def _block(self, ctx, blk: Multiresblock, xs, out=None, pooled=None, need_dx=True):
         """Multiresblock.forward (multiresunet.py:70-85)."""
         a0 = xs[0]
@@ -183,21 +197,31 @@ class MultiResUnet(HotPathModel):                         # multiresunet.py:137-
         p3, p5, p7 = (ceil8(w) for w in _widths(blk.corresponding_unet_filters, blk.alpha))
         bn1 = self._uz_shadow.of[id(blk.batch_norm1)]
         cat = ctx.new_buf(N, H, W, p3 + p5 + p7)                   # torch.cat([a, b, c]) with one padded segment each
-        temp = self._unit(ctx, xs, blk.conv2d_bn_1x1, need_dx=need_dx)
+        fused = ctx.training and not _UNFUSED
+        if fused:     # the shortcut's normalised tensor is never stored: relu(BN(cat) + BN(conv1x1(x))) in one pass
+            temp = self._branch(ctx, xs, blk.conv2d_bn_1x1, need_dx=need_dx)
+        else:
+            temp = self._unit(ctx, xs, blk.conv2d_bn_1x1, need_dx=need_dx)
         a = self._unit(ctx, xs, blk.conv2d_bn_3x3, out=E.Act(cat, 0, p3), need_dx=need_dx)
         b = self._unit(ctx, [a], blk.conv2d_bn_5x5, out=E.Act(cat, p3, p5))
         self._unit(ctx, [b], blk.conv2d_bn_7x7, out=E.Act(cat, p3 + p5, p7))
-        x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
-        s = E.residual_add(ctx, x1, temp, relu=True)
+        if fused:
+            s = E.dual_bn_add_relu(ctx, E.bn_branch_act(ctx, E.Act(cat), bn1), temp)
+        else:
+            x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
+            s = E.residual_add(ctx, x1, temp, relu=True)
         return E.bn_act(ctx, s, bn1, relu=False, out=out, pooled=pooled)
 
     def _respath(self, ctx, rp: Respath, x, out):
         """Respath.forward (multiresunet.py:121-135); the last BatchNorm writes into the decoder's concat buffer."""
         steps = rp.steps()
         for i, (c1, c3, bn) in enumerate(steps):
-            shortcut = self._unit(ctx, [x], c1)
-            y = self._unit(ctx, [x], c3)
-            s = E.residual_add(ctx, y, shortcut, relu=True)
+            if ctx.training and not _UNFUSED:
+                s = E.dual_bn_add_relu(ctx, self._branch(ctx, [x], c3), self._branch(ctx, [x], c1))
+            else:
+                shortcut = self._unit(ctx, [x], c1)
+                y = self._unit(ctx, [x], c3)
+                s = E.residual_add(ctx, y, shortcut, relu=True)
             x = E.bn_act(ctx, s, self._uz_shadow.of[id(bn)], relu=False, out=out if i == len(steps) - 1 else None)
         return x
 
