@@ -222,13 +222,14 @@ int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, con
  * Replaces `x = self.batch_norm1(cat); x = x + temp; x = F.relu(x)` of Multiresblock (multiresunet.py:79-83; a = the
  * concatenation, b = the 1x1 shortcut convolution's output) and `x = F.relu(conv3x3_bn_relu(x) + conv1x1_bn(x))` of
  * Respath (multiresunet.py:122-126,130-133; relu_a = 1); neither normalised branch is stored.
- * bnA / bnB: [4][C] {mean, invstd, scale, shift} of uz_bn_finalize.
+ * bnA / bnB: [4][C] {mean, invstd, scale, shift} of uz_bn_finalize.  y_stats (optional): [uz_reduce_rows()][2][C] partial
+ * sums / sums of squares of the stored y, i.e. what uz_bn_stats(y) would produce - for the BatchNorm that follows.
  * uz_dual_bn_add_relu_bwd: g = dy * [y > 0] (y recomputed from a and b), gA = g * [actA'], gB = g; both BatchNorm
  *   backwards from one reduce pass and one apply pass: dA, dB (bf16; may alias a / b; accA / accB: += into the
  *   destination), dbiasA / dbiasB (optional, overwritten): gradient of a convolution bias in front of the BatchNorm. */
 size_t uz_dual_bn_bwd_workspace_bytes(int C);
 int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
-                            const float* bnB, int N, int H, int W, int C, void* y, int y_ld, void* stream);
+                            const float* bnB, int N, int H, int W, int C, void* y, int y_ld, float* y_stats, void* stream);
 int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
                             const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld, void* dA, int dA_ld,
                             int accA, float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB, void* workspace,

@@ -131,7 +131,8 @@ def test_two_batchnorms_add_relu_in_one_pass(N, C, H, W, relu_a):
     xa, aa = make_act(ctx, x), make_act(ctx, a)
     A = E.bn_branch_conv(ctx, [xa], convA, bnA, relu=True) if relu_a else E.bn_branch_act(ctx, aa, bnA)
     B = E.bn_branch_conv(ctx, [xa], convB, bnB, relu=False, mode=L.CONV1X1)
-    out = E.dual_bn_add_relu(ctx, A, B)
+    stats = ctx.f32(ctx.reduce_rows, 2, C)
+    out = E.dual_bn_add_relu(ctx, A, B, stats=stats)
     ste = lambda t: t + (bf16r(t.detach()) - t.detach())      # noqa: E731
     xr, ar = x.clone().requires_grad_(True), a.clone().requires_grad_(True)
     ps = [p.detach().clone().requires_grad_(True) for p in params]
@@ -140,6 +141,9 @@ def test_two_batchnorms_add_relu_in_one_pass(N, C, H, W, relu_a):
     y = F.relu(ya + bn(ste(F.conv2d(xr, ps[2], ps[3]))))
     torch.cuda.synchronize()
     assert relmax(out.to_nchw(), y.detach()) < 1e-2
+    stored = out.to_nchw().double()      # the by-product statistics describe the tensor as stored
+    assert relmax(stats[:, 0].double().sum(0), stored.sum((0, 2, 3))) < 1e-5
+    assert relmax(stats[:, 1].double().sum(0), (stored * stored).sum((0, 2, 3))) < 1e-5
     dy = bf16r(torch.randn_like(y) * 0.1)
     (y * dy).sum().backward()
     set_grad(out, dy)

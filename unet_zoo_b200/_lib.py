@@ -68,7 +68,7 @@ _PROTOS = {
     "uz_residual_add_fwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int, c_int, _P]),
     "uz_nhwc_to_nchw_f32": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P]),
     "uz_dual_bn_bwd_workspace_bytes": (c_size_t, [c_int]),
-    "uz_dual_bn_add_relu_fwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P]),
+    "uz_dual_bn_add_relu_fwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, _P]),
     "uz_dual_bn_add_relu_bwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int,
                                         c_int, _P, _P, c_int, c_int, _P, _P, c_size_t, _P]),
     "uz_side_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int]),

@@ -768,7 +768,11 @@ struct DualArgs {
 };
 
 constexpr int kDualUnroll = 2;
-__global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, __nv_bfloat16* __restrict__ y, int y_ld) {
+// `partial` (optional): [gridDim.x][2][C] per-channel sum / sum of squares of the STORED (bf16) output - the statistics of
+// the BatchNorm that follows (multiresunet.py:84,127,134) without a pass of their own.
+__global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, __nv_bfloat16* __restrict__ y, int y_ld,
+                                                             float* __restrict__ partial) {
+  extern __shared__ float red[];
   const int g = threadIdx.x % d.cv;
   const int pl = threadIdx.x / d.cv;
   float sa[8], ha[8], sb[8], hb[8];
@@ -776,6 +780,9 @@ __global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, _
   load8f(d.bnA + 3 * d.C + g * 8, ha);
   load8f(d.bnB + 2 * d.C + g * 8, sb);
   load8f(d.bnB + 3 * d.C + g * 8, hb);
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   constexpr int U = 4;
   const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
   for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
@@ -801,8 +808,41 @@ __global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, _
           if (d.relu_a) ua = fmaxf(ua, 0.f);
           fa[j] = fmaxf(ua + fmaf(fb[j], sb[j], hb[j]), 0.f);
         }
-        *reinterpret_cast<uint4*>(y + p * y_ld + g * 8) = pack8(fa);
+        const uint4 o = pack8(fa);
+        *reinterpret_cast<uint4*>(y + p * y_ld + g * 8) = o;
+        if (partial) {
+          unpack8(o, fa);   // statistics of the values as stored
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s[j] += fa[j];
+            q[j] = fmaf(fa[j], fa[j], q[j]);
+          }
+        }
       }
+    }
+  }
+  if (!partial) return;
+  float* mine = red + static_cast<size_t>(threadIdx.x) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  if (pl == 0) {
+    for (int r = 1; r < d.ppb; ++r) {
+      const float* o = red + (static_cast<size_t>(r) * d.cv + g) * 16;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += o[j];
+        q[j] += o[8 + j];
+      }
+    }
+    float* dst = partial + static_cast<size_t>(blockIdx.x) * 2 * d.C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      dst[g * 8 + j] = s[j];
+      dst[d.C + g * 8 + j] = q[j];
     }
   }
 }
@@ -1285,13 +1325,20 @@ static int dual_args(DualArgs& d, Geo& g, const void* a, int a_ld, const float* 
 }
 
 extern "C" int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
-                                       const float* bnB, int N, int H, int W, int C, void* y, int y_ld, void* stream) {
+                                       const float* bnB, int N, int H, int W, int C, void* y, int y_ld, float* y_stats,
+                                       void* stream) {
   UZ_REQUIRE_DEVICE();
   DualArgs d;
   Geo g;
-  int rc = dual_args(d, g, a, a_ld, bnA, relu_a, b, b_ld, bnB, N, H, W, C, 4);
+  int rc = dual_args(d, g, a, a_ld, bnA, relu_a, b, b_ld, bnB, N, H, W, C, 4);   // grid <= uz_reduce_rows()
   if (rc || (rc = check_act("dual_bn(y)", y, C, y_ld))) return rc;
-  dual_bn_fwd_kernel<<<g.grid, g.block, 0, static_cast<cudaStream_t>(stream)>>>(d, static_cast<__nv_bfloat16*>(y), y_ld);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (y_stats) {   // every one of the uz_reduce_rows() rows is defined: the consumer (uz_bn_finalize) takes a fixed count
+    cudaError_t e = cudaMemsetAsync(y_stats, 0, sizeof(float) * 2 * C * uz_reduce_rows(), st);
+    if (e != cudaSuccess) return cuda_error(e, "dual_bn_fwd memset");
+  }
+  dual_bn_fwd_kernel<<<g.grid, g.block, y_stats ? g.block * 16 * sizeof(float) : 0, st>>>(
+      d, static_cast<__nv_bfloat16*>(y), y_ld, y_stats);
   UZ_CHECK_LAUNCH("dual_bn_fwd launch");
   return UZ_OK;
 }

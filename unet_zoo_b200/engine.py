@@ -871,7 +871,8 @@ def conv_stats(ctx: Ctx, xs: Sequence[Act], conv, bn, mode: int = L.CONV3X3) -> 
     return z, bnbuf
 
 
-def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True, out: Optional[Act] = None, pooled: Optional[Act] = None) -> Act:
+def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True, out: Optional[Act] = None, pooled: Optional[Act] = None,
+           stats: Optional[torch.Tensor] = None) -> Act:
     """[ReLU](BatchNorm2d(x)) on an existing activation - the pre-activation half of ResidualConv
     (common_layers.py:185-186,189-190) and the stand-alone BatchNorm2d(affine=False) layers of MultiResUnet
     (multiresunet.py:79,84,127,134); `pooled` receives MaxPool2d(2, 2) of the result (multiresunet.py:206).
@@ -888,9 +889,10 @@ def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True, out: Optional[Act] = None, p
         ctx.bn_apply(x, aff[2].data_ptr(), aff[3].data_ptr(), relu, out, pooled)
         return out
     rows = ctx.reduce_rows
-    stats = ctx.f32(rows, 2, x.C)
-    L.check(ctx.lib.uz_bn_stats(x.ptr, x.ld, x.npix, x.C, stats.data_ptr(), ctx.stream), "uz_bn_stats")
-    ctx.launches += 1
+    if stats is None:       # else: the producer of x already left its partial sums (dual_bn_add_relu)
+        stats = ctx.f32(rows, 2, x.C)
+        L.check(ctx.lib.uz_bn_stats(x.ptr, x.ld, x.npix, x.C, stats.data_ptr(), ctx.stream), "uz_bn_stats")
+        ctx.launches += 1
     bnbuf = ctx.f32(4, x.C)
     ctx.bn_finalize(stats, rows, x.C, x.npix, bn, bnbuf)
     ctx.bn_apply(x, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), relu, out, pooled)
@@ -1280,9 +1282,12 @@ def bn_branch_act(ctx: Ctx, x: Act, bn) -> BnBranch:
     return br
 
 
-def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = None) -> Act:
+def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = None,
+                     stats: Optional[torch.Tensor] = None) -> Act:
     """out = ReLU([ReLU](BN(A.z)) + BN(B.z)) in one pass over the two raw tensors (uz_dual_bn_add_relu_fwd / _bwd): the
-    tails of Multiresblock and Respath (multiresunet.py:79-83,122-126).  Training mode only (batch statistics)."""
+    tails of Multiresblock and Respath (multiresunet.py:79-83,122-126).  Training mode only (batch statistics).
+    `stats` ([reduce_rows][2][C] fp32): receives the sum / sum-of-squares partials of `out` for the BatchNorm that follows
+    (hand it to bn_act(stats=...))."""
     if ctx.fp32 or not ctx.training:
         raise RuntimeError("unet_zoo_b200: dual_bn_add_relu is a train-mode bf16 operator")
     a, b = A.z, B.z
@@ -1292,7 +1297,8 @@ def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = No
         out = ctx.new_act(a.N, a.H, a.W, a.C)
     with _Timed("bn_apply", 2.0 * a.npix * a.C * 3):
         L.check(ctx.lib.uz_dual_bn_add_relu_fwd(a.ptr, a.ld, A.bnbuf.data_ptr(), int(A.relu), b.ptr, b.ld, B.bnbuf.data_ptr(),
-                                                a.N, a.H, a.W, a.C, out.ptr, out.ld, ctx.stream), "uz_dual_bn_add_relu_fwd")
+                                                a.N, a.H, a.W, a.C, out.ptr, out.ld, _ptr(stats), ctx.stream),
+                "uz_dual_bn_add_relu_fwd")
     ctx.launches += 1
     if ctx.record:
         def backward(c: Ctx):
