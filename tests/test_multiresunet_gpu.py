@@ -469,3 +469,36 @@ def test_three_classes_non_square_and_graph_replay():
     grads = {k: p.grad.detach().cpu() for k, p in model.named_parameters()}
     for k in ("conv_final.conv1.weight", "multiresblock9.conv2d_bn_7x7.conv1.weight", "upsample9.weight", "upsample9.bias"):
         assert float((grads[k] - ref_grads[k]).norm() / ref_grads[k].norm().clamp_min(1e-20)) < 1.0, k
+
+
+def test_other_base_width_and_train_eval_transitions(monkeypatch):
+    """filters = 16 (branch widths 4 / 8 / 13 ... 71 / 142 / 213: other paddings, same code), two training steps with an
+    in-place parameter update between them, then eval: the padded operands follow the parameters, the inference memo is
+    dropped on train() and rebuilt on the next eval forward."""
+    model = seeded_model("multiresunet", filters=16)
+    assert model.multiresblock1.conv2d_bn_7x7.conv1.out_channels == 13 and model.in_filters5 == 426
+    x, mask = O.synthetic_batch(2, 3, 64, 64)
+    sd = copy.deepcopy(model.state_dict())
+    monkeypatch.setattr(O.Runner, "round_storage", torch.bfloat16)
+    out1 = _train_step(model, x, mask, O.gaussian_projection_loss)
+    ref1, _, _ = O.train_step("multiresunet", sd, x, mask, loss_fn=O.gaussian_projection_loss)
+    assert rel_err(out1, ref1.detach()) < MATCHED_TOL
+    gen = torch.Generator().manual_seed(9)
+    with torch.no_grad():                                      # an "optimizer step" that bypasses the version counters
+        for k, p in model.named_parameters():
+            step = torch.randn(p.shape, generator=gen) * 0.3 * float(p.detach().std() if p.numel() > 1 else 1.0)
+            p.data.add_(step.cuda())
+            sd[k].add_(step)
+            p.grad = None
+    out2 = _train_step(model, x, mask, O.gaussian_projection_loss)
+    ref2, _, _ = O.train_step("multiresunet", sd, x, mask, loss_fn=O.gaussian_projection_loss)
+    assert rel_err(out2, ref2.detach()) < MATCHED_TOL
+    monkeypatch.setattr(O.Runner, "round_storage", None)
+    model.eval()
+    with torch.no_grad():
+        oe = model(x.cuda()).cpu()
+        ref = O.multiresunet_forward({k: v.detach().cpu().clone() for k, v in model.state_dict().items()}, x, False)
+    assert rel_err(oe, ref) < EVAL_TOL
+    for k, v in sd.items():
+        if "num_batches" in k:
+            assert int(model.state_dict()[k]) == int(v)
