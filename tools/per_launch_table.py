@@ -13,8 +13,8 @@ UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "nsecond": 1e-6, 
         "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # kernel-name classes per tag kind: how many launches of which kernels one tagged call issues, in order
-CLASS = {"igemm_fwd": ("igemm_fwd",), "igemm_wgrad": ("igemm_wgrad",), "bn_apply": ("bn_apply", "bn_head_fwd"),
-         "bn_bwd": ("bn_bwd_reduce", "bn_head_bwd_reduce")}
+CLASS = {"igemm_fwd": ("igemm_fwd",), "igemm_wgrad": ("igemm_wgrad",), "bn_apply": ("bn_apply", "bn_head_fwd", "dual_bn_fwd"),
+         "bn_bwd": ("bn_bwd_reduce", "bn_head_bwd_reduce")}      # "dual_bn_bwd_reduce" contains "bn_bwd_reduce"
 
 
 def main():
@@ -45,6 +45,9 @@ def main():
     marker = "stem_im2col"
     idx = [i for i, r in enumerate(rows) if marker in r["name"]]
     step = rows[idx[-1]:] if idx else rows
+    if not idx:      # multiresunet: no im2col stem; uz_nchw_to_nhwc opens the forward and (output gradient) the backward
+        idx = [i for i, r in enumerate(rows) if "nchw_to_nhwc_kernel" in r["name"]]
+        step = rows[idx[-2]:] if len(idx) >= 2 else rows
     total = sum(r["ms"] for r in step)
     print(f"# {meta['model']} batch {meta['batch']} {meta['size']}^2 {'eval forward' if meta['eval'] else 'training step'}: "
           f"per-launch table (ncu, serialised, cold cache: read ratios and shares, not absolute times)\n")
