@@ -68,3 +68,42 @@ def test_bucketed_allreduce_world2():
         same_weights, averaged, nb, launched, keys = out[r]
         assert same_weights and averaged and launched and keys
         assert nb >= 2
+
+
+def _padded_worker(rank, world, port, out):
+    """multiresunet's zero-padded stand-ins under data parallelism: the padded gradients are gathered into the flat
+    buffer at the end of backward, and only then do the buckets see their parameters complete and all-reduce."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import unet_zoo_b200
+    from unet_zoo_b200.models._padded import Shadow
+    torch.manual_seed(7)
+    model = unet_zoo_b200.create_model("multiresunet", filters=8)
+    dp = P.DataParallel(model, bucket_mb=0.05)
+    params = list(model.parameters())
+    sh = Shadow(model, model._specs(), torch.device("cpu"))
+    sh.refresh(True)
+    pg = model._uz_make_param_grads(params, torch.device("cpu"))
+    sh.begin_backward(pg)
+    early = 0
+    for (t, _off) in sh.tensors:
+        pg.view(t).copy_(t.detach() * float(rank + 1))   # rank-dependent "gradient" of every padded operand
+        pg.ready(t)                                      # reported by the tape: must not complete any bucket
+        early += sum(pg.launched)
+    sh.end_backward(pg, params)                          # gather + report every parameter: buckets launch now
+    launched = all(pg.launched)
+    pg.finish()
+    ok = all(torch.allclose(pg.view(p), p.detach() * 1.5) for p in params)
+    out[rank] = (early == 0, launched, ok, len(pg.buckets), type(dp.module).__name__)
+    dist.destroy_process_group()
+
+
+def test_padded_operands_with_bucketed_allreduce_world2():
+    mgr = mp.Manager()
+    out = mgr.dict()
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_padded_worker, args=(2, port, out), nprocs=2, join=True)
+    for r in range(2):
+        nothing_early, launched, averaged, nb, name = out[r]
+        assert nothing_early and launched and averaged and nb >= 2 and name == "MultiResUnet"
