@@ -226,14 +226,24 @@ int uz_residual_add_bwd(const void* y, int y_ld, int N, int H, int W, int C, con
  * sums / sums of squares of the stored y, i.e. what uz_bn_stats(y) would produce - for the BatchNorm that follows.
  * uz_dual_bn_add_relu_bwd: g = dy * [y > 0] (y recomputed from a and b), gA = g * [actA'], gB = g; both BatchNorm
  *   backwards from one reduce pass and one apply pass: dA, dB (bf16; may alias a / b; accA / accB: += into the
- *   destination), dbiasA / dbiasB (optional, overwritten): gradient of a convolution bias in front of the BatchNorm. */
+ *   destination), dbiasA / dbiasB (optional, overwritten): gradient of a convolution bias in front of the BatchNorm.
+ *   bn_outer / coef_outer (optional, together): y is followed by out = BatchNorm_o(y) (multiresunet.py:84,127,134); then
+ *   `dy` is d(out) and the BatchNorm_o backward dy' = scale_o * d(out) + coef_outer[0] + coef_outer[1] * y is applied on
+ *   the fly to the recomputed y (coef_outer from uz_bn_bwd_coef) - d(y) is never stored. */
 size_t uz_dual_bn_bwd_workspace_bytes(int C);
 int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
                             const float* bnB, int N, int H, int W, int C, void* y, int y_ld, float* y_stats, void* stream);
 int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
-                            const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld, void* dA, int dA_ld,
-                            int accA, float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB, void* workspace,
-                            size_t workspace_bytes, void* stream);
+                            const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld,
+                            const float* bn_outer, const float* coef_outer, void* dA, int dA_ld, int accA, float* dbiasA,
+                            void* dB, int dB_ld, int accB, float* dbiasB, void* workspace, size_t workspace_bytes,
+                            void* stream);
+/* First half of uz_bn_bwd (no pooling): the reduce pass and the finalize, leaving coef[2][C] = {A, B} with
+ * dz = scale * g + A + B * z for a consumer that applies it on the fly (uz_dual_bn_add_relu_bwd's bn_outer / coef_outer);
+ * dgamma / dbeta / dbias as in uz_bn_bwd (optional).  Workspace: uz_bn_bwd_workspace_bytes(C). */
+int uz_bn_bwd_coef(const void* z, int z_ld, const void* dy, int dy_ld, int N, int H, int W, int C, const float* bn, int relu,
+                   float* coef, float* dgamma, float* dbeta, float* dbias, int accumulate, void* workspace,
+                   size_t workspace_bytes, void* stream);
 
 /* Channels [0, K), K <= 8, of an NHWC bf16 map as fp32 NCHW logits [N][K][H][W]: the output of MultiResUnet's conv_final
  * (Conv2d 1x1 -> BatchNorm2d(affine=False), no activation; multiresunet.py:200-201,238), which runs as a conv-BN pair

@@ -160,6 +160,56 @@ def test_two_batchnorms_add_relu_in_one_pass(N, C, H, W, relu_a):
     assert float(ctx.pgrads.view(convB.bias).abs().max()) < 2e-2 * float(dy.abs().sum() / C) + 1e-3
 
 
+@pytest.mark.parametrize("C,pool", [(64, False), (64, True), (120, False)])
+def test_whole_tail_with_the_following_batchnorm(C, pool):
+    """BN(relu(relu(BN(conv3x3(x))) + BN(conv1x1(x)))) [+ MaxPool2d] as one operator (engine.dual_bn_add_relu_bn): without a
+    pooled gradient the outer BatchNorm's backward is applied on the fly inside the fused backward (uz_bn_bwd_coef +
+    bn_outer / coef_outer of uz_dual_bn_add_relu_bwd); with one, it runs on its own first."""
+    from unet_zoo_b200 import _lib as L
+    N, H, W, cin = 2, 16, 24, 24
+    convA, bnA = nn.Conv2d(cin, C, 3, padding=1).to(DEV), nn.BatchNorm2d(C, affine=False).to(DEV)
+    convB, bnB = nn.Conv2d(cin, C, 1).to(DEV), nn.BatchNorm2d(C, affine=False).to(DEV)
+    bnO = nn.BatchNorm2d(C, affine=False).to(DEV)
+    with torch.no_grad():
+        convA.weight.copy_(bf16r(convA.weight))
+        convB.weight.copy_(bf16r(convB.weight))
+    x = bf16r(torch.randn(N, cin, H, W, device=DEV))
+    params = [convA.weight, convA.bias, convB.weight, convB.bias]
+    ctx = new_ctx(params=params)
+    xa = make_act(ctx, x)
+    A = E.bn_branch_conv(ctx, [xa], convA, bnA, relu=True)
+    B = E.bn_branch_conv(ctx, [xa], convB, bnB, relu=False, mode=L.CONV1X1)
+    out = E.Act(ctx.new_buf(N, H, W, C + 8), 8, C)
+    pooled = ctx.new_act(N, H // 2, W // 2, C) if pool else None
+    E.dual_bn_add_relu_bn(ctx, A, B, bnO, out=out, pooled=pooled)
+    ste = lambda t: t + (bf16r(t.detach()) - t.detach())      # noqa: E731
+    bn = lambda t: F.batch_norm(t, None, None, None, None, training=True, eps=1e-5)      # noqa: E731
+    xr = x.clone().requires_grad_(True)
+    ps = [p.detach().clone().requires_grad_(True) for p in params]
+    ya = F.relu(bn(ste(F.conv2d(xr, ps[0], ps[1], padding=1))))
+    s = ste(F.relu(ya + bn(ste(F.conv2d(xr, ps[2], ps[3])))))
+    o = ste(bn(s))
+    torch.cuda.synchronize()
+    assert relmax(out.to_nchw(), o.detach()) < 1e-2
+    assert int(bnO.num_batches_tracked) == 1 and relmax(bnO.running_var, 0.9 + 0.1 * s.detach().var((0, 2, 3))) < 1e-2
+    do = bf16r(torch.randn_like(o) * 0.1)
+    loss = (o * do).sum()
+    set_grad(out, do)
+    if pool:
+        p = F.max_pool2d(o, 2, 2)
+        assert relmax(pooled.to_nchw(), p.detach()) < 1e-2
+        dp = bf16r(torch.randn_like(p) * 0.1)
+        loss = loss + (p * dp).sum()
+        set_grad(pooled, dp)
+    loss.backward()
+    run_tape(ctx)
+    ctx.join_side()
+    torch.cuda.synchronize()
+    assert rel_l2(get_grad(xa), xr.grad) < 2e-2
+    assert rel_l2(ctx.pgrads.view(convA.weight), ps[0].grad) < 1.5e-2
+    assert rel_l2(ctx.pgrads.view(convB.weight), ps[2].grad) < 1.5e-2
+
+
 @pytest.mark.parametrize("K", [1, 3, 8])
 def test_logits_extraction_and_its_gradient(K):
     N, H, W = 2, 16, 24

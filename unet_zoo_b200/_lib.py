@@ -69,8 +69,10 @@ _PROTOS = {
     "uz_nhwc_to_nchw_f32": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P]),
     "uz_dual_bn_bwd_workspace_bytes": (c_size_t, [c_int]),
     "uz_dual_bn_add_relu_fwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, _P]),
-    "uz_dual_bn_add_relu_bwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, c_int,
-                                        c_int, _P, _P, c_int, c_int, _P, _P, c_size_t, _P]),
+    "uz_dual_bn_add_relu_bwd": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, c_int, c_int, _P, c_int, _P, _P,
+                                        _P, c_int, c_int, _P, _P, c_int, c_int, _P, _P, c_size_t, _P]),
+    "uz_bn_bwd_coef": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P, _P, _P, _P, c_int, _P,
+                               c_size_t, _P]),
     "uz_side_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int]),
     "uz_side_head_fwd": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "uz_side_head_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_int, _P, _P, _P, c_size_t, _P]),

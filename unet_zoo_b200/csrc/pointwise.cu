@@ -762,6 +762,12 @@ struct DualArgs {
   int a_ld, b_ld;
   const float* bnA;   // [4][C] mean, invstd, scale, shift
   const float* bnB;
+  // backward only, optional: the BatchNorm that FOLLOWS y (out = BN_o(y), multiresunet.py:84,127,134).  With bnO / coefO
+  // ([4][C] statistics, [2][C] coefficients of uz_bn_bwd_coef) the incoming gradient is d(out) and
+  // dy = scale_o * d(out) + coefO[0] + coefO[1] * y is formed on the fly from the recomputed y - the gradient of y is
+  // never written or read.
+  const float* bnO;
+  const float* coefO;
   int relu_a;
   long long npix;
   int C, cv, ppb;
@@ -848,23 +854,33 @@ __global__ void __launch_bounds__(256, 2) dual_bn_fwd_kernel(const DualArgs d, _
 }
 
 // gradient of one pixel group w.r.t. the two normalised branches (before the BatchNorm backward proper)
-__device__ __forceinline__ void dual_grad(const DualArgs& d, const uint4& ra, const uint4& rb, const uint4& rd,
+template <bool OUTER>
+__device__ __forceinline__ void dual_grad(const DualArgs& d, int g, const uint4& ra, const uint4& rb, const uint4& rd,
                                           const float (&sa)[8], const float (&ha)[8], const float (&sb)[8],
                                           const float (&hb)[8], float (&fa)[8], float (&fb)[8], float (&ga)[8],
                                           float (&gb)[8]) {
   unpack8(ra, fa);
   unpack8(rb, fb);
   unpack8(rd, gb);
+  float so[8], c0[8], c1[8];
+  if (OUTER) {        // L1-resident after the first pixel; kept out of the persistent registers
+    load8f(d.bnO + 2 * d.C + g * 8, so);
+    load8f(d.coefO + g * 8, c0);
+    load8f(d.coefO + d.C + g * 8, c1);
+  }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const float ua = fmaf(fa[j], sa[j], ha[j]);
     const float ya = d.relu_a ? fmaxf(ua, 0.f) : ua;
-    if (!(ya + fmaf(fb[j], sb[j], hb[j]) > 0.f)) gb[j] = 0.f;
+    const float sum = ya + fmaf(fb[j], sb[j], hb[j]);
+    if (OUTER) gb[j] = fmaf(so[j], gb[j], fmaf(c1[j], bf16_round(fmaxf(sum, 0.f)), c0[j]));   // y as it was stored
+    if (!(sum > 0.f)) gb[j] = 0.f;
     ga[j] = (d.relu_a && !(ua > 0.f)) ? 0.f : gb[j];
   }
 }
 
 // partialA[block][2][C] = { sum gA, sum gA*a } ; partialB[block][2][C] = { sum gB, sum gB*b }
+template <bool OUTER>
 __global__ void __launch_bounds__(256, 2) dual_bn_bwd_reduce_kernel(const DualArgs d, const __nv_bfloat16* __restrict__ dy,
                                                                     int dy_ld, float* __restrict__ partialA,
                                                                     float* __restrict__ partialB) {
@@ -879,7 +895,7 @@ __global__ void __launch_bounds__(256, 2) dual_bn_bwd_reduce_kernel(const DualAr
   float s1[8], q1[8], s2[8], q2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s1[j] = q1[j] = s2[j] = q2[j] = 0.f;
-  constexpr int U = kDualUnroll;
+  constexpr int U = OUTER ? 1 : kDualUnroll;
   const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
   for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
     uint4 ra[U], rb[U], rd[U];
@@ -896,7 +912,7 @@ __global__ void __launch_bounds__(256, 2) dual_bn_bwd_reduce_kernel(const DualAr
     for (int u = 0; u < U; ++u) {
       if (it + u * stride < d.npix) {
         float fa[8], fb[8], ga[8], gb[8];
-        dual_grad(d, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
+        dual_grad<OUTER>(d, g, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           s1[j] += ga[j];
@@ -940,6 +956,7 @@ __global__ void __launch_bounds__(256, 2) dual_bn_bwd_reduce_kernel(const DualAr
 }
 
 // dA = scaleA*gA + coefA[0] + coefA[1]*a ; dB likewise (coef from bn_bwd_finalize_kernel); dA may alias a, dB may alias b
+template <bool OUTER>
 __global__ void __launch_bounds__(256, 2) dual_bn_bwd_apply_kernel(const DualArgs d, const __nv_bfloat16* __restrict__ dy,
                                                                    int dy_ld, const float* __restrict__ coefA,
                                                                    const float* __restrict__ coefB,
@@ -952,7 +969,7 @@ __global__ void __launch_bounds__(256, 2) dual_bn_bwd_apply_kernel(const DualArg
   load8f(d.bnA + 3 * d.C + g * 8, ha);
   load8f(d.bnB + 2 * d.C + g * 8, sb);
   load8f(d.bnB + 3 * d.C + g * 8, hb);
-  constexpr int U = kDualUnroll;
+  constexpr int U = OUTER ? 1 : kDualUnroll;
   const long long stride = static_cast<long long>(gridDim.x) * d.ppb;
   for (long long it = static_cast<long long>(blockIdx.x) * d.ppb + pl; it < d.npix; it += U * stride) {
     uint4 ra[U], rb[U], rd[U];
@@ -970,7 +987,7 @@ __global__ void __launch_bounds__(256, 2) dual_bn_bwd_apply_kernel(const DualArg
       const long long p = it + u * stride;
       if (p < d.npix) {
         float fa[8], fb[8], ga[8], gb[8], c0[8], c1[8];
-        dual_grad(d, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
+        dual_grad<OUTER>(d, g, ra[u], rb[u], rd[u], sa, ha, sb, hb, fa, fb, ga, gb);
         load8f(coefA + g * 8, c0);
         load8f(coefA + d.C + g * 8, c1);
 #pragma unroll
@@ -1298,6 +1315,40 @@ extern "C" int uz_bn_bwd(const void* z, int z_ld, const void* dy, int dy_ld, con
   return UZ_OK;
 }
 
+extern "C" int uz_bn_bwd_coef(const void* z, int z_ld, const void* dy, int dy_ld, int N, int H, int W, int C, const float* bn,
+                              int relu, float* coef, float* dgamma, float* dbeta, float* dbias, int accumulate,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  UZ_REQUIRE_DEVICE();
+  int rc = check_act("bn_bwd_coef(z)", z, C, z_ld);
+  if (rc || (rc = check_act("bn_bwd_coef(dy)", dy, C, dy_ld))) return rc;
+  if (coef == nullptr || bn == nullptr) return set_error(UZ_ERR_INVALID, "bn_bwd_coef: missing statistics / output");
+  if (workspace_bytes < uz_bn_bwd_workspace_bytes(C) || !a16(workspace))
+    return set_error(UZ_ERR_WORKSPACE, "bn_bwd_coef: workspace too small (%zu < %zu)", workspace_bytes,
+                     uz_bn_bwd_workspace_bytes(C));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long items = static_cast<long long>(N) * H * W;
+  Geo g = make_geo(C, items, 4);
+  const size_t smem = static_cast<size_t>(g.block) * 16 * sizeof(float);
+  const int grid_r = resident_grid(bn_bwd_reduce_kernel<false>, g.block, smem, (items + g.ppb - 1) / g.ppb, 4);
+  BwdArgs a;
+  a.z = static_cast<const __nv_bfloat16*>(z);
+  a.z_ld = z_ld;
+  a.dy = static_cast<const __nv_bfloat16*>(dy);
+  a.dy_ld = dy_ld;
+  a.dpool = nullptr;
+  a.dpool_ld = 0;
+  a.N = N; a.H = H; a.W = W; a.C = C; a.cv = g.cv; a.ppb = g.ppb;
+  a.bn = bn;
+  a.relu = relu;
+  float* partial = static_cast<float*>(workspace);
+  bn_bwd_reduce_kernel<false><<<grid_r, g.block, smem, st>>>(a, partial);
+  UZ_CHECK_LAUNCH("bn_bwd_coef reduce launch");
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, grid_r, C, static_cast<double>(items), bn, dgamma, dbeta,
+                                                         accumulate & 1, coef, 1, dbias);
+  UZ_CHECK_LAUNCH("bn_bwd_coef finalize launch");
+  return UZ_OK;
+}
+
 extern "C" size_t uz_dual_bn_bwd_workspace_bytes(int C) {
   const int rows = uz_reduce_rows();
   if (rows < 0) return 0;
@@ -1315,6 +1366,8 @@ static int dual_args(DualArgs& d, Geo& g, const void* a, int a_ld, const float* 
   d.b_ld = b_ld;
   d.bnA = bnA;
   d.bnB = bnB;
+  d.bnO = nullptr;
+  d.coefO = nullptr;
   d.relu_a = relu_a;
   d.npix = static_cast<long long>(N) * H * W;
   d.C = C;
@@ -1344,13 +1397,18 @@ extern "C" int uz_dual_bn_add_relu_fwd(const void* a, int a_ld, const float* bnA
 }
 
 extern "C" int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA, int relu_a, const void* b, int b_ld,
-                                       const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld, void* dA,
-                                       int dA_ld, int accA, float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB,
-                                       void* workspace, size_t workspace_bytes, void* stream) {
+                                       const float* bnB, int N, int H, int W, int C, const void* dy, int dy_ld,
+                                       const float* bn_outer, const float* coef_outer, void* dA, int dA_ld, int accA,
+                                       float* dbiasA, void* dB, int dB_ld, int accB, float* dbiasB, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
   UZ_REQUIRE_DEVICE();
   DualArgs d;
   Geo g;
   int rc = dual_args(d, g, a, a_ld, bnA, relu_a, b, b_ld, bnB, N, H, W, C, 4);
+  if ((bn_outer == nullptr) != (coef_outer == nullptr))
+    return set_error(UZ_ERR_INVALID, "dual_bn_bwd: bn_outer and coef_outer must be given together");
+  d.bnO = bn_outer;
+  d.coefO = coef_outer;
   if (rc || (rc = check_act("dual_bn_bwd(dy)", dy, C, dy_ld)) || (rc = check_act("dual_bn_bwd(dA)", dA, C, dA_ld)) ||
       (rc = check_act("dual_bn_bwd(dB)", dB, C, dB_ld)))
     return rc;
@@ -1360,23 +1418,33 @@ extern "C" int uz_dual_bn_add_relu_bwd(const void* a, int a_ld, const float* bnA
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t smem = static_cast<size_t>(g.block) * 32 * sizeof(float);
   const long long need = (d.npix + g.ppb - 1) / g.ppb;
-  const int grid_r = resident_grid(dual_bn_bwd_reduce_kernel, g.block, smem, need, 4);
-  const int grid_a = resident_grid(dual_bn_bwd_apply_kernel, g.block, 0, need, 4);
+  const bool outer = coef_outer != nullptr;
+  const int grid_r = outer ? resident_grid(dual_bn_bwd_reduce_kernel<true>, g.block, smem, need, 4)
+                           : resident_grid(dual_bn_bwd_reduce_kernel<false>, g.block, smem, need, 4);
+  const int grid_a = outer ? resident_grid(dual_bn_bwd_apply_kernel<true>, g.block, 0, need, 4)
+                           : resident_grid(dual_bn_bwd_apply_kernel<false>, g.block, 0, need, 4);
   const size_t max_rows = static_cast<size_t>(uz_reduce_rows());
   float* partialA = static_cast<float*>(workspace);
   float* partialB = partialA + max_rows * 2 * C;
   float* coefA = partialB + max_rows * 2 * C;
   float* coefB = coefA + 2 * C;
   const __nv_bfloat16* g_dy = static_cast<const __nv_bfloat16*>(dy);
-  dual_bn_bwd_reduce_kernel<<<grid_r, g.block, smem, st>>>(d, g_dy, dy_ld, partialA, partialB);
+  if (outer)
+    dual_bn_bwd_reduce_kernel<true><<<grid_r, g.block, smem, st>>>(d, g_dy, dy_ld, partialA, partialB);
+  else
+    dual_bn_bwd_reduce_kernel<false><<<grid_r, g.block, smem, st>>>(d, g_dy, dy_ld, partialA, partialB);
   UZ_CHECK_LAUNCH("dual_bn_bwd_reduce launch");
   const double count = static_cast<double>(d.npix);
   bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partialA, grid_r, C, count, bnA, nullptr, nullptr, 0, coefA, 1, dbiasA);
   UZ_CHECK_LAUNCH("dual_bn_bwd finalize A launch");
   bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partialB, grid_r, C, count, bnB, nullptr, nullptr, 0, coefB, 1, dbiasB);
   UZ_CHECK_LAUNCH("dual_bn_bwd finalize B launch");
-  dual_bn_bwd_apply_kernel<<<grid_a, g.block, 0, st>>>(d, g_dy, dy_ld, coefA, coefB, static_cast<__nv_bfloat16*>(dA), dA_ld,
-                                                       accA, static_cast<__nv_bfloat16*>(dB), dB_ld, accB);
+  if (outer)
+    dual_bn_bwd_apply_kernel<true><<<grid_a, g.block, 0, st>>>(d, g_dy, dy_ld, coefA, coefB, static_cast<__nv_bfloat16*>(dA),
+                                                               dA_ld, accA, static_cast<__nv_bfloat16*>(dB), dB_ld, accB);
+  else
+    dual_bn_bwd_apply_kernel<false><<<grid_a, g.block, 0, st>>>(d, g_dy, dy_ld, coefA, coefB, static_cast<__nv_bfloat16*>(dA),
+                                                                dA_ld, accA, static_cast<__nv_bfloat16*>(dB), dB_ld, accB);
   UZ_CHECK_LAUNCH("dual_bn_bwd_apply launch");
   return UZ_OK;
 }

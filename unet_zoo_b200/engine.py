@@ -1282,12 +1282,35 @@ def bn_branch_act(ctx: Ctx, x: Act, bn) -> BnBranch:
     return br
 
 
-def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = None,
-                     stats: Optional[torch.Tensor] = None) -> Act:
-    """out = ReLU([ReLU](BN(A.z)) + BN(B.z)) in one pass over the two raw tensors (uz_dual_bn_add_relu_fwd / _bwd): the
-    tails of Multiresblock and Respath (multiresunet.py:79-83,122-126).  Training mode only (batch statistics).
-    `stats` ([reduce_rows][2][C] fp32): receives the sum / sum-of-squares partials of `out` for the BatchNorm that follows
-    (hand it to bn_act(stats=...))."""
+def _dual_backward(c: Ctx, A: BnBranch, B: BnBranch, dy_ptr: int, dy_ld: int, outer=None):
+    """Backward of relu([relu](BN(A.z)) + BN(B.z)): both BatchNorm backwards in one reduce + one apply pass, then the
+    branches' convolution backwards.  `outer` = (bnbuf, coef) of a BatchNorm that follows (see dual_bn_add_relu_bn)."""
+    a, b = A.z, B.z
+    dst = []
+    for br in (A, B):
+        if br.conv is not None:          # dz overwrites z in place, then the convolution's backward consumes it
+            dst.append((br.z.ptr, br.z.ld, 0, c.pgrad(br.conv.bias) if br.conv.bias is not None else None))
+        else:
+            runs = br.z.grad_writes()
+            if len(runs) != 1:
+                raise NotImplementedError("dual_bn_add_relu: operand gradient partly written by another consumer")
+            dst.append((br.z.gptr(), br.z.ld, int(runs[0][2]), None))
+    ws = c.workspace(c.lib.uz_dual_bn_bwd_workspace_bytes(a.C))
+    with _Timed("bn_bwd", 2.0 * a.npix * a.C * 8):
+        L.check(c.lib.uz_dual_bn_add_relu_bwd(a.ptr, a.ld, A.bnbuf.data_ptr(), int(A.relu), b.ptr, b.ld,
+                                              B.bnbuf.data_ptr(), a.N, a.H, a.W, a.C, dy_ptr, dy_ld,
+                                              outer[0].data_ptr() if outer else None, outer[1].data_ptr() if outer else None,
+                                              dst[0][0], dst[0][1], dst[0][2], _ptr(dst[0][3]),
+                                              dst[1][0], dst[1][1], dst[1][2], _ptr(dst[1][3]),
+                                              ws.data_ptr(), ws.numel(), c.stream), "uz_dual_bn_add_relu_bwd")
+    c.launches += 4
+    for br in (A, B):
+        if br.conv is not None:
+            c.pready(br.conv.bias)
+            _conv_backward(c, br.xs, br.conv, br.z, br.mode, False, br.cin_total, br.need_dx)
+
+
+def _dual_forward(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act], stats: Optional[torch.Tensor]) -> Act:
     if ctx.fp32 or not ctx.training:
         raise RuntimeError("unet_zoo_b200: dual_bn_add_relu is a train-mode bf16 operator")
     a, b = A.z, B.z
@@ -1300,31 +1323,61 @@ def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = No
                                                 a.N, a.H, a.W, a.C, out.ptr, out.ld, _ptr(stats), ctx.stream),
                 "uz_dual_bn_add_relu_fwd")
     ctx.launches += 1
+    return out
+
+
+def dual_bn_add_relu(ctx: Ctx, A: BnBranch, B: BnBranch, out: Optional[Act] = None,
+                     stats: Optional[torch.Tensor] = None) -> Act:
+    """out = ReLU([ReLU](BN(A.z)) + BN(B.z)) in one pass over the two raw tensors (uz_dual_bn_add_relu_fwd / _bwd): the
+    tails of Multiresblock and Respath (multiresunet.py:79-83,122-126).  Training mode only (batch statistics).
+    `stats` ([reduce_rows][2][C] fp32): receives the sum / sum-of-squares partials of `out` for the BatchNorm that follows
+    (hand it to bn_act(stats=...))."""
+    out = _dual_forward(ctx, A, B, out, stats)
     if ctx.record:
         def backward(c: Ctx):
             if not out.has_grad():
                 raise RuntimeError("unet_zoo_b200: dual_bn_add_relu output has no gradient")
-            dst = []
-            for br in (A, B):
-                if br.conv is not None:          # dz overwrites z in place, then the convolution's backward consumes it
-                    dst.append((br.z.ptr, br.z.ld, 0, c.pgrad(br.conv.bias) if br.conv.bias is not None else None))
-                else:
-                    runs = br.z.grad_writes()
-                    if len(runs) != 1:
-                        raise NotImplementedError("dual_bn_add_relu: operand gradient partly written by another consumer")
-                    dst.append((br.z.gptr(), br.z.ld, int(runs[0][2]), None))
-            ws = c.workspace(c.lib.uz_dual_bn_bwd_workspace_bytes(a.C))
-            with _Timed("bn_bwd", 2.0 * a.npix * a.C * 8):
-                L.check(c.lib.uz_dual_bn_add_relu_bwd(a.ptr, a.ld, A.bnbuf.data_ptr(), int(A.relu), b.ptr, b.ld,
-                                                      B.bnbuf.data_ptr(), a.N, a.H, a.W, a.C, out.gptr(), out.ld,
-                                                      dst[0][0], dst[0][1], dst[0][2], _ptr(dst[0][3]),
-                                                      dst[1][0], dst[1][1], dst[1][2], _ptr(dst[1][3]),
-                                                      ws.data_ptr(), ws.numel(), c.stream), "uz_dual_bn_add_relu_bwd")
-            c.launches += 4
-            for br in (A, B):
-                if br.conv is not None:
-                    c.pready(br.conv.bias)
-                    _conv_backward(c, br.xs, br.conv, br.z, br.mode, False, br.cin_total, br.need_dx)
+            _dual_backward(c, A, B, out.gptr(), out.ld)
+        ctx.tape.append(backward)
+    return out
+
+
+def dual_bn_add_relu_bn(ctx: Ctx, A: BnBranch, B: BnBranch, bn, out: Optional[Act] = None,
+                        pooled: Optional[Act] = None) -> Act:
+    """out = BatchNorm(ReLU([ReLU](BN(A.z)) + BN(B.z))) [+ MaxPool2d(2, 2) of it]: the whole tail of a Multiresblock /
+    Respath step (multiresunet.py:79-84,122-127).  Forward: the fused add emits the sum s and its statistics, one apply
+    pass normalises it.  Backward without a pooled gradient: the BatchNorm's backward is reduced to its coefficients
+    (uz_bn_bwd_coef, one pass over s and d(out)) and applied on the fly inside the fused add's backward, which recomputes
+    s from the raw tensors - d(s) is never written or read.  With a pooled gradient (window routing needs the stored
+    output) the BatchNorm backward runs on its own first."""
+    a = A.z
+    rows = ctx.reduce_rows
+    stats = ctx.f32(rows, 2, a.C)
+    s = _dual_forward(ctx, A, B, None, stats)
+    bnbuf = ctx.f32(4, a.C)
+    ctx.bn_finalize(stats, rows, a.C, a.npix, bn, bnbuf)
+    if out is None:
+        out = ctx.new_act(a.N, a.H, a.W, a.C)
+    ctx.bn_apply(s, bnbuf[2].data_ptr(), bnbuf[3].data_ptr(), False, out, pooled)
+    if ctx.record:
+        def backward(c: Ctx):
+            has_dy = out.has_grad()
+            has_dp = pooled is not None and pooled.has_grad()
+            if not (has_dy or has_dp):
+                raise RuntimeError("unet_zoo_b200: dual_bn_add_relu_bn output has no gradient")
+            if has_dp or os.environ.get("UZ_DUAL_BN_SPLIT") == "1":
+                c.bn_bwd(s, out.gptr() if has_dy else None, out.ld, pooled.gptr() if has_dp else None,
+                         pooled.ld if has_dp else 0, bnbuf, False, s.gptr(), s.ld, None, None, None)
+                _dual_backward(c, A, B, s.gptr(), s.ld)
+                return
+            coef = c.f32(2, a.C)
+            ws = c.workspace(c.lib.uz_bn_bwd_workspace_bytes(a.C))
+            with _Timed("bn_bwd", 2.0 * a.npix * a.C * 2):
+                L.check(c.lib.uz_bn_bwd_coef(s.ptr, s.ld, out.gptr(), out.ld, a.N, a.H, a.W, a.C, bnbuf.data_ptr(), 0,
+                                             coef.data_ptr(), None, None, None, 0, ws.data_ptr(), ws.numel(), c.stream),
+                        "uz_bn_bwd_coef")
+            c.launches += 2
+            _dual_backward(c, A, B, out.gptr(), out.ld, outer=(bnbuf, coef))
         ctx.tape.append(backward)
     return out
 

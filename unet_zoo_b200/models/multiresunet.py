@@ -205,28 +205,25 @@ class MultiResUnet(HotPathModel):                         # multiresunet.py:137-
         a = self._unit(ctx, xs, blk.conv2d_bn_3x3, out=E.Act(cat, 0, p3), need_dx=need_dx)
         b = self._unit(ctx, [a], blk.conv2d_bn_5x5, out=E.Act(cat, p3, p5))
         self._unit(ctx, [b], blk.conv2d_bn_7x7, out=E.Act(cat, p3 + p5, p7))
-        stats = None
-        if fused:
-            stats = ctx.f32(ctx.reduce_rows, 2, cat.ld)     # statistics of the sum, from the pass that writes it
-            s = E.dual_bn_add_relu(ctx, E.bn_branch_act(ctx, E.Act(cat), bn1), temp, stats=stats)
-        else:
-            x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
-            s = E.residual_add(ctx, x1, temp, relu=True)
-        return E.bn_act(ctx, s, bn1, relu=False, out=out, pooled=pooled, stats=stats)
+        if fused:     # the whole tail: BN(cat), + shortcut, ReLU, BN again (+ the stage's pooling)
+            return E.dual_bn_add_relu_bn(ctx, E.bn_branch_act(ctx, E.Act(cat), bn1), temp, bn1, out=out, pooled=pooled)
+        x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
+        s = E.residual_add(ctx, x1, temp, relu=True)
+        return E.bn_act(ctx, s, bn1, relu=False, out=out, pooled=pooled)
 
     def _respath(self, ctx, rp: Respath, x, out):
         """Respath.forward (multiresunet.py:121-135); the last BatchNorm writes into the decoder's concat buffer."""
         steps = rp.steps()
         for i, (c1, c3, bn) in enumerate(steps):
-            stats = None
+            dst = out if i == len(steps) - 1 else None
             if ctx.training and not _UNFUSED:
-                stats = ctx.f32(ctx.reduce_rows, 2, ceil8(rp.filters))
-                s = E.dual_bn_add_relu(ctx, self._branch(ctx, [x], c3), self._branch(ctx, [x], c1), stats=stats)
+                x = E.dual_bn_add_relu_bn(ctx, self._branch(ctx, [x], c3), self._branch(ctx, [x], c1),
+                                          self._uz_shadow.of[id(bn)], out=dst)
             else:
                 shortcut = self._unit(ctx, [x], c1)
                 y = self._unit(ctx, [x], c3)
                 s = E.residual_add(ctx, y, shortcut, relu=True)
-            x = E.bn_act(ctx, s, self._uz_shadow.of[id(bn)], relu=False, out=out if i == len(steps) - 1 else None, stats=stats)
+                x = E.bn_act(ctx, s, self._uz_shadow.of[id(bn)], relu=False, out=dst)
         return x
 
     def _graph(self, ctx: E.Ctx, x):
