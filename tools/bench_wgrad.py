@@ -14,6 +14,7 @@ ctx = E.Ctx(dev, training=True, record=False)
 LAYERS = [(512, 64, 64), (512, 128, 64), (256, 64, 128), (256, 128, 128), (256, 256, 128), (128, 128, 256),
           (128, 256, 256), (128, 512, 256), (64, 256, 512), (64, 512, 512), (64, 1024, 512), (32, 512, 1024),
           (32, 1024, 1024)]
+MODE, K = (L.CONV1X1, 1) if os.environ.get("MODE") == "1x1" else (L.CONV3X3, 3)      # MODE=1x1: first-generation kernel
 only = os.environ.get("ONLY")        # e.g. ONLY=128,256,256 (H, cin, cout)
 if only:
     LAYERS = [tuple(int(v) for v in only.split(","))]
@@ -23,18 +24,18 @@ for H, cin, cout in LAYERS:
     dz = E.Act(ctx.new_buf(N, H, H, cout))
     x.buf.data.normal_()
     dz.buf.data.normal_()
-    dw = torch.empty(cout, cin, 3, 3, device=dev)
+    dw = torch.empty(cout, cin, K, K, device=dev)
     times = []
     for i in range(7):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ctx.wgrad(L.CONV3X3, x.ptr, N, H, H, cin, x.ld, dz.ptr, cout, dz.ld, dw, cin, 0)
+        ctx.wgrad(MODE, x.ptr, N, H, H, cin, x.ld, dz.ptr, cout, dz.ld, dw, cin, 0)
         e1.record()
         torch.cuda.synchronize()
         if i >= 2:
             times.append(e0.elapsed_time(e1))
     ms = sum(times) / len(times)
-    fl = 2.0 * N * H * H * cin * cout * 9
+    fl = 2.0 * N * H * H * cin * cout * K * K
     tot += ms
     print(f"wgrad {cin:5d}->{cout:5d} @{H:3d}  {ms:8.3f} ms  {fl / ms / 1e9:8.1f} TFLOP/s")
     del x, dz, dw
