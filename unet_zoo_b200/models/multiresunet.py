@@ -12,10 +12,13 @@ unet_zoo/models/multiresunet.py:7-240.  What is particular about this model:
   in train mode each application uses its own batch statistics and updates the same running buffers, in that order;
 * the model's output IS a BatchNorm: ``conv_final`` = Conv2d(1x1) -> BatchNorm2d(affine=False) without activation (:200,238).
 
-A Multiresblock runs as: three conv-BN-ReLU written side by side into one buffer (the concatenation), the 1x1
-shortcut conv-BN, BatchNorm of the concatenation, one add+ReLU pass, BatchNorm of the sum (which also emits the stage's
-MaxPool2d).  A Respath step: two conv-BN, one add+ReLU pass, BatchNorm.  Inputs: multiples of 16 (the reference's
-decoder concatenates a 2 * floor(s / 2) tensor with an s tensor, so it fails on other sizes too); bf16 mode only.
+A Multiresblock runs (training) as: three conv-BN-ReLU written side by side into one buffer (the concatenation), the
+1x1 shortcut convolution with its batch statistics only, and ONE tail operator (`engine.dual_bn_add_relu_bn`):
+relu(BN(cat) + BN(shortcut)) from the two raw tensors in one pass that also leaves the statistics of the second
+`batch_norm1`, whose apply pass emits the stage's MaxPool2d.  A Respath step: two convolutions with statistics, the same
+tail operator (with the inner ReLU of the 3x3 branch).  Eval mode (and UZ_MULTIRES_UNFUSED=1): conv-BN units with the
+BatchNorm folded into the weights, `engine.residual_add(relu=True)`, `engine.bn_act`.  Inputs: multiples of 16 (the
+reference's decoder concatenates a 2 * floor(s / 2) tensor with an s tensor, so it fails on other sizes too); bf16 mode only.
 """
 import os
 
