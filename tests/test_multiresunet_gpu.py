@@ -589,3 +589,33 @@ def test_graphed_train_step_matches_eager_steps_and_learns():
             assert int(s0[k]) == int(s1[k]), k
     more = [float(step(x, m)) for _ in range(40)]
     assert more[-1] < 0.8 * l1[0], (l1[0], more[-1])
+
+
+def test_epoch_loops_with_the_fused_tail():
+    """training.train_one_epoch / validate_one_epoch (drop-ins for training_loop.py:86-180) with the fused criterion and the
+    flat optimizer on this model: finite numbers, the first batch's loss equals a plain forward's, parameters moved,
+    running statistics and counters advanced (batch_norm1: two per forward)."""
+    from unet_zoo_b200 import training as T
+    from unet_zoo_b200.loss import BCEDiceWithLogits
+    from unet_zoo_b200.optim import FlatAdamW
+    data = []
+    for i in range(3):
+        g = torch.Generator().manual_seed(200 + i)
+        data.append((torch.randn(2, 3, 64, 64, generator=g), (torch.rand(2, 1, 64, 64, generator=g) > 0.5).float(), f"p{i}"))
+    model = seeded_model("multiresunet").to(DEV)
+    probe = seeded_model("multiresunet").to(DEV).train()
+    with torch.no_grad():
+        first = float(F.binary_cross_entropy_with_logits(probe(data[0][0].to(DEV)), data[0][1].to(DEV)))
+    w0 = model.multiresblock5.conv2d_bn_7x7.conv1.weight.detach().clone()
+    opt = FlatAdamW(model.parameters(), lr=1e-3, weight_decay=1e-5, max_norm=1.0)
+    crit = BCEDiceWithLogits()
+    one = T.train_one_epoch(model, data[:1], opt, crit, DEV, None, 0, "multiresunet", None)
+    assert abs(one[0] - first) < 1e-5, (one, first)
+    got = T.train_one_epoch(model, data, opt, crit, DEV, None, 1, "multiresunet", None)
+    val = T.validate_one_epoch(model, data, crit, DEV, "multiresunet", None)
+    for v in tuple(got[:2]) + tuple(val[:2]):
+        assert v == v and abs(v) < 10.0
+    assert not torch.equal(model.multiresblock5.conv2d_bn_7x7.conv1.weight.detach(), w0)
+    assert int(model.multiresblock3.batch_norm1.num_batches_tracked) == 8        # 4 training forwards x 2
+    assert int(model.respath2.batch_norm_initial.num_batches_tracked) == 4
+    assert float(model.conv_final.batchnorm.running_var) != 1.0
