@@ -18,7 +18,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-FWD_GFLOP_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08}
+FWD_GFLOP_512 = {"unet": 385.34, "attention_unet": 531.40, "nested_unet": 275.88, "resunet": 311.08, "multiresunet": 125.24}
 
 
 def main():

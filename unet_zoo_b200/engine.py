@@ -915,6 +915,19 @@ def bn_act(ctx: Ctx, x: Act, bn, relu: bool = True, out: Optional[Act] = None, p
     return out
 
 
+def bn_add_relu_eval(ctx: Ctx, x: Act, bn, res: Act, out: Optional[Act] = None) -> Act:
+    """Inference only: ReLU(BatchNorm_running(x) + res) in one pass (uz_bn_apply with its residual operand) - the
+    `x = self.batch_norm1(x); x = x + temp; x = F.relu(x)` of a Multiresblock in eval mode (multiresunet.py:79-83)."""
+    if ctx.training or ctx.fp32:
+        raise RuntimeError("unet_zoo_b200: bn_add_relu_eval is an eval-mode bf16 operator")
+    if out is None:
+        out = ctx.new_act(x.N, x.H, x.W, x.C)
+    aff = ctx.cached(("affine", id(bn)), [bn.weight, bn.bias, bn.running_mean, bn.running_var],
+                     lambda: _running_affine(bn, ctx.device))
+    ctx.bn_apply(x, aff[2].data_ptr(), aff[3].data_ptr(), True, out, None, residual=res)
+    return out
+
+
 def conv_plain(ctx: Ctx, xs: Sequence[Act], conv, out: Optional[Act] = None, mode: int = L.CONV3X3,
                accumulate: bool = False, stem: Optional[str] = None, need_dx: bool = True) -> Act:
     """Conv2d without normalisation or activation, optionally accumulating into `out` (out += conv(x)): the last

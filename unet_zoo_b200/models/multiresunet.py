@@ -210,8 +210,11 @@ class MultiResUnet(HotPathModel):                         # multiresunet.py:137-
         self._unit(ctx, [b], blk.conv2d_bn_7x7, out=E.Act(cat, p3 + p5, p7))
         if fused:     # the whole tail: BN(cat), + shortcut, ReLU, BN again (+ the stage's pooling)
             return E.dual_bn_add_relu_bn(ctx, E.bn_branch_act(ctx, E.Act(cat), bn1), temp, bn1, out=out, pooled=pooled)
-        x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
-        s = E.residual_add(ctx, x1, temp, relu=True)
+        if not ctx.training and os.environ.get("UZ_MULTIRES_EVAL_UNFUSED") != "1":
+            s = E.bn_add_relu_eval(ctx, E.Act(cat), bn1, temp)       # running statistics: one pass
+        else:
+            x1 = E.bn_act(ctx, E.Act(cat), bn1, relu=False)
+            s = E.residual_add(ctx, x1, temp, relu=True)
         return E.bn_act(ctx, s, bn1, relu=False, out=out, pooled=pooled)
 
     def _respath(self, ctx, rp: Respath, x, out):
