@@ -619,3 +619,36 @@ def test_epoch_loops_with_the_fused_tail():
     assert int(model.multiresblock3.batch_norm1.num_batches_tracked) == 8        # 4 training forwards x 2
     assert int(model.respath2.batch_norm_initial.num_batches_tracked) == 4
     assert float(model.conv_final.batchnorm.running_var) != 1.0
+
+
+def test_baseline_resolution_512(monkeypatch):
+    """2 x 3 x 512 x 512 (the resolution of every BASELINE config; multi-wave persistent scheduling, split-K plans and
+    pooled / unpooled tails at their real sizes): one training step against the rounding-matched oracle, then the eval
+    forward on the statistics that step produced against the plain fp32 oracle."""
+    torch.set_num_threads(16)
+    x, mask = O.synthetic_batch(2, 3, 512, 512)
+    model = seeded_model("multiresunet")
+    sd = copy.deepcopy(model.state_dict())
+    out = _train_step(model, x, mask, O.gaussian_projection_loss)
+    monkeypatch.setattr(O.Runner, "round_storage", torch.bfloat16)
+    ref, _, ref_grads = O.train_step("multiresunet", sd, x, mask, loss_fn=O.gaussian_projection_loss)
+    monkeypatch.setattr(O.Runner, "round_storage", None)
+    ref = ref.detach()
+    err = rel_err(out, ref)
+    agree = float((O.threshold_mask(out) == O.threshold_mask(ref)).float().mean())
+    grads = {k: p.grad.detach().cpu() for k, p in model.named_parameters()}
+    e_all, per = grad_errors(grads, ref_grads)
+    ws = _worst_stats_error(model.state_dict(), sd)
+    parity_report("multiresunet_512/matched", logits=err, agree=agree, grad_all=e_all, grad_worst=per[:3], stats_worst=ws)
+    assert err < MATCHED_TOL and agree >= MATCHED_AGREE, (err, agree)
+    assert e_all < MATCHED_GRAD, (e_all, per[:3])
+    assert ws[0] < 5e-2, ws
+    state = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    model.eval()
+    with torch.no_grad():
+        oe = model(x.cuda()).cpu()
+        re = O.multiresunet_forward(state, x, False)
+    e_eval = rel_err(oe, re)
+    a_eval = float((O.threshold_mask(oe) == O.threshold_mask(re)).float().mean())
+    parity_report("multiresunet_512/eval", logits=e_eval, agree=a_eval)
+    assert e_eval < EVAL_TOL and a_eval >= 0.999, (e_eval, a_eval)
