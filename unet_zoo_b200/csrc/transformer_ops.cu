@@ -24,6 +24,13 @@ __device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&f)[8]) {
 }
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&f)[8]) { *reinterpret_cast<uint4*>(p) = pw_pack8(f); }
 __device__ __forceinline__ float bf16r(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+// eight consecutive fp32 (32-byte aligned: the positional-encoding table is [H][W][C] with C a multiple of 8) as two
+// 16-byte loads - eight scalar loads per 16 bytes of activation made these kernels LSU-issue bound
+__device__ __forceinline__ void ld8f(const float* p, float (&e)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  e[0] = a.x; e[1] = a.y; e[2] = a.z; e[3] = a.w;
+  e[4] = b.x; e[5] = b.y; e[6] = b.z; e[7] = b.w;
+}
 
 // y[n, h, w, :] = bf16(x + pe[h, w, :]); pooled = 2x2 max of y (floor), either output may be null
 __global__ void addpe_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, const float* __restrict__ pe, int N, int H,
@@ -39,9 +46,10 @@ __global__ void addpe_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, 
       const long long hw = p % (static_cast<long long>(H) * W);
       float f[8];
       ld8(x + p * x_ld + g * 8, f);
-      const float* e = pe + hw * C + g * 8;
+      float ev[8];
+      ld8f(pe + hw * C + g * 8, ev);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += __ldg(e + j);
+      for (int j = 0; j < 8; ++j) f[j] += ev[j];
       st8(y + p * y_ld + g * 8, f);
     }
     return;
@@ -64,9 +72,10 @@ __global__ void addpe_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, 
       const long long p = (n * H + yy) * W + xx;
       float f[8];
       ld8(x + p * x_ld + g * 8, f);
-      const float* e = pe + (static_cast<long long>(yy) * W + xx) * C + g * 8;
+      float ev[8];
+      ld8f(pe + (static_cast<long long>(yy) * W + xx) * C + g * 8, ev);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = bf16r(f[j] + __ldg(e + j));
+      for (int j = 0; j < 8; ++j) f[j] = bf16r(f[j] + ev[j]);
       if (y) st8(y + p * y_ld + g * 8, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) m[j] = (k == 0 || f[j] > m[j]) ? f[j] : m[j];
@@ -100,9 +109,10 @@ __global__ void addpe_bwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ld, 
       for (int k = 0; k < 4; ++k) {
         const long long p = (n * H + 2 * qy + (k >> 1)) * W + 2 * qx + (k & 1);
         ld8(x + p * x_ld + g * 8, s[k]);
-        const float* e = pe + (static_cast<long long>(2 * qy + (k >> 1)) * W + 2 * qx + (k & 1)) * C + g * 8;
+        float ev[8];
+        ld8f(pe + (static_cast<long long>(2 * qy + (k >> 1)) * W + 2 * qx + (k & 1)) * C + g * 8, ev);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s[k][j] = bf16r(s[k][j] + __ldg(e + j));
+        for (int j = 0; j < 8; ++j) s[k][j] = bf16r(s[k][j] + ev[j]);
       }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -506,6 +516,7 @@ extern "C" int uz_addpe_fwd(const void* x, int x_ld, const float* pe, int N, int
   int rc = chk("addpe_fwd(x)", x, C, x_ld);
   if (rc) return rc;
   if (!pe || (!y && !pooled) || N < 1 || H < 1 || W < 1) return set_error(UZ_ERR_INVALID, "addpe_fwd: bad arguments");
+  if (reinterpret_cast<uintptr_t>(pe) & 15u) return set_error(UZ_ERR_INVALID, "addpe_fwd: pe must be 16-byte aligned");
   if (y && (rc = chk("addpe_fwd(y)", y, C, y_ld))) return rc;
   if (pooled && (rc = chk("addpe_fwd(pooled)", pooled, C, pooled_ld))) return rc;
   if (pooled && (H < 2 || W < 2)) return set_error(UZ_ERR_INVALID, "addpe_fwd: pooling needs H, W >= 2");
@@ -528,6 +539,7 @@ extern "C" int uz_addpe_bwd(const void* x, int x_ld, const float* pe, int N, int
   if (dy && (rc = chk("addpe_bwd(dy)", dy, C, dy_ld))) return rc;
   if (dpooled && ((rc = chk("addpe_bwd(dpooled)", dpooled, C, dpooled_ld)) || (rc = chk("addpe_bwd(x)", x, C, x_ld)))) return rc;
   if (dpooled && !pe) return set_error(UZ_ERR_INVALID, "addpe_bwd: the pooled path needs x and pe");
+  if (pe && (reinterpret_cast<uintptr_t>(pe) & 15u)) return set_error(UZ_ERR_INVALID, "addpe_bwd: pe must be 16-byte aligned");
   const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   addpe_bwd_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), x_ld, pe, N, H, W, C, static_cast<const __nv_bfloat16*>(dy), dy_ld,
